@@ -1,0 +1,156 @@
+/* qtts_b200.h — C ABI of the B200-native Qwen3-TTS codec-frame engine (libqtts_b200.so).
+ *
+ * This is the drop-in boundary for ONE hot path of syb0rg/qwen3-tts-jetson: the per-frame
+ * codec-token generation loop (Talker decode step -> Code Predictor 5 layers x 16 positions ->
+ * sampling).  Every entry point below names the reference interface it replaces.  Signatures
+ * carry only plain pointers and sizes (host memory unless stated); no torch / ggml types.
+ *
+ * Conventions (mirroring the reference, src/tts_transformer.h:164-245):
+ *   - return value 1 = success, 0 = failure; qtts_last_error() gives the message
+ *     (reference: bool + get_error()).
+ *   - caller owns every buffer passed in or out; they are only used during the call.
+ *   - one caller thread per engine (reference classes are not thread safe either).
+ *   - there is NO CPU fallback: every call fails loudly if CUDA is unavailable.
+ */
+#ifndef QTTS_B200_H
+#define QTTS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct qtts_engine qtts_engine;
+
+/* Hyper-parameters and special ids.  Reference: tts_transformer_config,
+ * src/tts_transformer.h:21-69, filled by parse_config src/tts_transformer.cpp:288-442. */
+typedef struct qtts_config {
+    int32_t hidden_size, n_layers, n_heads, n_kv_heads, intermediate_size, head_dim;
+    int32_t codec_vocab_size, n_codebooks;
+    int32_t cp_layers, cp_vocab_size, cp_hidden_size, cp_intermediate_size;
+    int32_t cp_n_heads, cp_n_kv_heads, cp_head_dim;
+    int32_t text_vocab_size, text_embd_dim;
+    float   rms_norm_eps, rope_theta;
+    int32_t codec_pad_id, codec_bos_id, codec_eos_id;
+    int32_t codec_think_id, codec_nothink_id, codec_think_bos_id, codec_think_eos_id;
+    int32_t tts_bos_id, tts_eos_id, tts_pad_id;
+} qtts_config;
+
+/* tensor element types accepted by qtts_upload_tensor (GGUF stores 2-D as F16, 1-D as F32:
+ * scripts/convert_tts_to_gguf.py:289-297) */
+enum { QTTS_F32 = 0, QTTS_F16 = 1 };
+
+/* numerics modes (see DESIGN.md "Numerics"):
+ *   REFERENCE: reproduces the rounding points of the reference's ggml-cpu execution, including
+ *              the sequential F16 V-accumulator of its flash attention (ops.cpp:8108-8344);
+ *   FAST:      same rounding points for every projection, KV cache and Q, but the Talker's
+ *              decode attention accumulates P.V in FP32 with a parallel split-KV reduction. */
+enum { QTTS_NUMERICS_REFERENCE = 0, QTTS_NUMERICS_FAST = 1 };
+
+/* ---- life cycle ------------------------------------------------------------------------- */
+
+/* Create an engine on CUDA device `device` for up to `max_streams` concurrent utterances
+ * with `max_ctx` KV slots each.  Replaces TTSTransformer() + backend selection
+ * (src/tts_transformer.cpp:51-153, src/gguf_loader.cpp:26-76). */
+int qtts_create(const qtts_config * cfg, int device, int max_streams, int max_ctx,
+                qtts_engine ** out);
+void qtts_destroy(qtts_engine * e);                       /* ~TTSTransformer / unload_model */
+const char * qtts_last_error(const qtts_engine * e);      /* get_error() */
+/* message of the last failed qtts_create (no engine to ask) */
+const char * qtts_create_error(void);
+
+/* Upload one GGUF tensor by its GGUF name (names: scripts/convert_tts_to_gguf.py:42-109,
+ * consumed by create_tensors src/tts_transformer.cpp:444-731).  dims are in GGUF/ggml order
+ * (dims[0] = innermost = input features).  Replaces load_tensor_data
+ * (src/tts_transformer.cpp:733-792).  Projection matrices are converted to BF16 on the device;
+ * the count of values not exactly representable in BF16 is accumulated (qtts_weight_stats). */
+int qtts_upload_tensor(qtts_engine * e, const char * name, int dtype,
+                       const int64_t * dims, int n_dims, const void * host_data);
+/* Build the fused device layouts (QKV concatenation, gate/up row interleave), check that every
+ * tensor of the path is present.  Must be called once after the uploads. */
+int qtts_finalize(qtts_engine * e);
+/* out[0] = #projection weights uploaded, out[1] = #of those not BF16-exact,
+ * out[2] = device bytes held by weights, out[3] = device bytes held by KV caches */
+int qtts_weight_stats(const qtts_engine * e, int64_t out[4]);
+
+int qtts_set_numerics(qtts_engine * e, int mode, int reference_threads);
+/* persistent = 1: one cooperative launch per frame group (default); 0: one launch per stage
+ * (debug path, same device code). */
+int qtts_set_persistent(qtts_engine * e, int persistent);
+
+/* ---- reference-level entry points (TTSTransformer methods, one stream = `slot`) ----------- */
+
+/* init_kv_cache / clear_kv_cache (src/tts_transformer.cpp:794-900).  The cache is F16,
+ * token-major [n_ctx][n_kv_heads*head_dim] per layer, like the reference's (:823-833). */
+int qtts_clear_kv_cache(qtts_engine * e, int slot);
+
+/* build_prefill_graph + project_text_tokens (src/tts_transformer.cpp:1026-1231): assemble the
+ * prefill embeddings, the trailing text rows and the pad row for `slot` on the device.
+ * speaker may be NULL (no speaker row).  Optional outputs (may be NULL):
+ *   prefill_out [prefill_len*H], trailing_out [trailing_len*H], pad_out [H]. */
+int qtts_build_prefill(qtts_engine * e, int slot, const int32_t * text_tokens, int32_t n_tokens,
+                       const float * speaker_embd, int32_t language_id,
+                       int32_t * prefill_len, int32_t * trailing_len,
+                       float * prefill_out, float * trailing_out, float * pad_out);
+
+/* forward_prefill (src/tts_transformer.cpp:1829-1920): n_tokens rows of embeddings at
+ * positions n_past.. ; hidden_out [H] = normalised hidden of the LAST token, logits_out [V]. */
+int qtts_forward_prefill(qtts_engine * e, int slot, const float * embd, int32_t n_tokens,
+                         int32_t n_past, float * hidden_out, float * logits_out);
+
+/* forward_step (src/tts_transformer.cpp:1952-2028). */
+int qtts_forward_step(qtts_engine * e, int slot, const float * step_embd, int32_t n_past,
+                      float * logits_out, float * hidden_out);
+
+/* predict_codes_autoregressive (src/tts_transformer.cpp:2153-2340) and
+ * TRTCodePredictor::run_greedy_loop / run_sampling_loop (src/trt_code_predictor.cpp:484-726).
+ * temperature <= 0: greedy.  uniforms15: one uniform in [0,1) per code (as run_sampling_loop's
+ * rand_vals); NULL draws them from the engine's counter-based generator.
+ * forced15 (may be NULL): teacher forcing — the code fed back after step s is forced15[s]
+ * while out15[s] is still the engine's own choice.  logits_out (may be NULL): [15*cp_vocab]. */
+int qtts_predict_codes(qtts_engine * e, int slot, const float * hidden, int32_t cb0,
+                       float temperature, int32_t top_k, const float * uniforms15,
+                       const int32_t * forced15, int32_t * out15, float * logits_out);
+
+/* frame callback: frame_callback_t (src/tts_transformer.h:164-170): codes for n_frames frames,
+ * row-major [n_frames][n_codebooks]; return 0 to stop generation. */
+typedef int (*qtts_frame_cb)(const int32_t * codes, int32_t n_frames, int32_t n_codebooks,
+                             void * user);
+
+/* generate (src/tts_transformer.cpp:2342-2574).  codes_out must hold max_len*n_codebooks
+ * values; *n_frames_out receives the number of frames produced.  seed drives the sampler
+ * when temperature > 0 (the reference seeds from std::random_device,
+ * src/tts_transformer.h:298, so its sampled streams are not reproducible). */
+int qtts_generate(qtts_engine * e, int slot, const int32_t * text_tokens, int32_t n_tokens,
+                  const float * speaker_embd, int32_t max_len, int32_t language_id,
+                  float repetition_penalty, float temperature, int32_t top_k, uint64_t seed,
+                  int32_t * codes_out, int32_t * n_frames_out,
+                  qtts_frame_cb on_frames, int32_t callback_interval, void * user);
+
+/* ---- concurrent-utterance engine (the axis the reference lacks: SURVEY.md §8e) ----------- */
+
+/* Start an utterance in `slot`: build_prefill + forward_prefill; the stream is then advanced
+ * by qtts_step_frames together with every other active stream. */
+int qtts_stream_begin(qtts_engine * e, int slot, const int32_t * text_tokens, int32_t n_tokens,
+                      const float * speaker_embd, int32_t max_len, int32_t language_id,
+                      float repetition_penalty, float temperature, int32_t top_k, uint64_t seed);
+/* Advance every active stream by up to n_frames frames.  codes_out is
+ * [max_streams][n_frames][n_codebooks]; produced[slot] = frames written for that slot;
+ * active[slot] = 1 while the stream has neither hit EOS nor max_len. */
+int qtts_step_frames(qtts_engine * e, int32_t n_frames, int32_t * codes_out,
+                     int32_t * produced, int32_t * active);
+
+/* ---- instrumentation -------------------------------------------------------------------- */
+/* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
+int64_t qtts_launch_count(const qtts_engine * e);
+/* device time (ms, CUDA events on the engine's stream) of the last qtts_generate /
+ * qtts_step_frames frame loop, prefill excluded */
+double qtts_last_loop_ms(const qtts_engine * e);
+/* the engine's CUDA stream as a void* (cudaStream_t), for callers that time with events */
+void * qtts_stream_handle(const qtts_engine * e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QTTS_B200_H */

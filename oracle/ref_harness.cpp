@@ -208,7 +208,9 @@ int ref_predict_codes_logits(void * h, const float * hidden, int cb0, const int3
         const int32_t n_past = step + 1;
         struct ggml_cgraph * gf = t.build_code_pred_step_graph(n_past, step);
         if (!ggml_backend_sched_alloc_graph(t.state_.sched, gf)) return 0;
-        ggml_backend_tensor_set(ggml_graph_get_tensor(gf, "inp_hidden"), hidden, 0, cfg.hidden_size * sizeof(float));
+        // inp_hidden only feeds the graph when generation_step == 0 (reference :1700-1707)
+        if (struct ggml_tensor * ih = ggml_graph_get_tensor(gf, "inp_hidden"))
+            ggml_backend_tensor_set(ih, hidden, 0, cfg.hidden_size * sizeof(float));
         int32_t prev = forced15 ? forced15[step - 1] : out15[step - 1];
         ggml_backend_tensor_set(ggml_graph_get_tensor(gf, "inp_code"), &prev, 0, sizeof(int32_t));
         int32_t pos = n_past;

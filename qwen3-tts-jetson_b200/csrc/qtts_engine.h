@@ -1,0 +1,123 @@
+// qtts_engine.h — host-side engine state behind the C ABI (include/qtts_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <map>
+#include <string>
+#include <vector>
+#include "../../include/qtts_b200.h"
+#include "qtts_ops.cuh"
+
+namespace qtts {
+
+struct DevTensor {
+    void * raw = nullptr;          // as uploaded: F16 (2-D) or F32 (1-D)
+    __nv_bfloat16 * bf = nullptr;  // BF16 copy (projection matrices only)
+    int dtype = 0;
+    int64_t ne[4] = {1, 1, 1, 1};  // ggml order (ne[0] innermost)
+    int n_dims = 0;
+    size_t n_elem = 0;
+};
+
+struct LayerW {
+    __nv_bfloat16 * wqkv = nullptr, * wo = nullptr, * wgu = nullptr, * wdown = nullptr;
+    float * attn_norm = nullptr, * ffn_norm = nullptr, * q_norm = nullptr, * k_norm = nullptr;
+};
+
+struct Dims { int H, nh, nkv, ffn; };
+
+// per-slot device buffers
+struct Slot {
+    StreamState * st = nullptr;
+    float * x = nullptr, * qkv = nullptr, * attn = nullptr, * act = nullptr;
+    float * logits = nullptr, * hidden = nullptr, * in_embd = nullptr;
+    float * cp_x = nullptr, * cp_qkv = nullptr, * cp_attn = nullptr, * cp_act = nullptr, * cp_logits = nullptr;
+    float * cp_hidden_in = nullptr;        // hidden handed to predict_codes by the API
+    float * cp_dump = nullptr;             // [15][cp_vocab]
+    float * cb0_dump = nullptr;            // [V]
+    float * uniforms = nullptr;            // [max(16, max_len)]
+    int32_t * forced = nullptr;            // [15]
+    __half * kc = nullptr, * vc = nullptr;           // [n_layers][max_ctx][kvw]
+    __half * cp_kc = nullptr, * cp_vc = nullptr;     // [cp_layers][16][cp_kvw]
+    float * cp_kv0 = nullptr;                        // [cp_layers][2][cp_kvw]
+    float * prefill = nullptr;             // [max_prefill][H]
+    float * trailing = nullptr;            // [max_text+1][H]
+    float * pad = nullptr;                 // [H]
+    float * tp_tmp = nullptr;              // [E]
+    float * misc = nullptr;                // [8][H] scratch rows for the embedding assembly
+    float * speaker = nullptr;             // [H]
+    int32_t * tokens = nullptr;            // [max_text]
+    int32_t * codes = nullptr;             // [max_ctx][n_books]
+    EmbedSumArgs * es = nullptr;
+    Op * frame_prog = nullptr; int frame_prog_n = 0;
+    std::vector<Op> frame_host;
+    Op * scratch_prog = nullptr; int scratch_cap = 0;
+    // host mirrors
+    int32_t prefill_len = 0, trailing_len = 0, n_text_tokens = 0;
+    bool active = false;
+};
+
+struct Engine {
+    qtts_config cfg{};
+    int device = 0, max_streams = 0, max_ctx = 0, max_text = 0;
+    int n_sms = 0;
+    size_t smem_bytes = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    std::map<std::string, DevTensor> tensors;
+    std::vector<void *> allocs;
+    bool finalized = false;
+    int numerics = QTTS_NUMERICS_REFERENCE;
+    int ref_threads = 4;          // ggml's default thread count (ggml/include/ggml.h:232)
+    int persistent = 1;
+    int64_t n_weights = 0, n_inexact = 0, weight_bytes = 0, kv_bytes = 0;
+    int64_t launches = 0;
+    double last_loop_ms = 0.0;
+    unsigned long long * d_inexact = nullptr;
+    GridBarrier * bar = nullptr;
+    float * rope = nullptr;
+    // fused weights
+    std::vector<LayerW> talker, cp;
+    __nv_bfloat16 * codec_head = nullptr, * fc1 = nullptr, * fc2 = nullptr, * mtp = nullptr;
+    std::vector<__nv_bfloat16 *> lm_head;
+    float * output_norm = nullptr, * cp_output_norm = nullptr, * fc1_b = nullptr, * fc2_b = nullptr, * mtp_b = nullptr;
+    const __half * codec_embd = nullptr, * text_embd = nullptr;
+    std::vector<const __half *> cp_embd;
+    std::vector<Slot> slots;
+
+    bool fail(const std::string & m) { err = m; return false; }
+    template <typename T> T * dalloc(size_t n, bool zero = true) {
+        void * p = nullptr;
+        if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        if (zero) cudaMemset(p, 0, n * sizeof(T));
+        allocs.push_back(p);
+        return (T *) p;
+    }
+};
+
+// qtts_weights.cu
+bool engine_upload(Engine * e, const char * name, int dtype, const int64_t * dims, int n_dims, const void * host);
+bool engine_finalize(Engine * e);
+
+// qtts_kernels.cu
+size_t smem_required(int k_max, int max_ctx);
+
+// qtts_program.cu
+void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, const float * in_vec,
+                      bool use_n_past, int pos_abs, int attn_mode, bool with_head, bool inc_npast);
+void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float * hidden,
+                         float * dump, const int32_t * forced, const float * uniforms,
+                         bool override_sampling, float temperature, int top_k);
+void emit_frame(Engine * e, Slot & s, std::vector<Op> & P);
+bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t * tokens, int n_tokens,
+                        bool has_speaker, int language_id);
+bool run_program(Engine * e, Slot & s, const std::vector<Op> & P, int n_frames, bool check_done);
+bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vector<Op> * host_ops, int n_ops,
+                        int n_frames, bool check_done);
+
+#define QTTS_CUDA(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
+    e->err = std::string(#call) + ": " + cudaGetErrorString(_e); return false; } } while (0)
+
+}  // namespace qtts

@@ -1,0 +1,130 @@
+// qtts_ops.cuh — op descriptors shared by the host-side program builder and the device stages.
+//
+// The frame is the unit of GPU work: the host builds, once per stream, a linear "program" of
+// stage descriptors (Op) for one codec frame; a persistent cooperative kernel walks it with a
+// grid-wide barrier between stages (qtts_kernels.cu).  The same device code runs with one
+// launch per stage when persistent mode is switched off (debug path).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace qtts {
+
+constexpr int kThreads   = 512;   // threads per CTA (16 warps)
+constexpr int kWarps     = kThreads / 32;
+constexpr int kHeadDim   = 128;   // every Qwen3-TTS config uses 128 (src/tts_transformer.h:33,47)
+constexpr int kMaxVocab  = 4096;  // codec vocab 3072, code-pred vocab 2048
+constexpr int kMaxBooks  = 32;
+
+enum OpType : int32_t {
+    OP_GEMV       = 0,   // skinny projection: y = W . f16round(x)  (+ prologue / epilogue)
+    OP_ATTN       = 1,   // QK-norm + NEOX RoPE + KV append + attention over the cache
+    OP_SAMPLE_CB0 = 2,   // codebook-0 logit post-processing + argmax / top-k sample
+    OP_SAMPLE_CP  = 3,   // code-predictor argmax / top-k sample of one codebook
+    OP_FRAME_END  = 4,   // append the 16 codes of the frame, frame++ , max_len check
+    OP_COPY       = 5,   // small f32 vector copy / add (prefill embedding assembly)
+};
+
+enum InKind : int32_t {
+    IN_VEC       = 0,    // f32 vector in global memory
+    IN_EMBED_ROW = 1,    // one row of an F16 embedding table, row id read from device memory
+    IN_EMBED_SUM = 2,    // next Talker input: sum of the 16 code embeddings + text row
+};
+
+enum Epilogue : int32_t {
+    EPI_STORE     = 0,   // out[r] = acc
+    EPI_ADD       = 1,   // out[r] = acc + res[r]          (residual)
+    EPI_SWIGLU    = 2,   // rows interleaved gate/up: out[p] = silu(acc[2p]) * acc[2p+1]
+    EPI_BIAS      = 3,   // out[r] = acc + bias[r]
+    EPI_BIAS_SILU = 4,   // out[r] = silu(acc + bias[r])
+};
+
+enum AttnMode : int32_t {
+    ATTN_FLASH_F16SEQ = 0,  // ggml-cpu flash_attn_ext: F16 Q, sequential F16 V accumulator
+    ATTN_SOFTMAX_P16  = 1,  // ggml-cpu mul_mat/soft_max/mul_mat: F16 Q, F32 softmax, F16 P
+    ATTN_F32          = 2,  // code-predictor 2-token prefill: everything F32, unrounded K/V
+    ATTN_FAST         = 3,  // F16 Q/K/V, FP32 softmax and FP32 P.V accumulation, parallel
+};
+
+// Per-stream device state (one per slot).
+struct StreamState {
+    int32_t n_past;          // Talker KV entries in use (= position of the next token)
+    int32_t frame;           // frames emitted so far
+    int32_t done;            // 1 once EOS was sampled or max_len reached
+    int32_t eos;             // 1 if the stream ended by EOS
+    int32_t max_len;
+    int32_t n_text_tokens;   // drives the EOS boost (src/tts_transformer.cpp:2439)
+    int32_t trailing_len;
+    int32_t top_k;
+    float   rep_pen;
+    float   temperature;
+    uint64_t seed;
+    int32_t cur_codes[kMaxBooks];   // codes of the frame being produced (cb0..cb15)
+    int32_t feed_codes[kMaxBooks];  // codes fed back inside the code predictor (forced or own)
+    uint32_t seen[kMaxVocab / 32];  // bitmap of distinct cb0 tokens emitted so far
+};
+
+struct EmbedSumArgs {
+    const __half * tables[kMaxBooks];   // [0] = talker codec_embd, [c] = code_pred_embd[c-1]
+    int32_t n_books;
+    const float * trailing;             // [trailing_len][H]
+    const float * pad;                  // [H]
+};
+
+struct Op {
+    int32_t type;
+    int32_t flags;           // F_* below
+    // ---- OP_GEMV ----
+    const __nv_bfloat16 * W; // [rows][K] row-major
+    int32_t rows, K;
+    int32_t in_kind, epi;
+    const float * in;        // IN_VEC
+    const __half * table;    // IN_EMBED_ROW
+    const int32_t * tok_ptr; // IN_EMBED_ROW: row id
+    const EmbedSumArgs * es; // IN_EMBED_SUM
+    const float * norm_w;    // RMSNorm weight (nullptr: no norm)
+    float * x_out;           // CTA 0 stores the raw input vector here (residual stream init)
+    float * hid_out;         // CTA 0 stores the normalised (unrounded) vector here
+    const float * bias;
+    const float * res;
+    float * out;
+    float eps;
+    // ---- OP_ATTN ----
+    const float * qkv;       // [(n_heads + 2 n_kv_heads) * 128] raw projections
+    const float * q_norm_w, * k_norm_w;
+    __half * kcache, * vcache;   // [n_ctx][n_kv_heads*128] of this layer / slot
+    float * kv0_f32;             // ATTN_F32 only: unrounded K,V of position 0 [2][n_kv_heads*128]
+    const float * rope;          // [max_pos][64][2] cos,sin
+    int32_t n_heads, n_kv_heads;
+    int32_t pos_off;             // position = (use_n_past ? state.n_past : 0) + pos_off
+    int32_t use_n_past;
+    int32_t mode;
+    int32_t ref_threads;         // thread count of the reference's split-KV path (>=512 keys)
+    float   kq_scale;
+    // ---- sampling ----
+    const float * logits; int32_t n_vocab;
+    int32_t book;                // OP_SAMPLE_CP: index 1..15 of the code written
+    const float * uniforms;      // optional [.] host-supplied uniforms (nullptr: Philox)
+    const int32_t * forced;      // optional teacher-forcing codes for the code predictor
+    float * dump;                // optional copy of the logits (parity hooks)
+    int32_t eos_id, suppress_start;
+    float temperature_override;  // < -1e29: use stream state
+    int32_t top_k_override;
+    // ---- OP_FRAME_END ----
+    int32_t * codes_out;         // [max_len][n_books]
+    int32_t n_books;
+    // ---- OP_COPY ----  out[i] = a[i] (+ b[i])
+    const float * a, * b; int32_t n;
+};
+
+enum OpFlags : int32_t {
+    F_INC_NPAST = 1,     // CTA 0 increments state.n_past when the stage completes
+};
+
+struct GridBarrier {
+    unsigned int count;   // monotonically increasing arrival counter
+    unsigned int pad[31];
+};
+
+}  // namespace qtts

@@ -1,0 +1,262 @@
+// qtts_program.cu — host-side builders of the per-frame stage programs and the launcher.
+//
+// One codec frame (reference: the body of the loop at src/tts_transformer.cpp:2416-2560) is
+//   SAMPLE_CB0 -> code predictor (16 positions x [5 layers x 5 stages] + 15 x [head, sample])
+//   -> FRAME_END -> Talker step (28 layers x 5 stages + head), whose first stage gathers the
+//   16 code embeddings + text row (src/tts_transformer.cpp:2529-2553).
+#include "qtts_engine.h"
+#include <cstring>
+
+namespace qtts {
+
+extern "C" __global__ void qtts_run_program(const Op * ops, int n_ops, StreamState * st, GridBarrier * bar,
+                                            int n_frames, int persistent, int check_done);
+
+static Op blank() {
+    Op o;
+    memset(&o, 0, sizeof(o));
+    o.temperature_override = -1e30f;
+    return o;
+}
+
+static Op gemv(const __nv_bfloat16 * W, int rows, int K, const float * in, const float * norm_w, float eps,
+               int epi, float * out) {
+    Op o = blank();
+    o.type = OP_GEMV; o.W = W; o.rows = rows; o.K = K; o.in_kind = IN_VEC; o.in = in;
+    o.norm_w = norm_w; o.eps = eps; o.epi = epi; o.out = out;
+    return o;
+}
+
+struct LayerBuf { float * x, * qkv, * attn, * act; __half * kc, * vc; float * kv0; size_t kv_layer_stride; };
+
+// five stages of one decoder layer; `first` (if non-null) replaces the QKV stage's input setup
+static void emit_layer(Engine * e, std::vector<Op> & P, const LayerW & L, const Dims & D, const LayerBuf & B,
+                       int layer, const Op * first, bool use_n_past, int pos_off, int mode) {
+    const float eps = e->cfg.rms_norm_eps;
+    const int qkv_rows = (D.nh + 2 * D.nkv) * kHeadDim;
+    Op q = gemv(L.wqkv, qkv_rows, D.H, B.x, L.attn_norm, eps, EPI_STORE, B.qkv);
+    if (first) {
+        q.in_kind = first->in_kind; q.in = first->in; q.table = first->table; q.tok_ptr = first->tok_ptr;
+        q.es = first->es; q.x_out = first->x_out;
+    }
+    P.push_back(q);
+    Op a = blank();
+    a.type = OP_ATTN; a.qkv = B.qkv; a.q_norm_w = L.q_norm; a.k_norm_w = L.k_norm;
+    a.kcache = B.kc + (size_t) layer * B.kv_layer_stride;
+    a.vcache = B.vc + (size_t) layer * B.kv_layer_stride;
+    a.kv0_f32 = B.kv0 ? B.kv0 + (size_t) layer * 2 * D.nkv * kHeadDim : nullptr;
+    a.rope = e->rope; a.n_heads = D.nh; a.n_kv_heads = D.nkv; a.pos_off = pos_off; a.use_n_past = use_n_past ? 1 : 0;
+    a.mode = mode; a.ref_threads = e->ref_threads; a.kq_scale = 1.0f / sqrtf((float) kHeadDim);
+    a.eps = eps; a.out = B.attn;
+    P.push_back(a);
+    Op o = gemv(L.wo, D.H, D.nh * kHeadDim, B.attn, nullptr, eps, EPI_ADD, B.x);
+    o.res = B.x;
+    P.push_back(o);
+    P.push_back(gemv(L.wgu, 2 * D.ffn, D.H, B.x, L.ffn_norm, eps, EPI_SWIGLU, B.act));
+    Op d = gemv(L.wdown, D.H, D.ffn, B.act, nullptr, eps, EPI_ADD, B.x);
+    d.res = B.x;
+    P.push_back(d);
+}
+
+// One Talker token: forward_step graph (src/tts_transformer.cpp:1376-1512).
+void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, const float * in_vec,
+                      bool use_n_past, int pos_abs, int attn_mode, bool with_head, bool inc_npast) {
+    const qtts_config & c = e->cfg;
+    const Dims D{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
+    LayerBuf B{s.x, s.qkv, s.attn, s.act, s.kc, s.vc, nullptr, (size_t) e->max_ctx * c.n_kv_heads * kHeadDim};
+    Op first = blank();
+    first.in_kind = in_kind; first.in = in_vec; first.es = s.es; first.x_out = s.x;
+    for (int l = 0; l < c.n_layers; ++l)
+        emit_layer(e, P, e->talker[l], D, B, l, l == 0 ? &first : nullptr, use_n_past, use_n_past ? 0 : pos_abs, attn_mode);
+    if (with_head) {
+        Op h = gemv(e->codec_head, c.codec_vocab_size, c.hidden_size, s.x, e->output_norm, c.rms_norm_eps, EPI_STORE, s.logits);
+        h.hid_out = s.hidden;
+        if (inc_npast) h.flags |= F_INC_NPAST;
+        P.push_back(h);
+    } else if (inc_npast) {
+        P.back().flags |= F_INC_NPAST;
+    }
+}
+
+// predict_codes_autoregressive (src/tts_transformer.cpp:2153-2340) as 16 single-token passes:
+// positions 0 and 1 use the all-F32 attention of the reference's 2-token prefill graph
+// (:1613-1626), positions >= 2 the F16-cache / F16-P attention of its step graph (:1779-1792).
+void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float * hidden,
+                         float * dump, const int32_t * forced, const float * uniforms,
+                         bool override_sampling, float temperature, int top_k) {
+    const qtts_config & c = e->cfg;
+    const Dims D{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
+    LayerBuf B{s.cp_x, s.cp_qkv, s.cp_attn, s.cp_act, s.cp_kc, s.cp_vc, s.cp_kv0, (size_t) 16 * c.cp_n_kv_heads * kHeadDim};
+    const int n_pos = c.n_codebooks;   // 16 positions -> 15 sampled codes
+    for (int p = 0; p < n_pos; ++p) {
+        Op first = blank();
+        if (p == 0) { first.in_kind = IN_VEC; first.in = hidden; }
+        else {
+            first.in_kind = IN_EMBED_ROW;
+            first.table = (p == 1) ? e->codec_embd : e->cp_embd[p - 2];
+            first.tok_ptr = &s.st->feed_codes[p - 1];
+        }
+        if (e->mtp) {
+            // talker space -> code-predictor space (src/tts_transformer.cpp:1709-1715)
+            Op m = gemv(e->mtp, c.cp_hidden_size, c.hidden_size, hidden, nullptr, c.rms_norm_eps,
+                        e->mtp_b ? EPI_BIAS : EPI_STORE, s.cp_x);
+            m.in_kind = first.in_kind; m.table = first.table; m.tok_ptr = first.tok_ptr; m.bias = e->mtp_b;
+            P.push_back(m);
+            first = blank(); first.in_kind = IN_VEC; first.in = s.cp_x;
+        } else {
+            first.x_out = s.cp_x;
+        }
+        const int mode = (p < 2) ? ATTN_F32 : ATTN_SOFTMAX_P16;
+        for (int l = 0; l < c.cp_layers; ++l)
+            emit_layer(e, P, e->cp[l], D, B, l, l == 0 ? &first : nullptr, false, p, mode);
+        if (p >= 1) {
+            P.push_back(gemv(e->lm_head[p - 1], c.cp_vocab_size, c.cp_hidden_size, s.cp_x, e->cp_output_norm,
+                             c.rms_norm_eps, EPI_STORE, s.cp_logits));
+            Op sp = blank();
+            sp.type = OP_SAMPLE_CP; sp.logits = s.cp_logits; sp.n_vocab = c.cp_vocab_size; sp.book = p;
+            sp.uniforms = uniforms; sp.forced = forced;
+            sp.dump = dump ? dump + (size_t) (p - 1) * c.cp_vocab_size : nullptr;
+            if (override_sampling) { sp.temperature_override = temperature; sp.top_k_override = top_k; }
+            P.push_back(sp);
+        }
+    }
+}
+
+void emit_frame(Engine * e, Slot & s, std::vector<Op> & P) {
+    const qtts_config & c = e->cfg;
+    Op s0 = blank();
+    s0.type = OP_SAMPLE_CB0; s0.logits = s.logits; s0.n_vocab = c.codec_vocab_size;
+    s0.eos_id = c.codec_eos_id; s0.suppress_start = c.codec_vocab_size - 1024;
+    s0.dump = s.cb0_dump;
+    P.push_back(s0);
+    emit_code_predictor(e, s, P, s.hidden, nullptr, nullptr, nullptr, false, 0.f, 0);
+    Op fe = blank();
+    fe.type = OP_FRAME_END; fe.codes_out = s.codes; fe.n_books = c.n_codebooks;
+    P.push_back(fe);
+    const int mode = (e->numerics == QTTS_NUMERICS_REFERENCE) ? ATTN_FLASH_F16SEQ : ATTN_FAST;
+    emit_talker_step(e, s, P, IN_EMBED_SUM, nullptr, true, 0, mode, true, true);
+}
+
+static Op copy_op(float * out, const float * a, const float * b, int n) {
+    Op o = blank();
+    o.type = OP_COPY; o.out = out; o.a = a; o.b = b; o.n = n;
+    return o;
+}
+static Op row_op(float * out, const __half * table, const int32_t * tok_ptr, const float * b, int n) {
+    Op o = blank();
+    o.type = OP_COPY; o.out = out; o.table = table; o.tok_ptr = tok_ptr; o.b = b; o.n = n;
+    return o;
+}
+
+// build_prefill_graph (src/tts_transformer.cpp:1093-1231) on the device.  Token ids are staged in
+// s.tokens: [0..n) the text tokens, then the 3 special text ids, then the codec ids.
+bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t * tokens, int n_tokens,
+                        bool has_speaker, int language_id) {
+    const qtts_config & c = e->cfg;
+    const int H = c.hidden_size, E = c.text_embd_dim;
+    if (n_tokens < 4) return e->fail("Need at least 4 text tokens for prefill");
+    if (n_tokens > e->max_text) return e->fail("text longer than the engine's max_text");
+    std::vector<int32_t> ids(tokens, tokens + n_tokens);
+    for (int i = 0; i < n_tokens; ++i)
+        if (ids[i] < 0 || ids[i] >= c.text_vocab_size) return e->fail("text token id out of range");
+    const int sp0 = n_tokens;
+    ids.push_back(c.tts_bos_id); ids.push_back(c.tts_eos_id); ids.push_back(c.tts_pad_id);
+    std::vector<int32_t> codec;
+    if (language_id < 0) codec = {c.codec_nothink_id, c.codec_think_bos_id, c.codec_think_eos_id};
+    else codec = {c.codec_think_id, c.codec_think_bos_id, language_id, c.codec_think_eos_id};
+    const int n_codec_prefill = (int) codec.size();
+    codec.push_back(c.codec_pad_id); codec.push_back(c.codec_bos_id);
+    for (int v : codec) if (v < 0 || v >= c.codec_vocab_size) return e->fail("codec prefill id out of range");
+    const int cd0 = (int) ids.size();
+    ids.insert(ids.end(), codec.begin(), codec.end());
+    QTTS_CUDA(cudaMemcpyAsync(s.tokens, ids.data(), ids.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));   // ids is a stack-lifetime host buffer
+
+    auto text_proj = [&](int tok_index, float * dst) {   // project_text_tokens (:1026-1091)
+        Op f1 = gemv(e->fc1, E, E, nullptr, nullptr, c.rms_norm_eps, EPI_BIAS_SILU, s.tp_tmp);
+        f1.in_kind = IN_EMBED_ROW; f1.table = e->text_embd; f1.tok_ptr = s.tokens + tok_index; f1.bias = e->fc1_b;
+        P.push_back(f1);
+        Op f2 = gemv(e->fc2, H, E, s.tp_tmp, nullptr, c.rms_norm_eps, EPI_BIAS, dst);
+        f2.bias = e->fc2_b;
+        P.push_back(f2);
+    };
+    float * bos = s.misc, * eos = s.misc + H, * first_text = s.misc + 2 * (size_t) H;
+    text_proj(sp0 + 0, bos);
+    text_proj(sp0 + 1, eos);
+    text_proj(sp0 + 2, s.pad);
+    for (int t = 0; t < 3; ++t) text_proj(t, s.prefill + (size_t) t * H);     // role rows
+    // codec rows (+ speaker) with the tts_pad / tts_bos overlay (:1165-1193)
+    const int codec_input_len = n_codec_prefill + (has_speaker ? 1 : 0) + 2;
+    const int overlay_len = codec_input_len - 1;
+    for (int t = 0; t < overlay_len; ++t) {
+        const float * overlay = (t == overlay_len - 1) ? bos : s.pad;
+        float * dst = s.prefill + (size_t) (3 + t) * H;
+        if (has_speaker && t == n_codec_prefill) {
+            P.push_back(copy_op(dst, overlay, s.speaker, H));
+        } else {
+            const int ci = (t < n_codec_prefill) ? t : t - (has_speaker ? 1 : 0);
+            P.push_back(row_op(dst, e->codec_embd, s.tokens + cd0 + ci, overlay, H));
+        }
+    }
+    // last prefill row: text_proj(tokens[3]) + codec_embd(codec_bos) (:1195-1204)
+    text_proj(3, first_text);
+    const int prefill_len = 3 + overlay_len + 1;
+    P.push_back(row_op(s.prefill + (size_t) (prefill_len - 1) * H, e->codec_embd,
+                       s.tokens + cd0 + n_codec_prefill + 1, first_text, H));
+    // trailing text rows + tts_eos (:1214-1228)
+    const int trailing_tokens = n_tokens - 9 > 0 ? n_tokens - 9 : 0;
+    for (int t = 0; t < trailing_tokens; ++t) text_proj(4 + t, s.trailing + (size_t) t * H);
+    P.push_back(copy_op(s.trailing + (size_t) trailing_tokens * H, eos, nullptr, H));
+    s.prefill_len = prefill_len;
+    s.trailing_len = trailing_tokens + 1;
+    s.n_text_tokens = n_tokens;
+    return true;
+}
+
+bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vector<Op> * host_ops, int n_ops,
+                        int n_frames, bool check_done) {
+    if (n_ops == 0) return true;
+    if (e->persistent) {
+        QTTS_CUDA(cudaMemsetAsync(&e->bar->count, 0, sizeof(unsigned int), e->stream));
+        int persistent = 1, cd = check_done ? 1 : 0;
+        StreamState * st = s.st;
+        GridBarrier * bar = e->bar;
+        void * args[] = {(void *) &d_ops, (void *) &n_ops, (void *) &st, (void *) &bar, (void *) &n_frames,
+                         (void *) &persistent, (void *) &cd};
+        QTTS_CUDA(cudaLaunchCooperativeKernel((const void *) qtts_run_program, dim3(e->n_sms), dim3(kThreads),
+                                              args, e->smem_bytes, e->stream));
+        e->launches += 1;
+        return true;
+    }
+    // debug path: one launch per stage; needs the host copy of the program to find sampling stages
+    for (int f = 0; f < n_frames; ++f) {
+        for (int i = 0; i < n_ops; ++i) {
+            qtts_run_program<<<e->n_sms, kThreads, e->smem_bytes, e->stream>>>(d_ops + i, 1, s.st, e->bar, 1, 0, 0);
+            e->launches += 1;
+            const int type = host_ops ? (*host_ops)[i].type : -1;
+            if (check_done && (type == OP_SAMPLE_CB0 || type == OP_FRAME_END || !host_ops)) {
+                int done = 0;
+                QTTS_CUDA(cudaMemcpyAsync(&done, &s.st->done, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+                QTTS_CUDA(cudaStreamSynchronize(e->stream));
+                if (done) return true;
+            }
+        }
+    }
+    QTTS_CUDA(cudaGetLastError());
+    return true;
+}
+
+bool run_program(Engine * e, Slot & s, const std::vector<Op> & P, int n_frames, bool check_done) {
+    if (P.empty()) return true;
+    if ((int) P.size() > s.scratch_cap) {
+        const int cap = (int) P.size() + 256;
+        Op * p = e->dalloc<Op>(cap, false);
+        if (!p) return e->fail("out of device memory for program");
+        s.scratch_prog = p; s.scratch_cap = cap;   // older buffer stays in allocs until destroy
+    }
+    QTTS_CUDA(cudaMemcpyAsync(s.scratch_prog, P.data(), P.size() * sizeof(Op), cudaMemcpyHostToDevice, e->stream));
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));   // P may be freed by the caller right after
+    return run_device_program(e, s, s.scratch_prog, &P, (int) P.size(), n_frames, check_done);
+}
+
+}  // namespace qtts

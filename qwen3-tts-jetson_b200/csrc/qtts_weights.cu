@@ -1,0 +1,301 @@
+// qtts_weights.cu — GGUF tensor upload and the fused BF16 device layouts.
+//
+// Replaces TTSTransformer::create_tensors / load_tensor_data
+// (reference: src/tts_transformer.cpp:444-792).  The on-disk contract is the GGUF tensor set of
+// scripts/convert_tts_to_gguf.py:42-109 (2-D F16 [out,in] row-major, 1-D F32); the HBM layout
+// is ours: per layer one [q;k;v] matrix, one gate/up matrix with rows interleaved
+// (row 2i = gate_i, row 2i+1 = up_i) so the SwiGLU epilogue sees both halves in one warp, all
+// projection weights in BF16, embedding tables kept in F16 (bit copies of the file).
+#include "qtts_engine.h"
+#include <cmath>
+#include <cstring>
+
+namespace qtts {
+
+__global__ void k_f16_to_bf16(const __half * __restrict__ src, __nv_bfloat16 * __restrict__ dst,
+                              size_t n, unsigned long long * inexact) {
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int bad = 0;
+    for (; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        const float f = __half2float(src[i]);
+        const __nv_bfloat16 b = __float2bfloat16_rn(f);
+        dst[i] = b;
+        bad += (__bfloat162float(b) != f);
+    }
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(inexact, (unsigned long long) bad);
+}
+
+// dst[(2r+which)*K + k] = src[r*K + k]
+__global__ void k_f16_to_bf16_interleave(const __half * __restrict__ src, __nv_bfloat16 * __restrict__ dst,
+                                         int rows, int K, int which, unsigned long long * inexact) {
+    size_t n = (size_t) rows * K;
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int bad = 0;
+    for (; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / K, k = i % K;
+        const float f = __half2float(src[i]);
+        const __nv_bfloat16 b = __float2bfloat16_rn(f);
+        dst[(2 * r + which) * K + k] = b;
+        bad += (__bfloat162float(b) != f);
+    }
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(inexact, (unsigned long long) bad);
+}
+
+static bool wanted(const std::string & n) {
+    return n.rfind("talker.", 0) == 0 || n.rfind("code_pred.", 0) == 0;
+}
+
+bool engine_upload(Engine * e, const char * name_c, int dtype, const int64_t * dims, int n_dims, const void * host) {
+    if (e->finalized) return e->fail("upload after finalize");
+    const std::string name(name_c);
+    if (!wanted(name)) return true;   // spk_enc.* / tok_* are not on the path (src/tts_transformer.cpp:473)
+    if (n_dims < 1 || n_dims > 2) return e->fail("tensor " + name + ": unsupported rank");
+    if (dtype != QTTS_F32 && dtype != QTTS_F16) return e->fail("tensor " + name + ": unsupported dtype (only F32/F16; quantised GGUF types are rejected)");
+    DevTensor t;
+    t.n_dims = n_dims;
+    t.n_elem = 1;
+    for (int i = 0; i < n_dims; ++i) { t.ne[i] = dims[i]; t.n_elem *= (size_t) dims[i]; }
+    // canonical storage: 1-D -> F32, 2-D -> F16
+    const int want = (n_dims == 1) ? QTTS_F32 : QTTS_F16;
+    std::vector<uint8_t> conv;
+    const void * src = host;
+    if (dtype != want) {
+        if (want == QTTS_F32) {
+            conv.resize(t.n_elem * 4);
+            float * d = (float *) conv.data();
+            const __half * s = (const __half *) host;
+            for (size_t i = 0; i < t.n_elem; ++i) d[i] = __half2float(s[i]);
+        } else {
+            conv.resize(t.n_elem * 2);
+            __half * d = (__half *) conv.data();
+            const float * s = (const float *) host;
+            for (size_t i = 0; i < t.n_elem; ++i) d[i] = __float2half_rn(s[i]);
+        }
+        src = conv.data();
+    }
+    t.dtype = want;
+    const size_t bytes = t.n_elem * (want == QTTS_F32 ? 4 : 2);
+    if (cudaMalloc(&t.raw, bytes) != cudaSuccess) { cudaGetLastError(); return e->fail("cudaMalloc failed for " + name); }
+    QTTS_CUDA(cudaMemcpy(t.raw, src, bytes, cudaMemcpyHostToDevice));
+    auto it = e->tensors.find(name);
+    if (it != e->tensors.end()) { cudaFree(it->second.raw); }
+    e->tensors[name] = t;
+    return true;
+}
+
+static DevTensor * need(Engine * e, const std::string & name, int64_t ne0, int64_t ne1) {
+    auto it = e->tensors.find(name);
+    if (it == e->tensors.end()) { e->err = "missing tensor " + name; return nullptr; }
+    DevTensor & t = it->second;
+    if (t.ne[0] != ne0 || (ne1 > 0 && t.ne[1] != ne1) || (ne1 == 0 && t.n_dims != 1)) {
+        e->err = "tensor " + name + " has shape [" + std::to_string(t.ne[0]) + "," + std::to_string(t.ne[1]) +
+                 "], expected [" + std::to_string(ne0) + "," + std::to_string(ne1) + "]";
+        return nullptr;
+    }
+    return &t;
+}
+
+static bool to_bf16(Engine * e, DevTensor * t, __nv_bfloat16 * dst) {
+    k_f16_to_bf16<<<592, 256, 0, e->stream>>>((const __half *) t->raw, dst, t->n_elem, e->d_inexact);
+    e->n_weights += (int64_t) t->n_elem;
+    QTTS_CUDA(cudaGetLastError());
+    return true;
+}
+
+static void drop_raw(Engine * e, const std::string & name) {
+    auto it = e->tensors.find(name);
+    if (it != e->tensors.end() && it->second.raw) { cudaFree(it->second.raw); it->second.raw = nullptr; }
+}
+
+static bool build_layer(Engine * e, const std::string & pre, const Dims & D, LayerW & L) {
+    const int hd = kHeadDim;
+    const int64_t qr = (int64_t) D.nh * hd, kr = (int64_t) D.nkv * hd;
+    DevTensor * q = need(e, pre + ".attn_q.weight", D.H, qr);          if (!q) return false;
+    DevTensor * k = need(e, pre + ".attn_k.weight", D.H, kr);          if (!k) return false;
+    DevTensor * v = need(e, pre + ".attn_v.weight", D.H, kr);          if (!v) return false;
+    DevTensor * o = need(e, pre + ".attn_output.weight", qr, D.H);     if (!o) return false;
+    DevTensor * g = need(e, pre + ".ffn_gate.weight", D.H, D.ffn);     if (!g) return false;
+    DevTensor * u = need(e, pre + ".ffn_up.weight", D.H, D.ffn);       if (!u) return false;
+    DevTensor * d = need(e, pre + ".ffn_down.weight", D.ffn, D.H);     if (!d) return false;
+    DevTensor * an = need(e, pre + ".attn_norm.weight", D.H, 0);       if (!an) return false;
+    DevTensor * fn = need(e, pre + ".ffn_norm.weight", D.H, 0);        if (!fn) return false;
+    L.attn_norm = (float *) an->raw;
+    L.ffn_norm = (float *) fn->raw;
+    // Qwen3 QK-norm is optional in the reference graph (src/tts_transformer.cpp:1424-1432)
+    auto qn = e->tensors.find(pre + ".attn_q_norm.weight");
+    auto kn = e->tensors.find(pre + ".attn_k_norm.weight");
+    L.q_norm = (qn != e->tensors.end()) ? (float *) qn->second.raw : nullptr;
+    L.k_norm = (kn != e->tensors.end()) ? (float *) kn->second.raw : nullptr;
+
+    L.wqkv = e->dalloc<__nv_bfloat16>((size_t) (qr + 2 * kr) * D.H, false);
+    L.wo = e->dalloc<__nv_bfloat16>((size_t) D.H * qr, false);
+    L.wgu = e->dalloc<__nv_bfloat16>((size_t) 2 * D.ffn * D.H, false);
+    L.wdown = e->dalloc<__nv_bfloat16>((size_t) D.H * D.ffn, false);
+    if (!L.wqkv || !L.wo || !L.wgu || !L.wdown) return e->fail("out of device memory for " + pre);
+    if (!to_bf16(e, q, L.wqkv)) return false;
+    if (!to_bf16(e, k, L.wqkv + (size_t) qr * D.H)) return false;
+    if (!to_bf16(e, v, L.wqkv + (size_t) (qr + kr) * D.H)) return false;
+    if (!to_bf16(e, o, L.wo)) return false;
+    if (!to_bf16(e, d, L.wdown)) return false;
+    k_f16_to_bf16_interleave<<<592, 256, 0, e->stream>>>((const __half *) g->raw, L.wgu, D.ffn, D.H, 0, e->d_inexact);
+    k_f16_to_bf16_interleave<<<592, 256, 0, e->stream>>>((const __half *) u->raw, L.wgu, D.ffn, D.H, 1, e->d_inexact);
+    e->n_weights += (int64_t) g->n_elem + (int64_t) u->n_elem;
+    QTTS_CUDA(cudaGetLastError());
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    e->weight_bytes += (int64_t) ((qr + 2 * kr) * D.H + D.H * qr + 3 * (int64_t) D.ffn * D.H) * 2;
+    for (const char * s : {".attn_q.weight", ".attn_k.weight", ".attn_v.weight", ".attn_output.weight",
+                           ".ffn_gate.weight", ".ffn_up.weight", ".ffn_down.weight"})
+        drop_raw(e, pre + s);
+    return true;
+}
+
+static bool single_bf16(Engine * e, const std::string & name, int64_t ne0, int64_t ne1, __nv_bfloat16 ** out) {
+    DevTensor * t = need(e, name, ne0, ne1);
+    if (!t) return false;
+    *out = e->dalloc<__nv_bfloat16>(t->n_elem, false);
+    if (!*out) return e->fail("out of device memory for " + name);
+    if (!to_bf16(e, t, *out)) return false;
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    e->weight_bytes += (int64_t) t->n_elem * 2;
+    drop_raw(e, name);
+    return true;
+}
+
+static bool alloc_slot(Engine * e, Slot & s) {
+    const qtts_config & c = e->cfg;
+    const int H = c.hidden_size, cpH = c.cp_hidden_size, E = c.text_embd_dim;
+    const int qkvw = (c.n_heads + 2 * c.n_kv_heads) * kHeadDim;
+    const int cqkvw = (c.cp_n_heads + 2 * c.cp_n_kv_heads) * kHeadDim;
+    const int kvw = c.n_kv_heads * kHeadDim, ckvw = c.cp_n_kv_heads * kHeadDim;
+    const int maxH = H > cpH ? H : cpH;
+    s.st = e->dalloc<StreamState>(1);
+    s.x = e->dalloc<float>(maxH);
+    s.qkv = e->dalloc<float>(qkvw);
+    s.attn = e->dalloc<float>((size_t) c.n_heads * kHeadDim);
+    s.act = e->dalloc<float>(c.intermediate_size);
+    s.logits = e->dalloc<float>(c.codec_vocab_size);
+    s.hidden = e->dalloc<float>(H);
+    s.in_embd = e->dalloc<float>(H);
+    s.cp_x = e->dalloc<float>(maxH);
+    s.cp_qkv = e->dalloc<float>(cqkvw);
+    s.cp_attn = e->dalloc<float>((size_t) c.cp_n_heads * kHeadDim);
+    s.cp_act = e->dalloc<float>(c.cp_intermediate_size);
+    s.cp_logits = e->dalloc<float>(c.cp_vocab_size);
+    s.cp_hidden_in = e->dalloc<float>(H);
+    s.cp_dump = e->dalloc<float>((size_t) 16 * c.cp_vocab_size);
+    s.cb0_dump = e->dalloc<float>(c.codec_vocab_size);
+    s.uniforms = e->dalloc<float>((size_t) e->max_ctx + 16);
+    s.forced = e->dalloc<int32_t>(16);
+    const size_t kvn = (size_t) c.n_layers * e->max_ctx * kvw;
+    s.kc = e->dalloc<__half>(kvn);
+    s.vc = e->dalloc<__half>(kvn);
+    s.cp_kc = e->dalloc<__half>((size_t) c.cp_layers * 16 * ckvw);
+    s.cp_vc = e->dalloc<__half>((size_t) c.cp_layers * 16 * ckvw);
+    s.cp_kv0 = e->dalloc<float>((size_t) c.cp_layers * 2 * ckvw);
+    s.prefill = e->dalloc<float>((size_t) 64 * H);
+    s.trailing = e->dalloc<float>((size_t) (e->max_text + 1) * H);
+    s.pad = e->dalloc<float>(H);
+    s.tp_tmp = e->dalloc<float>(E);
+    s.misc = e->dalloc<float>((size_t) 16 * H);
+    s.speaker = e->dalloc<float>(H);
+    s.tokens = e->dalloc<int32_t>((size_t) e->max_text + 16);
+    s.codes = e->dalloc<int32_t>((size_t) e->max_ctx * c.n_codebooks);
+    s.es = e->dalloc<EmbedSumArgs>(1);
+    if (!s.es || !s.codes || !s.kc || !s.vc || !s.trailing) return e->fail("out of device memory for stream slots");
+    e->kv_bytes += (int64_t) kvn * 2 * 2;
+    EmbedSumArgs es{};
+    es.tables[0] = e->codec_embd;
+    for (int i = 1; i < c.n_codebooks; ++i) es.tables[i] = e->cp_embd[i - 1];
+    es.n_books = c.n_codebooks;
+    es.trailing = s.trailing;
+    es.pad = s.pad;
+    QTTS_CUDA(cudaMemcpy(s.es, &es, sizeof(es), cudaMemcpyHostToDevice));
+    s.frame_host.clear();
+    emit_frame(e, s, s.frame_host);
+    s.frame_prog_n = (int) s.frame_host.size();
+    s.frame_prog = e->dalloc<Op>(s.frame_host.size(), false);
+    if (!s.frame_prog) return e->fail("out of device memory for frame program");
+    QTTS_CUDA(cudaMemcpy(s.frame_prog, s.frame_host.data(), s.frame_host.size() * sizeof(Op), cudaMemcpyHostToDevice));
+    return true;
+}
+
+bool engine_finalize(Engine * e) {
+    if (e->finalized) return true;
+    const qtts_config & c = e->cfg;
+    if (c.head_dim != kHeadDim || c.cp_head_dim != kHeadDim) return e->fail("head_dim must be 128");
+    if (c.n_codebooks > kMaxBooks || c.codec_vocab_size > kMaxVocab || c.cp_vocab_size > kMaxVocab)
+        return e->fail("vocab / codebook count exceeds engine limits");
+    for (int k : {c.hidden_size, c.intermediate_size, c.cp_hidden_size, c.cp_intermediate_size, c.text_embd_dim,
+                  c.n_heads * kHeadDim, c.cp_n_heads * kHeadDim})
+        if (k % 256 != 0) return e->fail("feature dimensions must be multiples of 256");
+    e->d_inexact = e->dalloc<unsigned long long>(1);
+    e->bar = e->dalloc<GridBarrier>(1);
+    if (!e->d_inexact || !e->bar) return e->fail("out of device memory");
+
+    const Dims T{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
+    const Dims C{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
+    e->talker.resize(c.n_layers);
+    for (int i = 0; i < c.n_layers; ++i)
+        if (!build_layer(e, "talker.blk." + std::to_string(i), T, e->talker[i])) return false;
+    e->cp.resize(c.cp_layers);
+    for (int i = 0; i < c.cp_layers; ++i)
+        if (!build_layer(e, "code_pred.blk." + std::to_string(i), C, e->cp[i])) return false;
+
+    if (!single_bf16(e, "talker.codec_head.weight", c.hidden_size, c.codec_vocab_size, &e->codec_head)) return false;
+    if (!single_bf16(e, "talker.text_proj.fc1.weight", c.text_embd_dim, c.text_embd_dim, &e->fc1)) return false;
+    if (!single_bf16(e, "talker.text_proj.fc2.weight", c.text_embd_dim, c.hidden_size, &e->fc2)) return false;
+    e->lm_head.resize(c.n_codebooks - 1);
+    for (int i = 0; i < c.n_codebooks - 1; ++i)
+        if (!single_bf16(e, "code_pred.lm_head." + std::to_string(i) + ".weight", c.cp_hidden_size, c.cp_vocab_size, &e->lm_head[i])) return false;
+    if (c.cp_hidden_size != c.hidden_size || e->tensors.count("code_pred.mtp_proj.weight")) {
+        if (!single_bf16(e, "code_pred.mtp_proj.weight", c.hidden_size, c.cp_hidden_size, &e->mtp)) return false;
+        auto b = e->tensors.find("code_pred.mtp_proj.bias");
+        e->mtp_b = (b != e->tensors.end()) ? (float *) b->second.raw : nullptr;
+    }
+    DevTensor * t;
+    if (!(t = need(e, "talker.output_norm.weight", c.hidden_size, 0))) return false;   e->output_norm = (float *) t->raw;
+    if (!(t = need(e, "code_pred.output_norm.weight", c.cp_hidden_size, 0))) return false; e->cp_output_norm = (float *) t->raw;
+    if (!(t = need(e, "talker.text_proj.fc1.bias", c.text_embd_dim, 0))) return false; e->fc1_b = (float *) t->raw;
+    if (!(t = need(e, "talker.text_proj.fc2.bias", c.hidden_size, 0))) return false;   e->fc2_b = (float *) t->raw;
+    if (!(t = need(e, "talker.codec_embd.weight", c.hidden_size, c.codec_vocab_size))) return false; e->codec_embd = (const __half *) t->raw;
+    e->weight_bytes += (int64_t) t->n_elem * 2;
+    if (!(t = need(e, "talker.text_embd.weight", c.text_embd_dim, c.text_vocab_size))) return false; e->text_embd = (const __half *) t->raw;
+    e->weight_bytes += (int64_t) t->n_elem * 2;
+    e->cp_embd.resize(c.n_codebooks - 1);
+    for (int i = 0; i < c.n_codebooks - 1; ++i) {
+        if (!(t = need(e, "code_pred.codec_embd." + std::to_string(i) + ".weight", c.hidden_size, c.cp_vocab_size))) return false;
+        e->cp_embd[i] = (const __half *) t->raw;
+        e->weight_bytes += (int64_t) t->n_elem * 2;
+    }
+    unsigned long long bad = 0;
+    QTTS_CUDA(cudaMemcpy(&bad, e->d_inexact, sizeof(bad), cudaMemcpyDeviceToHost));
+    e->n_inexact = (int64_t) bad;
+
+    // RoPE table exactly as ggml_rope_cache_init computes it (ops.cpp:5612-5627): theta starts at
+    // the position and is multiplied by theta_scale = powf(base, -2/n_dims) pair after pair, in
+    // float; cosf/sinf from the host libm.
+    {
+        const int max_pos = e->max_ctx > 16 ? e->max_ctx : 16;
+        std::vector<float> tab((size_t) max_pos * 64 * 2);
+        const float theta_scale = powf(c.rope_theta, -2.0f / (float) kHeadDim);
+        for (int p = 0; p < max_pos; ++p) {
+            float theta = (float) p;
+            for (int i = 0; i < 64; ++i) {
+                tab[((size_t) p * 64 + i) * 2] = cosf(theta);
+                tab[((size_t) p * 64 + i) * 2 + 1] = sinf(theta);
+                theta *= theta_scale;
+            }
+        }
+        e->rope = e->dalloc<float>(tab.size(), false);
+        if (!e->rope) return e->fail("out of device memory for rope table");
+        QTTS_CUDA(cudaMemcpy(e->rope, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    e->slots.resize(e->max_streams);
+    for (auto & s : e->slots) if (!alloc_slot(e, s)) return false;
+    e->finalized = true;
+    return true;
+}
+
+}  // namespace qtts

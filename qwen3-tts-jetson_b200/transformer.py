@@ -1,0 +1,276 @@
+"""Host-side mirror of `qwen3_tts::TTSTransformer` (reference: src/tts_transformer.h:164-245) and of
+`qwen3_tts::TRTCodePredictor`'s loops (src/trt_code_predictor.h:25-87) over the C ABI of
+libqtts_b200.so (include/qtts_b200.h).  Same method names, argument meaning and error
+behaviour (bool return + get_error()); numpy arrays stand in for std::vector.
+
+The library is the product; this module only marshals pointers.  There is no CPU fallback:
+if the CUDA library is missing or no B200 is present every call fails.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+from . import gguf_io
+
+NUMERICS_REFERENCE = 0
+NUMERICS_FAST = 1
+
+_CFG_INT_FIELDS = ["hidden_size", "n_layers", "n_heads", "n_kv_heads", "intermediate_size", "head_dim",
+                   "codec_vocab_size", "n_codebooks", "cp_layers", "cp_vocab_size", "cp_hidden_size",
+                   "cp_intermediate_size", "cp_n_heads", "cp_n_kv_heads", "cp_head_dim",
+                   "text_vocab_size", "text_embd_dim"]
+_CFG_TAIL_FIELDS = ["codec_pad_id", "codec_bos_id", "codec_eos_id", "codec_think_id", "codec_nothink_id",
+                    "codec_think_bos_id", "codec_think_eos_id", "tts_bos_id", "tts_eos_id", "tts_pad_id"]
+
+
+class QttsConfig(C.Structure):
+    _fields_ = ([(n, C.c_int32) for n in _CFG_INT_FIELDS] +
+                [("rms_norm_eps", C.c_float), ("rope_theta", C.c_float)] +
+                [(n, C.c_int32) for n in _CFG_TAIL_FIELDS])
+
+
+FRAME_CB = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_void_p)
+
+# every symbol include/qtts_b200.h declares
+EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error", "qtts_upload_tensor",
+           "qtts_finalize", "qtts_weight_stats", "qtts_set_numerics", "qtts_set_persistent",
+           "qtts_clear_kv_cache", "qtts_build_prefill", "qtts_forward_prefill", "qtts_forward_step",
+           "qtts_predict_codes", "qtts_generate", "qtts_stream_begin", "qtts_step_frames",
+           "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
+
+_lib = None
+
+
+def load_library(path: str | None = None):
+    """dlopen libqtts_b200.so (built in-tree by build.py) and declare the prototypes."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or _build.LIB
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} is missing: run __graft_entry__.build() (nvcc, sm_100a). "
+                           "There is no CPU fallback for this path.")
+    lib = C.CDLL(path)
+    vp, i32, f32p, i32p = C.c_void_p, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int32)
+    lib.qtts_create.argtypes = [C.POINTER(QttsConfig), C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    lib.qtts_destroy.argtypes = [vp]
+    lib.qtts_destroy.restype = None
+    lib.qtts_last_error.argtypes = [vp]
+    lib.qtts_last_error.restype = C.c_char_p
+    lib.qtts_create_error.restype = C.c_char_p
+    lib.qtts_upload_tensor.argtypes = [vp, C.c_char_p, C.c_int, C.POINTER(C.c_int64), C.c_int, vp]
+    lib.qtts_finalize.argtypes = [vp]
+    lib.qtts_weight_stats.argtypes = [vp, C.POINTER(C.c_int64)]
+    lib.qtts_set_numerics.argtypes = [vp, C.c_int, C.c_int]
+    lib.qtts_set_persistent.argtypes = [vp, C.c_int]
+    lib.qtts_clear_kv_cache.argtypes = [vp, C.c_int]
+    lib.qtts_build_prefill.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32p, i32p, vp, vp, vp]
+    lib.qtts_forward_prefill.argtypes = [vp, C.c_int, vp, i32, i32, vp, vp]
+    lib.qtts_forward_step.argtypes = [vp, C.c_int, vp, i32, vp, vp]
+    lib.qtts_predict_codes.argtypes = [vp, C.c_int, vp, i32, C.c_float, i32, vp, vp, vp, vp]
+    lib.qtts_generate.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64,
+                                  vp, i32p, FRAME_CB, i32, vp]
+    lib.qtts_stream_begin.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64]
+    lib.qtts_step_frames.argtypes = [vp, i32, vp, vp, vp]
+    lib.qtts_launch_count.argtypes = [vp]
+    lib.qtts_launch_count.restype = C.c_int64
+    lib.qtts_last_loop_ms.argtypes = [vp]
+    lib.qtts_last_loop_ms.restype = C.c_double
+    lib.qtts_stream_handle.argtypes = [vp]
+    lib.qtts_stream_handle.restype = vp
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class TTSTransformer:
+    """Drop-in for the reference class on one B200.  `max_streams` > 1 adds the concurrent
+    utterance slots the reference lacks (each reference-level method takes `slot`)."""
+
+    def __init__(self, device: int = 0, max_streams: int = 1, max_ctx: int = 4224):
+        self._lib = load_library()
+        self._h = C.c_void_p()
+        self._err = ""
+        self.device, self.max_streams, self.max_ctx = device, max_streams, max_ctx
+        self.config: dict = {}
+
+    # -- error handling (bool + get_error(), like the reference) --------------------------------
+    def get_error(self) -> str:
+        if self._h:
+            return self._lib.qtts_last_error(self._h).decode()
+        return self._err
+
+    def get_config(self) -> dict:
+        return self.config
+
+    # -- load_model (src/tts_transformer.cpp:51-153) ----------------------------------------------
+    def load_model(self, model_path: str) -> bool:
+        self.unload_model()
+        try:
+            cfg, tensors = gguf_io.read_gguf(model_path)
+        except Exception as ex:  # unreadable file / unsupported tensor type
+            self._err = f"Failed to open GGUF file: {ex}"
+            return False
+        return self.load_tensors(cfg, tensors())
+
+    def load_tensors(self, cfg: dict, tensors) -> bool:
+        """cfg: gguf_io.parse_config dict; tensors: iterable of (name, dtype_code, ggml_dims, array)."""
+        self.config = dict(cfg)
+        c = QttsConfig()
+        for n in _CFG_INT_FIELDS + _CFG_TAIL_FIELDS:
+            setattr(c, n, int(cfg[n]))
+        c.rms_norm_eps, c.rope_theta = cfg["rms_norm_eps"], cfg["rope_theta"]
+        h = C.c_void_p()
+        if not self._lib.qtts_create(C.byref(c), self.device, self.max_streams, self.max_ctx, C.byref(h)):
+            self._err = self._lib.qtts_create_error().decode()
+            return False
+        self._h = h
+        for name, code, dims, arr in tensors:
+            d = (C.c_int64 * len(dims))(*dims)
+            if not self._lib.qtts_upload_tensor(self._h, name.encode(), code, d, len(dims), _ptr(arr)):
+                return False
+        return bool(self._lib.qtts_finalize(self._h))
+
+    def unload_model(self):
+        if self._h:
+            self._lib.qtts_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.unload_model()
+        except Exception:
+            pass
+
+    def is_loaded(self) -> bool:
+        return bool(self._h)
+
+    # -- engine switches -----------------------------------------------------------------------
+    def set_numerics(self, mode: int, reference_threads: int = 4) -> bool:
+        return bool(self._lib.qtts_set_numerics(self._h, mode, reference_threads))
+
+    def set_persistent(self, on: bool) -> bool:
+        return bool(self._lib.qtts_set_persistent(self._h, 1 if on else 0))
+
+    def weight_stats(self) -> dict:
+        out = (C.c_int64 * 4)()
+        self._lib.qtts_weight_stats(self._h, out)
+        return {"n_weights": out[0], "n_not_bf16_exact": out[1], "weight_bytes": out[2], "kv_bytes": out[3]}
+
+    def launch_count(self) -> int:
+        return int(self._lib.qtts_launch_count(self._h))
+
+    def last_loop_ms(self) -> float:
+        return float(self._lib.qtts_last_loop_ms(self._h))
+
+    # -- KV cache (src/tts_transformer.cpp:794-900) -------------------------------------------------
+    def init_kv_cache(self, n_ctx: int) -> bool:
+        if n_ctx > self.max_ctx:
+            self._err = "init_kv_cache: n_ctx exceeds the engine's max_ctx"
+            return False
+        return True   # KV slabs are allocated once per slot at load time (max_ctx entries)
+
+    def clear_kv_cache(self, slot: int = 0) -> bool:
+        return bool(self._lib.qtts_clear_kv_cache(self._h, slot))
+
+    # -- build_prefill_graph (src/tts_transformer.cpp:1093-1231) ------------------------------------
+    def build_prefill(self, text_tokens, speaker_embd=None, language_id: int = 2050, slot: int = 0):
+        toks = np.ascontiguousarray(text_tokens, dtype=np.int32)
+        spk = None if speaker_embd is None else np.ascontiguousarray(speaker_embd, dtype=np.float32)
+        H = self.config["hidden_size"]
+        pre = np.zeros((16, H), np.float32)
+        trail = np.zeros((max(len(toks), 1) + 1, H), np.float32)
+        pad = np.zeros(H, np.float32)
+        pl, tl = C.c_int32(), C.c_int32()
+        ok = self._lib.qtts_build_prefill(self._h, slot, _ptr(toks), len(toks), _ptr(spk), language_id,
+                                          C.byref(pl), C.byref(tl), _ptr(pre), _ptr(trail), _ptr(pad))
+        if not ok:
+            return None
+        return pre[:pl.value].copy(), trail[:tl.value].copy(), pad
+
+    # -- forward_prefill / forward_step (src/tts_transformer.cpp:1829-2028) -------------------------
+    def forward_prefill(self, prefill_embd, n_past: int = 0, slot: int = 0):
+        e = np.ascontiguousarray(prefill_embd, dtype=np.float32)
+        hid = np.zeros(self.config["hidden_size"], np.float32)
+        logits = np.zeros(self.config["codec_vocab_size"], np.float32)
+        if not self._lib.qtts_forward_prefill(self._h, slot, _ptr(e), e.shape[0], n_past, _ptr(hid), _ptr(logits)):
+            return None
+        return hid, logits
+
+    def forward_step(self, step_embd, n_past: int, slot: int = 0):
+        e = np.ascontiguousarray(step_embd, dtype=np.float32)
+        hid = np.zeros(self.config["hidden_size"], np.float32)
+        logits = np.zeros(self.config["codec_vocab_size"], np.float32)
+        if not self._lib.qtts_forward_step(self._h, slot, _ptr(e), n_past, _ptr(logits), _ptr(hid)):
+            return None
+        return logits, hid
+
+    # -- predict_codes_autoregressive (src/tts_transformer.cpp:2153-2340) ---------------------------
+    def predict_codes_autoregressive(self, hidden, codebook_0_token: int, temperature: float = 0.9,
+                                     top_k: int = 50, uniforms=None, forced=None, want_logits: bool = False,
+                                     slot: int = 0):
+        hid = np.ascontiguousarray(hidden, dtype=np.float32)
+        nb = self.config["n_codebooks"] - 1
+        out = np.zeros(nb, np.int32)
+        logits = np.zeros((nb, self.config["cp_vocab_size"]), np.float32) if want_logits else None
+        u = None if uniforms is None else np.ascontiguousarray(uniforms, dtype=np.float32)
+        f = None if forced is None else np.ascontiguousarray(forced, dtype=np.int32)
+        ok = self._lib.qtts_predict_codes(self._h, slot, _ptr(hid), int(codebook_0_token), temperature, top_k,
+                                          _ptr(u), _ptr(f), _ptr(out), _ptr(logits))
+        if not ok:
+            return None
+        return (out, logits) if want_logits else out
+
+    # TRTCodePredictor::run_greedy_loop / run_sampling_loop (src/trt_code_predictor.cpp:484-726)
+    def run_greedy_loop(self, hidden, cb0_token: int, slot: int = 0):
+        return self.predict_codes_autoregressive(hidden, cb0_token, 0.0, 0, slot=slot)
+
+    def run_sampling_loop(self, hidden, cb0_token: int, temperature: float, top_k: int, rand_vals, slot: int = 0):
+        return self.predict_codes_autoregressive(hidden, cb0_token, temperature, top_k, uniforms=rand_vals, slot=slot)
+
+    # -- generate (src/tts_transformer.cpp:2342-2574) -----------------------------------------------
+    def generate(self, text_tokens, speaker_embd=None, max_len: int = 4096, language_id: int = 2050,
+                 repetition_penalty: float = 1.05, temperature: float = 0.9, top_k: int = 50,
+                 on_frames=None, callback_interval: int = 40, seed: int = 0, slot: int = 0):
+        """Returns int32 [n_frames, n_codebooks] or None (see get_error())."""
+        toks = np.ascontiguousarray(text_tokens, dtype=np.int32)
+        spk = None if speaker_embd is None else np.ascontiguousarray(speaker_embd, dtype=np.float32)
+        nb = self.config["n_codebooks"]
+        codes = np.zeros(max(max_len, 1) * nb, np.int32)
+        nf = C.c_int32()
+
+        def _cb(ptr, n_frames, n_books, _user):
+            arr = np.ctypeslib.as_array(ptr, shape=(n_frames * n_books,)).reshape(n_frames, n_books)
+            return 1 if on_frames(arr.copy(), n_frames, n_books) else 0
+
+        cb = FRAME_CB(_cb) if on_frames else C.cast(None, FRAME_CB)
+        ok = self._lib.qtts_generate(self._h, slot, _ptr(toks), len(toks), _ptr(spk), max_len, language_id,
+                                     repetition_penalty, temperature, top_k, seed, _ptr(codes), C.byref(nf),
+                                     cb, callback_interval, None)
+        if not ok:
+            return None
+        return codes[: nf.value * nb].reshape(nf.value, nb).copy()
+
+    # -- concurrent utterances ----------------------------------------------------------------------
+    def stream_begin(self, slot: int, text_tokens, speaker_embd=None, max_len: int = 4096, language_id: int = 2050,
+                     repetition_penalty: float = 1.05, temperature: float = 0.9, top_k: int = 50, seed: int = 0) -> bool:
+        toks = np.ascontiguousarray(text_tokens, dtype=np.int32)
+        spk = None if speaker_embd is None else np.ascontiguousarray(speaker_embd, dtype=np.float32)
+        return bool(self._lib.qtts_stream_begin(self._h, slot, _ptr(toks), len(toks), _ptr(spk), max_len, language_id,
+                                                repetition_penalty, temperature, top_k, seed))
+
+    def step_frames(self, n_frames: int):
+        nb = self.config["n_codebooks"]
+        codes = np.zeros((self.max_streams, n_frames, nb), np.int32)
+        produced = np.zeros(self.max_streams, np.int32)
+        active = np.zeros(self.max_streams, np.int32)
+        if not self._lib.qtts_step_frames(self._h, n_frames, _ptr(codes), _ptr(produced), _ptr(active)):
+            return None
+        return codes, produced, active
