@@ -78,6 +78,10 @@ int qtts_set_numerics(qtts_engine * e, int mode, int reference_threads);
 /* persistent = 1: one cooperative launch per frame group (default); 0: one launch per stage
  * (debug path, same device code). */
 int qtts_set_persistent(qtts_engine * e, int persistent);
+/* BENCHMARK switch, not reference behaviour: on = 1 makes codebook-0 EOS unselectable for
+ * streams begun afterwards, so every utterance runs exactly max_len frames (BASELINE configs
+ * quote fixed frame counts; a random-init model otherwise samples EOS at a random frame). */
+int qtts_set_ignore_eos(qtts_engine * e, int on);
 
 /* ---- reference-level entry points (TTSTransformer methods, one stream = `slot`) ----------- */
 

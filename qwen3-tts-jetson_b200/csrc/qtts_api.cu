@@ -115,6 +115,8 @@ int qtts_set_numerics(qtts_engine * h, int mode, int reference_threads) {
 
 int qtts_set_persistent(qtts_engine * h, int persistent) { h->e.persistent = persistent ? 1 : 0; return 1; }
 
+int qtts_set_ignore_eos(qtts_engine * h, int on) { h->e.ignore_eos = on ? 1 : 0; return 1; }
+
 int qtts_clear_kv_cache(qtts_engine * h, int slot) {
     Engine * e = &h->e;
     Slot * s = get_slot(e, slot);
@@ -244,6 +246,7 @@ static bool stream_begin(Engine * e, Slot & s, const int32_t * tokens, int32_t n
     StreamState st{};
     st.max_len = max_len; st.n_text_tokens = n; st.trailing_len = s.trailing_len;
     st.top_k = top_k; st.rep_pen = rep_pen; st.temperature = temperature; st.seed = seed;
+    st.ignore_eos = e->ignore_eos;
     QTTS_CUDA(cudaMemcpyAsync(s.st, &st, sizeof(st), cudaMemcpyHostToDevice, e->stream));
     QTTS_CUDA(cudaStreamSynchronize(e->stream));
     if (!do_forward_prefill(e, s, s.prefill_len, 0)) return false;

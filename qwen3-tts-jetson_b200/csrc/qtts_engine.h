@@ -72,6 +72,7 @@ struct Engine {
     int numerics = QTTS_NUMERICS_REFERENCE;
     int ref_threads = 4;          // ggml's default thread count (ggml/include/ggml.h:232)
     int persistent = 1;
+    int ignore_eos = 0;
     int64_t n_weights = 0, n_inexact = 0, weight_bytes = 0, kv_bytes = 0;
     int64_t launches = 0;
     double last_loop_ms = 0.0;

@@ -717,13 +717,18 @@ __device__ void stage_sample_cb0(const Op & op, StreamState * st, float * smem_f
         __syncthreads();
     }
     if (op.dump) for (int i = threadIdx.x; i < n; i += kThreads) op.dump[i] = sm->l[i];
+    const int ignore_eos = st->ignore_eos;
+    if (ignore_eos) {   // benchmark switch (not reference behaviour): fixed-length utterances
+        if (threadIdx.x == 0) sm->l[op.eos_id] = -CUDART_INF_F;
+        __syncthreads();
+    }
     int tok;
     if (temperature <= 0.0f) {
         tok = block_argmax(sm->l, n, sm);
     } else {
         const float u = op.uniforms ? __ldcg(op.uniforms + frame)
                                     : philox_uniform(st->seed, (uint32_t) frame, 0u, 0x0cb0u);
-        tok = block_sample(n, temperature, top_k, u, op.eos_id, sm);
+        tok = block_sample(n, temperature, top_k, u, ignore_eos ? -1 : op.eos_id, sm);
     }
     if (threadIdx.x == 0) {
         if (tok == op.eos_id) {

@@ -60,6 +60,8 @@ struct StreamState {
     float   rep_pen;
     float   temperature;
     uint64_t seed;
+    int32_t ignore_eos;      // benchmark switch: EOS can never be chosen (fixed-length utterances)
+    int32_t pad0;
     int32_t cur_codes[kMaxBooks];   // codes of the frame being produced (cb0..cb15)
     int32_t feed_codes[kMaxBooks];  // codes fed back inside the code predictor (forced or own)
     uint32_t seen[kMaxVocab / 32];  // bitmap of distinct cb0 tokens emitted so far

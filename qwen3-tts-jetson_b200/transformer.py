@@ -37,7 +37,7 @@ FRAME_CB = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_
 
 # every symbol include/qtts_b200.h declares
 EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error", "qtts_upload_tensor",
-           "qtts_finalize", "qtts_weight_stats", "qtts_set_numerics", "qtts_set_persistent",
+           "qtts_finalize", "qtts_weight_stats", "qtts_set_numerics", "qtts_set_persistent", "qtts_set_ignore_eos",
            "qtts_clear_kv_cache", "qtts_build_prefill", "qtts_forward_prefill", "qtts_forward_step",
            "qtts_predict_codes", "qtts_generate", "qtts_stream_begin", "qtts_step_frames",
            "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
@@ -67,6 +67,7 @@ def load_library(path: str | None = None):
     lib.qtts_weight_stats.argtypes = [vp, C.POINTER(C.c_int64)]
     lib.qtts_set_numerics.argtypes = [vp, C.c_int, C.c_int]
     lib.qtts_set_persistent.argtypes = [vp, C.c_int]
+    lib.qtts_set_ignore_eos.argtypes = [vp, C.c_int]
     lib.qtts_clear_kv_cache.argtypes = [vp, C.c_int]
     lib.qtts_build_prefill.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32p, i32p, vp, vp, vp]
     lib.qtts_forward_prefill.argtypes = [vp, C.c_int, vp, i32, i32, vp, vp]
@@ -158,6 +159,10 @@ class TTSTransformer:
 
     def set_persistent(self, on: bool) -> bool:
         return bool(self._lib.qtts_set_persistent(self._h, 1 if on else 0))
+
+    def set_ignore_eos(self, on: bool) -> bool:
+        """Benchmark switch (fixed-length utterances); not reference behaviour."""
+        return bool(self._lib.qtts_set_ignore_eos(self._h, 1 if on else 0))
 
     def weight_stats(self) -> dict:
         out = (C.c_int64 * 4)()
