@@ -146,6 +146,14 @@ int qtts_step_frames(qtts_engine * e, int32_t n_frames, int32_t * codes_out,
                      int32_t * produced, int32_t * active);
 
 /* ---- instrumentation -------------------------------------------------------------------- */
+/* stage profiler: CTA 0 of the frame kernel accumulates SM-clock cycles per op type
+ * (0 GEMV, 1 ATTN, 2 SAMPLE_CB0, 3 SAMPLE_CP, 4 FRAME_END, 5 COPY): out64[type*8 + {0 count,
+ * 1 stage, 2 barrier wait, 3 GEMV input load, 4 GEMV norm, 5 GEMV rows}].  out64 (may be NULL)
+ * receives the 64 + 4*256 counters accumulated so far (after the first 64: per-CTA [cta][gemv stage, gemv barrier, attn stage, attn barrier]); they are then cleared.  on = 0: off; on = 1 + c:
+ * CTA c records.  [6] = cycles thread 0 waited for ring chunks. */
+int qtts_profile(qtts_engine * e, int on, uint64_t * out64);
+/* instrumentation: microseconds per grid-wide barrier of `variant` (see csrc/qtts_microbench.cu) */
+double qtts_debug_barrier_us(int device, int variant, int iters);
 /* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
 int64_t qtts_launch_count(const qtts_engine * e);
 /* device time (ms, CUDA events on the engine's stream) of the last qtts_generate /

@@ -4,3 +4,4 @@
 #include "qtts_weights.cu"
 #include "qtts_program.cu"
 #include "qtts_api.cu"
+#include "qtts_microbench.cu"

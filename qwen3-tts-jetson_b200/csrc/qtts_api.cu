@@ -7,7 +7,7 @@ using namespace qtts;
 
 namespace qtts {
 extern "C" __global__ void qtts_run_program(const Op * ops, int n_ops, StreamState * st, GridBarrier * bar,
-                                            int n_frames, int persistent, int check_done);
+                                            int n_frames, RunCfg cfg);
 }
 
 struct qtts_engine { Engine e; };
@@ -48,10 +48,15 @@ int qtts_create(const qtts_config * cfg, int device, int max_streams, int max_ct
     e->n_sms = prop.multiProcessorCount;
     int k_max = std::max({cfg->hidden_size, cfg->intermediate_size, cfg->cp_hidden_size, cfg->cp_intermediate_size,
                           cfg->text_embd_dim, cfg->n_heads * cfg->head_dim, cfg->cp_n_heads * cfg->cp_head_dim});
-    e->smem_bytes = smem_required(k_max, max_ctx);
-    if (e->smem_bytes > (size_t) prop.sharedMemPerBlockOptin) {
-        g_create_err = "max_ctx too large for the shared-memory score buffer"; delete h; return 0;
-    }
+    // widest input of a two-token (merged code-predictor) stage
+    const int k2_max = std::max({cfg->cp_hidden_size, cfg->cp_intermediate_size, cfg->cp_n_heads * cfg->cp_head_dim,
+                                 cfg->cp_hidden_size != cfg->hidden_size ? cfg->hidden_size : 0});
+    if (max_ctx > kMaxScores) { g_create_err = "max_ctx exceeds the engine limit (kMaxScores)"; delete h; return 0; }
+    e->n_slots = n_slots_for(k_max, k2_max, (size_t) prop.sharedMemPerBlockOptin);
+    if (e->n_slots < 2) { g_create_err = "model too wide for the shared-memory weight ring"; delete h; return 0; }
+    e->slot_bytes = (int) slot_bytes_for(k_max);
+    e->xs_elems = (int) xs_elems_for(k_max, k2_max);
+    e->smem_bytes = smem_required(k_max, k2_max, e->n_slots);
     if (cudaFuncSetAttribute(qtts_run_program, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) e->smem_bytes) != cudaSuccess) {
         g_create_err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(cudaGetLastError()); delete h; return 0;
     }
@@ -100,6 +105,8 @@ static bool rebuild_frame_programs(Engine * e) {
         s.frame_host.clear();
         emit_frame(e, s, s.frame_host);
         QTTS_CUDA(cudaMemcpy(s.frame_prog, s.frame_host.data(), s.frame_host.size() * sizeof(Op), cudaMemcpyHostToDevice));
+        const std::vector<WSched> S = build_sched(e, s.frame_host);
+        QTTS_CUDA(cudaMemcpy(s.frame_sched, S.data(), S.size() * sizeof(WSched), cudaMemcpyHostToDevice));
     }
     return true;
 }
@@ -270,7 +277,7 @@ int qtts_generate(qtts_engine * h, int slot, const int32_t * tokens, int32_t n, 
     bool stop = false;
     cudaEventRecord(e->ev0, e->stream);
     while (!stop) {
-        if (!run_device_program(e, *s, s->frame_prog, &s->frame_host, s->frame_prog_n, chunk, true)) return 0;
+        if (!run_device_program(e, *s, s->frame_prog, &s->frame_host, s->frame_prog_n, s->frame_sched, s->frame_sched_n, chunk, true)) return 0;
         StreamState hs;
         if (cudaMemcpyAsync(&hs, s->st, sizeof(hs), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
             cudaStreamSynchronize(e->stream) != cudaSuccess) {
@@ -330,7 +337,7 @@ int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int
         cudaMemcpyAsync(&hs, s.st, sizeof(hs), cudaMemcpyDeviceToHost, e->stream);
         cudaStreamSynchronize(e->stream);
         before[i] = hs.frame;
-        if (!run_device_program(e, s, s.frame_prog, &s.frame_host, s.frame_prog_n, n_frames, true)) return 0;
+        if (!run_device_program(e, s, s.frame_prog, &s.frame_host, s.frame_prog_n, s.frame_sched, s.frame_sched_n, n_frames, true)) return 0;
     }
     cudaEventRecord(e->ev1, e->stream);
     for (size_t i = 0; i < e->slots.size(); ++i) {
@@ -350,6 +357,17 @@ int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e->ev0, e->ev1);
     e->last_loop_ms = ms;
+    return 1;
+}
+
+int qtts_profile(qtts_engine * h, int on, uint64_t * out64) {
+    Engine * e = &h->e;
+    if (!e->finalized) { e->err = "engine not finalized"; return 0; }
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    if (out64) cudaMemcpy(out64, e->prof, (64 + 4 * 256) * sizeof(uint64_t), cudaMemcpyDeviceToHost);
+    if (on != e->prof_on || on) cudaMemset(e->prof, 0, (64 + 4 * 256) * sizeof(uint64_t));
+    e->prof_on = on > 0 ? on : 0;      // on = 1 + index of the CTA that records
     return 1;
 }
 

@@ -40,7 +40,8 @@ struct Slot {
     int32_t * forced = nullptr;            // [15]
     __half * kc = nullptr, * vc = nullptr;           // [n_layers][max_ctx][kvw]
     __half * cp_kc = nullptr, * cp_vc = nullptr;     // [cp_layers][16][cp_kvw]
-    float * cp_kv0 = nullptr;                        // [cp_layers][2][cp_kvw]
+    float * attn_part = nullptr;                     // ATTN_FAST partials [n_heads][kMaxSplits][kPartStride]
+    unsigned int * attn_cnt = nullptr;               // [n_kv_heads]
     float * prefill = nullptr;             // [max_prefill][H]
     float * trailing = nullptr;            // [max_text+1][H]
     float * pad = nullptr;                 // [H]
@@ -51,6 +52,8 @@ struct Slot {
     int32_t * codes = nullptr;             // [max_ctx][n_books]
     EmbedSumArgs * es = nullptr;
     Op * frame_prog = nullptr; int frame_prog_n = 0;
+    WSched * frame_sched = nullptr; int frame_sched_n = 0;
+    WSched * scratch_sched = nullptr; int scratch_sched_cap = 0;
     std::vector<Op> frame_host;
     Op * scratch_prog = nullptr; int scratch_cap = 0;
     // host mirrors
@@ -63,6 +66,7 @@ struct Engine {
     int device = 0, max_streams = 0, max_ctx = 0, max_text = 0;
     int n_sms = 0;
     size_t smem_bytes = 0;
+    int slot_bytes = 0, n_slots = 0, xs_elems = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
@@ -78,6 +82,7 @@ struct Engine {
     double last_loop_ms = 0.0;
     unsigned long long * d_inexact = nullptr;
     GridBarrier * bar = nullptr;
+    unsigned long long * prof = nullptr; int prof_on = 0;   // [8][8] stage cycle counters (instrumentation)
     float * rope = nullptr;
     // fused weights
     std::vector<LayerW> talker, cp;
@@ -103,7 +108,10 @@ bool engine_upload(Engine * e, const char * name, int dtype, const int64_t * dim
 bool engine_finalize(Engine * e);
 
 // qtts_kernels.cu
-size_t smem_required(int k_max, int max_ctx);
+size_t slot_bytes_for(int k_max);
+size_t xs_elems_for(int k_max, int k2_max);
+int n_slots_for(int k_max, int k2_max, size_t smem_limit);
+size_t smem_required(int k_max, int k2_max, int n_slots);
 
 // qtts_program.cu
 void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, const float * in_vec,
@@ -116,7 +124,8 @@ bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t
                         bool has_speaker, int language_id);
 bool run_program(Engine * e, Slot & s, const std::vector<Op> & P, int n_frames, bool check_done);
 bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vector<Op> * host_ops, int n_ops,
-                        int n_frames, bool check_done);
+                        const WSched * d_sched, int n_sched, int n_frames, bool check_done);
+std::vector<WSched> build_sched(Engine * e, const std::vector<Op> & P);
 
 #define QTTS_CUDA(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
     e->err = std::string(#call) + ": " + cudaGetErrorString(_e); return false; } } while (0)

@@ -1,6 +1,14 @@
 // qtts_kernels.cu — sm_100a device stages of the Qwen3-TTS codec-frame loop, batch-1 /
 // small-batch regime (HBM-bound GEMV path).  See DESIGN.md for the stage list and rooflines.
 //
+// Structure: ONE persistent cooperative kernel (1 CTA per SM, 512 threads) walks a linear program
+// of stage descriptors (Op) for n_frames codec frames, with a grid-wide barrier after every
+// all-to-all stage.  Weight bytes never wait for a barrier: thread 0 of every CTA streams the
+// CTA's row slices of the NEXT projections into a shared-memory ring with bulk asynchronous
+// copies (cp.async.bulk + mbarrier complete_tx, the TMA engine), up to kNumSlots*slot_bytes
+// ahead of execution and across stage / frame boundaries, so that by the time a barrier opens the
+// stage's weights are already on chip and the critical path is barrier + input vector + FMAs.
+//
 // Reference behaviour each stage reproduces (file:line into the reference tree):
 //   stage_gemv  : ggml_mul_mat with F16 weights and F32 activations rounded to F16
 //                 (ggml/src/ggml-cpu/ggml-cpu.c:1229-1320) + ggml_rms_norm/ggml_mul prologue
@@ -19,16 +27,6 @@ namespace qtts {
 // small helpers
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ float f16r(float v) { return __half2float(__float2half_rn(v)); }
-
-__device__ __forceinline__ uint4 ld_stream(const uint4 * p) {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
-}
-__device__ __forceinline__ void prefetch_l2(const void * p) {
-    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-}
 __device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 
@@ -77,19 +75,147 @@ __device__ __forceinline__ float expf_cr(float x) { return (float) exp((double) 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 
 // ------------------------------------------------------------------------------------------
-// grid barrier (cooperative launch: all CTAs co-resident)
+// CTA-local copy of the mutable stream state.  Sampling and bookkeeping stages are executed by
+// EVERY CTA redundantly (deterministic code, identical results), so no grid barrier is needed
+// between a sampling stage and the stage that consumes the sampled id; CTA 0 mirrors the state
+// to global memory for the host.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void grid_barrier(GridBarrier * bar, unsigned int & epoch) {
+struct LocalState {
+    int32_t n_past, frame, done, eos;
+    int32_t cur_codes[kMaxBooks];
+    int32_t feed_codes[kMaxBooks];
+    uint32_t seen[kMaxVocab / 32];
+};
+
+struct RunCfg {
+    int32_t slot_bytes;     // bytes per ring slot (multiple of 1024, >= 2 weight rows)
+    int32_t n_slots;        // ring slots in use (<= kNumSlots)
+    int32_t xs_elems;       // floats in the input-vector area
+    int32_t persistent;     // 1: cooperative launch with grid barriers; 0: one op per launch
+    int32_t check_done;
+    int32_t prof_cta;
+    int32_t n_sched;        // GEMV stages per frame
+    const WSched * sched;   // [n_sched]
+    unsigned long long * prof;   // optional [8 op types][8] cycle counters filled by CTA 0 (nullptr: off)
+};
+
+// ------------------------------------------------------------------------------------------
+// mbarrier + bulk copy (TMA engine, 1-D) wrappers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t * bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t * bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
+    const uint32_t a = smem_u32(bar);
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    }
+}
+// global -> shared bulk copy, completion counted in bytes on `bar`; weights are streamed once
+// per use, so they are marked evict-first in L2.
+__device__ __forceinline__ void bulk_g2s(void * dst, const void * src, uint32_t bytes, uint64_t * bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+
+// ------------------------------------------------------------------------------------------
+// the weight ring: every GEMV op contributes, per CTA, ceil(pairs_cta / pairs_per_chunk) chunks
+// (a chunk = whole row pairs, <= slot_bytes); chunk number `seq` (counted from kernel start)
+// lives in slot seq % kNumSlots and completes phase (seq / kNumSlots) & 1 of that slot's mbarrier.
+// ------------------------------------------------------------------------------------------
+struct Ring {
+    unsigned char * base;
+    uint64_t * full;        // [kNumSlots]
+    int32_t slot_bytes;
+    int32_t n_slots;
+};
+
+constexpr int kPfThread = kThreads - 32;   // lane 0 of the last warp issues the bulk copies
+
+struct Prefetch {           // lives in the prefetcher thread's registers
+    int32_t idx, frame;     // schedule entry, frame being prefetched
+    int32_t q, p1;          // next row pair / end of this CTA's slice of the entry
+    int32_t K, ppc, slot;
+    const __nv_bfloat16 * W;
+    uint32_t seq;
+    uint64_t policy;
+    int4 n0, n1;            // schedule entry idx+1, requested one entry ahead (hides the L2 latency)
+};
+
+__device__ __forceinline__ void cta_pairs(const Op & op, int & p0, int & p1) {
+    const unsigned pairs = (unsigned) op.rows >> 1;
+    p0 = (int) (pairs * blockIdx.x / gridDim.x);
+    p1 = (int) (pairs * (blockIdx.x + 1) / gridDim.x);
+}
+
+// thread 0 only: issue bulk copies for upcoming chunks while ring slots are free
+__device__ __forceinline__ void prefetch_issue(const WSched * __restrict__ sched, int n_sched, int n_frames, Prefetch & pf,
+                                               uint32_t cons_seq, const Ring & ring) {
+    while (pf.seq - cons_seq < (uint32_t) ring.n_slots && pf.frame < n_frames) {
+        if (pf.q >= pf.p1) {
+            if (++pf.idx >= n_sched) { pf.idx = 0; if (++pf.frame >= n_frames) break; }
+            const int4 e0 = pf.n0, e1 = pf.n1;
+            {
+                const int nxt = (pf.idx + 1 < n_sched) ? pf.idx + 1 : 0;
+                pf.n0 = __ldg(reinterpret_cast<const int4 *>(sched + nxt));
+                pf.n1 = __ldg(reinterpret_cast<const int4 *>(sched + nxt) + 1);
+            }
+            pf.W = reinterpret_cast<const __nv_bfloat16 *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
+            pf.K = e0.z;
+            const unsigned pairs = (unsigned) e0.w;
+            pf.ppc = e1.x;
+            pf.q = (int) (pairs * blockIdx.x / gridDim.x);
+            pf.p1 = (int) (pairs * (blockIdx.x + 1) / gridDim.x);
+            continue;
+        }
+        const int nq = min(pf.ppc, pf.p1 - pf.q);
+        const uint32_t bytes = (uint32_t) nq * 4u * (uint32_t) pf.K;
+        mbar_expect_tx(ring.full + pf.slot, bytes);
+        bulk_g2s(ring.base + (size_t) pf.slot * ring.slot_bytes, pf.W + (size_t) 2 * pf.q * pf.K, bytes,
+                 ring.full + pf.slot, pf.policy);
+        pf.q += nq;
+        pf.seq++;
+        if (++pf.slot == ring.n_slots) pf.slot = 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// grid barrier (cooperative launch: all CTAs co-resident).  Between arriving and polling,
+// thread 0 refills the weight ring, so the copy engine works through the barrier latency.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void grid_barrier(GridBarrier * bar, unsigned int & epoch,
+                                             const WSched * sched, int n_sched, int n_frames, Prefetch & pf,
+                                             uint32_t cons_seq, const Ring & ring, unsigned long long * prof_sync = nullptr) {
+    const long long ts = prof_sync ? clock64() : 0;
     __syncthreads();
     if (threadIdx.x == 0) {
+        if (prof_sync) *prof_sync += (unsigned long long) (clock64() - ts);
         epoch += gridDim.x;
         __threadfence();
         atomicAdd(&bar->count, 1u);
+        // relaxed polling (an acquire load invalidates L1 on every iteration), one acquire at the end;
+        // activations are read with ld.cg (L2), constants with ld.nc, so nothing stale can be hit
         unsigned int v;
         do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&bar->count));
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&bar->count) : "memory");
         } while ((int) (v - epoch) < 0);
-        __threadfence();
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&bar->count) : "memory");
+    } else if (threadIdx.x == kPfThread) {
+        prefetch_issue(sched, n_sched, n_frames, pf, cons_seq, ring);
     }
     __syncthreads();
 }
@@ -97,149 +223,298 @@ __device__ __forceinline__ void grid_barrier(GridBarrier * bar, unsigned int & e
 // ------------------------------------------------------------------------------------------
 // OP_GEMV
 // ------------------------------------------------------------------------------------------
-__device__ void gemv_load_input(const Op & op, const StreamState * st, float * xs) {
+constexpr int kMaxPerThread = 12;     // input elements per thread: K <= kThreads * 12 = 6144
+
+// raw input element i of token t (before the norm)
+__device__ __forceinline__ float gemv_input_elem(const Op & op, const LocalState * ls, const __half * row,
+                                                 const float * trow, int t, int i) {
     const int K = op.K;
-    if (op.in_kind == IN_VEC) {
-        for (int i = threadIdx.x; i < K; i += kThreads) xs[i] = __ldcg(op.in + i);
-    } else if (op.in_kind == IN_EMBED_ROW) {
-        const int tok = __ldcg(op.tok_ptr);
-        const __half * row = op.table + (size_t) tok * K;
-        for (int i = threadIdx.x; i < K; i += kThreads) xs[i] = __half2float(row[i]);
-    } else {
-        // next Talker input (src/tts_transformer.cpp:2529-2553): sequential f32 sum, same order
-        const EmbedSumArgs * es = op.es;
-        const int frame = __ldcg(&st->frame) - 1;   // frame already counted by OP_FRAME_END
-        const int tl = __ldcg(&st->trailing_len);
-        const float * trow = (frame < tl) ? es->trailing + (size_t) frame * K : es->pad;
-        for (int i = threadIdx.x; i < K; i += kThreads) {
-            float acc = __half2float(es->tables[0][(size_t) __ldcg(&st->cur_codes[0]) * K + i]);
+    switch (op.in_kind) {
+        case IN_VEC:       return __ldcg(op.in + (size_t) t * op.in_stride + i);
+        case IN_EMBED_ROW: return __half2float(row[i]);
+        case IN_CP_FIRST:  return (t == 0) ? __ldcg(op.in + i) : __half2float(row[i]);
+        default: {
+            // next Talker input (src/tts_transformer.cpp:2529-2553): sequential f32 sum, same order
+            const EmbedSumArgs * es = op.es;
+            float acc = __half2float(es->tables[0][(size_t) ls->cur_codes[0] * K + i]);
             for (int c = 1; c < es->n_books; ++c)
-                acc += __half2float(es->tables[c][(size_t) __ldcg(&st->cur_codes[c]) * K + i]);
-            acc += __ldcg(trow + i);
-            xs[i] = acc;
+                acc += __half2float(es->tables[c][(size_t) ls->cur_codes[c] * K + i]);
+            return acc + __ldcg(trow + i);
         }
     }
 }
 
-__device__ __forceinline__ float dot8(const uint4 w, const float4 a, const float4 b) {
-    float s = bf_lo(w.x) * a.x;
-    s = fmaf(bf_hi(w.x), a.y, s);
-    s = fmaf(bf_lo(w.y), a.z, s);
-    s = fmaf(bf_hi(w.y), a.w, s);
-    s = fmaf(bf_lo(w.z), b.x, s);
-    s = fmaf(bf_hi(w.z), b.y, s);
-    s = fmaf(bf_lo(w.w), b.z, s);
-    s = fmaf(bf_hi(w.w), b.w, s);
+// 8 weights (bf16, one uint4) x 8 activations (f16, one uint4), f32 accumulate
+__device__ __forceinline__ float dot8h(const uint4 w, const uint4 x) {
+    const __half2 * xh = reinterpret_cast<const __half2 *>(&x);
+    const float2 x0 = __half22float2(xh[0]), x1 = __half22float2(xh[1]);
+    const float2 x2 = __half22float2(xh[2]), x3 = __half22float2(xh[3]);
+    float s = bf_lo(w.x) * x0.x;
+    s = fmaf(bf_hi(w.x), x0.y, s);
+    s = fmaf(bf_lo(w.y), x1.x, s);
+    s = fmaf(bf_hi(w.y), x1.y, s);
+    s = fmaf(bf_lo(w.z), x2.x, s);
+    s = fmaf(bf_hi(w.z), x2.y, s);
+    s = fmaf(bf_lo(w.w), x3.x, s);
+    s = fmaf(bf_hi(w.w), x3.y, s);
     return s;
 }
 
-__device__ void stage_gemv(const Op & op, StreamState * st, float * smem, double * red) {
-    const int K = op.K;
-    float * xs = smem;
+// rows are handled as pairs (2p, 2p+1) — EPI_SWIGLU needs exactly that pairing; the pair's
+// weights are read from the shared-memory ring (chunk = cons_seq + q / pairs_per_chunk), the
+// F16-rounded activations from xh.  Residual / bias values are requested before the dot products.
+template <int NT>
+__device__ void gemv_rows(const Op & op, const __half * xh, const Ring & ring, uint32_t cons_seq, int p0,
+                          int q_begin, int q_end, unsigned long long * prof_wait) {
+    const int K = op.K, kv = K >> 3;      // uint4 per row
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-    gemv_load_input(op, st, xs);
-    __syncthreads();
-    if (op.x_out && blockIdx.x == 0)
-        for (int i = threadIdx.x; i < K; i += kThreads) op.x_out[i] = xs[i];
-
-    if (op.norm_w) {
-        // ggml_compute_forward_rms_norm_f32: double sum of float squares (ops.cpp:3738-3747)
-        double ss = 0.0;
-        for (int i = threadIdx.x; i < K; i += kThreads) ss += (double) (xs[i] * xs[i]);
-        ss = block_sum_d(ss, red);
-        const float mean = (float) (ss / (double) K);
-        const float scale = 1.0f / sqrtf(mean + op.eps);
-        for (int i = threadIdx.x; i < K; i += kThreads) {
-            const float v = (xs[i] * scale) * op.norm_w[i];
-            if (op.hid_out && blockIdx.x == 0) op.hid_out[i] = v;
-            xs[i] = f16r(v);
+    const int ppc = ring.slot_bytes / (4 * K);
+    const uint4 * x4 = reinterpret_cast<const uint4 *>(xh);
+    for (int q = q_begin + warp; q < q_end; q += kWarps) {
+        const int p = p0 + q;
+        float side = 0.f;       // residual or bias of (token lane>>1, row 2p + (lane&1))
+        if (lane < 2 * NT) {
+            const int t = lane >> 1, r = 2 * p + (lane & 1);
+            if (op.epi == EPI_ADD) side = __ldcg(op.res + (size_t) t * op.out_stride + r);
+            else if (op.epi == EPI_BIAS || op.epi == EPI_BIAS_SILU) side = __ldg(op.bias + r);
         }
-    } else {
-        for (int i = threadIdx.x; i < K; i += kThreads) xs[i] = f16r(xs[i]);
-    }
-    __syncthreads();
-
-    // rows are handled as pairs (2p, 2p+1); EPI_SWIGLU needs exactly that pairing
-    const int pairs = op.rows >> 1;
-    const int p0 = (int) ((long long) pairs * blockIdx.x / gridDim.x);
-    const int p1 = (int) ((long long) pairs * (blockIdx.x + 1) / gridDim.x);
-    const int kv = K >> 3;   // uint4 per row
-    const float4 * xs4 = reinterpret_cast<const float4 *>(xs);
-
-    for (int p = p0 + warp; p < p1; p += kWarps) {
-        const uint4 * w0 = reinterpret_cast<const uint4 *>(op.W + (size_t) (2 * p) * K);
+        const int j = q / ppc;
+        const uint32_t seq = cons_seq + (uint32_t) j;
+        const int slot = (int) (seq % (uint32_t) ring.n_slots);
+        if (prof_wait && threadIdx.x == 0) {
+            const long long tw = clock64();
+            mbar_wait(ring.full + slot, (seq / (uint32_t) ring.n_slots) & 1u);
+            *prof_wait += (unsigned long long) (clock64() - tw);
+        } else {
+            mbar_wait(ring.full + slot, (seq / (uint32_t) ring.n_slots) & 1u);
+        }
+        const uint4 * w0 = reinterpret_cast<const uint4 *>(ring.base + (size_t) slot * ring.slot_bytes +
+                                                            (size_t) (q - j * ppc) * 4 * K);
         const uint4 * w1 = w0 + kv;
-        float a0 = 0.f, a1 = 0.f;
+        float a0[NT], a1[NT];
+#pragma unroll
+        for (int t = 0; t < NT; ++t) { a0[t] = 0.f; a1[t] = 0.f; }
         for (int j0 = 0; j0 < kv; j0 += 128) {
             uint4 A[4], B[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int j = j0 + u * 32 + lane;
-                if (j < kv) { A[u] = ld_stream(w0 + j); B[u] = ld_stream(w1 + j); }
+                const int i = j0 + u * 32 + lane;
+                if (i < kv) { A[u] = w0[i]; B[u] = w1[i]; }
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int j = j0 + u * 32 + lane;
-                if (j < kv) {
-                    const float4 xa = xs4[2 * j], xb = xs4[2 * j + 1];
-                    a0 += dot8(A[u], xa, xb);
-                    a1 += dot8(B[u], xa, xb);
+                const int i = j0 + u * 32 + lane;
+                if (i < kv) {
+#pragma unroll
+                    for (int t = 0; t < NT; ++t) {
+                        const uint4 xv = x4[t * kv + i];
+                        a0[t] += dot8h(A[u], xv);
+                        a1[t] += dot8h(B[u], xv);
+                    }
                 }
             }
         }
-        a0 = warp_sum(a0);
-        a1 = warp_sum(a1);
-        if (lane == 0) {
-            const int r0 = 2 * p, r1 = 2 * p + 1;
-            switch (op.epi) {
-                case EPI_STORE: op.out[r0] = a0; op.out[r1] = a1; break;
-                case EPI_ADD:
-                    op.out[r0] = a0 + __ldcg(op.res + r0);
-                    op.out[r1] = a1 + __ldcg(op.res + r1);
-                    break;
-                case EPI_SWIGLU: op.out[p] = silu_f(a0) * a1; break;
-                case EPI_BIAS:
-                    op.out[r0] = a0 + op.bias[r0];
-                    op.out[r1] = a1 + op.bias[r1];
-                    break;
-                case EPI_BIAS_SILU:
-                    op.out[r0] = silu_f(a0 + op.bias[r0]);
-                    op.out[r1] = silu_f(a1 + op.bias[r1]);
-                    break;
+#pragma unroll
+        for (int t = 0; t < NT; ++t) { a0[t] = warp_sum(a0[t]); a1[t] = warp_sum(a1[t]); }
+        if (op.epi == EPI_SWIGLU) {
+            if (lane < NT) {
+                const float g = (lane == 0) ? a0[0] : a0[NT - 1], u = (lane == 0) ? a1[0] : a1[NT - 1];
+                op.out[(size_t) lane * op.out_stride + p] = silu_f(g) * u;
             }
+        } else if (lane < 2 * NT) {
+            const int t = lane >> 1, r = 2 * p + (lane & 1);
+            float acc = (lane & 1) ? ((t == 0) ? a1[0] : a1[NT - 1]) : ((t == 0) ? a0[0] : a0[NT - 1]);
+            acc += side;
+            if (op.epi == EPI_BIAS_SILU) acc = silu_f(acc);
+            op.out[(size_t) t * op.out_stride + r] = acc;
         }
     }
-    if ((op.flags & F_INC_NPAST) && blockIdx.x == 0 && threadIdx.x == 0) st->n_past = st->n_past + 1;
 }
 
-// issue L2 prefetches for the weight rows this CTA will read in a following GEMV stage
-__device__ void gemv_prefetch(const Op & op) {
-    if (op.type != OP_GEMV) return;
-    const int pairs = op.rows >> 1;
-    const int p0 = (int) ((long long) pairs * blockIdx.x / gridDim.x);
-    const int p1 = (int) ((long long) pairs * (blockIdx.x + 1) / gridDim.x);
-    const char * base = reinterpret_cast<const char *>(op.W + (size_t) (2 * p0) * op.K);
-    const size_t bytes = (size_t) (p1 - p0) * 2 * op.K * sizeof(__nv_bfloat16);
-    for (size_t off = (size_t) threadIdx.x * 128; off < bytes; off += (size_t) kThreads * 128)
-        prefetch_l2(base + off);
+// input vector of token t -> F16-rounded activations in shared memory.  Every thread owns elements
+// tid + j*kThreads (j < NPER); the input and the norm weights are requested together (one L2
+// round trip) and the RMSNorm runs out of registers.
+template <int NPER>
+__device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * ls, const __half * row, const float * trow,
+                                             int t, __half * xh, double * red) {
+    const int K = op.K;
+    float xv[NPER], nw[NPER];
+#pragma unroll
+    for (int j = 0; j < NPER; ++j) {
+        const int i = threadIdx.x + j * kThreads;
+        xv[j] = 0.f; nw[j] = 1.f;
+        if (i < K) {
+            xv[j] = gemv_input_elem(op, ls, row, trow, t, i);
+            if (op.norm_w) nw[j] = __ldg(op.norm_w + i);
+        }
+    }
+    if (op.x_out && blockIdx.x == 0) {
+#pragma unroll
+        for (int j = 0; j < NPER; ++j) {
+            const int i = threadIdx.x + j * kThreads;
+            if (i < K) op.x_out[t * K + i] = xv[j];
+        }
+    }
+    float scale = 1.0f;
+    if (op.norm_w) {
+        // ggml_compute_forward_rms_norm_f32: double sum of float squares (ops.cpp:3738-3747)
+        double ss = 0.0;
+#pragma unroll
+        for (int j = 0; j < NPER; ++j) ss += (double) (xv[j] * xv[j]);
+        ss = block_sum_d(ss, red);
+        const float mean = (float) (ss / (double) K);
+        scale = 1.0f / sqrtf(mean + op.eps);
+    }
+#pragma unroll
+    for (int j = 0; j < NPER; ++j) {
+        const int i = threadIdx.x + j * kThreads;
+        if (i < K) {
+            float v = xv[j];
+            if (op.norm_w) {
+                v = (v * scale) * nw[j];
+                if (op.hid_out && blockIdx.x == 0) op.hid_out[t * K + i] = v;
+            }
+            xh[t * K + i] = __float2half_rn(v);     // ggml_mul_mat rounds the activation to F16
+        }
+    }
+}
+
+// returns the number of ring chunks this CTA consumed
+__device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, LocalState * ls, float * xs, double * red,
+                               const Ring & ring, uint32_t cons_seq,
+                               const WSched * sched, int n_sched, int n_frames, Prefetch & pf, unsigned long long * prof) {
+    const int K = op.K;
+    const bool prof_on = prof && threadIdx.x == 0;
+    long long tA = prof_on ? clock64() : 0;
+    __half * xh = reinterpret_cast<__half *>(xs);
+
+    // input row pointers (token ids are CTA-local state or device memory written before the launch)
+    const __half * row = nullptr;
+    const float * trow = nullptr;
+    if (op.in_kind == IN_EMBED_ROW) {
+        const int tok = (op.tok_slot >= 0) ? ls->feed_codes[op.tok_slot] : __ldcg(op.tok_ptr);
+        row = op.table + (size_t) tok * K;
+    } else if (op.in_kind == IN_CP_FIRST) {
+        row = op.table + (size_t) ls->feed_codes[0] * K;
+    } else if (op.in_kind == IN_EMBED_SUM) {
+        const int frame = ls->frame - 1;            // frame already counted by OP_FRAME_END
+        trow = (frame < st->trailing_len) ? op.es->trailing + (size_t) frame * K : op.es->pad;
+    }
+    const int nper = (K + kThreads - 1) / kThreads;
+    for (int t = 0; t < op.n_tok; ++t) {
+        if (nper <= 2)      gemv_prepare<2>(op, ls, row, trow, t, xh, red);
+        else if (nper <= 4) gemv_prepare<4>(op, ls, row, trow, t, xh, red);
+        else if (nper <= 6) gemv_prepare<6>(op, ls, row, trow, t, xh, red);
+        else                gemv_prepare<kMaxPerThread>(op, ls, row, trow, t, xh, red);
+    }
+    __syncthreads();
+    if (prof_on) { const long long t = clock64(); prof[OP_GEMV * 8 + 4] += (unsigned long long) (t - tA); tA = t; }
+
+    int p0, p1;
+    cta_pairs(op, p0, p1);
+    const int ppc = ring.slot_bytes / (4 * K);
+    const int nch = (p1 - p0 + ppc - 1) / ppc;
+    // a slice longer than the ring is consumed in rounds of n_slots chunks; between rounds the
+    // freed slots are refilled
+    for (int c0 = 0; c0 < nch; c0 += ring.n_slots) {
+        const int c1 = min(c0 + ring.n_slots, nch);
+        const int qb = c0 * ppc, qe = min(c1 * ppc, p1 - p0);
+        if (op.n_tok == 2) gemv_rows<2>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr);
+        else               gemv_rows<1>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr);
+        if (c1 < nch) {
+            __syncthreads();
+            if (threadIdx.x == kPfThread) prefetch_issue(sched, n_sched, n_frames, pf, cons_seq + (uint32_t) c1, ring);
+        }
+    }
+    if (op.flags & F_INC_NPAST) {
+        if (threadIdx.x == 0) {
+            ls->n_past += 1;
+            if (blockIdx.x == 0) st->n_past = ls->n_past;
+        }
+    }
+    if (prof_on) { const long long t = clock64(); prof[OP_GEMV * 8 + 5] += (unsigned long long) (t - tA); }
+    return (uint32_t) nch;
 }
 
 // ------------------------------------------------------------------------------------------
-// OP_ATTN — one CTA per query head
+// OP_ATTN
 // ------------------------------------------------------------------------------------------
+constexpr int kMaxRep = 4;      // query heads per KV head handled by one CTA in ATTN_FAST
+constexpr int kTile   = 512;    // keys per tile of the sequential flash emulation
+
 struct AttnSmem {
-    float q[kHeadDim];        // query after norm+rope (rounded to F16 unless ATTN_F32)
-    float kf[kHeadDim];       // current key, unrounded
-    float vf[kHeadDim];       // current value, unrounded
+    float q[kMaxRep][kHeadDim];   // queries after norm+rope (rounded to F16 unless ATTN_F32)
+    float kf[kHeadDim];           // current key, unrounded
+    float vf[kHeadDim];           // current value, unrounded
+    float k0f[kHeadDim];          // ATTN_F32: key / value of position 0, unrounded
+    float v0f[kHeadDim];
     __half k16[kHeadDim];
     __half v16[kHeadDim];
-    float tmp[3 * kHeadDim];  // raw q,k,v staging
+    float tmp[(kMaxRep + 2) * kHeadDim];   // raw q heads, k, v staging
     double red[kWarps];
     float redf[kWarps];
-    float part[4][kHeadDim];  // partial P.V sums
+    float part[4][kMaxRep][kHeadDim];      // partial P.V sums per key partition
     float chunkM[64], chunkS[64];
+    float hm[kMaxRep], hl[kMaxRep];
+    int   flag;
 };
+
+// q (nq heads from h_first), k, v of one token: per-head RMSNorm (double sum), NEOX RoPE at `pos`
+__device__ void attn_prepare(const Op & op, const float * qkv, int h_first, int nq, int g, int pos, AttnSmem * sm) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rows = nq + 2;
+    __syncthreads();
+    for (int idx = tid; idx < rows * kHeadDim; idx += kThreads) {
+        const int row = idx / kHeadDim, d = idx % kHeadDim;
+        const float * src = (row < nq)  ? qkv + (size_t) (h_first + row) * kHeadDim
+                          : (row == nq) ? qkv + (size_t) (op.n_heads + g) * kHeadDim
+                                        : qkv + (size_t) (op.n_heads + op.n_kv_heads + g) * kHeadDim;
+        sm->tmp[idx] = __ldcg(src + d);
+    }
+    __syncthreads();
+    if (warp <= nq) {       // rows 0..nq (queries and the key) are normalised
+        double ss = 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { const float v = sm->tmp[warp * kHeadDim + u * 32 + lane]; ss += (double) (v * v); }
+        ss = warp_sum_d(ss);
+        if (lane == 0) sm->red[warp] = ss;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < (nq + 1) * kHeadDim; idx += kThreads) {
+        const int row = idx / kHeadDim, d = idx % kHeadDim;
+        // QK-norm only when the layer has the weight (src/tts_transformer.cpp:1424-1432)
+        const float * w = (row < nq) ? op.q_norm_w : op.k_norm_w;
+        if (w) {
+            const float mean = (float) (sm->red[row] / (double) kHeadDim);
+            const float scale = 1.0f / sqrtf(mean + op.eps);
+            sm->tmp[idx] = (sm->tmp[idx] * scale) * w[d];
+        }
+    }
+    __syncthreads();
+    for (int idx = tid; idx < rows * kHeadDim; idx += kThreads) {
+        const int row = idx / kHeadDim, d = idx % kHeadDim;
+        if (row <= nq) {
+            const int i = d & 63;
+            const float c = op.rope[((size_t) pos * 64 + i) * 2], s = op.rope[((size_t) pos * 64 + i) * 2 + 1];
+            const float x0 = sm->tmp[row * kHeadDim + i], x1 = sm->tmp[row * kHeadDim + i + 64];
+            const float r = (d < 64) ? (x0 * c - x1 * s) : (x0 * s + x1 * c);
+            if (row < nq) sm->q[row][d] = (op.mode == ATTN_F32) ? r : f16r(r);
+            else { sm->kf[d] = r; sm->k16[d] = __float2half_rn(r); }
+        } else {
+            const float v = sm->tmp[idx];
+            sm->vf[d] = v;
+            sm->v16[d] = __float2half_rn(v);
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void attn_append(const Op & op, int g, int pos, int kvw, const AttnSmem * sm) {
+    if (threadIdx.x < kHeadDim) {
+        op.kcache[(size_t) pos * kvw + g * kHeadDim + threadIdx.x] = sm->k16[threadIdx.x];
+        op.vcache[(size_t) pos * kvw + g * kHeadDim + threadIdx.x] = sm->v16[threadIdx.x];
+    }
+}
 
 // dot of 16 consecutive dims (2 x uint4 of halves) with q registers
 __device__ __forceinline__ float dot16h(const uint4 a, const uint4 b, const float * q) {
@@ -261,135 +536,186 @@ __device__ __forceinline__ float dot16h(const uint4 a, const uint4 b, const floa
     return s;
 }
 
-__device__ void stage_attn(const Op & op, StreamState * st, float * smem_f) {
+// scores sc[r][j - j0] = scale * <K16_j, q_r> for keys j0..j1 (8 lanes per key, 16 dims per lane);
+// key `pos` (the token being appended) is read from shared memory
+template <int REP>
+__device__ void attn_scores(const Op & op, const AttnSmem * sm, int g, int kvw, int pos, int j0, int j1,
+                            float * sc, int sc_stride) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane & 7, kin = lane >> 3;
+    float qreg[REP][16];
+#pragma unroll
+    for (int r = 0; r < REP; ++r)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) qreg[r][i] = sm->q[r][sub * 16 + i];
+    for (int jb = j0 + warp * 4; jb < j1; jb += kWarps * 4) {
+        const int j = jb + kin;
+        uint4 ka = make_uint4(0, 0, 0, 0), kb = ka;
+        if (j < j1) {
+            if (j < pos) {
+                const uint4 * k4 = reinterpret_cast<const uint4 *>(op.kcache + (size_t) j * kvw + g * kHeadDim + sub * 16);
+                ka = __ldcg(k4); kb = __ldcg(k4 + 1);
+            } else {
+                const uint4 * k4 = reinterpret_cast<const uint4 *>(sm->k16 + sub * 16);
+                ka = k4[0]; kb = k4[1];
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < REP; ++r) {
+            float s = dot16h(ka, kb, qreg[r]);
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            s += __shfl_xor_sync(0xffffffffu, s, 4);
+            if (sub == 0 && j < j1) sc[r * sc_stride + (j - j0)] = s * op.kq_scale;
+        }
+    }
+}
+
+// ---- ATTN_FAST: split-KV over (KV group, key range) CTAs, REP query heads per CTA; the last CTA
+// of a group to finish merges the partials (fixed order -> deterministic)
+template <int REP>
+__device__ __noinline__ void attn_fast(const Op & op, const float * qkv, float * out, int pos, AttnSmem * sm, float * sc) {
+    const int tid = threadIdx.x;
+    const int n_kv = pos + 1, kvw = op.n_kv_heads * kHeadDim;
+    int S = (n_kv + kSplitKeys - 1) / kSplitKeys;
+    S = max(1, min(S, min(kMaxSplits, (int) gridDim.x / op.n_kv_heads)));
+    const int b = blockIdx.x;
+    if (b >= op.n_kv_heads * S) return;
+    const int g = b / S, s = b % S;
+    const int range = (n_kv + S - 1) / S;
+    const int j0 = s * range, j1 = min(j0 + range, n_kv);
+    attn_prepare(op, qkv, g * REP, REP, g, pos, sm);
+    if (s == S - 1) attn_append(op, g, pos, kvw, sm);
+    const int cnt = max(j1 - j0, 0);
+    attn_scores<REP>(op, sm, g, kvw, pos, j0, j1, sc, range);
+    __syncthreads();
+    float m[REP], l[REP];
+#pragma unroll
+    for (int r = 0; r < REP; ++r) {
+        float mx = -CUDART_INF_F;
+        for (int j = tid; j < cnt; j += kThreads) mx = fmaxf(mx, sc[r * range + j]);
+        mx = block_max_f(mx, sm->redf);
+        double sum = 0.0;
+        for (int j = tid; j < cnt; j += kThreads) {
+            const float e = __expf(sc[r * range + j] - mx);
+            sc[r * range + j] = e;
+            sum += (double) e;
+        }
+        sum = block_sum_d(sum, sm->red);
+        m[r] = mx; l[r] = (float) sum;
+    }
+    __syncthreads();
+    {   // P.V : 4 key partitions x 128 dims
+        const int d = tid & (kHeadDim - 1), part = tid >> 7;
+        float acc[REP];
+#pragma unroll
+        for (int r = 0; r < REP; ++r) acc[r] = 0.f;
+        for (int j = part; j < cnt; j += 4) {
+            const int jj = j0 + j;
+            const float v = __half2float((jj < pos) ? __ldcg(op.vcache + (size_t) jj * kvw + g * kHeadDim + d) : sm->v16[d]);
+#pragma unroll
+            for (int r = 0; r < REP; ++r) acc[r] = fmaf(v, sc[r * range + j], acc[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < REP; ++r) sm->part[part][r][d] = acc[r];
+    }
+    __syncthreads();
+    for (int idx = tid; idx < REP * kHeadDim; idx += kThreads) {
+        const int r = idx / kHeadDim, d = idx % kHeadDim;
+        const float o = (sm->part[0][r][d] + sm->part[1][r][d]) + (sm->part[2][r][d] + sm->part[3][r][d]);
+        if (S == 1) {
+            out[(size_t) (g * REP + r) * kHeadDim + d] = o / l[r];
+        } else {
+            float * p = op.attn_part + ((size_t) (g * REP + r) * kMaxSplits + s) * kPartStride;
+            p[4 + d] = o;
+            if (d == 0) { p[0] = m[r]; p[1] = l[r]; }
+        }
+    }
+    if (S == 1) return;
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        const unsigned int old = atomicAdd(op.attn_cnt + g, 1u);
+        sm->flag = (old == (unsigned int) (S - 1));
+    }
+    __syncthreads();
+    if (!sm->flag) return;
+    __threadfence();
+    if (tid == 0) op.attn_cnt[g] = 0;
+    for (int idx = tid; idx < REP * kHeadDim; idx += kThreads) {
+        const int r = idx / kHeadDim, d = idx % kHeadDim;
+        const float * base = op.attn_part + (size_t) (g * REP + r) * kMaxSplits * kPartStride;
+        float M = -CUDART_INF_F;
+        for (int i = 0; i < S; ++i) M = fmaxf(M, __ldcg(base + (size_t) i * kPartStride));
+        float L = 0.f, o = 0.f;
+        for (int i = 0; i < S; ++i) {
+            const float w = __expf(__ldcg(base + (size_t) i * kPartStride) - M);
+            L = fmaf(__ldcg(base + (size_t) i * kPartStride + 1), w, L);
+            o = fmaf(__ldcg(base + (size_t) i * kPartStride + 4 + d), w, o);
+        }
+        out[(size_t) (g * REP + r) * kHeadDim + d] = o / L;
+    }
+}
+
+// ---- ATTN_F32: code-predictor positions 0 and 1 in one stage (n_tok = 2), everything F32 with the
+// un-cached K/V, as the reference's 2-token prefill graph (src/tts_transformer.cpp:1613-1626)
+__device__ __noinline__ void attn_f32_pair(const Op & op, AttnSmem * sm, float * sc) {
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (b >= 2 * op.n_heads) return;
+    const int t = b / op.n_heads, h = b % op.n_heads;
+    const int rep = op.n_heads / op.n_kv_heads, g = h / rep;
+    const int kvw = op.n_kv_heads * kHeadDim;
+    const int pos = op.pos_off + t;
+    float * out = op.out + (size_t) t * op.out_stride + (size_t) h * kHeadDim;
+    if (t == 1) {   // position 0's key / value, recomputed from token 0's projections
+        attn_prepare(op, op.qkv, h, 0, g, op.pos_off, sm);
+        if (tid < kHeadDim) { sm->k0f[tid] = sm->kf[tid]; sm->v0f[tid] = sm->vf[tid]; }
+    }
+    attn_prepare(op, op.qkv + (size_t) t * op.qkv_stride, h, 1, g, pos, sm);
+    if (h % rep == 0) attn_append(op, g, pos, kvw, sm);
+    if (t == 0) {   // softmax over one key = 1.0 exactly
+        if (tid < kHeadDim) out[tid] = sm->vf[tid];
+        return;
+    }
+    if (warp < 2) {
+        float s = 0.f;
+        for (int d = lane; d < kHeadDim; d += 32) {
+            const float kd = (warp == 0) ? sm->k0f[d] : sm->kf[d];
+            s = fmaf(kd, sm->q[0][d], s);
+        }
+        s = warp_sum(s);
+        if (lane == 0) sc[warp] = s * op.kq_scale;
+    }
+    __syncthreads();
+    if (tid < kHeadDim) {
+        const float mx = fmaxf(sc[0], sc[1]);
+        const float e0 = expf(sc[0] - mx), e1 = expf(sc[1] - mx);
+        const float inv = (float) (1.0 / ((double) e0 + (double) e1));
+        const float p0 = e0 * inv, p1 = e1 * inv;
+        out[tid] = fmaf(sm->vf[tid], p1, sm->v0f[tid] * p0);
+    }
+}
+
+// ---- ATTN_SOFTMAX_P16 / ATTN_FLASH_F16SEQ: one CTA per query head, the reference's exact
+// rounding points (parity modes; the sequential F16 accumulator is inherently serial per dim)
+__device__ __noinline__ void attn_reference(const Op & op, const LocalState * ls, AttnSmem * sm, float * sc) {
     const int h = blockIdx.x;
     if (h >= op.n_heads) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = h / (op.n_heads / op.n_kv_heads);
-    const int kvw = op.n_kv_heads * kHeadDim;            // cache row width (elements)
-    const int pos = (op.use_n_past ? __ldcg(&st->n_past) : 0) + op.pos_off;
+    const int kvw = op.n_kv_heads * kHeadDim;
+    const int pos = (op.use_n_past ? ls->n_past : 0) + op.pos_off;
     const int n_kv = pos + 1;
-    const int mode = op.mode;
+    float * ms = sc + kMaxScores;
+    float * vs = ms + kTile;
+    float * out = op.out + (size_t) h * kHeadDim;
 
-    AttnSmem * sm = reinterpret_cast<AttnSmem *>(smem_f);
-    float * sc = smem_f + (sizeof(AttnSmem) + 3) / 4;    // scores [n_kv]
-    float * ms = sc + ((n_kv + 3) & ~3);                 // per-key rescale factors
-    float * vs = ms + ((n_kv + 3) & ~3);
-
-    // ---- load raw q,k,v; per-head RMSNorm (double sum) ; NEOX RoPE -------------------------
-    if (tid < 3 * kHeadDim) {
-        const int which = tid / kHeadDim, d = tid % kHeadDim;
-        const float * src = (which == 0) ? op.qkv + (size_t) h * kHeadDim
-                          : (which == 1) ? op.qkv + (size_t) (op.n_heads + g) * kHeadDim
-                                         : op.qkv + (size_t) (op.n_heads + op.n_kv_heads + g) * kHeadDim;
-        sm->tmp[tid] = __ldcg(src + d);
-    }
-    __syncthreads();
-    {
-        // warps 0-3: q, warps 4-7: k  -> sums in red[0..7]
-        double ss = 0.0;
-        if (tid < 2 * kHeadDim) ss = (double) (sm->tmp[tid] * sm->tmp[tid]);
-        ss = warp_sum_d(ss);
-        if (lane == 0) sm->red[warp] = ss;
-    }
-    __syncthreads();
-    if (tid < 2 * kHeadDim) {
-        const int which = tid / kHeadDim, d = tid % kHeadDim;
-        const double tot = sm->red[which * 4] + sm->red[which * 4 + 1] + sm->red[which * 4 + 2] + sm->red[which * 4 + 3];
-        const float mean = (float) (tot / (double) kHeadDim);
-        const float scale = 1.0f / sqrtf(mean + op.eps);
-        // QK-norm only when the layer has the weight (src/tts_transformer.cpp:1424-1432)
-        const float * w = which ? op.k_norm_w : op.q_norm_w;
-        if (w) sm->tmp[tid] = (sm->tmp[tid] * scale) * w[d];
-    }
-    __syncthreads();
-    if (tid < 2 * kHeadDim) {
-        const int which = tid / kHeadDim, d = tid % kHeadDim;
-        const int i = d & 63;
-        const float c = op.rope[((size_t) pos * 64 + i) * 2], s = op.rope[((size_t) pos * 64 + i) * 2 + 1];
-        const float x0 = sm->tmp[which * kHeadDim + i], x1 = sm->tmp[which * kHeadDim + i + 64];
-        const float r = (d < 64) ? (x0 * c - x1 * s) : (x0 * s + x1 * c);
-        if (which == 0) {
-            sm->q[d] = (mode == ATTN_F32) ? r : f16r(r);
-        } else {
-            sm->kf[d] = r;
-            sm->k16[d] = __float2half_rn(r);
-        }
-    } else if (tid < 3 * kHeadDim) {
-        const int d = tid - 2 * kHeadDim;
-        const float v = sm->tmp[tid];
-        sm->vf[d] = v;
-        sm->v16[d] = __float2half_rn(v);
-    }
-    __syncthreads();
-    // append to the cache (first query head of each KV group writes)
-    if (h % (op.n_heads / op.n_kv_heads) == 0 && tid < kHeadDim) {
-        op.kcache[(size_t) pos * kvw + g * kHeadDim + tid] = sm->k16[tid];
-        op.vcache[(size_t) pos * kvw + g * kHeadDim + tid] = sm->v16[tid];
-        if (mode == ATTN_F32 && pos == 0) {
-            op.kv0_f32[g * kHeadDim + tid] = sm->kf[tid];
-            op.kv0_f32[kvw + g * kHeadDim + tid] = sm->vf[tid];
-        }
-    }
-    float * out = const_cast<float *>(op.out) + (size_t) h * kHeadDim;
-
-    // ---- ATTN_F32: code-predictor positions 0 and 1, all-F32 (src/tts_transformer.cpp:1613-1626)
-    if (mode == ATTN_F32) {
-        if (pos == 0) {   // softmax over one key = 1.0 exactly
-            if (tid < kHeadDim) out[tid] = sm->vf[tid];
-            return;
-        }
-        // pos == 1: keys {0 (from kv0_f32), 1 (own)}
-        if (warp < 2) {
-            float s = 0.f;
-            for (int d = lane; d < kHeadDim; d += 32) {
-                const float kd = (warp == 0) ? __ldcg(op.kv0_f32 + g * kHeadDim + d) : sm->kf[d];
-                s = fmaf(kd, sm->q[d], s);
-            }
-            s = warp_sum(s);
-            if (lane == 0) sc[warp] = s * op.kq_scale;
-        }
-        __syncthreads();
-        if (tid < kHeadDim) {
-            const float mx = fmaxf(sc[0], sc[1]);
-            const float e0 = expf(sc[0] - mx), e1 = expf(sc[1] - mx);
-            const float inv = (float) (1.0 / ((double) e0 + (double) e1));
-            const float p0 = e0 * inv, p1 = e1 * inv;
-            const float v0 = __ldcg(op.kv0_f32 + kvw + g * kHeadDim + tid);
-            out[tid] = fmaf(sm->vf[tid], p1, v0 * p0);
-        }
-        return;
-    }
-
-    // ---- scores s_j = scale * <K16_j, q16>  (8 lanes per key, 16 dims per lane) -------------
-    {
-        float qreg[16];
-        const int sub = lane & 7, kin = lane >> 3;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) qreg[i] = sm->q[sub * 16 + i];
-        for (int j0 = warp * 4; j0 < n_kv; j0 += kWarps * 4) {
-            const int j = j0 + kin;
-            float s = 0.f;
-            if (j < n_kv) {
-                uint4 ka, kb;
-                if (j < pos) {
-                    const uint4 * k4 = reinterpret_cast<const uint4 *>(op.kcache + (size_t) j * kvw + g * kHeadDim + sub * 16);
-                    ka = __ldcg(k4); kb = __ldcg(k4 + 1);
-                } else {
-                    const uint4 * k4 = reinterpret_cast<const uint4 *>(sm->k16 + sub * 16);
-                    ka = k4[0]; kb = k4[1];
-                }
-                s = dot16h(ka, kb, qreg);
-            }
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            s += __shfl_xor_sync(0xffffffffu, s, 4);
-            if (sub == 0 && j < n_kv) sc[j] = s * op.kq_scale;
-        }
-    }
+    attn_prepare(op, op.qkv, h, 1, g, pos, sm);
+    if (h % (op.n_heads / op.n_kv_heads) == 0) attn_append(op, g, pos, kvw, sm);
+    attn_scores<1>(op, sm, g, kvw, pos, 0, n_kv, sc, 0);
     __syncthreads();
 
-    if (mode == ATTN_SOFTMAX_P16 || mode == ATTN_FAST) {
+    if (op.mode == ATTN_SOFTMAX_P16) {
         float mx = -CUDART_INF_F;
         for (int j = tid; j < n_kv; j += kThreads) mx = fmaxf(mx, sc[j]);
         mx = block_max_f(mx, sm->redf);
@@ -401,100 +727,91 @@ __device__ void stage_attn(const Op & op, StreamState * st, float * smem_f) {
         }
         sum = block_sum_d(sum, sm->red);
         const float inv = (float) (1.0 / sum);
-        if (mode == ATTN_SOFTMAX_P16) {
-            // soft_max scales by 1/sum (ops.cpp:5322-5323); the following mul_mat rounds P to F16
-            for (int j = tid; j < n_kv; j += kThreads) sc[j] = f16r(sc[j] * inv);
-        } else {
-            for (int j = tid; j < n_kv; j += kThreads) sc[j] = sc[j] * inv;
-        }
+        // soft_max scales by 1/sum (ops.cpp:5322-5323); the following mul_mat rounds P to F16
+        for (int j = tid; j < n_kv; j += kThreads) sc[j] = f16r(sc[j] * inv);
         __syncthreads();
-        // P.V : 4 key partitions x 128 dims
         const int d = tid & (kHeadDim - 1), part = tid >> 7;
         float acc = 0.f;
         for (int j = part; j < n_kv; j += 4) {
             const __half hv = (j < pos) ? __ldcg(op.vcache + (size_t) j * kvw + g * kHeadDim + d) : sm->v16[d];
             acc = fmaf(__half2float(hv), sc[j], acc);
         }
-        sm->part[part][d] = acc;
+        sm->part[part][0][d] = acc;
         __syncthreads();
         if (tid < kHeadDim)
-            out[tid] = (sm->part[0][tid] + sm->part[1][tid]) + (sm->part[2][tid] + sm->part[3][tid]);
+            out[tid] = (sm->part[0][0][tid] + sm->part[1][0][tid]) + (sm->part[2][0][tid] + sm->part[3][0][tid]);
         return;
     }
 
-    // ---- ATTN_FLASH_F16SEQ: ggml_compute_forward_flash_attn_ext_f16_one_chunk ---------------
-    // split-KV only when n_kv >= 512 (ops.cpp:8740): chunk = ceil(n_kv / n_threads)
+    // ggml_compute_forward_flash_attn_ext_f16_one_chunk; split-KV only when n_kv >= 512
+    // (ops.cpp:8740): chunk = ceil(n_kv / n_threads)
     int n_chunks = 1, chunk = n_kv;
     if (n_kv >= 512 && op.ref_threads > 1) {
         n_chunks = op.ref_threads;
         chunk = (n_kv + n_chunks - 1) / n_chunks;
     }
-    // per-key (ms, vs): depends only on the running max of the chunk's earlier scores
-    if (warp == 0) {
-        for (int c = 0; c < n_chunks; ++c) {
-            const int c0 = c * chunk, c1 = min(c0 + chunk, n_kv);
-            float run = -CUDART_INF_F;      // max of scores before the current 32-group
-            for (int j0 = c0; j0 < c1; j0 += 32) {
-                const int j = j0 + lane;
-                const float s = (j < c1) ? sc[j] : -CUDART_INF_F;
-                float incl = s;             // inclusive prefix max within the group
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const float t = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl = fmaxf(incl, t);
-                }
-                float excl = __shfl_up_sync(0xffffffffu, incl, 1);
-                if (lane == 0) excl = -CUDART_INF_F;
-                const float mprev = fmaxf(run, excl);
-                if (j < c1) ms[j] = mprev;  // stash M_{j-1}; turned into factors below
-                run = fmaxf(run, __shfl_sync(0xffffffffu, incl, 31));
-            }
-            if (lane == 0) sm->chunkM[c] = run;
-        }
-    }
-    __syncthreads();
-    for (int j = tid; j < n_kv; j += kThreads) {
-        const float mprev = ms[j], s = sc[j];
-        if (s > mprev) { ms[j] = expf_cr(mprev - s); vs[j] = 1.0f; }
-        else           { ms[j] = 1.0f;               vs[j] = expf_cr(s - mprev); }
-    }
-    __syncthreads();
-
     float outv = 0.f;   // valid for tid < 128
     float Mf = -CUDART_INF_F, Sf = 0.f;
     for (int c = 0; c < n_chunks; ++c) {
         const int c0 = c * chunk, c1 = min(c0 + chunk, n_kv);
         if (c0 >= n_kv) break;
-        float acc = 0.f;
-        if (tid < kHeadDim) {
-            const __half * vbase = op.vcache + g * kHeadDim + tid;
-            for (int j0 = c0; j0 < c1; j0 += 8) {
-                float vv[8];
+        float run = -CUDART_INF_F;      // warp 0: running max of the chunk's earlier scores
+        float acc = 0.f, S = 0.f;
+        for (int t0 = c0; t0 < c1; t0 += kTile) {
+            const int t1 = min(t0 + kTile, c1);
+            if (warp == 0) {
+                for (int j0 = t0; j0 < t1; j0 += 32) {
+                    const int j = j0 + lane;
+                    const float s = (j < t1) ? sc[j] : -CUDART_INF_F;
+                    float incl = s;             // inclusive prefix max within the group
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int j = j0 + u;
-                    vv[u] = (j < c1) ? __half2float((j < pos) ? __ldcg(vbase + (size_t) j * kvw) : sm->v16[tid]) : 0.f;
-                }
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int j = j0 + u;
-                    if (j < c1) {
-                        const float m = ms[j];
-                        if (m != 1.0f) acc = f16r(acc * m);          // ggml_vec_scale_f16
-                        acc = f16r(fmaf(vv[u], vs[j], acc));          // ggml_vec_mad_f16
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const float tt = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl = fmaxf(incl, tt);
                     }
+                    float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+                    if (lane == 0) excl = -CUDART_INF_F;
+                    if (j < t1) ms[j - t0] = fmaxf(run, excl);   // M_{j-1}
+                    run = fmaxf(run, __shfl_sync(0xffffffffu, incl, 31));
                 }
             }
-        } else if (tid == kHeadDim) {
-            float S = 0.f;
-            for (int j = c0; j < c1; ++j) S = fmaf(S, ms[j], vs[j]);  // S = S*ms + vs
-            sm->chunkS[c] = S;
+            __syncthreads();
+            for (int j = t0 + tid; j < t1; j += kThreads) {
+                const float mprev = ms[j - t0], s = sc[j];
+                if (s > mprev) { ms[j - t0] = expf_cr(mprev - s); vs[j - t0] = 1.0f; }
+                else           { ms[j - t0] = 1.0f;               vs[j - t0] = expf_cr(s - mprev); }
+            }
+            __syncthreads();
+            if (tid < kHeadDim) {
+                const __half * vbase = op.vcache + g * kHeadDim + tid;
+                for (int j0 = t0; j0 < t1; j0 += 8) {
+                    float vv[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int j = j0 + u;
+                        vv[u] = (j < t1) ? __half2float((j < pos) ? __ldcg(vbase + (size_t) j * kvw) : sm->v16[tid]) : 0.f;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int j = j0 + u;
+                        if (j < t1) {
+                            const float m = ms[j - t0];
+                            if (m != 1.0f) acc = f16r(acc * m);               // ggml_vec_scale_f16
+                            acc = f16r(fmaf(vv[u], vs[j - t0], acc));         // ggml_vec_mad_f16
+                        }
+                    }
+                }
+            } else if (tid == kHeadDim) {
+                for (int j = t0; j < t1; ++j) S = fmaf(S, ms[j - t0], vs[j - t0]);   // S = S*ms + vs
+            }
+            __syncthreads();
         }
+        if (warp == 0 && lane == 0) sm->chunkM[c] = run;
+        if (tid == kHeadDim) sm->chunkS[c] = S;
         __syncthreads();
         if (n_chunks == 1) {
-            const float S = sm->chunkS[0];
-            const float S_inv = (S == 0.0f) ? 0.0f : 1.0f / S;
-            outv = acc * S_inv;
+            const float Sc = sm->chunkS[0];
+            outv = acc * ((Sc == 0.0f) ? 0.0f : 1.0f / Sc);
         } else {
             // ggml_flash_attn_ext_reduce_partials (ops.cpp:8652-8688)
             const float Mc = sm->chunkM[c], Sc = sm->chunkS[c];
@@ -511,13 +828,24 @@ __device__ void stage_attn(const Op & op, StreamState * st, float * smem_f) {
     if (tid < kHeadDim) out[tid] = outv;
 }
 
+__device__ __noinline__ void stage_attn(const Op & op, const LocalState * ls, float * scratch) {
+    AttnSmem * sm = reinterpret_cast<AttnSmem *>(scratch);
+    float * sc = scratch + (sizeof(AttnSmem) + 15) / 16 * 4;
+    if (op.mode == ATTN_F32) { attn_f32_pair(op, sm, sc); return; }
+    if (op.mode != ATTN_FAST) { attn_reference(op, ls, sm, sc); return; }
+    const int pos = (op.use_n_past ? ls->n_past : 0) + op.pos_off;
+    const int rep = op.n_heads / op.n_kv_heads;
+    if (rep == 1)      attn_fast<1>(op, op.qkv, op.out, pos, sm, sc);
+    else if (rep == 2) attn_fast<2>(op, op.qkv, op.out, pos, sm, sc);
+    else               attn_fast<4>(op, op.qkv, op.out, pos, sm, sc);
+}
+
 // ------------------------------------------------------------------------------------------
-// sampling
+// sampling (executed by every CTA; CTA 0 mirrors results to global memory)
 // ------------------------------------------------------------------------------------------
 struct SampleSmem {
     float l[kMaxVocab];
-    float p[kMaxVocab];
-    int   idx[kMaxVocab];
+    unsigned short idx[kMaxVocab];
     unsigned int hist[256];
     float redf[kWarps];
     int   redi[kWarps];
@@ -559,7 +887,7 @@ __device__ int block_argmax(const float * l, int n, SampleSmem * sm) {
 }
 
 // k-th largest value of l[0..n) (radix select on order-preserving keys), 1 <= k <= n
-__device__ float block_kth_largest(const float * l, int n, int k, SampleSmem * sm) {
+__device__ __noinline__ float block_kth_largest(const float * l, int n, int k, SampleSmem * sm) {
     unsigned int prefix = 0, mask = 0;
     int kk = k;
     for (int shift = 24; shift >= 0; shift -= 8) {
@@ -601,8 +929,7 @@ __device__ float block_kth_largest(const float * l, int n, int k, SampleSmem * s
         kk = (int) sm->sel_k;
         __syncthreads();
     }
-    // invert ord_key
-    const unsigned int u = (prefix & 0x80000000u) ? (prefix & 0x7fffffffu) : ~prefix;
+    const unsigned int u = (prefix & 0x80000000u) ? (prefix & 0x7fffffffu) : ~prefix;   // invert ord_key
     return __uint_as_float(u);
 }
 
@@ -621,11 +948,11 @@ __device__ float philox_uniform(uint64_t seed, uint32_t c0, uint32_t c1, uint32_
     return (float) (x0 >> 8) * (1.0f / 16777216.0f);
 }
 
-// temperature / top-k / softmax / CDF scan on sm->l[0..n).  eos_id >= 0: EOS survives top-k
-// (src/tts_transformer.cpp:2451-2494); eos_id < 0: code-predictor rule (:2202-2232) with the
-// CDF scan of the TRT sampler (src/trt_cuda_kernels.cu:160-180) in place of
-// std::discrete_distribution.
-__device__ int block_sample(int n, float temperature, int top_k, float u, int eos_id, SampleSmem * sm) {
+// temperature / top-k / softmax / CDF scan on sm->l[0..n); p = scratch for n probabilities.
+// eos_id >= 0: EOS survives top-k (src/tts_transformer.cpp:2451-2494); eos_id < 0: code-predictor
+// rule (:2202-2232) with the CDF scan of the TRT sampler (src/trt_cuda_kernels.cu:160-180) in
+// place of std::discrete_distribution.
+__device__ __noinline__ int block_sample(int n, float temperature, int top_k, float u, int eos_id, SampleSmem * sm, float * p) {
     float * l = sm->l;
     for (int i = threadIdx.x; i < n; i += kThreads) l[i] = l[i] / temperature;
     __syncthreads();
@@ -643,7 +970,7 @@ __device__ int block_sample(int n, float temperature, int top_k, float u, int eo
     double sum = 0.0;
     for (int i = threadIdx.x; i < n; i += kThreads) {
         const float e = expf(l[i] - mx);
-        sm->p[i] = e;
+        p[i] = e;
         sum += (double) e;
     }
     sum = block_sum_d(sum, sm->red);
@@ -652,11 +979,10 @@ __device__ int block_sample(int n, float temperature, int top_k, float u, int eo
     const int b0 = threadIdx.x * per, b1 = min(b0 + per, n);
     int cnt = 0;
     for (int i = b0; i < b1; ++i) {
-        const float pr = (float) ((double) sm->p[i] / sum);
-        sm->p[i] = pr;
+        const float pr = (float) ((double) p[i] / sum);
+        p[i] = pr;
         cnt += (pr != 0.0f);
     }
-    // block exclusive scan of cnt
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int incl = cnt;
 #pragma unroll
@@ -669,7 +995,7 @@ __device__ int block_sample(int n, float temperature, int top_k, float u, int eo
     int base = 0;
     for (int w = 0; w < warp; ++w) base += sm->wcount[w];
     int pos = base + incl - cnt;
-    for (int i = b0; i < b1; ++i) if (sm->p[i] != 0.0f) { sm->idx[pos++] = i; }
+    for (int i = b0; i < b1; ++i) if (p[i] != 0.0f) { sm->idx[pos++] = (unsigned short) i; }
     if (threadIdx.x == kThreads - 1) sm->count = base + incl;
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -678,7 +1004,7 @@ __device__ int block_sample(int n, float temperature, int top_k, float u, int eo
         const int m = sm->count;
         for (int t = 0; t < m; ++t) {
             const int i = sm->idx[t];
-            cum += sm->p[i];
+            cum += p[i];
             if (cum >= u) { tok = i; break; }
         }
         sm->token = tok;
@@ -687,18 +1013,19 @@ __device__ int block_sample(int n, float temperature, int top_k, float u, int eo
     return sm->token;
 }
 
-__device__ void stage_sample_cb0(const Op & op, StreamState * st, float * smem_f) {
-    if (blockIdx.x != 0) return;
-    SampleSmem * sm = reinterpret_cast<SampleSmem *>(smem_f);
+__device__ __noinline__ void stage_sample_cb0(const Op & op, StreamState * st, LocalState * ls, float * scratch, float * xs) {
+    SampleSmem * sm = reinterpret_cast<SampleSmem *>(scratch);
+    const bool lead = (blockIdx.x == 0);
     const int n = op.n_vocab;
-    const int frame = st->frame;
+    const int frame = ls->frame;
     const float rep = st->rep_pen;
     const float temperature = (op.temperature_override < -1e29f) ? st->temperature : op.temperature_override;
     const int top_k = (op.temperature_override < -1e29f) ? st->top_k : op.top_k_override;
+    __syncthreads();
     for (int i = threadIdx.x; i < n; i += kThreads) {
         float v = __ldcg(op.logits + i);
         if (i >= op.suppress_start && i != op.eos_id) v = -CUDART_INF_F;      // :2418-2422
-        if (rep != 1.0f && ((st->seen[i >> 5] >> (i & 31)) & 1u)) {           // :2425-2435
+        if (rep != 1.0f && ((ls->seen[i >> 5] >> (i & 31)) & 1u)) {           // :2425-2435
             v = (v > 0.0f) ? v / rep : v * rep;
         }
         sm->l[i] = v;
@@ -716,7 +1043,7 @@ __device__ void stage_sample_cb0(const Op & op, StreamState * st, float * smem_f
         }
         __syncthreads();
     }
-    if (op.dump) for (int i = threadIdx.x; i < n; i += kThreads) op.dump[i] = sm->l[i];
+    if (op.dump && lead) for (int i = threadIdx.x; i < n; i += kThreads) op.dump[i] = sm->l[i];
     const int ignore_eos = st->ignore_eos;
     if (ignore_eos) {   // benchmark switch (not reference behaviour): fixed-length utterances
         if (threadIdx.x == 0) sm->l[op.eos_id] = -CUDART_INF_F;
@@ -728,29 +1055,34 @@ __device__ void stage_sample_cb0(const Op & op, StreamState * st, float * smem_f
     } else {
         const float u = op.uniforms ? __ldcg(op.uniforms + frame)
                                     : philox_uniform(st->seed, (uint32_t) frame, 0u, 0x0cb0u);
-        tok = block_sample(n, temperature, top_k, u, ignore_eos ? -1 : op.eos_id, sm);
+        tok = block_sample(n, temperature, top_k, u, ignore_eos ? -1 : op.eos_id, sm, xs);
     }
+    __syncthreads();
     if (threadIdx.x == 0) {
         if (tok == op.eos_id) {
-            st->done = 1; st->eos = 1;
+            ls->done = 1; ls->eos = 1;
+            if (lead) { st->done = 1; st->eos = 1; }
         } else {
-            st->cur_codes[0] = tok;
-            st->feed_codes[0] = tok;
-            st->seen[tok >> 5] |= 1u << (tok & 31);
+            ls->cur_codes[0] = tok;
+            ls->feed_codes[0] = tok;
+            ls->seen[tok >> 5] |= 1u << (tok & 31);
+            if (lead) { st->cur_codes[0] = tok; st->feed_codes[0] = tok; st->seen[tok >> 5] = ls->seen[tok >> 5]; }
         }
     }
+    __syncthreads();
 }
 
-__device__ void stage_sample_cp(const Op & op, StreamState * st, float * smem_f) {
-    if (blockIdx.x != 0) return;
-    SampleSmem * sm = reinterpret_cast<SampleSmem *>(smem_f);
+__device__ __noinline__ void stage_sample_cp(const Op & op, StreamState * st, LocalState * ls, float * scratch, float * xs) {
+    SampleSmem * sm = reinterpret_cast<SampleSmem *>(scratch);
+    const bool lead = (blockIdx.x == 0);
     const int n = op.n_vocab;
     const float temperature = (op.temperature_override < -1e29f) ? st->temperature : op.temperature_override;
     const int top_k = (op.temperature_override < -1e29f) ? st->top_k : op.top_k_override;
+    __syncthreads();
     for (int i = threadIdx.x; i < n; i += kThreads) {
         const float v = __ldcg(op.logits + i);
         sm->l[i] = v;
-        if (op.dump) op.dump[i] = v;
+        if (op.dump && lead) op.dump[i] = v;
     }
     __syncthreads();
     int tok;
@@ -758,24 +1090,37 @@ __device__ void stage_sample_cp(const Op & op, StreamState * st, float * smem_f)
         tok = block_argmax(sm->l, n, sm);
     } else {
         const float u = op.uniforms ? __ldcg(op.uniforms + (op.book - 1))
-                                    : philox_uniform(st->seed, (uint32_t) st->frame, (uint32_t) op.book, 0x0c9du);
-        tok = block_sample(n, temperature, top_k, u, -1, sm);
+                                    : philox_uniform(st->seed, (uint32_t) ls->frame, (uint32_t) op.book, 0x0c9du);
+        tok = block_sample(n, temperature, top_k, u, -1, sm, xs);
     }
+    __syncthreads();
     if (threadIdx.x == 0) {
-        st->cur_codes[op.book] = tok;
-        st->feed_codes[op.book] = op.forced ? __ldcg(op.forced + (op.book - 1)) : tok;
+        const int feed = op.forced ? __ldcg(op.forced + (op.book - 1)) : tok;
+        ls->cur_codes[op.book] = tok;
+        ls->feed_codes[op.book] = feed;
+        if (lead) { st->cur_codes[op.book] = tok; st->feed_codes[op.book] = feed; }
     }
+    __syncthreads();
 }
 
-__device__ void stage_frame_end(const Op & op, StreamState * st) {
-    if (blockIdx.x != 0 || threadIdx.x != 0) return;
-    const int f = st->frame;
-    for (int c = 0; c < op.n_books; ++c) op.codes_out[(size_t) f * op.n_books + c] = st->cur_codes[c];
-    st->frame = f + 1;
-    if (f + 1 >= st->max_len) st->done = 1;     // src/tts_transformer.cpp:2525-2527
+__device__ __noinline__ void stage_frame_end(const Op & op, StreamState * st, LocalState * ls) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int f = ls->frame;
+        if (blockIdx.x == 0) {
+            for (int c = 0; c < op.n_books; ++c) op.codes_out[(size_t) f * op.n_books + c] = ls->cur_codes[c];
+            st->frame = f + 1;
+        }
+        ls->frame = f + 1;
+        if (f + 1 >= st->max_len) {             // src/tts_transformer.cpp:2525-2527
+            ls->done = 1;
+            if (blockIdx.x == 0) st->done = 1;
+        }
+    }
+    __syncthreads();
 }
 
-__device__ void stage_copy(const Op & op) {
+__device__ __noinline__ void stage_copy(const Op & op) {
     const int i0 = blockIdx.x * kThreads + threadIdx.x;
     const __half * row = op.table ? op.table + (size_t) __ldcg(op.tok_ptr) * op.n : nullptr;
     for (int i = i0; i < op.n; i += gridDim.x * kThreads) {
@@ -787,46 +1132,133 @@ __device__ void stage_copy(const Op & op) {
 // ------------------------------------------------------------------------------------------
 // the program runner
 // ------------------------------------------------------------------------------------------
-// persistent = 1: cooperative launch, grid barrier between stages, loops over n_frames frames.
-// persistent = 0: runs exactly ops[0] (host launches stage by stage).
+// persistent = 1: cooperative launch, grid barrier after every all-to-all stage, loops over
+//                 n_frames frames (stops early once the stream is done when check_done is set).
+// persistent = 0: debug path, the host launches the same code one op at a time (n_ops = 1).
+// Dynamic shared memory: [ring: n_slots x slot_bytes][xs: xs_elems floats][scratch].
+constexpr int kScratchBytes = 40 * 1024;
+
 extern "C" __global__ void __launch_bounds__(kThreads, 1)
 qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridBarrier * bar,
-                 int n_frames, int persistent, int check_done) {
-    extern __shared__ __align__(16) float smem[];
+                 int n_frames, RunCfg cfg) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kNumSlots];
     __shared__ double red[kWarps];
-    unsigned int epoch = 0;
-    // bar->count is zeroed by the host (stream-ordered memset) before every persistent launch
-    for (int f = 0; f < n_frames; ++f) {
-        if (check_done && __ldcg(&st->done)) break;
-        bool stop = false;
+    __shared__ LocalState ls;
+
+    Ring ring;
+    ring.base = smem_raw;
+    ring.full = full_bar;
+    ring.slot_bytes = cfg.slot_bytes;
+    ring.n_slots = cfg.n_slots;
+    float * xs = reinterpret_cast<float *>(smem_raw + (size_t) cfg.n_slots * cfg.slot_bytes);
+    float * scratch = xs + cfg.xs_elems;
+
+    // CTA-local state from the stream's global state (the previous launch has completed)
+    for (int i = threadIdx.x; i < (int) (sizeof(LocalState) / 4); i += kThreads) {
+        int32_t * dst = reinterpret_cast<int32_t *>(&ls);
+        const int nb = kMaxBooks, o_cur = 4, o_feed = 4 + nb, o_seen = 4 + 2 * nb;
+        int32_t v;
+        if (i == 0) v = st->n_past;
+        else if (i == 1) v = st->frame;
+        else if (i == 2) v = st->done;
+        else if (i == 3) v = st->eos;
+        else if (i < o_feed) v = st->cur_codes[i - o_cur];
+        else if (i < o_seen) v = st->feed_codes[i - o_feed];
+        else v = (int32_t) st->seen[i - o_seen];
+        dst[i] = v;
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kNumSlots; ++i) mbar_init(full_bar + i, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    Prefetch pf;
+    pf.idx = -1; pf.frame = (cfg.n_sched > 0) ? 0 : n_frames; pf.q = 0; pf.p1 = 0; pf.K = 0; pf.ppc = 1; pf.slot = 0;
+    pf.W = nullptr; pf.seq = 0; pf.policy = 0; pf.n0 = make_int4(0, 0, 0, 0); pf.n1 = pf.n0;
+    uint32_t cons_seq = 0;          // ring chunks consumed so far (uniform across the CTA)
+    unsigned int epoch = 0;         // bar->count is zeroed by the host before every persistent launch
+    if (threadIdx.x == kPfThread) {
+        pf.policy = policy_evict_first();
+        if (cfg.n_sched > 0) {
+            pf.n0 = __ldg(reinterpret_cast<const int4 *>(cfg.sched));
+            pf.n1 = __ldg(reinterpret_cast<const int4 *>(cfg.sched) + 1);
+        }
+        prefetch_issue(cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring);
+    }
+
+    bool stop = false;
+    for (int f = 0; f < n_frames && !stop; ++f) {
+        if (cfg.check_done && ls.done) break;
         for (int i = 0; i < n_ops && !stop; ++i) {
             const Op & op = ops[i];
+            bool all_to_all = true;
+            const bool prof_on = cfg.prof && blockIdx.x == cfg.prof_cta && threadIdx.x == 0;
+            const long long t0 = prof_on ? clock64() : 0;
+            const long long t0p = (cfg.prof && threadIdx.x == 0) ? clock64() : 0;
             switch (op.type) {
-                case OP_GEMV:       stage_gemv(op, st, smem, red); break;
-                case OP_ATTN:       stage_attn(op, st, smem); break;
-                case OP_SAMPLE_CB0: stage_sample_cb0(op, st, smem); break;
-                case OP_SAMPLE_CP:  stage_sample_cp(op, st, smem); break;
-                case OP_FRAME_END:  stage_frame_end(op, st); break;
+                case OP_GEMV:       cons_seq += stage_gemv(op, st, &ls, xs, red, ring, cons_seq, cfg.sched, cfg.n_sched, n_frames, pf, prof_on ? cfg.prof : nullptr); break;
+                case OP_ATTN:       stage_attn(op, &ls, scratch); break;
                 case OP_COPY:       stage_copy(op); break;
+                case OP_SAMPLE_CB0: stage_sample_cb0(op, st, &ls, scratch, xs); all_to_all = false; break;
+                case OP_SAMPLE_CP:  stage_sample_cp(op, st, &ls, scratch, xs); all_to_all = false; break;
+                case OP_FRAME_END:  stage_frame_end(op, st, &ls); all_to_all = false; break;
             }
-            if (persistent) {
-                if (i + 1 < n_ops) gemv_prefetch(ops[i + 1]);
-                grid_barrier(bar, epoch);
-                if (check_done && (op.type == OP_SAMPLE_CB0 || op.type == OP_FRAME_END) && __ldcg(&st->done))
-                    stop = true;
+            const long long t1 = prof_on ? clock64() : 0;
+            const long long t1p = (cfg.prof && threadIdx.x == 0) ? clock64() : 0;
+            if (!all_to_all) {
+                if (cfg.check_done && op.type != OP_SAMPLE_CP && ls.done) stop = true;
+            } else if (cfg.persistent) {
+                grid_barrier(bar, epoch, cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring, prof_on ? cfg.prof + op.type * 8 + 7 : nullptr);
+            } else {
+                __syncthreads();
+            }
+            if (cfg.prof && threadIdx.x == 0 && op.type <= OP_ATTN) {   // per-CTA view: prof[64 + cta*4 + ...]
+                const long long t2 = clock64();
+                cfg.prof[64 + blockIdx.x * 4 + op.type * 2 + 0] += (unsigned long long) (t1p - t0p);
+                cfg.prof[64 + blockIdx.x * 4 + op.type * 2 + 1] += (unsigned long long) (t2 - t1p);
+            }
+            if (prof_on) {      // [type][0] = count, [1] = stage cycles, [2] = barrier cycles (CTA 0's view)
+                const long long t2 = clock64();
+                cfg.prof[op.type * 8 + 0] += 1;
+                cfg.prof[op.type * 8 + 1] += (unsigned long long) (t1 - t0);
+                cfg.prof[op.type * 8 + 2] += (unsigned long long) (t2 - t1);
             }
         }
-        if (stop) break;
     }
+    // drain: every bulk copy issued into this CTA's shared memory must land before it exits
+    __syncthreads();
+    if (threadIdx.x == kPfThread) {
+        for (uint32_t s = cons_seq; s != pf.seq; ++s)
+            mbar_wait(full_bar + (s % (uint32_t) cfg.n_slots), (s / (uint32_t) cfg.n_slots) & 1u);
+    }
+    __syncthreads();
 }
 
-size_t smem_required(int k_max, int max_ctx) {
-    size_t a = (size_t) k_max * sizeof(float);
-    size_t b = sizeof(SampleSmem);
-    size_t c = ((sizeof(AttnSmem) + 3) / 4) * 4 + 3 * (size_t) ((max_ctx + 8) & ~3) * sizeof(float);
-    size_t m = a > b ? a : b;
-    m = m > c ? m : c;
-    return (m + 127) & ~(size_t) 127;
+// ring slot size: >= two rows of the widest projection input, multiple of 1024, at least 16 KiB
+size_t slot_bytes_for(int k_max) {
+    size_t b = (size_t) 4 * k_max;
+    if (b < 16384) b = 16384;
+    return (b + 1023) & ~(size_t) 1023;
 }
+size_t xs_elems_for(int k_max, int k2_max) {
+    size_t e = (size_t) k_max;
+    if ((size_t) 2 * k2_max > e) e = (size_t) 2 * k2_max;
+    if (e < (size_t) kMaxVocab) e = kMaxVocab;
+    return (e + 31) & ~(size_t) 31;
+}
+int n_slots_for(int k_max, int k2_max, size_t smem_limit) {
+    const size_t fixed = xs_elems_for(k_max, k2_max) * sizeof(float) + kScratchBytes + 2048 /* static */;
+    if (smem_limit < fixed + 2 * slot_bytes_for(k_max)) return 0;
+    size_t n = (smem_limit - fixed) / slot_bytes_for(k_max);
+    return (int) (n > (size_t) kNumSlots ? kNumSlots : n);
+}
+size_t smem_required(int k_max, int k2_max, int n_slots) {
+    return (size_t) n_slots * slot_bytes_for(k_max) + xs_elems_for(k_max, k2_max) * sizeof(float) + kScratchBytes;
+}
+static_assert(sizeof(AttnSmem) + (kMaxScores + 2 * kTile) * sizeof(float) + 64 <= kScratchBytes, "attention scratch");
+static_assert(sizeof(SampleSmem) <= kScratchBytes, "sampling scratch");
 
 }  // namespace qtts

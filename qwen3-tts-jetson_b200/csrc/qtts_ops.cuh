@@ -16,6 +16,11 @@ constexpr int kWarps     = kThreads / 32;
 constexpr int kHeadDim   = 128;   // every Qwen3-TTS config uses 128 (src/tts_transformer.h:33,47)
 constexpr int kMaxVocab  = 4096;  // codec vocab 3072, code-pred vocab 2048
 constexpr int kMaxBooks  = 32;
+constexpr int kNumSlots  = 10;    // shared-memory weight ring: slots of slot_bytes each
+constexpr int kMaxSplits = 16;    // ATTN_FAST: key ranges per KV group
+constexpr int kSplitKeys = 128;   // ATTN_FAST: target keys per split
+constexpr int kPartStride = 132;  // m, l, pad, pad, o[128]
+constexpr int kMaxScores = 4608;  // attention scores kept in shared memory (>= max_ctx)
 
 enum OpType : int32_t {
     OP_GEMV       = 0,   // skinny projection: y = W . f16round(x)  (+ prologue / epilogue)
@@ -27,9 +32,12 @@ enum OpType : int32_t {
 };
 
 enum InKind : int32_t {
-    IN_VEC       = 0,    // f32 vector in global memory
-    IN_EMBED_ROW = 1,    // one row of an F16 embedding table, row id read from device memory
+    IN_VEC       = 0,    // f32 vector(s) in global memory: in + t * in_stride
+    IN_EMBED_ROW = 1,    // one row of an F16 embedding table; row id = tok_ptr (device memory) or,
+                         // when tok_slot >= 0, the CTA-local feed_codes[tok_slot]
     IN_EMBED_SUM = 2,    // next Talker input: sum of the 16 code embeddings + text row
+    IN_CP_FIRST  = 3,    // code-predictor positions 0 and 1 together (n_tok = 2):
+                         // token 0 = f32 vector `in` (Talker hidden), token 1 = table[feed_codes[0]]
 };
 
 enum Epilogue : int32_t {
@@ -81,6 +89,9 @@ struct Op {
     const __nv_bfloat16 * W; // [rows][K] row-major
     int32_t rows, K;
     int32_t in_kind, epi;
+    int32_t n_tok;           // 1, or 2 for the merged code-predictor positions 0/1 (also OP_ATTN)
+    int32_t tok_slot;        // IN_EMBED_ROW: index into the local feed_codes (-1: use tok_ptr)
+    int32_t in_stride, out_stride;   // element strides between the n_tok vectors of in/res and out
     const float * in;        // IN_VEC
     const __half * table;    // IN_EMBED_ROW
     const int32_t * tok_ptr; // IN_EMBED_ROW: row id
@@ -104,6 +115,9 @@ struct Op {
     int32_t mode;
     int32_t ref_threads;         // thread count of the reference's split-KV path (>=512 keys)
     float   kq_scale;
+    int32_t qkv_stride;          // element stride between the n_tok qkv vectors
+    float * attn_part;           // ATTN_FAST split-KV partials [n_heads][kMaxSplits][kPartStride]
+    unsigned int * attn_cnt;     // ATTN_FAST arrival counters [n_kv_heads]
     // ---- sampling ----
     const float * logits; int32_t n_vocab;
     int32_t book;                // OP_SAMPLE_CP: index 1..15 of the code written
@@ -123,6 +137,16 @@ struct Op {
 enum OpFlags : int32_t {
     F_INC_NPAST = 1,     // CTA 0 increments state.n_past when the stage completes
 };
+
+// Host-built list of the program's GEMV stages in execution order (one frame); the prefetcher
+// walks it cyclically, so that issuing a chunk costs a handful of integer instructions.
+struct WSched {
+    const __nv_bfloat16 * W;
+    int32_t K, pairs, ppc, pad;     // ppc = row pairs per ring chunk
+    int32_t pad2[2];                // 32-byte entries: read as two 16-byte loads
+};
+
+static_assert(sizeof(WSched) == 32, "WSched is read as two int4");
 
 struct GridBarrier {
     unsigned int count;   // monotonically increasing arrival counter

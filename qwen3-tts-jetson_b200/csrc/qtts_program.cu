@@ -10,12 +10,14 @@
 namespace qtts {
 
 extern "C" __global__ void qtts_run_program(const Op * ops, int n_ops, StreamState * st, GridBarrier * bar,
-                                            int n_frames, int persistent, int check_done);
+                                            int n_frames, RunCfg cfg);
 
 static Op blank() {
     Op o;
     memset(&o, 0, sizeof(o));
     o.temperature_override = -1e30f;
+    o.n_tok = 1;
+    o.tok_slot = -1;
     return o;
 }
 
@@ -27,34 +29,40 @@ static Op gemv(const __nv_bfloat16 * W, int rows, int K, const float * in, const
     return o;
 }
 
-struct LayerBuf { float * x, * qkv, * attn, * act; __half * kc, * vc; float * kv0; size_t kv_layer_stride; };
+struct LayerBuf { float * x, * qkv, * attn, * act; __half * kc, * vc; size_t kv_layer_stride; float * attn_part; unsigned int * attn_cnt; };
 
-// five stages of one decoder layer; `first` (if non-null) replaces the QKV stage's input setup
+// five stages of one decoder layer over n_tok tokens (2 only for the merged code-predictor
+// positions 0/1); `first` (if non-null) replaces the QKV stage's input setup
 static void emit_layer(Engine * e, std::vector<Op> & P, const LayerW & L, const Dims & D, const LayerBuf & B,
-                       int layer, const Op * first, bool use_n_past, int pos_off, int mode) {
+                       int layer, const Op * first, bool use_n_past, int pos_off, int mode, int n_tok = 1) {
     const float eps = e->cfg.rms_norm_eps;
     const int qkv_rows = (D.nh + 2 * D.nkv) * kHeadDim;
+    const int aw = D.nh * kHeadDim;
     Op q = gemv(L.wqkv, qkv_rows, D.H, B.x, L.attn_norm, eps, EPI_STORE, B.qkv);
+    q.n_tok = n_tok; q.in_stride = D.H; q.out_stride = qkv_rows;
     if (first) {
         q.in_kind = first->in_kind; q.in = first->in; q.table = first->table; q.tok_ptr = first->tok_ptr;
-        q.es = first->es; q.x_out = first->x_out;
+        q.tok_slot = first->tok_slot; q.es = first->es; q.x_out = first->x_out;
     }
     P.push_back(q);
     Op a = blank();
     a.type = OP_ATTN; a.qkv = B.qkv; a.q_norm_w = L.q_norm; a.k_norm_w = L.k_norm;
     a.kcache = B.kc + (size_t) layer * B.kv_layer_stride;
     a.vcache = B.vc + (size_t) layer * B.kv_layer_stride;
-    a.kv0_f32 = B.kv0 ? B.kv0 + (size_t) layer * 2 * D.nkv * kHeadDim : nullptr;
     a.rope = e->rope; a.n_heads = D.nh; a.n_kv_heads = D.nkv; a.pos_off = pos_off; a.use_n_past = use_n_past ? 1 : 0;
     a.mode = mode; a.ref_threads = e->ref_threads; a.kq_scale = 1.0f / sqrtf((float) kHeadDim);
     a.eps = eps; a.out = B.attn;
+    a.n_tok = n_tok; a.qkv_stride = qkv_rows; a.out_stride = aw;
+    a.attn_part = B.attn_part; a.attn_cnt = B.attn_cnt;
     P.push_back(a);
-    Op o = gemv(L.wo, D.H, D.nh * kHeadDim, B.attn, nullptr, eps, EPI_ADD, B.x);
-    o.res = B.x;
+    Op o = gemv(L.wo, D.H, aw, B.attn, nullptr, eps, EPI_ADD, B.x);
+    o.res = B.x; o.n_tok = n_tok; o.in_stride = aw; o.out_stride = D.H;
     P.push_back(o);
-    P.push_back(gemv(L.wgu, 2 * D.ffn, D.H, B.x, L.ffn_norm, eps, EPI_SWIGLU, B.act));
+    Op gu = gemv(L.wgu, 2 * D.ffn, D.H, B.x, L.ffn_norm, eps, EPI_SWIGLU, B.act);
+    gu.n_tok = n_tok; gu.in_stride = D.H; gu.out_stride = D.ffn;
+    P.push_back(gu);
     Op d = gemv(L.wdown, D.H, D.ffn, B.act, nullptr, eps, EPI_ADD, B.x);
-    d.res = B.x;
+    d.res = B.x; d.n_tok = n_tok; d.in_stride = D.ffn; d.out_stride = D.H;
     P.push_back(d);
 }
 
@@ -63,7 +71,7 @@ void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, co
                       bool use_n_past, int pos_abs, int attn_mode, bool with_head, bool inc_npast) {
     const qtts_config & c = e->cfg;
     const Dims D{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
-    LayerBuf B{s.x, s.qkv, s.attn, s.act, s.kc, s.vc, nullptr, (size_t) e->max_ctx * c.n_kv_heads * kHeadDim};
+    LayerBuf B{s.x, s.qkv, s.attn, s.act, s.kc, s.vc, (size_t) e->max_ctx * c.n_kv_heads * kHeadDim, s.attn_part, s.attn_cnt};
     Op first = blank();
     first.in_kind = in_kind; first.in = in_vec; first.es = s.es; first.x_out = s.x;
     for (int l = 0; l < c.n_layers; ++l)
@@ -78,47 +86,47 @@ void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, co
     }
 }
 
-// predict_codes_autoregressive (src/tts_transformer.cpp:2153-2340) as 16 single-token passes:
-// positions 0 and 1 use the all-F32 attention of the reference's 2-token prefill graph
-// (:1613-1626), positions >= 2 the F16-cache / F16-P attention of its step graph (:1779-1792).
+// predict_codes_autoregressive (src/tts_transformer.cpp:2153-2340): positions 0 and 1 as ONE
+// two-token pass with the all-F32 attention of the reference's prefill graph (:1514-1664,
+// :1613-1626), then 14 single-token passes with the F16-cache / F16-P attention of its step graph
+// (:1666-1827).  Sampling stages are not followed by a grid barrier (every CTA samples).
 void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float * hidden,
                          float * dump, const int32_t * forced, const float * uniforms,
                          bool override_sampling, float temperature, int top_k) {
     const qtts_config & c = e->cfg;
     const Dims D{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
-    LayerBuf B{s.cp_x, s.cp_qkv, s.cp_attn, s.cp_act, s.cp_kc, s.cp_vc, s.cp_kv0, (size_t) 16 * c.cp_n_kv_heads * kHeadDim};
+    LayerBuf B{s.cp_x, s.cp_qkv, s.cp_attn, s.cp_act, s.cp_kc, s.cp_vc, (size_t) 16 * c.cp_n_kv_heads * kHeadDim,
+               s.attn_part, s.attn_cnt};
     const int n_pos = c.n_codebooks;   // 16 positions -> 15 sampled codes
-    for (int p = 0; p < n_pos; ++p) {
+    for (int p = 1; p < n_pos; ++p) {
+        const int n_tok = (p == 1) ? 2 : 1;
         Op first = blank();
-        if (p == 0) { first.in_kind = IN_VEC; first.in = hidden; }
-        else {
-            first.in_kind = IN_EMBED_ROW;
-            first.table = (p == 1) ? e->codec_embd : e->cp_embd[p - 2];
-            first.tok_ptr = &s.st->feed_codes[p - 1];
-        }
+        if (p == 1) { first.in_kind = IN_CP_FIRST; first.in = hidden; first.table = e->codec_embd; }
+        else { first.in_kind = IN_EMBED_ROW; first.table = e->cp_embd[p - 2]; first.tok_slot = p - 1; }
         if (e->mtp) {
             // talker space -> code-predictor space (src/tts_transformer.cpp:1709-1715)
             Op m = gemv(e->mtp, c.cp_hidden_size, c.hidden_size, hidden, nullptr, c.rms_norm_eps,
                         e->mtp_b ? EPI_BIAS : EPI_STORE, s.cp_x);
-            m.in_kind = first.in_kind; m.table = first.table; m.tok_ptr = first.tok_ptr; m.bias = e->mtp_b;
+            m.in_kind = first.in_kind; m.table = first.table; m.tok_slot = first.tok_slot; m.bias = e->mtp_b;
+            m.n_tok = n_tok; m.out_stride = c.cp_hidden_size;
             P.push_back(m);
             first = blank(); first.in_kind = IN_VEC; first.in = s.cp_x;
         } else {
             first.x_out = s.cp_x;
         }
-        const int mode = (p < 2) ? ATTN_F32 : ATTN_SOFTMAX_P16;
+        const int mode = (p == 1) ? ATTN_F32 : ATTN_SOFTMAX_P16;
         for (int l = 0; l < c.cp_layers; ++l)
-            emit_layer(e, P, e->cp[l], D, B, l, l == 0 ? &first : nullptr, false, p, mode);
-        if (p >= 1) {
-            P.push_back(gemv(e->lm_head[p - 1], c.cp_vocab_size, c.cp_hidden_size, s.cp_x, e->cp_output_norm,
-                             c.rms_norm_eps, EPI_STORE, s.cp_logits));
-            Op sp = blank();
-            sp.type = OP_SAMPLE_CP; sp.logits = s.cp_logits; sp.n_vocab = c.cp_vocab_size; sp.book = p;
-            sp.uniforms = uniforms; sp.forced = forced;
-            sp.dump = dump ? dump + (size_t) (p - 1) * c.cp_vocab_size : nullptr;
-            if (override_sampling) { sp.temperature_override = temperature; sp.top_k_override = top_k; }
-            P.push_back(sp);
-        }
+            emit_layer(e, P, e->cp[l], D, B, l, l == 0 ? &first : nullptr, false, p == 1 ? 0 : p, mode, n_tok);
+        // the head reads the LAST token of the pass
+        P.push_back(gemv(e->lm_head[p - 1], c.cp_vocab_size, c.cp_hidden_size,
+                         s.cp_x + (size_t) (n_tok - 1) * c.cp_hidden_size, e->cp_output_norm,
+                         c.rms_norm_eps, EPI_STORE, s.cp_logits));
+        Op sp = blank();
+        sp.type = OP_SAMPLE_CP; sp.logits = s.cp_logits; sp.n_vocab = c.cp_vocab_size; sp.book = p;
+        sp.uniforms = uniforms; sp.forced = forced;
+        sp.dump = dump ? dump + (size_t) (p - 1) * c.cp_vocab_size : nullptr;
+        if (override_sampling) { sp.temperature_override = temperature; sp.top_k_override = top_k; }
+        P.push_back(sp);
     }
 }
 
@@ -213,25 +221,38 @@ bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t
     return true;
 }
 
+std::vector<WSched> build_sched(Engine * e, const std::vector<Op> & P) {
+    std::vector<WSched> S;
+    for (const Op & op : P)
+        if (op.type == OP_GEMV) S.push_back(WSched{op.W, op.K, op.rows >> 1, e->slot_bytes / (4 * op.K), 0});
+    return S;
+}
+
 bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vector<Op> * host_ops, int n_ops,
-                        int n_frames, bool check_done) {
+                        const WSched * d_sched, int n_sched, int n_frames, bool check_done) {
     if (n_ops == 0) return true;
     if (e->persistent) {
         QTTS_CUDA(cudaMemsetAsync(&e->bar->count, 0, sizeof(unsigned int), e->stream));
-        int persistent = 1, cd = check_done ? 1 : 0;
+        RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 1, check_done ? 1 : 0, e->prof_on - 1, n_sched, d_sched,
+                   e->prof_on ? e->prof : nullptr};
         StreamState * st = s.st;
         GridBarrier * bar = e->bar;
         void * args[] = {(void *) &d_ops, (void *) &n_ops, (void *) &st, (void *) &bar, (void *) &n_frames,
-                         (void *) &persistent, (void *) &cd};
+                         (void *) &cfg};
         QTTS_CUDA(cudaLaunchCooperativeKernel((const void *) qtts_run_program, dim3(e->n_sms), dim3(kThreads),
                                               args, e->smem_bytes, e->stream));
         e->launches += 1;
         return true;
     }
     // debug path: one launch per stage; needs the host copy of the program to find sampling stages
+    if (!host_ops) return e->fail("stage-by-stage mode needs the host copy of the program");
     for (int f = 0; f < n_frames; ++f) {
+        int si = 0;     // schedule entry of the i-th op when it is a GEMV
         for (int i = 0; i < n_ops; ++i) {
-            qtts_run_program<<<e->n_sms, kThreads, e->smem_bytes, e->stream>>>(d_ops + i, 1, s.st, e->bar, 1, 0, 0);
+            const bool is_gemv = (*host_ops)[i].type == OP_GEMV;
+            RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 0, 0, 0, is_gemv ? 1 : 0, d_sched + si, nullptr};
+            if (is_gemv) ++si;
+            qtts_run_program<<<e->n_sms, kThreads, e->smem_bytes, e->stream>>>(d_ops + i, 1, s.st, e->bar, 1, cfg);
             e->launches += 1;
             const int type = host_ops ? (*host_ops)[i].type : -1;
             if (check_done && (type == OP_SAMPLE_CB0 || type == OP_FRAME_END || !host_ops)) {
@@ -254,9 +275,18 @@ bool run_program(Engine * e, Slot & s, const std::vector<Op> & P, int n_frames, 
         if (!p) return e->fail("out of device memory for program");
         s.scratch_prog = p; s.scratch_cap = cap;   // older buffer stays in allocs until destroy
     }
+    const std::vector<WSched> S = build_sched(e, P);
+    if ((int) S.size() > s.scratch_sched_cap) {
+        const int cap = (int) S.size() + 256;
+        WSched * p = e->dalloc<WSched>(cap, false);
+        if (!p) return e->fail("out of device memory for program schedule");
+        s.scratch_sched = p; s.scratch_sched_cap = cap;
+    }
     QTTS_CUDA(cudaMemcpyAsync(s.scratch_prog, P.data(), P.size() * sizeof(Op), cudaMemcpyHostToDevice, e->stream));
-    QTTS_CUDA(cudaStreamSynchronize(e->stream));   // P may be freed by the caller right after
-    return run_device_program(e, s, s.scratch_prog, &P, (int) P.size(), n_frames, check_done);
+    if (!S.empty())
+        QTTS_CUDA(cudaMemcpyAsync(s.scratch_sched, S.data(), S.size() * sizeof(WSched), cudaMemcpyHostToDevice, e->stream));
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));   // P / S may be freed by the caller right after
+    return run_device_program(e, s, s.scratch_prog, &P, (int) P.size(), s.scratch_sched, (int) S.size(), n_frames, check_done);
 }
 
 }  // namespace qtts

@@ -178,10 +178,11 @@ static bool alloc_slot(Engine * e, Slot & s) {
     s.logits = e->dalloc<float>(c.codec_vocab_size);
     s.hidden = e->dalloc<float>(H);
     s.in_embd = e->dalloc<float>(H);
-    s.cp_x = e->dalloc<float>(maxH);
-    s.cp_qkv = e->dalloc<float>(cqkvw);
-    s.cp_attn = e->dalloc<float>((size_t) c.cp_n_heads * kHeadDim);
-    s.cp_act = e->dalloc<float>(c.cp_intermediate_size);
+    // code-predictor activations hold two tokens (positions 0 and 1 run as one pass)
+    s.cp_x = e->dalloc<float>(2 * (size_t) maxH);
+    s.cp_qkv = e->dalloc<float>(2 * (size_t) cqkvw);
+    s.cp_attn = e->dalloc<float>(2 * (size_t) c.cp_n_heads * kHeadDim);
+    s.cp_act = e->dalloc<float>(2 * (size_t) c.cp_intermediate_size);
     s.cp_logits = e->dalloc<float>(c.cp_vocab_size);
     s.cp_hidden_in = e->dalloc<float>(H);
     s.cp_dump = e->dalloc<float>((size_t) 16 * c.cp_vocab_size);
@@ -193,7 +194,8 @@ static bool alloc_slot(Engine * e, Slot & s) {
     s.vc = e->dalloc<__half>(kvn);
     s.cp_kc = e->dalloc<__half>((size_t) c.cp_layers * 16 * ckvw);
     s.cp_vc = e->dalloc<__half>((size_t) c.cp_layers * 16 * ckvw);
-    s.cp_kv0 = e->dalloc<float>((size_t) c.cp_layers * 2 * ckvw);
+    s.attn_part = e->dalloc<float>((size_t) c.n_heads * kMaxSplits * kPartStride);
+    s.attn_cnt = e->dalloc<unsigned int>(c.n_kv_heads);
     s.prefill = e->dalloc<float>((size_t) 64 * H);
     s.trailing = e->dalloc<float>((size_t) (e->max_text + 1) * H);
     s.pad = e->dalloc<float>(H);
@@ -218,6 +220,11 @@ static bool alloc_slot(Engine * e, Slot & s) {
     s.frame_prog = e->dalloc<Op>(s.frame_host.size(), false);
     if (!s.frame_prog) return e->fail("out of device memory for frame program");
     QTTS_CUDA(cudaMemcpy(s.frame_prog, s.frame_host.data(), s.frame_host.size() * sizeof(Op), cudaMemcpyHostToDevice));
+    const std::vector<WSched> S = build_sched(e, s.frame_host);
+    s.frame_sched_n = (int) S.size();
+    s.frame_sched = e->dalloc<WSched>(S.size(), false);
+    if (!s.frame_sched) return e->fail("out of device memory for frame schedule");
+    QTTS_CUDA(cudaMemcpy(s.frame_sched, S.data(), S.size() * sizeof(WSched), cudaMemcpyHostToDevice));
     return true;
 }
 
@@ -232,6 +239,7 @@ bool engine_finalize(Engine * e) {
         if (k % 256 != 0) return e->fail("feature dimensions must be multiples of 256");
     e->d_inexact = e->dalloc<unsigned long long>(1);
     e->bar = e->dalloc<GridBarrier>(1);
+    e->prof = e->dalloc<unsigned long long>(64 + 4 * 256);
     if (!e->d_inexact || !e->bar) return e->fail("out of device memory");
 
     const Dims T{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};

@@ -40,7 +40,7 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_finalize", "qtts_weight_stats", "qtts_set_numerics", "qtts_set_persistent", "qtts_set_ignore_eos",
            "qtts_clear_kv_cache", "qtts_build_prefill", "qtts_forward_prefill", "qtts_forward_step",
            "qtts_predict_codes", "qtts_generate", "qtts_stream_begin", "qtts_step_frames",
-           "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
+           "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
 
 _lib = None
 
@@ -77,6 +77,9 @@ def load_library(path: str | None = None):
                                   vp, i32p, FRAME_CB, i32, vp]
     lib.qtts_stream_begin.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64]
     lib.qtts_step_frames.argtypes = [vp, i32, vp, vp, vp]
+    lib.qtts_profile.argtypes = [vp, C.c_int, vp]
+    lib.qtts_debug_barrier_us.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.qtts_debug_barrier_us.restype = C.c_double
     lib.qtts_launch_count.argtypes = [vp]
     lib.qtts_launch_count.restype = C.c_int64
     lib.qtts_last_loop_ms.argtypes = [vp]
@@ -168,6 +171,15 @@ class TTSTransformer:
         out = (C.c_int64 * 4)()
         self._lib.qtts_weight_stats(self._h, out)
         return {"n_weights": out[0], "n_not_bf16_exact": out[1], "weight_bytes": out[2], "kv_bytes": out[3]}
+
+    def profile(self, on):
+        """Read-and-clear the stage cycle counters (see qtts_profile), then switch profiling."""
+        out = np.zeros(64 + 4 * 256, np.uint64)
+        self._lib.qtts_profile(self._h, int(on), _ptr(out))
+        names = ["gemv", "attn", "sample_cb0", "sample_cp", "frame_end", "copy"]
+        d = {n: out[i * 8:(i + 1) * 8].tolist() for i, n in enumerate(names)}
+        d["per_cta"] = out[64:].reshape(256, 4)
+        return d
 
     def launch_count(self) -> int:
         return int(self._lib.qtts_launch_count(self._h))
