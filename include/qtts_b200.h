@@ -39,7 +39,7 @@ typedef struct qtts_config {
 
 /* tensor element types accepted by qtts_upload_tensor (GGUF stores 2-D as F16, 1-D as F32:
  * scripts/convert_tts_to_gguf.py:289-297) */
-enum { QTTS_F32 = 0, QTTS_F16 = 1 };
+enum { QTTS_F32 = 0, QTTS_F16 = 1, QTTS_BF16 = 2 };
 
 /* numerics modes (see DESIGN.md "Numerics"):
  *   REFERENCE: reproduces the rounding points of the reference's ggml-cpu execution, including
@@ -145,6 +145,17 @@ int qtts_stream_begin(qtts_engine * e, int slot, const int32_t * text_tokens, in
 int qtts_step_frames(qtts_engine * e, int32_t n_frames, int32_t * codes_out,
                      int32_t * produced, int32_t * active);
 
+/* 1 (default): qtts_step_frames advances all active streams in lock step with the batched tcgen05
+ * kernel (groups of <= 128 slots); 0: the batch-1 kernel, one stream after another. */
+int qtts_set_batched(qtts_engine * e, int on);
+/* B-operand (weight) element type of the batched kernel's tensor-core GEMMs: QTTS_BF16 (default) or
+ * QTTS_F16 (the GGUF file's own type; activations are F16 either way, as in the reference's
+ * ggml_mul_mat).  Must be called before qtts_finalize. */
+int qtts_set_batched_weight_format(qtts_engine * e, int fmt);
+/* parity hook: processed codebook-0 logits [V] (after suppress / penalty / EOS ramp) and, batched
+ * mode only, the 15 code-predictor logit vectors [15*cp_vocab] of the LAST frame of `slot`. */
+int qtts_stream_logits(qtts_engine * e, int slot, float * cb0_out, float * cp_out);
+
 /* ---- instrumentation -------------------------------------------------------------------- */
 /* stage profiler: CTA 0 of the frame kernel accumulates SM-clock cycles per op type
  * (0 GEMV, 1 ATTN, 2 SAMPLE_CB0, 3 SAMPLE_CP, 4 FRAME_END, 5 COPY): out64[type*8 + {0 count,
@@ -154,6 +165,16 @@ int qtts_step_frames(qtts_engine * e, int32_t n_frames, int32_t * codes_out,
 int qtts_profile(qtts_engine * e, int on, uint64_t * out64);
 /* instrumentation: microseconds per grid-wide barrier of `variant` (see csrc/qtts_microbench.cu) */
 double qtts_debug_barrier_us(int device, int variant, int iters);
+/* batched kernel stage timers (CTA 0, SM clock cycles): out64[(2*type + 8*f16_input)*4 + {0 count,
+ * 1 stage cycles, 2 barrier cycles}], type 0 GEMM, 1 code-predictor attention, 2 Talker attention,
+ * 3 sampling; cleared after the read. */
+int qtts_batched_profile(qtts_engine * e, int on, uint64_t * out64);
+/* unit test of ONE projection stage of the batched kernel on caller-supplied operands: W [rows][K],
+ * X [n_tok*n_streams][K] (F32 on the host; W rounded to BF16, X to F16 when in_f16).  norm_w, res,
+ * bias, ssq_out may be NULL.  epi: 0 store, 1 +res, 2 SwiGLU (out [rows_act][rows/2]), 3 +bias. */
+int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int rows, int K, int epi, int in_f16,
+                     const float * W, const float * X, const float * norm_w, const float * res, const float * bias,
+                     float eps, float * out, float * ssq_out);
 /* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
 int64_t qtts_launch_count(const qtts_engine * e);
 /* device time (ms, CUDA events on the engine's stream) of the last qtts_generate /

@@ -4,5 +4,6 @@ Only the hot path of syb0rg/qwen3-tts-jetson lives here: csrc/ (CUDA kernels + C
 host-side mirror of the reference's TTSTransformer interface (transformer.py).  The directory
 name is not a Python identifier; import it through `qtts_pkg.load()` at the repo root.
 """
-from .transformer import TTSTransformer, load_library, EXPORTS, NUMERICS_FAST, NUMERICS_REFERENCE  # noqa: F401
+from .transformer import (TTSTransformer, load_library, debug_bgemm, EXPORTS, NUMERICS_FAST,  # noqa: F401
+                          NUMERICS_REFERENCE, F32, F16, BF16, EPI_STORE, EPI_ADD, EPI_SWIGLU, EPI_BIAS)
 from . import build, gguf_io, synth  # noqa: F401

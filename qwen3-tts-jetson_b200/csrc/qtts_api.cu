@@ -8,6 +8,7 @@ using namespace qtts;
 namespace qtts {
 extern "C" __global__ void qtts_run_program(const Op * ops, int n_ops, StreamState * st, GridBarrier * bar,
                                             int n_frames, RunCfg cfg);
+extern "C" __global__ void qtts_run_batched(BRun run);
 }
 
 struct qtts_engine { Engine e; };
@@ -320,44 +321,189 @@ int qtts_stream_begin(qtts_engine * h, int slot, const int32_t * tokens, int32_t
     return stream_begin(e, *s, tokens, n, speaker, max_len, language_id, rep_pen, temperature, top_k, seed) ? 1 : 0;
 }
 
-// v1: streams are advanced one after another with the batch-1 frame kernel (weights re-streamed
-// per stream); the batched tcgen05 path replaces this loop.
+// Batched mode (default): all active streams of a group of <= 128 slots advance in lock step inside
+// ONE launch of the tcgen05 frame kernel (qtts_batched.cu), weights streamed once per frame for the
+// whole group.  Sequential mode (qtts_set_batched(e, 0)): the batch-1 kernel, one stream after
+// another (kept as the A/B reference of the parity tests).
 int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int32_t * produced, int32_t * active) {
     Engine * e = &h->e;
     if (!e->finalized) { e->err = "engine not finalized"; return 0; }
     cudaSetDevice(e->device);
     const int nb = e->cfg.n_codebooks;
-    std::vector<int> before(e->slots.size(), 0);
+    const size_t ns = e->slots.size();
+    std::vector<StreamState> hs0(ns), hs1(ns);
+    if (cudaMemcpyAsync(hs0.data(), e->bb.st, ns * sizeof(StreamState), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
+        cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = "step_frames: state read failed"; return 0; }
     cudaEventRecord(e->ev0, e->stream);
-    for (size_t i = 0; i < e->slots.size(); ++i) {
+    if (e->batched && e->batched_ready) {
+        for (auto & G : e->groups) if (!run_batched_group(e, G, n_frames)) return 0;
+    } else {
+        for (size_t i = 0; i < ns; ++i) {
+            Slot & s = e->slots[i];
+            if (!s.active) continue;
+            if (!run_device_program(e, s, s.frame_prog, &s.frame_host, s.frame_prog_n, s.frame_sched, s.frame_sched_n, n_frames, true)) return 0;
+        }
+    }
+    cudaEventRecord(e->ev1, e->stream);
+    if (cudaMemcpyAsync(hs1.data(), e->bb.st, ns * sizeof(StreamState), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
+        cudaStreamSynchronize(e->stream) != cudaSuccess) {
+        e->err = std::string("step_frames: ") + cudaGetErrorString(cudaGetLastError());
+        return 0;
+    }
+    for (size_t i = 0; i < ns; ++i) {
         Slot & s = e->slots[i];
         produced[i] = 0;
         if (!s.active) { active[i] = 0; continue; }
-        StreamState hs;
-        cudaMemcpyAsync(&hs, s.st, sizeof(hs), cudaMemcpyDeviceToHost, e->stream);
-        cudaStreamSynchronize(e->stream);
-        before[i] = hs.frame;
-        if (!run_device_program(e, s, s.frame_prog, &s.frame_host, s.frame_prog_n, s.frame_sched, s.frame_sched_n, n_frames, true)) return 0;
-    }
-    cudaEventRecord(e->ev1, e->stream);
-    for (size_t i = 0; i < e->slots.size(); ++i) {
-        Slot & s = e->slots[i];
-        if (!s.active) continue;
-        StreamState hs;
-        cudaMemcpyAsync(&hs, s.st, sizeof(hs), cudaMemcpyDeviceToHost, e->stream);
-        if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("step_frames: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
-        const int newf = hs.frame - before[i];
+        const int newf = hs1[i].frame - hs0[i].frame;
         produced[i] = newf;
         if (newf > 0)
-            cudaMemcpy(codes_out + ((size_t) i * n_frames) * nb, s.codes + (size_t) before[i] * nb,
-                       (size_t) newf * nb * sizeof(int32_t), cudaMemcpyDeviceToHost);
-        if (hs.done) s.active = false;
+            cudaMemcpyAsync(codes_out + ((size_t) i * n_frames) * nb, s.codes + (size_t) hs0[i].frame * nb,
+                            (size_t) newf * nb * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream);
+        if (hs1[i].done) s.active = false;
         active[i] = s.active ? 1 : 0;
     }
+    if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("step_frames: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e->ev0, e->ev1);
     e->last_loop_ms = ms;
     return 1;
+}
+
+int qtts_set_batched(qtts_engine * h, int on) { h->e.batched = on ? 1 : 0; return 1; }
+
+int qtts_set_batched_weight_format(qtts_engine * h, int fmt) {
+    Engine * e = &h->e;
+    if (e->finalized) { e->err = "weight format must be chosen before qtts_finalize"; return 0; }
+    if (fmt != QTTS_F16 && fmt != QTTS_BF16) { e->err = "unknown weight format"; return 0; }
+    e->bfmt = (fmt == QTTS_BF16) ? 1 : 0;
+    return 1;
+}
+
+int qtts_stream_logits(qtts_engine * h, int slot, float * cb0_out, float * cp_out) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    const qtts_config & c = e->cfg;
+    if (e->batched && e->batched_ready) {
+        BGroup & G = e->groups[slot / 128];
+        const int b = slot - G.s0;
+        if (cb0_out) cudaMemcpy(cb0_out, G.cb0_dump + (size_t) b * c.codec_vocab_size, c.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
+        if (cp_out)
+            for (int p = 0; p < c.n_codebooks - 1; ++p)
+                cudaMemcpy(cp_out + (size_t) p * c.cp_vocab_size, G.cp_dump + ((size_t) p * G.n + b) * c.cp_vocab_size,
+                           c.cp_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
+    } else {
+        if (cb0_out) cudaMemcpy(cb0_out, s->cb0_dump, c.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
+        if (cp_out) { e->err = "code-predictor logits of the last frame are only kept by the batched kernel"; return 0; }
+    }
+    if (cudaGetLastError() != cudaSuccess) { e->err = "stream_logits: copy failed"; return 0; }
+    return 1;
+}
+
+int qtts_batched_profile(qtts_engine * h, int on, uint64_t * out64) {
+    Engine * e = &h->e;
+    if (!e->finalized) { e->err = "engine not finalized"; return 0; }
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    if (out64) cudaMemcpy(out64, e->prof + 2048, 64 * sizeof(uint64_t), cudaMemcpyDeviceToHost);
+    cudaMemset(e->prof + 2048, 0, 64 * sizeof(uint64_t));
+    e->prof_on = on ? 1 : 0;
+    return 1;
+}
+
+// Runs ONE projection stage of the batched kernel on caller-supplied operands (unit test of the
+// tcgen05 path: descriptors, operand layouts, epilogues).  W [rows][K] and X [rows_act][K] are
+// F32 on the host (W is rounded to BF16, X to F16 when in_f16); norm_w / res / bias may be NULL.
+// out receives [rows_act][rows] floats (EPI_SWIGLU: [rows_act][rows/2]); ssq_out (may be NULL)
+// [rows_act][rows/16].
+int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int rows, int K, int epi, int in_f16,
+                     const float * W, const float * X, const float * norm_w, const float * res, const float * bias,
+                     float eps, float * out, float * ssq_out) {
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device >= n_dev) { g_create_err = "no CUDA device"; return 0; }
+    cudaSetDevice(device);
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    const int rows_act = n_streams * n_tok;
+    if (rows_act > kBMaxRows || n_tok < 1 || n_tok > 2 || rows % 16 || K % kKc) { g_create_err = "bgemm: bad shape"; return 0; }
+    Engine eng;
+    Engine * e = &eng;
+    e->device = device; e->n_sms = prop.multiProcessorCount; e->bfmt = (weight_fmt == QTTS_BF16) ? 1 : 0;
+    cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    auto cleanup = [&](int rc) {
+        cudaStreamSynchronize(e->stream);
+        for (void * p : e->allocs) cudaFree(p);
+        cudaStreamDestroy(e->stream);
+        if (!rc) g_create_err = e->err;
+        return rc;
+    };
+    if (cudaFuncSetAttribute(qtts_run_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess) {
+        e->err = "bgemm: cudaFuncSetAttribute failed"; return cleanup(0);
+    }
+    e->bar = e->dalloc<GridBarrier>(1);
+    const size_t nW = (size_t) rows * K, nX = (size_t) rows_act * K;
+    std::vector<__nv_bfloat16> wb(nW);
+    for (size_t i = 0; i < nW; ++i) wb[i] = __float2bfloat16_rn(W[i]);
+    __nv_bfloat16 * dW = e->dalloc<__nv_bfloat16>(nW, false);
+    cudaMemcpy(dW, wb.data(), nW * 2, cudaMemcpyHostToDevice);
+    TiledW T;
+    if (!tile_matrix(e, dW, rows, K, T)) return cleanup(0);
+    void * dX = nullptr;
+    if (in_f16) {
+        std::vector<__half> xh(nX);
+        for (size_t i = 0; i < nX; ++i) xh[i] = __float2half_rn(X[i]);
+        dX = e->dalloc<__half>(nX, false);
+        cudaMemcpy(dX, xh.data(), nX * 2, cudaMemcpyHostToDevice);
+    } else {
+        dX = e->dalloc<float>(nX, false);
+        cudaMemcpy(dX, X, nX * 4, cudaMemcpyHostToDevice);
+    }
+    const int outw = (epi == EPI_SWIGLU) ? rows / 2 : rows;
+    float * d_out = e->dalloc<float>((size_t) rows_act * rows);
+    __half * d_out16 = e->dalloc<__half>((size_t) rows_act * rows);
+    float * d_res = nullptr, * d_bias = nullptr, * d_norm = nullptr, * d_ssq_in = nullptr;
+    float * d_ssq = e->dalloc<float>((size_t) rows_act * (rows / 16));
+    if (res) { d_res = e->dalloc<float>((size_t) rows_act * rows, false); cudaMemcpy(d_res, res, (size_t) rows_act * rows * 4, cudaMemcpyHostToDevice); }
+    if (bias) { d_bias = e->dalloc<float>(rows, false); cudaMemcpy(d_bias, bias, rows * 4, cudaMemcpyHostToDevice); }
+    if (norm_w) {
+        d_norm = e->dalloc<float>(K, false); cudaMemcpy(d_norm, norm_w, K * 4, cudaMemcpyHostToDevice);
+        // sums of squares split over 4 partials to exercise the reduction
+        std::vector<float> ss((size_t) rows_act * 4, 0.f);
+        for (int r = 0; r < rows_act; ++r)
+            for (int k = 0; k < K; ++k) ss[(size_t) r * 4 + (k * 4) / K] += X[(size_t) r * K + k] * X[(size_t) r * K + k];
+        d_ssq_in = e->dalloc<float>(ss.size(), false); cudaMemcpy(d_ssq_in, ss.data(), ss.size() * 4, cudaMemcpyHostToDevice);
+    }
+    BOp o;
+    memset(&o, 0, sizeof(o));
+    o.type = BOP_GEMM; o.n_streams = n_streams; o.rows_act = rows_act; o.n_tok = n_tok;
+    o.flags = ssq_out ? BF_SSQ_OUT : 0;
+    o.Wt = T.p; o.rows = rows; o.K = K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = 5; o.kpp = T.kpp; o.n_pieces = T.n_pieces;
+    o.in_kind = in_f16 ? BIN_F16 : BIN_F32; o.in = dX; o.in_row_stride = K; o.in_tok_stride = n_streams * K;
+    o.norm_w = d_norm; o.ssq_in = d_ssq_in; o.n_parts_in = 4; o.eps = eps;
+    o.epi = epi; o.out32 = d_out; o.out16 = d_out16; o.res = d_res; o.bias = d_bias;
+    o.out_row_stride = outw; o.out_tok_stride = n_streams * outw; o.ssq_out = d_ssq;
+    BSched sc{T.p, T.n_tile * K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles, 5, 0};
+    BOp * d_ops = e->dalloc<BOp>(1, false);
+    BSched * d_sc = e->dalloc<BSched>(1, false);
+    StreamState * d_st = e->dalloc<StreamState>(n_streams);
+    int32_t * d_act = e->dalloc<int32_t>(n_streams);
+    cudaMemcpy(d_ops, &o, sizeof(o), cudaMemcpyHostToDevice);
+    cudaMemcpy(d_sc, &sc, sizeof(sc), cudaMemcpyHostToDevice);
+    // two "frames": the second pass exercises ring slot / barrier phase recycling
+    if (!launch_batched(e, d_ops, 1, d_sc, 1, d_st, d_act, n_streams, epi == EPI_ADD && res == nullptr ? 1 : 2, false)) return cleanup(0);
+    cudaError_t r = cudaStreamSynchronize(e->stream);
+    if (r != cudaSuccess) { e->err = std::string("bgemm: ") + cudaGetErrorString(r); return cleanup(0); }
+    if (epi == EPI_SWIGLU) {
+        std::vector<__half> oh((size_t) rows_act * outw);
+        cudaMemcpy(oh.data(), d_out16, oh.size() * 2, cudaMemcpyDeviceToHost);
+        for (size_t i = 0; i < oh.size(); ++i) out[i] = __half2float(oh[i]);
+    } else {
+        cudaMemcpy(out, d_out, (size_t) rows_act * outw * 4, cudaMemcpyDeviceToHost);
+    }
+    if (ssq_out) cudaMemcpy(ssq_out, d_ssq, (size_t) rows_act * (rows / 16) * 4, cudaMemcpyDeviceToHost);
+    return cleanup(1);
 }
 
 int qtts_profile(qtts_engine * h, int on, uint64_t * out64) {

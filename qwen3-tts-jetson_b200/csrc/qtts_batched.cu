@@ -1,0 +1,811 @@
+// qtts_batched.cu — the BATCHED frame kernel: all concurrent utterance streams of a GPU advance
+// in lock step inside ONE persistent cooperative launch (1 CTA per SM, 512 threads).
+//
+// Per frame the kernel walks the same stage list as the batch-1 kernel (qtts_kernels.cu), but
+//   * every projection is a GEMM  D[rows_act x n_tile] = A[rows_act x K] . W_tile[n_tile x K]^T  issued
+//     by ONE thread per CTA as tcgen05.mma (cta_group::1, kind::f16, M = 128, N = n_tile) with the
+//     FP32 accumulator in TMEM; A = the streams' F16-rounded activations (the reference's
+//     ggml_mul_mat rounding point, ggml/src/ggml-cpu/ggml-cpu.c:1229-1320), staged into shared memory
+//     by all threads in 128-column chunks (double buffered, RMSNorm applied on the way); W tiles
+//     are pre-arranged in HBM in the UMMA canonical layout and stream through a shared-memory
+//     ring with cp.async.bulk (TMA, 1-D) + mbarrier complete_tx, prefetched across stage and
+//     frame boundaries exactly like the batch-1 kernel's ring; ring slots are recycled by
+//     tcgen05.commit -> mbarrier; the epilogue reads TMEM with tcgen05.ld (32x32b.x16) and fuses
+//     residual add / SwiGLU / bias and the sum-of-squares partials the next RMSNorm needs;
+//   * weight tiles of one stage go to CTAs (cta_off + t) mod grid with cta_off rotating from
+//     stage to stage, so that the HBM stream is spread over all SMs across a frame although one
+//     stage has fewer tiles than SMs;
+//   * attention: code predictor = one warp per (stream, KV group) (<= 16 keys); Talker = one CTA
+//     pass per (stream, KV group) with FP32 softmax / P.V (the batch-1 kernel's ATTN_FAST numerics);
+//   * sampling / embedding / frame end run per stream, distributed over CTAs.
+// Reference behaviour reproduced: src/tts_transformer.cpp:2416-2560 (frame loop), :2153-2340 (code
+// predictor), :1376-1512 (Talker step), :2417-2499 (CB0 post-processing and sampling).
+#include "qtts_bops.cuh"
+
+namespace qtts {
+
+// ------------------------------------------------------------------------------------------
+// tcgen05 / TMEM wrappers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    // cute::UMMA::SmemDescriptor: start >> 4 [0,14), LBO >> 4 [16,30), SBO >> 4 [32,46), version 1 [46,48),
+    // layout type SWIZZLE_NONE [61,64) = 0
+    return (uint64_t) ((addr & 0x3FFFFu) >> 4) | ((uint64_t) (lbo_bytes >> 4) << 16) |
+           ((uint64_t) (sbo_bytes >> 4) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ void umma_f16_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t * bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                 :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float * v) {
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ bool mbar_test(uint64_t * bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// weight ring (one per CTA): piece number `seq` (counted from kernel start, in the CTA's own
+// consumption order) lives in slot seq % kBSlots; full[slot] completes by bytes (bulk copy),
+// empty[slot] by the tcgen05.commit that follows the last MMA reading the slot.
+// ------------------------------------------------------------------------------------------
+struct BRing {
+    unsigned char * base;
+    uint64_t * full, * empty;
+};
+
+struct BPrefetch {           // registers of the prefetcher thread
+    int32_t idx, frame, t, p;
+    int32_t n_tiles, n_pieces, tile_bytes, piece_bytes;
+    const unsigned char * W;
+    uint32_t seq;
+    uint64_t policy;
+    bool exhausted;
+};
+
+__device__ __forceinline__ int first_tile(int cta_off) {
+    const int G = (int) gridDim.x;
+    int f = ((int) blockIdx.x - cta_off) % G;
+    return f < 0 ? f + G : f;
+}
+
+// advance to the next piece of this CTA; false when the launch needs no more weights
+__device__ __forceinline__ bool bpf_advance(const BRun & run, BPrefetch & pf) {
+    if (pf.exhausted) return false;
+    if (pf.p >= pf.n_pieces) { pf.t += (int) gridDim.x; pf.p = 0; }
+    while (pf.t >= pf.n_tiles) {
+        if (++pf.idx >= run.n_sched) { pf.idx = 0; if (++pf.frame >= run.n_frames) { pf.exhausted = true; return false; } }
+        const int4 e0 = __ldg(reinterpret_cast<const int4 *>(run.sched + pf.idx));
+        const int4 e1 = __ldg(reinterpret_cast<const int4 *>(run.sched + pf.idx) + 1);
+        pf.W = reinterpret_cast<const unsigned char *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
+        pf.tile_bytes = e0.z; pf.piece_bytes = e0.w; pf.n_pieces = e1.x; pf.n_tiles = e1.y;
+        pf.t = first_tile(e1.z); pf.p = 0;
+    }
+    return true;
+}
+
+// issue the bulk copy of the next piece; blocking = wait for the slot to be recycled
+__device__ __forceinline__ bool bpf_issue(const BRun & run, BPrefetch & pf, const BRing & ring, bool blocking) {
+    if (!bpf_advance(run, pf)) return false;
+    const int slot = (int) (pf.seq % (uint32_t) kBSlots);
+    const uint32_t par = ((pf.seq / (uint32_t) kBSlots) & 1u) ^ 1u;
+    if (blocking) mbar_wait(ring.empty + slot, par);
+    else if (!mbar_test(ring.empty + slot, par)) return false;
+    const int off = pf.p * pf.piece_bytes;
+    const uint32_t bytes = (uint32_t) min(pf.piece_bytes, pf.tile_bytes - off);
+    mbar_expect_tx(ring.full + slot, bytes);
+    bulk_g2s(ring.base + (size_t) slot * kBSlotBytes, pf.W + (size_t) pf.t * pf.tile_bytes + off, bytes,
+             ring.full + slot, pf.policy);
+    pf.p++; pf.seq++;
+    return true;
+}
+__device__ __forceinline__ void bpf_poll(const BRun & run, BPrefetch & pf, const BRing & ring) {
+    while (bpf_issue(run, pf, ring, false)) {}
+}
+__device__ __forceinline__ void bpf_ensure(const BRun & run, BPrefetch & pf, const BRing & ring, uint32_t seq_needed) {
+    while ((int32_t) (pf.seq - seq_needed) <= 0) if (!bpf_issue(run, pf, ring, true)) break;
+}
+
+__device__ __forceinline__ void bgrid_barrier(const BRun & run, unsigned int & epoch, BPrefetch & pf, const BRing & ring) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        epoch += gridDim.x;
+        __threadfence();
+        atomicAdd(&run.bar->count, 1u);
+        unsigned int v;
+        do {
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&run.bar->count) : "memory");
+        } while ((int) (v - epoch) < 0);
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&run.bar->count) : "memory");
+    } else if (threadIdx.x == kPfThread) {
+        bpf_poll(run, pf, ring);
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------
+// BOP_GEMM
+// ------------------------------------------------------------------------------------------
+struct BCtx {                // uniform across the CTA's threads
+    uint32_t cons_seq;       // ring pieces consumed so far
+    uint32_t a_use[2];       // commits issued on abar[i]
+    uint32_t d_use;          // commits issued on dbar
+    uint32_t tmem_base;
+    uint64_t * abar, * dbar;
+    unsigned char * abuf;    // 2 x kABufBytes
+    float * scale;           // [kBMaxRows]
+};
+
+__device__ __forceinline__ int row_off(int r, int B, int row_stride, int tok_stride) {
+    const int t = (r >= B) ? 1 : 0;
+    return (r - t * B) * row_stride + t * tok_stride;
+}
+
+template <int IN_KIND> struct BLoad { static constexpr int NV = (IN_KIND == BIN_F32) ? 8 : 4; };
+
+// global -> registers for chunk (kc, mt)
+template <int IN_KIND>
+__device__ __forceinline__ void bload(const BOp & op, int kc, int mt, uint4 * v, float4 & nw) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (IN_KIND == BIN_F32) {
+        const float * in = reinterpret_cast<const float *>(op.in);
+        const int k = kc * kKc + lane * 4;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int r = mt * 128 + warp + 16 * i;
+            if (r < op.rows_act)
+                v[i] = __ldcg(reinterpret_cast<const uint4 *>(in + row_off(r, op.n_streams, op.in_row_stride, op.in_tok_stride) + k));
+        }
+        if (op.norm_w) nw = __ldg(reinterpret_cast<const float4 *>(op.norm_w + k));
+    } else {
+        const __half * in = reinterpret_cast<const __half *>(op.in);
+        const int k = kc * kKc + (lane & 15) * 8;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = mt * 128 + warp * 2 + (lane >> 4) + 32 * i;
+            if (r < op.rows_act)
+                v[i] = __ldcg(reinterpret_cast<const uint4 *>(in + row_off(r, op.n_streams, op.in_row_stride, op.in_tok_stride) + k));
+        }
+    }
+}
+
+// registers -> A buffer (F16, UMMA canonical K-major layout), RMSNorm applied for BIN_F32
+template <int IN_KIND>
+__device__ __forceinline__ void bstore(const BOp & op, const BCtx & cx, int kc, int mt, int buf, const uint4 * v, const float4 & nw,
+                                       bool write_hid) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char * A = cx.abuf + (size_t) buf * kABufBytes;
+    if (IN_KIND == BIN_F32) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int rl = warp + 16 * i, r = mt * 128 + rl;
+            if (r < op.rows_act) {
+                float x0 = __uint_as_float(v[i].x), x1 = __uint_as_float(v[i].y);
+                float x2 = __uint_as_float(v[i].z), x3 = __uint_as_float(v[i].w);
+                if (op.norm_w) {
+                    const float s = cx.scale[r];
+                    x0 = (x0 * s) * nw.x; x1 = (x1 * s) * nw.y; x2 = (x2 * s) * nw.z; x3 = (x3 * s) * nw.w;
+                    if (write_hid)
+                        *reinterpret_cast<float4 *>(op.hid_out + (size_t) r * op.K + kc * kKc + lane * 4) = make_float4(x0, x1, x2, x3);
+                }
+                const __half2 h0 = __floats2half2_rn(x0, x1), h1 = __floats2half2_rn(x2, x3);
+                uint2 pk;
+                pk.x = *reinterpret_cast<const uint32_t *>(&h0);
+                pk.y = *reinterpret_cast<const uint32_t *>(&h1);
+                *reinterpret_cast<uint2 *>(A + (rl >> 3) * kASbo + (lane >> 1) * kALbo + (rl & 7) * 16 + (lane & 1) * 8) = pk;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int rl = warp * 2 + (lane >> 4) + 32 * i, r = mt * 128 + rl;
+            if (r < op.rows_act)
+                *reinterpret_cast<uint4 *>(A + (rl >> 3) * kASbo + (lane & 15) * kALbo + (rl & 7) * 16) = v[i];
+        }
+    }
+}
+
+// epilogue of one 16-column group of one m-tile: thread = activation row
+__device__ __forceinline__ void bepilogue16(const BOp & op, int r, int n0, const float * acc, const float4 * side) {
+    const int B = op.n_streams;
+    if (op.epi == EPI_SWIGLU) {
+        // weight rows interleaved gate_i, up_i (qtts_weights.cu): out[n0/2 + i] = silu(acc[2i]) * acc[2i+1]
+        __half2 h[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            h[i] = __floats2half2_rn(silu_f(acc[4 * i]) * acc[4 * i + 1], silu_f(acc[4 * i + 2]) * acc[4 * i + 3]);
+        uint4 pk;
+        pk.x = *reinterpret_cast<const uint32_t *>(&h[0]); pk.y = *reinterpret_cast<const uint32_t *>(&h[1]);
+        pk.z = *reinterpret_cast<const uint32_t *>(&h[2]); pk.w = *reinterpret_cast<const uint32_t *>(&h[3]);
+        *reinterpret_cast<uint4 *>(op.out16 + row_off(r, B, op.out_row_stride, op.out_tok_stride) + (n0 >> 1)) = pk;
+        return;
+    }
+    float o[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        o[4 * i] = acc[4 * i]; o[4 * i + 1] = acc[4 * i + 1]; o[4 * i + 2] = acc[4 * i + 2]; o[4 * i + 3] = acc[4 * i + 3];
+        if (op.epi == EPI_ADD || op.epi == EPI_BIAS) {
+            o[4 * i] += side[i].x; o[4 * i + 1] += side[i].y; o[4 * i + 2] += side[i].z; o[4 * i + 3] += side[i].w;
+        }
+    }
+    float * out = op.out32 + row_off(r, B, op.out_row_stride, op.out_tok_stride) + n0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4 *>(out + 4 * i) = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+    if (op.flags & BF_SSQ_OUT) {
+        float ss = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) ss += o[i] * o[i];
+        op.ssq_out[(size_t) r * (op.rows >> 4) + (n0 >> 4)] = ss;
+    }
+}
+
+template <int IN_KIND>
+__device__ __noinline__ void bstage_gemm(const BOp & op, const BRun & run, BCtx & cx, BPrefetch & pf, const BRing & ring) {
+    constexpr int NV = BLoad<IN_KIND>::NV;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int G = (int) gridDim.x;
+    const int t_first = first_tile(op.cta_off);
+    if (t_first < op.n_tiles) {
+        const int m_tiles = (op.rows_act + 127) >> 7;
+        const int nkc = op.K / kKc;
+        const int steps = nkc * m_tiles;
+        const uint32_t idesc = run.idesc_base | ((uint32_t) (op.n_tile >> 3) << 17);
+        const bool write_hid = (op.hid_out != nullptr) && (t_first == 0);
+
+        // per-row RMSNorm scale from the producers' partial sums (double sum like ggml's rms_norm,
+        // ops.cpp:3738-3747)
+        if (IN_KIND == BIN_F32 && op.norm_w) {
+            if (tid < op.rows_act) {
+                double ss = 0.0;
+                const float * p = op.ssq_in + (size_t) tid * op.n_parts_in;
+                for (int i = 0; i < op.n_parts_in; i += 8) {
+                    float q[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) q[u] = (i + u < op.n_parts_in) ? __ldcg(p + i + u) : 0.f;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) ss += (double) q[u];
+                }
+                const float mean = (float) (ss / (double) op.K);
+                cx.scale[tid] = 1.0f / sqrtf(mean + op.eps);
+            }
+            __syncthreads();
+        }
+
+        for (int t = t_first; t < op.n_tiles; t += G) {
+            uint4 cur[NV], nxt[NV];
+            float4 nwc = make_float4(1.f, 1.f, 1.f, 1.f), nwn = nwc;
+            bload<IN_KIND>(op, 0, 0, cur, nwc);
+            if (tid == kPfThread) bpf_ensure(run, pf, ring, cx.cons_seq);
+            for (int s = 0; s < steps; ++s) {
+                const int kc = s / m_tiles, mt = s - kc * m_tiles;
+                const int buf = s & 1;
+                if (s + 1 < steps) {
+                    const int kc1 = (s + 1) / m_tiles, mt1 = (s + 1) - kc1 * m_tiles;
+                    bload<IN_KIND>(op, kc1, mt1, nxt, nwn);
+                }
+                if (cx.a_use[buf] > 0) mbar_wait(cx.abar + buf, (cx.a_use[buf] - 1) & 1u);
+                bstore<IN_KIND>(op, cx, kc, mt, buf, cur, nwc, write_hid);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncthreads();
+                const int kin = kc * kKc;
+                const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
+                const int kp = min(op.kpp, op.K - piece * op.kpp);
+                if (tid == 0) {
+                    tc_fence_after();
+                    const uint32_t seq = cx.cons_seq + (uint32_t) piece;
+                    const int slot = (int) (seq % (uint32_t) kBSlots);
+                    if (mt == 0 && koff == 0) mbar_wait(ring.full + slot, (seq / (uint32_t) kBSlots) & 1u);
+                    const uint32_t a0 = smem_u32(cx.abuf + (size_t) buf * kABufBytes);
+                    const uint32_t w0 = smem_u32(ring.base + (size_t) slot * kBSlotBytes) + (uint32_t) (koff >> 3) * 128u;
+                    const uint32_t d = cx.tmem_base + (uint32_t) (mt * op.n_tile);
+#pragma unroll
+                    for (int ks = 0; ks < kKc / 16; ++ks) {
+                        const uint64_t ad = umma_smem_desc(a0 + ks * 2 * kALbo, kALbo, kASbo);
+                        const uint64_t bd = umma_smem_desc(w0 + ks * 256, 128, (uint32_t) kp * 16u);
+                        umma_f16_ss(d, ad, bd, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+                    }
+                    umma_commit(cx.abar + buf);
+                    if (mt == m_tiles - 1 && koff + kKc == kp) umma_commit(ring.empty + slot);
+                    if (s == steps - 1) umma_commit(cx.dbar);
+                } else if (tid == kPfThread) {
+                    // the piece the NEXT step needs must be in flight before thread 0 waits for it
+                    const int kin1 = min(kin + kKc, op.K - kKc);
+                    bpf_ensure(run, pf, ring, cx.cons_seq + (uint32_t) (kin1 / op.kpp));
+                    bpf_poll(run, pf, ring);
+                }
+                cx.a_use[buf]++;
+#pragma unroll
+                for (int i = 0; i < NV; ++i) cur[i] = nxt[i];
+                nwc = nwn;
+            }
+            // ---- epilogue: warp w reads TMEM lanes 32*(w%4).. (its sub-partition), 16 columns per pass
+            const int q = warp & 3;
+            const int ncg = op.n_tile >> 4;
+            bool waited = false;
+            for (int cg = warp >> 2; cg < ncg; cg += 4) {
+                const int n0 = t * op.n_tile + cg * 16;
+                for (int mt = 0; mt < m_tiles; ++mt) {
+                    const int r = mt * 128 + q * 32 + lane;
+                    const bool valid = r < op.rows_act;
+                    float4 side[4];
+                    if (valid && op.epi == EPI_ADD) {
+                        const float * rs = op.res + row_off(r, op.n_streams, op.out_row_stride, op.out_tok_stride) + n0;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) side[i] = __ldcg(reinterpret_cast<const float4 *>(rs + 4 * i));
+                    } else if (op.epi == EPI_BIAS) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) side[i] = __ldg(reinterpret_cast<const float4 *>(op.bias + n0 + 4 * i));
+                    }
+                    if (!waited) { mbar_wait(cx.dbar, cx.d_use & 1u); tc_fence_after(); waited = true; }
+                    __syncwarp();
+                    float acc[16];
+                    tmem_ld16(cx.tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
+                    if (valid) bepilogue16(op, r, n0, acc, side);
+                }
+            }
+            cx.d_use++;
+            tc_fence_before();
+            __syncthreads();
+            cx.cons_seq += (uint32_t) op.n_pieces;
+        }
+    }
+    if ((op.flags & BF_INC_NPAST) && blockIdx.x == 0 && tid < op.n_streams) {
+        StreamState * st = run.st + tid;
+        if (run.active[tid] && !st->done) st->n_past += 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// BOP_ATTN_CP — one warp per (stream, KV group); lane holds dims lane + 32 j (j < 4), so the NEOX
+// pairs (i, i + 64) sit in one lane.  pair_f32: positions 0 and 1 in one pass with the all-F32
+// arithmetic of the reference's 2-token prefill graph (src/tts_transformer.cpp:1613-1626);
+// otherwise the step graph's F16 cache / F32 softmax / F16-rounded P (:1666-1827).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void warp_norm_rope(float * x, const float * w, const float * rope, int pos, float eps, int lane, bool do_norm) {
+    if (do_norm) {
+        double ss = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ss += (double) (x[j] * x[j]);
+        ss = warp_sum_d(ss);
+        const float mean = (float) (ss / (double) kHeadDim);
+        const float scale = 1.0f / sqrtf(mean + eps);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) x[j] = (x[j] * scale) * __ldg(w + lane + 32 * j);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const int i = lane + 32 * j;
+        const float c = __ldg(rope + ((size_t) pos * 64 + i) * 2), s = __ldg(rope + ((size_t) pos * 64 + i) * 2 + 1);
+        const float x0 = x[j], x1 = x[j + 2];
+        x[j] = x0 * c - x1 * s;
+        x[j + 2] = x0 * s + x1 * c;
+    }
+}
+
+__device__ __noinline__ void bstage_attn_cp(const BOp & op) {
+    const int lane = threadIdx.x & 31;
+    const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
+    const int B = op.n_streams, nkv = op.n_kv_heads, rep = op.n_heads / nkv;
+    const int kvw = nkv * kHeadDim;
+    for (int item = gw; item < B * nkv; item += nw) {
+        const int b = item / nkv, g = item - b * nkv;
+        __half * kc = op.kc + (size_t) b * op.kv_stream_stride;
+        __half * vc = op.vc + (size_t) b * op.kv_stream_stride;
+        float k0f[4], v0f[4];
+        for (int t = 0; t < op.n_tok; ++t) {
+            const int pos = op.pos + t;
+            const float * base = op.qkv + (size_t) (t * B + b) * op.qkvw;
+            float k[4], v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                k[j] = __ldcg(base + (size_t) (op.n_heads + g) * kHeadDim + lane + 32 * j);
+                v[j] = __ldcg(base + (size_t) (op.n_heads + nkv + g) * kHeadDim + lane + 32 * j);
+            }
+            warp_norm_rope(k, op.k_norm_w, op.rope, pos, op.eps, lane, op.k_norm_w != nullptr);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                kc[(size_t) pos * kvw + g * kHeadDim + lane + 32 * j] = __float2half_rn(k[j]);
+                vc[(size_t) pos * kvw + g * kHeadDim + lane + 32 * j] = __float2half_rn(v[j]);
+            }
+            if (op.pair_f32 && t == 0) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { k0f[j] = k[j]; v0f[j] = v[j]; }
+            }
+            __syncwarp();
+            for (int r = 0; r < rep; ++r) {
+                const int h = g * rep + r;
+                float q[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) q[j] = __ldcg(base + (size_t) h * kHeadDim + lane + 32 * j);
+                warp_norm_rope(q, op.q_norm_w, op.rope, pos, op.eps, lane, op.q_norm_w != nullptr);
+                float o[4];
+                if (op.pair_f32) {
+                    if (t == 0) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) o[j] = v[j];      // softmax over one key = 1
+                    } else {
+                        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { s0 = fmaf(k0f[j], q[j], s0); s1 = fmaf(k[j], q[j], s1); }
+                        s0 = warp_sum(s0) * op.kq_scale; s1 = warp_sum(s1) * op.kq_scale;
+                        const float mx = fmaxf(s0, s1);
+                        const float e0 = expf(s0 - mx), e1 = expf(s1 - mx);
+                        const float inv = (float) (1.0 / ((double) e0 + (double) e1));
+                        const float p0 = e0 * inv, p1 = e1 * inv;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) o[j] = fmaf(v[j], p1, v0f[j] * p0);
+                    }
+                } else {
+                    // F16 Q, keys/values from the F16 cache (the current token included: just written)
+                    float qh[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) qh[j] = f16r(q[j]);
+                    const int n_kv = pos + 1;       // <= 16
+                    float sc[16];
+                    float mx = -CUDART_INF_F;
+#pragma unroll
+                    for (int jk = 0; jk < 16; ++jk) {
+                        float s = 0.f;
+                        if (jk < n_kv) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                s = fmaf(__half2float(kc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), qh[j], s);
+                        }
+                        s = warp_sum(s) * op.kq_scale;
+                        sc[jk] = s;
+                        if (jk < n_kv) mx = fmaxf(mx, s);
+                    }
+                    double sum = 0.0;
+#pragma unroll
+                    for (int jk = 0; jk < 16; ++jk) {
+                        const float e = (jk < n_kv) ? expf(sc[jk] - mx) : 0.f;
+                        sc[jk] = e;
+                        sum += (double) e;
+                    }
+                    const float inv = (float) (1.0 / sum);
+                    float part[4][4];
+#pragma unroll
+                    for (int pp = 0; pp < 4; ++pp)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) part[pp][j] = 0.f;
+#pragma unroll
+                    for (int jk = 0; jk < 16; ++jk) {
+                        if (jk < n_kv) {
+                            const float p = f16r(sc[jk] * inv);     // the P.V mul_mat rounds P to F16
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                part[jk & 3][j] = fmaf(__half2float(vc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), p, part[jk & 3][j]);
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) o[j] = (part[0][j] + part[1][j]) + (part[2][j] + part[3][j]);
+                }
+                __half * out = op.attn16 + (size_t) (t * B + b) * op.attn_w + (size_t) h * kHeadDim;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) out[lane + 32 * j] = __float2half_rn(o[j]);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// BOP_ATTN_TK — Talker decode attention, one CTA pass per (stream, KV group): QK-norm + NEOX RoPE
+// + F16 KV append, FP32 softmax and P.V over the F16 cache (ATTN_FAST numerics of qtts_kernels.cu).
+// ------------------------------------------------------------------------------------------
+template <int REP>
+__device__ void battn_tk_item(const Op & iop, const float * qkv, __half * out16, int pos, AttnSmem * sm, float * sc) {
+    const int tid = threadIdx.x;
+    const int n_kv = pos + 1, kvw = iop.n_kv_heads * kHeadDim;
+    const int g = iop.book;                      // KV group of this item (field reused)
+    const int stride = (n_kv + 3) & ~3;
+    attn_prepare(iop, qkv, g * REP, REP, g, pos, sm);
+    attn_append(iop, g, pos, kvw, sm);
+    attn_scores<REP>(iop, sm, g, kvw, pos, 0, n_kv, sc, stride);
+    __syncthreads();
+    float l[REP];
+#pragma unroll
+    for (int r = 0; r < REP; ++r) {
+        float mx = -CUDART_INF_F;
+        for (int j = tid; j < n_kv; j += kThreads) mx = fmaxf(mx, sc[r * stride + j]);
+        mx = block_max_f(mx, sm->redf);
+        double sum = 0.0;
+        for (int j = tid; j < n_kv; j += kThreads) {
+            const float e = __expf(sc[r * stride + j] - mx);
+            sc[r * stride + j] = e;
+            sum += (double) e;
+        }
+        sum = block_sum_d(sum, sm->red);
+        l[r] = (float) sum;
+    }
+    __syncthreads();
+    {
+        const int d = tid & (kHeadDim - 1), part = tid >> 7;
+        float acc[REP];
+#pragma unroll
+        for (int r = 0; r < REP; ++r) acc[r] = 0.f;
+        for (int j = part; j < n_kv; j += 4) {
+            const float v = __half2float((j < pos) ? __ldcg(iop.vcache + (size_t) j * kvw + g * kHeadDim + d) : sm->v16[d]);
+#pragma unroll
+            for (int r = 0; r < REP; ++r) acc[r] = fmaf(v, sc[r * stride + j], acc[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < REP; ++r) sm->part[part][r][d] = acc[r];
+    }
+    __syncthreads();
+    for (int idx = tid; idx < REP * kHeadDim; idx += kThreads) {
+        const int r = idx / kHeadDim, d = idx % kHeadDim;
+        const float o = (sm->part[0][r][d] + sm->part[1][r][d]) + (sm->part[2][r][d] + sm->part[3][r][d]);
+        const float lr = (r == 0) ? l[0] : l[REP - 1 < r ? REP - 1 : r];
+        out16[(size_t) (g * REP + r) * kHeadDim + d] = __float2half_rn(o / lr);
+    }
+    __syncthreads();
+}
+
+__device__ __noinline__ void bstage_attn_tk(const BOp & op, const BRun & run, unsigned char * scratch, Op * iop) {
+    AttnSmem * sm = reinterpret_cast<AttnSmem *>(scratch);
+    float * sc = reinterpret_cast<float *>(scratch + ((sizeof(AttnSmem) + 15) & ~(size_t) 15));
+    const int B = op.n_streams, nkv = op.n_kv_heads, rep = op.n_heads / nkv;
+    for (int item = blockIdx.x; item < B * nkv; item += gridDim.x) {
+        const int b = item / nkv, g = item - b * nkv;
+        const int pos = __ldcg(&run.st[b].n_past);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            iop->n_heads = op.n_heads; iop->n_kv_heads = nkv;
+            iop->q_norm_w = op.q_norm_w; iop->k_norm_w = op.k_norm_w;
+            iop->eps = op.eps; iop->rope = op.rope; iop->mode = ATTN_FAST; iop->kq_scale = op.kq_scale;
+            iop->kcache = op.kc + (size_t) b * op.kv_stream_stride;
+            iop->vcache = op.vc + (size_t) b * op.kv_stream_stride;
+            iop->book = g;
+        }
+        __syncthreads();
+        const float * qkv = op.qkv + (size_t) b * op.qkvw;
+        __half * out16 = op.attn16 + (size_t) b * op.attn_w;
+        if (rep == 1)      battn_tk_item<1>(*iop, qkv, out16, pos, sm, sc);
+        else if (rep == 2) battn_tk_item<2>(*iop, qkv, out16, pos, sm, sc);
+        else               battn_tk_item<4>(*iop, qkv, out16, pos, sm, sc);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// BOP_SAMPLE — per stream (CTA b mod grid): logits post-processing + sampling
+// (src/tts_transformer.cpp:2417-2499 for codebook 0, :2198-2236 for the code predictor), then the
+// embedding rows of the NEXT pass, and for the last codebook the frame end (:2500-2527) and the
+// next Talker input sum (:2529-2553).
+// ------------------------------------------------------------------------------------------
+__device__ __noinline__ void bstage_sample(const BOp & op, const BRun & run, unsigned char * scratch, double * red) {
+    SampleSmem * sm = reinterpret_cast<SampleSmem *>(scratch);
+    float * pbuf = reinterpret_cast<float *>(scratch + ((sizeof(SampleSmem) + 15) & ~(size_t) 15));
+    const int B = op.n_streams, n = op.n_vocab, tid = threadIdx.x;
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+        StreamState * st = run.st + b;
+        __syncthreads();
+        const bool live = run.active[b] && !__ldcg(&st->done);
+        const int frame = __ldcg(&st->frame);
+        const float temperature = st->temperature;
+        const int top_k = st->top_k;
+        const float * lg = op.logits + (size_t) b * op.logits_stride;
+        int tok;
+        if (op.kind == 0) {
+            const float rep = st->rep_pen;
+            for (int i = tid; i < n; i += kThreads) {
+                float v = __ldcg(lg + i);
+                if (i >= op.suppress_start && i != op.eos_id) v = -CUDART_INF_F;
+                if (rep != 1.0f && ((__ldcg(&st->seen[i >> 5]) >> (i & 31)) & 1u)) v = (v > 0.0f) ? v / rep : v * rep;
+                sm->l[i] = v;
+            }
+            __syncthreads();
+            const int expected = max(20, st->n_text_tokens * 4);
+            if (frame >= expected) {
+                float mx = -CUDART_INF_F;
+                for (int i = tid; i < n; i += kThreads) mx = fmaxf(mx, sm->l[i]);
+                mx = block_max_f(mx, sm->redf);
+                if (tid == 0) {
+                    const float ramp = fminf(1.0f, (float) (frame - expected) / (float) expected);
+                    const float target = mx + 5.0f;
+                    sm->l[op.eos_id] += ramp * (target - sm->l[op.eos_id]);
+                }
+                __syncthreads();
+            }
+            if (op.dump) for (int i = tid; i < n; i += kThreads) op.dump[(size_t) b * op.dump_stride + i] = sm->l[i];
+            const int ignore_eos = st->ignore_eos;
+            if (ignore_eos) {
+                if (tid == 0) sm->l[op.eos_id] = -CUDART_INF_F;
+                __syncthreads();
+            }
+            if (temperature <= 0.0f) tok = block_argmax(sm->l, n, sm);
+            else tok = block_sample(n, temperature, top_k, philox_uniform(st->seed, (uint32_t) frame, 0u, 0x0cb0u),
+                                    ignore_eos ? -1 : op.eos_id, sm, pbuf);
+            __syncthreads();
+            if (tid == 0 && live) {
+                if (tok == op.eos_id) { st->done = 1; st->eos = 1; }
+                else {
+                    st->cur_codes[0] = tok; st->feed_codes[0] = tok;
+                    st->seen[tok >> 5] |= 1u << (tok & 31);
+                }
+            }
+            // code-predictor input rows: token 0 = Talker hidden, token 1 = codec_embd[cb0]
+            const int feed = (live && tok != op.eos_id) ? tok : __ldcg(&st->feed_codes[0]);
+            const __half * row = op.table + (size_t) feed * op.xw;
+            double s0 = 0.0, s1 = 0.0;
+            for (int i = tid; i < op.xw; i += kThreads) {
+                const float h = __ldcg(op.hidden + (size_t) b * op.hidden_stride + i);
+                const float e = __half2float(row[i]);
+                op.x_out[(size_t) b * op.xw + i] = h;
+                op.x_out[(size_t) (B + b) * op.xw + i] = e;
+                s0 += (double) (h * h); s1 += (double) (e * e);
+            }
+            s0 = block_sum_d(s0, red);
+            s1 = block_sum_d(s1, red);
+            if (tid == 0) { op.ssq_e[b] = (float) s0; op.ssq_e[B + b] = (float) s1; }
+        } else {
+            for (int i = tid; i < n; i += kThreads) {
+                const float v = __ldcg(lg + i);
+                sm->l[i] = v;
+                if (op.dump) op.dump[(size_t) b * op.dump_stride + i] = v;
+            }
+            __syncthreads();
+            if (temperature <= 0.0f) tok = block_argmax(sm->l, n, sm);
+            else tok = block_sample(n, temperature, top_k, philox_uniform(st->seed, (uint32_t) frame, (uint32_t) op.book, 0x0c9du),
+                                    -1, sm, pbuf);
+            __syncthreads();
+            if (tid == 0) { st->cur_codes[op.book] = tok; st->feed_codes[op.book] = tok; }
+            if (op.book < op.n_books - 1) {
+                const __half * row = op.table + (size_t) tok * op.xw;
+                double s0 = 0.0;
+                for (int i = tid; i < op.xw; i += kThreads) {
+                    const float e = __half2float(row[i]);
+                    op.x_out[(size_t) b * op.xw + i] = e;
+                    s0 += (double) (e * e);
+                }
+                s0 = block_sum_d(s0, red);
+                if (tid == 0) op.ssq_e[b] = (float) s0;
+            } else {
+                // frame end + next Talker input
+                __syncthreads();
+                if (tid < op.n_books) sm->idx[tid] = (unsigned short) ((tid == op.book) ? tok : __ldcg(&st->cur_codes[tid]));
+                __syncthreads();
+                int f1 = frame;
+                if (live) {
+                    if (tid < op.n_books)
+                        op.codes_out[(size_t) b * op.codes_stride + (size_t) frame * op.n_books + tid] = (int32_t) sm->idx[tid];
+                    f1 = frame + 1;
+                    if (tid == 0) {
+                        st->frame = f1;
+                        if (f1 >= st->max_len) st->done = 1;
+                    }
+                }
+                const int ft = max(f1 - 1, 0);
+                const float * trow = (ft < st->trailing_len) ? op.trailing + (size_t) b * op.trailing_stride + (size_t) ft * op.xw
+                                                             : op.pad + (size_t) b * op.pad_stride;
+                const EmbedSumArgs * es = op.es;
+                double s0 = 0.0;
+                for (int i = tid; i < op.xw; i += kThreads) {
+                    float acc = __half2float(es->tables[0][(size_t) sm->idx[0] * op.xw + i]);
+                    for (int c = 1; c < es->n_books; ++c)
+                        acc += __half2float(es->tables[c][(size_t) sm->idx[c] * op.xw + i]);
+                    acc += __ldcg(trow + i);
+                    op.x_out[(size_t) b * op.xw + i] = acc;
+                    s0 += (double) (acc * acc);
+                }
+                s0 = block_sum_d(s0, red);
+                if (tid == 0) op.ssq_e[b] = (float) s0;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// the batched program runner
+// ------------------------------------------------------------------------------------------
+constexpr size_t kBSmemBytes = (size_t) kBSlots * kBSlotBytes + 2 * (size_t) kABufBytes;
+static_assert(sizeof(AttnSmem) + 64 + 2 * kMaxScores * sizeof(float) <= 2 * (size_t) kABufBytes, "attention scratch overlays the A buffers");
+static_assert(sizeof(SampleSmem) + 64 + kMaxVocab * sizeof(float) <= 2 * (size_t) kABufBytes, "sampling scratch overlays the A buffers");
+
+extern "C" __global__ void __launch_bounds__(kThreads, 1)
+qtts_run_batched(BRun run) {
+    extern __shared__ __align__(128) unsigned char bsm[];
+    __shared__ __align__(8) uint64_t full_bar[kBSlots], empty_bar[kBSlots], a_bar[2], d_bar;
+    __shared__ uint32_t tmem_slot;
+    __shared__ float scale_s[kBMaxRows];
+    __shared__ double red[kWarps];
+    __shared__ Op item_op;
+    __shared__ int all_done;
+
+    BRing ring;
+    ring.base = bsm; ring.full = full_bar; ring.empty = empty_bar;
+    BCtx cx;
+    cx.cons_seq = 0; cx.a_use[0] = cx.a_use[1] = 0; cx.d_use = 0;
+    cx.abar = a_bar; cx.dbar = &d_bar;
+    cx.abuf = bsm + (size_t) kBSlots * kBSlotBytes;
+    cx.scale = scale_s;
+    unsigned char * scratch = cx.abuf;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kBSlots; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); }
+        mbar_init(a_bar, 1); mbar_init(a_bar + 1, 1); mbar_init(&d_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&tmem_slot)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    cx.tmem_base = tmem_slot;
+
+    BPrefetch pf;
+    pf.idx = -1; pf.frame = 0; pf.t = 0; pf.p = 0; pf.n_tiles = 0; pf.n_pieces = 0; pf.tile_bytes = 0; pf.piece_bytes = 0;
+    pf.W = nullptr; pf.seq = 0; pf.policy = 0; pf.exhausted = (run.n_sched <= 0);
+    if (threadIdx.x == kPfThread) {
+        pf.policy = policy_evict_first();
+        bpf_poll(run, pf, ring);
+    }
+    unsigned int epoch = 0;
+
+    for (int f = 0; f < run.n_frames; ++f) {
+        if (run.check_done) {
+            // uniform across the grid: the states were published by the previous frame's barriers
+            if (threadIdx.x == 0) all_done = 1;
+            __syncthreads();
+            for (int b = threadIdx.x; b < run.n_streams; b += kThreads)
+                if (run.active[b] && !__ldcg(&run.st[b].done)) all_done = 0;
+            __syncthreads();
+            if (all_done) break;
+        }
+        for (int i = 0; i < run.n_ops; ++i) {
+            const BOp & op = run.ops[i];
+            const long long t0 = (run.prof && threadIdx.x == 0) ? clock64() : 0;
+            switch (op.type) {
+                case BOP_GEMM:
+                    if (op.in_kind == BIN_F32) bstage_gemm<BIN_F32>(op, run, cx, pf, ring);
+                    else                       bstage_gemm<BIN_F16>(op, run, cx, pf, ring);
+                    break;
+                case BOP_ATTN_CP: bstage_attn_cp(op); break;
+                case BOP_ATTN_TK: bstage_attn_tk(op, run, scratch, &item_op); break;
+                case BOP_SAMPLE:  bstage_sample(op, run, scratch, red); break;
+            }
+            const long long t1 = (run.prof && threadIdx.x == 0) ? clock64() : 0;
+            bgrid_barrier(run, epoch, pf, ring);
+            if (run.prof && threadIdx.x == 0 && blockIdx.x == 0) {
+                const long long t2 = clock64();
+                const int slot = op.type * 2 + ((op.type == BOP_GEMM && op.in_kind == BIN_F16) ? 8 : 0);
+                run.prof[slot * 4 + 0] += 1;
+                run.prof[slot * 4 + 1] += (unsigned long long) (t1 - t0);
+                run.prof[slot * 4 + 2] += (unsigned long long) (t2 - t1);
+            }
+        }
+    }
+    // drain: every bulk copy issued into this CTA's shared memory must land before it exits
+    __syncthreads();
+    if (threadIdx.x == kPfThread) {
+        for (uint32_t s = cx.cons_seq; s != pf.seq; ++s)
+            mbar_wait(full_bar + (s % (uint32_t) kBSlots), (s / (uint32_t) kBSlots) & 1u);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(cx.tmem_base), "r"(512));
+    }
+}
+
+}  // namespace qtts

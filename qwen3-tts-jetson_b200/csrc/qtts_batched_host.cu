@@ -1,0 +1,288 @@
+// qtts_batched_host.cu — host side of the batched frame kernel: load-time re-tiling of the
+// projection weights into the UMMA operand layout, the per-group frame program, the launcher.
+#include "qtts_engine.h"
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+namespace qtts {
+
+extern "C" __global__ void qtts_run_batched(BRun run);
+
+// src: BF16 [rows][K] row-major (the batch-1 kernel's fused layouts).  dst: for tile t (n_tile
+// rows) and piece p (kpp K-elements, the last one shorter), the piece is one contiguous block in
+// the K-major no-swizzle canonical layout: (row r, 8-element chunk c) at
+//   (r / 8) * (kp * 16) + c * 128 + (r % 8) * 16,  kp = K-extent of the piece.
+__global__ void k_tile_weights(const __nv_bfloat16 * __restrict__ src, unsigned char * __restrict__ dst,
+                               int rows, int K, int n_tile, int kpp, int to_f16) {
+    const size_t n_units = (size_t) rows * (K / 8);
+    for (size_t u = (size_t) blockIdx.x * blockDim.x + threadIdx.x; u < n_units; u += (size_t) gridDim.x * blockDim.x) {
+        const int r = (int) (u / (K / 8)), c = (int) (u % (K / 8));
+        const int t = r / n_tile, rr = r % n_tile;
+        const int k = c * 8, p = k / kpp, kin = k - p * kpp;
+        const int kp = min(kpp, K - p * kpp);
+        const size_t off = (size_t) t * n_tile * K * 2 + (size_t) p * n_tile * kpp * 2 +
+                           (size_t) (rr / 8) * (kp * 16) + (size_t) (kin / 8) * 128 + (size_t) (rr % 8) * 16;
+        uint4 v = *reinterpret_cast<const uint4 *>(src + (size_t) r * K + k);
+        if (to_f16) {
+            const __nv_bfloat16 * b = reinterpret_cast<const __nv_bfloat16 *>(&v);
+            __half h[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) h[i] = __float2half_rn(__bfloat162float(b[i]));
+            v = *reinterpret_cast<const uint4 *>(h);
+        }
+        *reinterpret_cast<uint4 *>(dst + off) = v;
+    }
+}
+
+static int pick_n_tile(int rows, int grid) {
+    const char * env = getenv("QTTS_NTILE");
+    if (env) { const int v = atoi(env); if (v >= 16 && v <= 96 && v % 16 == 0 && rows % v == 0) return v; }
+    int best = 16;
+    for (int nt = 16; nt <= 96; nt += 16) {
+        if (rows % nt) continue;
+        best = nt;
+        if (rows / nt <= grid) break;
+    }
+    return best;
+}
+
+bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T) {
+    if (rows % 16 || K % kKc) return e->fail("batched path: projection shape must be a multiple of 16 x 128");
+    T.rows = rows; T.K = K;
+    T.n_tile = pick_n_tile(rows, e->n_sms);
+    T.n_tiles = rows / T.n_tile;
+    int kpp = (kBSlotBytes / (T.n_tile * 2)) / kKc * kKc;
+    if (kpp > K) kpp = K;
+    T.kpp = kpp;
+    T.n_pieces = (K + kpp - 1) / kpp;
+    T.p = e->dalloc<unsigned char>((size_t) rows * K * 2, false);
+    if (!T.p) return e->fail("out of device memory for tiled weights");
+    k_tile_weights<<<1184, 256, 0, e->stream>>>(src, T.p, rows, K, T.n_tile, kpp, e->bfmt == 0 ? 1 : 0);
+    QTTS_CUDA(cudaGetLastError());
+    e->weight_bytes_batched += (int64_t) rows * K * 2;
+    return true;
+}
+
+static BOp bblank(int B) {
+    BOp o;
+    memset(&o, 0, sizeof(o));
+    o.n_streams = B; o.rows_act = B; o.n_tok = 1;
+    return o;
+}
+
+struct BEmit {
+    Engine * e;
+    std::vector<BOp> P;
+    std::vector<BSched> S;
+    int B, cta_off = 0;
+
+    void gemm(const TiledW & T, int rows_act, int in_kind, const void * in, int in_row_stride, int in_tok_stride,
+              const float * norm_w, const float * ssq_in, int n_parts_in, int epi, float * out32, __half * out16,
+              const float * res, const float * bias, int out_row_stride, int out_tok_stride, float * ssq_out,
+              float * hid_out = nullptr, int flags = 0) {
+        BOp o = bblank(B);
+        o.type = BOP_GEMM; o.rows_act = rows_act; o.flags = flags | (ssq_out ? BF_SSQ_OUT : 0);
+        o.Wt = T.p; o.rows = T.rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = cta_off;
+        o.kpp = T.kpp; o.n_pieces = T.n_pieces;
+        o.in_kind = in_kind; o.in = in; o.in_row_stride = in_row_stride; o.in_tok_stride = in_tok_stride;
+        o.norm_w = norm_w; o.ssq_in = ssq_in; o.n_parts_in = n_parts_in; o.eps = e->cfg.rms_norm_eps;
+        o.epi = epi; o.out32 = out32; o.out16 = out16; o.res = res; o.bias = bias;
+        o.out_row_stride = out_row_stride; o.out_tok_stride = out_tok_stride; o.ssq_out = ssq_out; o.hid_out = hid_out;
+        P.push_back(o);
+        S.push_back(BSched{T.p, T.n_tile * T.K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles, cta_off, 0});
+        cta_off = (cta_off + T.n_tiles) % e->n_sms;
+    }
+};
+
+// one decoder layer: QKV | attention | O (+res) | gate/up (SwiGLU) | down (+res)
+static void emit_blayer(BEmit & E, const TiledLayer & L, const LayerW & W, const Dims & D, int rows_act, int n_tok,
+                        float * x, float * qkv, __half * attn16, __half * act16, const float * ssq_first, int parts_first,
+                        float * ssq_p, BOp attn) {
+    const int B = E.B;
+    const int qkvw = (D.nh + 2 * D.nkv) * kHeadDim, aw = D.nh * kHeadDim, parts = D.H / 16;
+    E.gemm(L.qkv, rows_act, BIN_F32, x, D.H, B * D.H, W.attn_norm, ssq_first, parts_first, EPI_STORE,
+           qkv, nullptr, nullptr, nullptr, qkvw, B * qkvw, nullptr);
+    attn.qkv = qkv; attn.qkvw = qkvw; attn.q_norm_w = W.q_norm; attn.k_norm_w = W.k_norm;
+    attn.n_heads = D.nh; attn.n_kv_heads = D.nkv; attn.n_tok = n_tok; attn.rows_act = rows_act;
+    attn.attn16 = attn16; attn.attn_w = aw;
+    E.P.push_back(attn);
+    E.gemm(L.o, rows_act, BIN_F16, attn16, aw, B * aw, nullptr, nullptr, 0, EPI_ADD,
+           x, nullptr, x, nullptr, D.H, B * D.H, ssq_p);
+    E.gemm(L.gu, rows_act, BIN_F32, x, D.H, B * D.H, W.ffn_norm, ssq_p, parts, EPI_SWIGLU,
+           nullptr, act16, nullptr, nullptr, D.ffn, B * D.ffn, nullptr);
+    E.gemm(L.down, rows_act, BIN_F16, act16, D.ffn, B * D.ffn, nullptr, nullptr, 0, EPI_ADD,
+           x, nullptr, x, nullptr, D.H, B * D.H, ssq_p);
+}
+
+// frame program of the stream group [s0, s0 + B)
+static void emit_bframe(Engine * e, BGroup & G, BEmit & E) {
+    const qtts_config & c = e->cfg;
+    BatchBufs & bb = e->bb;
+    const int B = G.n, s0 = G.s0;
+    const int H = c.hidden_size, cpH = c.cp_hidden_size;
+    const Dims T{H, c.n_heads, c.n_kv_heads, c.intermediate_size};
+    const Dims C{cpH, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
+    const float eps = c.rms_norm_eps;
+    const float kq = 1.0f / sqrtf((float) kHeadDim);
+    const bool mtp = e->mtp != nullptr;
+    const int last = c.n_codebooks - 1;
+
+    BOp s = bblank(B);
+    s.type = BOP_SAMPLE; s.kind = 0; s.book = 0; s.n_books = c.n_codebooks;
+    s.logits = bb.logits + (size_t) s0 * c.codec_vocab_size; s.logits_stride = c.codec_vocab_size; s.n_vocab = c.codec_vocab_size;
+    s.eos_id = c.codec_eos_id; s.suppress_start = c.codec_vocab_size - 1024;
+    s.x_out = mtp ? G.emb : G.cp_x; s.xw = H; s.ssq_e = G.cp_ssq_e;
+    s.hidden = bb.hidden + (size_t) s0 * H; s.hidden_stride = H; s.table = e->codec_embd;
+    s.dump = G.cb0_dump; s.dump_stride = c.codec_vocab_size;
+    E.P.push_back(s);
+
+    for (int p = 1; p <= last; ++p) {
+        const int n_tok = (p == 1) ? 2 : 1, rows_act = n_tok * B;
+        const float * ssq_first = G.cp_ssq_e; int parts_first = 1;
+        if (mtp) {
+            // talker space -> code-predictor space (src/tts_transformer.cpp:1709-1715)
+            E.gemm(e->t_mtp, rows_act, BIN_F32, G.emb, H, B * H, nullptr, nullptr, 0, e->mtp_b ? EPI_BIAS : EPI_STORE,
+                   G.cp_x, nullptr, nullptr, e->mtp_b, cpH, B * cpH, G.cp_ssq_p);
+            ssq_first = G.cp_ssq_p; parts_first = cpH / 16;
+        }
+        for (int l = 0; l < c.cp_layers; ++l) {
+            BOp a = bblank(B);
+            a.type = BOP_ATTN_CP; a.rope = e->rope; a.eps = eps; a.kq_scale = kq;
+            a.pos = (p == 1) ? 0 : p; a.pair_f32 = (p == 1) ? 1 : 0;
+            a.kc = G.cp_kc + (size_t) l * 16 * C.nkv * kHeadDim; a.vc = G.cp_vc + (size_t) l * 16 * C.nkv * kHeadDim;
+            a.kv_stream_stride = (int64_t) c.cp_layers * 16 * C.nkv * kHeadDim;
+            emit_blayer(E, e->t_cp[l], e->cp[l], C, rows_act, n_tok, G.cp_x, G.cp_qkv, G.cp_attn16, G.cp_act16,
+                        l == 0 ? ssq_first : G.cp_ssq_p, l == 0 ? parts_first : cpH / 16, G.cp_ssq_p, a);
+        }
+        // the head reads the LAST token of the pass
+        E.gemm(e->t_lm_head[p - 1], B, BIN_F32, G.cp_x + (size_t) (n_tok - 1) * B * cpH, cpH, 0, e->cp_output_norm,
+               G.cp_ssq_p + (size_t) (n_tok - 1) * B * (cpH / 16), cpH / 16, EPI_STORE,
+               G.cp_logits, nullptr, nullptr, nullptr, c.cp_vocab_size, 0, nullptr);
+        BOp sp = bblank(B);
+        sp.type = BOP_SAMPLE; sp.kind = 1; sp.book = p; sp.n_books = c.n_codebooks;
+        sp.logits = G.cp_logits; sp.logits_stride = c.cp_vocab_size; sp.n_vocab = c.cp_vocab_size;
+        sp.xw = H;
+        sp.dump = G.cp_dump ? G.cp_dump + (size_t) (p - 1) * B * c.cp_vocab_size : nullptr; sp.dump_stride = c.cp_vocab_size;
+        if (p < last) {
+            sp.table = e->cp_embd[p - 1]; sp.x_out = mtp ? G.emb : G.cp_x; sp.ssq_e = G.cp_ssq_e;
+        } else {
+            sp.es = e->slots[s0].es; sp.x_out = G.x; sp.ssq_e = G.ssq_e;
+            sp.trailing = bb.trailing + (size_t) s0 * bb.trailing_stride; sp.trailing_stride = (int32_t) bb.trailing_stride;
+            sp.pad = bb.pad + (size_t) s0 * H; sp.pad_stride = H;
+            sp.codes_out = bb.codes + (size_t) s0 * bb.codes_stride; sp.codes_stride = (int32_t) bb.codes_stride;
+        }
+        E.P.push_back(sp);
+    }
+    for (int l = 0; l < c.n_layers; ++l) {
+        BOp a = bblank(B);
+        a.type = BOP_ATTN_TK; a.rope = e->rope; a.eps = eps; a.kq_scale = kq;
+        a.kc = bb.kc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
+        a.vc = bb.vc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
+        a.kv_stream_stride = (int64_t) bb.kv_slab;
+        emit_blayer(E, e->t_talker[l], e->talker[l], T, B, 1, G.x, G.qkv, G.attn16, G.act16,
+                    l == 0 ? G.ssq_e : G.ssq_p, l == 0 ? 1 : H / 16, G.ssq_p, a);
+    }
+    E.gemm(e->t_codec_head, B, BIN_F32, G.x, H, 0, e->output_norm, G.ssq_p, H / 16, EPI_STORE,
+           bb.logits + (size_t) s0 * c.codec_vocab_size, nullptr, nullptr, nullptr, c.codec_vocab_size, 0, nullptr,
+           bb.hidden + (size_t) s0 * H, BF_INC_NPAST);
+}
+
+uint32_t batched_idesc(const Engine * e) {
+    // cute::UMMA::InstrDescriptor: c_format F32 [4,6) = 1, a_format [7,10) F16 = 0, b_format [10,13)
+    // (F16 = 0 / BF16 = 1), a/b K-major (bits 15, 16 = 0), N >> 3 [17,23) (per stage), M >> 4 [24,29)
+    return (1u << 4) | (0u << 7) | ((uint32_t) (e->bfmt ? 1 : 0) << 10) | ((128u >> 4) << 24);
+}
+
+bool batched_init(Engine * e) {
+    const qtts_config & c = e->cfg;
+    if (cudaFuncSetAttribute(qtts_run_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess)
+        return e->fail(std::string("batched kernel: cudaFuncSetAttribute: ") + cudaGetErrorString(cudaGetLastError()));
+    int occ = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, qtts_run_batched, kThreads, kBSmemBytes);
+    if (occ < 1) return e->fail("batched kernel does not fit one CTA per SM");
+    const int rep = c.n_heads / c.n_kv_heads;
+    if (rep > kMaxRep || e->max_ctx * rep > 2 * kMaxScores) return e->fail("batched path: context too long for the attention scratch");
+    // tiled weights
+    e->t_talker.resize(c.n_layers); e->t_cp.resize(c.cp_layers); e->t_lm_head.resize(c.n_codebooks - 1);
+    auto layer = [&](const LayerW & W, const Dims & D, TiledLayer & L) {
+        return tile_matrix(e, W.wqkv, (D.nh + 2 * D.nkv) * kHeadDim, D.H, L.qkv) &&
+               tile_matrix(e, W.wo, D.H, D.nh * kHeadDim, L.o) &&
+               tile_matrix(e, W.wgu, 2 * D.ffn, D.H, L.gu) &&
+               tile_matrix(e, W.wdown, D.H, D.ffn, L.down);
+    };
+    const Dims T{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
+    const Dims C{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
+    for (int i = 0; i < c.n_layers; ++i) if (!layer(e->talker[i], T, e->t_talker[i])) return false;
+    for (int i = 0; i < c.cp_layers; ++i) if (!layer(e->cp[i], C, e->t_cp[i])) return false;
+    for (int i = 0; i < c.n_codebooks - 1; ++i)
+        if (!tile_matrix(e, e->lm_head[i], c.cp_vocab_size, c.cp_hidden_size, e->t_lm_head[i])) return false;
+    if (!tile_matrix(e, e->codec_head, c.codec_vocab_size, c.hidden_size, e->t_codec_head)) return false;
+    if (e->mtp && !tile_matrix(e, e->mtp, c.cp_hidden_size, c.hidden_size, e->t_mtp)) return false;
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));
+
+    // stream groups of at most 128 streams (the merged code-predictor pass has 2 rows per stream)
+    const int H = c.hidden_size, cpH = c.cp_hidden_size;
+    const int qkvw = (c.n_heads + 2 * c.n_kv_heads) * kHeadDim, cqkvw = (c.cp_n_heads + 2 * c.cp_n_kv_heads) * kHeadDim;
+    for (int s0 = 0; s0 < e->max_streams; s0 += 128) {
+        BGroup G;
+        G.s0 = s0; G.n = std::min(128, e->max_streams - s0);
+        const size_t B = (size_t) G.n;
+        G.x = e->dalloc<float>(B * H); G.qkv = e->dalloc<float>(B * qkvw);
+        G.attn16 = e->dalloc<__half>(B * c.n_heads * kHeadDim); G.act16 = e->dalloc<__half>(B * c.intermediate_size);
+        G.ssq_e = e->dalloc<float>(B); G.ssq_p = e->dalloc<float>(B * (H / 16));
+        G.emb = e->dalloc<float>(2 * B * H);
+        G.cp_x = e->dalloc<float>(2 * B * std::max(H, cpH)); G.cp_qkv = e->dalloc<float>(2 * B * cqkvw);
+        G.cp_attn16 = e->dalloc<__half>(2 * B * c.cp_n_heads * kHeadDim); G.cp_act16 = e->dalloc<__half>(2 * B * c.cp_intermediate_size);
+        G.cp_ssq_e = e->dalloc<float>(2 * B); G.cp_ssq_p = e->dalloc<float>(2 * B * (cpH / 16));
+        G.cp_logits = e->dalloc<float>(B * c.cp_vocab_size);
+        G.cp_kc = e->dalloc<__half>(B * c.cp_layers * 16 * c.cp_n_kv_heads * kHeadDim);
+        G.cp_vc = e->dalloc<__half>(B * c.cp_layers * 16 * c.cp_n_kv_heads * kHeadDim);
+        G.cb0_dump = e->dalloc<float>(B * c.codec_vocab_size);
+        G.cp_dump = e->dalloc<float>(B * 15 * c.cp_vocab_size);
+        G.active = e->dalloc<int32_t>(B);
+        if (!G.x || !G.qkv || !G.cp_x || !G.cp_qkv || !G.cp_logits || !G.cp_kc || !G.cp_vc || !G.cp_dump || !G.active)
+            return e->fail("out of device memory for the batched activations");
+        BEmit E{e, {}, {}, G.n, 0};
+        emit_bframe(e, G, E);
+        G.n_ops = (int) E.P.size(); G.n_sched = (int) E.S.size();
+        G.ops = e->dalloc<BOp>(E.P.size(), false);
+        G.sched = e->dalloc<BSched>(E.S.size(), false);
+        if (!G.ops || !G.sched) return e->fail("out of device memory for the batched program");
+        QTTS_CUDA(cudaMemcpy(G.ops, E.P.data(), E.P.size() * sizeof(BOp), cudaMemcpyHostToDevice));
+        QTTS_CUDA(cudaMemcpy(G.sched, E.S.data(), E.S.size() * sizeof(BSched), cudaMemcpyHostToDevice));
+        G.host_ops = E.P;
+        e->groups.push_back(G);
+    }
+    e->batched_ready = true;
+    return true;
+}
+
+bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_sched, int n_sched, StreamState * st,
+                    const int32_t * d_active, int n_streams, int n_frames, bool check_done) {
+    QTTS_CUDA(cudaMemsetAsync(&e->bar->count, 0, sizeof(unsigned int), e->stream));
+    BRun run;
+    memset(&run, 0, sizeof(run));
+    run.ops = d_ops; run.n_ops = n_ops; run.sched = d_sched; run.n_sched = n_sched;
+    run.st = st; run.active = d_active; run.bar = e->bar;
+    run.n_streams = n_streams; run.n_frames = n_frames; run.check_done = check_done ? 1 : 0;
+    run.idesc_base = batched_idesc(e);
+    run.prof = e->prof_on ? e->prof + 2048 : nullptr;
+    void * args[] = {(void *) &run};
+    QTTS_CUDA(cudaLaunchCooperativeKernel((const void *) qtts_run_batched, dim3(e->n_sms), dim3(kThreads), args,
+                                          kBSmemBytes, e->stream));
+    e->launches += 1;
+    return true;
+}
+
+bool run_batched_group(Engine * e, BGroup & G, int n_frames) {
+    std::vector<int32_t> act(G.n);
+    bool any = false;
+    for (int i = 0; i < G.n; ++i) { act[i] = e->slots[G.s0 + i].active ? 1 : 0; any |= act[i] != 0; }
+    if (!any) return true;
+    QTTS_CUDA(cudaMemcpyAsync(G.active, act.data(), act.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    return launch_batched(e, G.ops, G.n_ops, G.sched, G.n_sched, e->bb.st + G.s0, G.active, G.n, n_frames, true);
+}
+
+}  // namespace qtts

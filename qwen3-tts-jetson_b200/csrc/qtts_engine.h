@@ -8,6 +8,7 @@
 #include <vector>
 #include "../../include/qtts_b200.h"
 #include "qtts_ops.cuh"
+#include "qtts_bops.cuh"
 
 namespace qtts {
 
@@ -26,6 +27,34 @@ struct LayerW {
 };
 
 struct Dims { int H, nh, nkv, ffn; };
+
+// projection matrix re-tiled for the batched (tcgen05) kernel, see qtts_batched_host.cu
+struct TiledW { unsigned char * p = nullptr; int rows = 0, K = 0, n_tile = 0, n_tiles = 0, kpp = 0, n_pieces = 0; };
+struct TiledLayer { TiledW qkv, o, gu, down; };
+
+// per-stream buffers shared by the batch-1 and the batched kernels: one contiguous array over all
+// slots (slot i = base + i * stride), so the batched kernel indexes streams directly
+struct BatchBufs {
+    StreamState * st = nullptr;
+    float * logits = nullptr, * hidden = nullptr, * trailing = nullptr, * pad = nullptr;
+    __half * kc = nullptr, * vc = nullptr;
+    int32_t * codes = nullptr;
+    size_t kv_slab = 0, trailing_stride = 0, codes_stride = 0;
+};
+
+// one group of <= 128 streams advanced by one batched launch
+struct BGroup {
+    int s0 = 0, n = 0;
+    float * x = nullptr, * qkv = nullptr, * ssq_e = nullptr, * ssq_p = nullptr, * emb = nullptr;
+    __half * attn16 = nullptr, * act16 = nullptr;
+    float * cp_x = nullptr, * cp_qkv = nullptr, * cp_ssq_e = nullptr, * cp_ssq_p = nullptr, * cp_logits = nullptr;
+    __half * cp_attn16 = nullptr, * cp_act16 = nullptr, * cp_kc = nullptr, * cp_vc = nullptr;
+    float * cb0_dump = nullptr, * cp_dump = nullptr;
+    int32_t * active = nullptr;
+    BOp * ops = nullptr; int n_ops = 0;
+    BSched * sched = nullptr; int n_sched = 0;
+    std::vector<BOp> host_ops;
+};
 
 // per-slot device buffers
 struct Slot {
@@ -92,6 +121,16 @@ struct Engine {
     const __half * codec_embd = nullptr, * text_embd = nullptr;
     std::vector<const __half *> cp_embd;
     std::vector<Slot> slots;
+    // batched (tcgen05) path
+    int bfmt = 1;                 // B-operand (weight) format: 1 = BF16, 0 = F16
+    int batched = 1;              // qtts_step_frames uses the batched kernel
+    bool batched_ready = false;
+    int64_t weight_bytes_batched = 0;
+    BatchBufs bb;
+    std::vector<BGroup> groups;
+    std::vector<TiledLayer> t_talker, t_cp;
+    std::vector<TiledW> t_lm_head;
+    TiledW t_codec_head, t_mtp;
 
     bool fail(const std::string & m) { err = m; return false; }
     template <typename T> T * dalloc(size_t n, bool zero = true) {
@@ -126,6 +165,14 @@ bool run_program(Engine * e, Slot & s, const std::vector<Op> & P, int n_frames, 
 bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vector<Op> * host_ops, int n_ops,
                         const WSched * d_sched, int n_sched, int n_frames, bool check_done);
 std::vector<WSched> build_sched(Engine * e, const std::vector<Op> & P);
+
+// qtts_batched_host.cu
+bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T);
+bool batched_init(Engine * e);
+uint32_t batched_idesc(const Engine * e);
+bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_sched, int n_sched, StreamState * st,
+                    const int32_t * d_active, int n_streams, int n_frames, bool check_done);
+bool run_batched_group(Engine * e, BGroup & G, int n_frames);
 
 #define QTTS_CUDA(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
     e->err = std::string(#call) + ": " + cudaGetErrorString(_e); return false; } } while (0)

@@ -163,20 +163,21 @@ static bool single_bf16(Engine * e, const std::string & name, int64_t ne0, int64
     return true;
 }
 
-static bool alloc_slot(Engine * e, Slot & s) {
+static bool alloc_slot(Engine * e, Slot & s, int index) {
     const qtts_config & c = e->cfg;
     const int H = c.hidden_size, cpH = c.cp_hidden_size, E = c.text_embd_dim;
     const int qkvw = (c.n_heads + 2 * c.n_kv_heads) * kHeadDim;
     const int cqkvw = (c.cp_n_heads + 2 * c.cp_n_kv_heads) * kHeadDim;
     const int kvw = c.n_kv_heads * kHeadDim, ckvw = c.cp_n_kv_heads * kHeadDim;
     const int maxH = H > cpH ? H : cpH;
-    s.st = e->dalloc<StreamState>(1);
+    BatchBufs & bb = e->bb;
+    s.st = bb.st + index;
     s.x = e->dalloc<float>(maxH);
     s.qkv = e->dalloc<float>(qkvw);
     s.attn = e->dalloc<float>((size_t) c.n_heads * kHeadDim);
     s.act = e->dalloc<float>(c.intermediate_size);
-    s.logits = e->dalloc<float>(c.codec_vocab_size);
-    s.hidden = e->dalloc<float>(H);
+    s.logits = bb.logits + (size_t) index * c.codec_vocab_size;
+    s.hidden = bb.hidden + (size_t) index * H;
     s.in_embd = e->dalloc<float>(H);
     // code-predictor activations hold two tokens (positions 0 and 1 run as one pass)
     s.cp_x = e->dalloc<float>(2 * (size_t) maxH);
@@ -190,20 +191,20 @@ static bool alloc_slot(Engine * e, Slot & s) {
     s.uniforms = e->dalloc<float>((size_t) e->max_ctx + 16);
     s.forced = e->dalloc<int32_t>(16);
     const size_t kvn = (size_t) c.n_layers * e->max_ctx * kvw;
-    s.kc = e->dalloc<__half>(kvn);
-    s.vc = e->dalloc<__half>(kvn);
+    s.kc = bb.kc + (size_t) index * kvn;
+    s.vc = bb.vc + (size_t) index * kvn;
     s.cp_kc = e->dalloc<__half>((size_t) c.cp_layers * 16 * ckvw);
     s.cp_vc = e->dalloc<__half>((size_t) c.cp_layers * 16 * ckvw);
     s.attn_part = e->dalloc<float>((size_t) c.n_heads * kMaxSplits * kPartStride);
     s.attn_cnt = e->dalloc<unsigned int>(c.n_kv_heads);
     s.prefill = e->dalloc<float>((size_t) 64 * H);
-    s.trailing = e->dalloc<float>((size_t) (e->max_text + 1) * H);
-    s.pad = e->dalloc<float>(H);
+    s.trailing = bb.trailing + (size_t) index * bb.trailing_stride;
+    s.pad = bb.pad + (size_t) index * H;
     s.tp_tmp = e->dalloc<float>(E);
     s.misc = e->dalloc<float>((size_t) 16 * H);
     s.speaker = e->dalloc<float>(H);
     s.tokens = e->dalloc<int32_t>((size_t) e->max_text + 16);
-    s.codes = e->dalloc<int32_t>((size_t) e->max_ctx * c.n_codebooks);
+    s.codes = bb.codes + (size_t) index * bb.codes_stride;
     s.es = e->dalloc<EmbedSumArgs>(1);
     if (!s.es || !s.codes || !s.kc || !s.vc || !s.trailing) return e->fail("out of device memory for stream slots");
     e->kv_bytes += (int64_t) kvn * 2 * 2;
@@ -239,7 +240,7 @@ bool engine_finalize(Engine * e) {
         if (k % 256 != 0) return e->fail("feature dimensions must be multiples of 256");
     e->d_inexact = e->dalloc<unsigned long long>(1);
     e->bar = e->dalloc<GridBarrier>(1);
-    e->prof = e->dalloc<unsigned long long>(64 + 4 * 256);
+    e->prof = e->dalloc<unsigned long long>(4096);
     if (!e->d_inexact || !e->bar) return e->fail("out of device memory");
 
     const Dims T{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
@@ -300,8 +301,26 @@ bool engine_finalize(Engine * e) {
         if (!e->rope) return e->fail("out of device memory for rope table");
         QTTS_CUDA(cudaMemcpy(e->rope, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice));
     }
+    {   // per-stream buffers shared with the batched kernel: contiguous over the slots
+        BatchBufs & bb = e->bb;
+        const size_t n = (size_t) e->max_streams;
+        bb.kv_slab = (size_t) c.n_layers * e->max_ctx * c.n_kv_heads * kHeadDim;
+        bb.trailing_stride = (size_t) (e->max_text + 1) * c.hidden_size;
+        bb.codes_stride = (size_t) e->max_ctx * c.n_codebooks;
+        bb.st = e->dalloc<StreamState>(n);
+        bb.logits = e->dalloc<float>(n * c.codec_vocab_size);
+        bb.hidden = e->dalloc<float>(n * c.hidden_size);
+        bb.kc = e->dalloc<__half>(n * bb.kv_slab);
+        bb.vc = e->dalloc<__half>(n * bb.kv_slab);
+        bb.trailing = e->dalloc<float>(n * bb.trailing_stride);
+        bb.pad = e->dalloc<float>(n * c.hidden_size);
+        bb.codes = e->dalloc<int32_t>(n * bb.codes_stride);
+        if (!bb.st || !bb.logits || !bb.hidden || !bb.kc || !bb.vc || !bb.trailing || !bb.pad || !bb.codes)
+            return e->fail("out of device memory for stream slots");
+    }
     e->slots.resize(e->max_streams);
-    for (auto & s : e->slots) if (!alloc_slot(e, s)) return false;
+    for (int i = 0; i < e->max_streams; ++i) if (!alloc_slot(e, e->slots[i], i)) return false;
+    if (!batched_init(e)) return false;
     e->finalized = true;
     return true;
 }

@@ -18,6 +18,8 @@ from . import gguf_io
 
 NUMERICS_REFERENCE = 0
 NUMERICS_FAST = 1
+F32, F16, BF16 = 0, 1, 2
+EPI_STORE, EPI_ADD, EPI_SWIGLU, EPI_BIAS = 0, 1, 2, 3
 
 _CFG_INT_FIELDS = ["hidden_size", "n_layers", "n_heads", "n_kv_heads", "intermediate_size", "head_dim",
                    "codec_vocab_size", "n_codebooks", "cp_layers", "cp_vocab_size", "cp_hidden_size",
@@ -40,7 +42,8 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_finalize", "qtts_weight_stats", "qtts_set_numerics", "qtts_set_persistent", "qtts_set_ignore_eos",
            "qtts_clear_kv_cache", "qtts_build_prefill", "qtts_forward_prefill", "qtts_forward_step",
            "qtts_predict_codes", "qtts_generate", "qtts_stream_begin", "qtts_step_frames",
-           "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
+           "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
+           "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
 
 _lib = None
 
@@ -78,6 +81,11 @@ def load_library(path: str | None = None):
     lib.qtts_stream_begin.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64]
     lib.qtts_step_frames.argtypes = [vp, i32, vp, vp, vp]
     lib.qtts_profile.argtypes = [vp, C.c_int, vp]
+    lib.qtts_set_batched.argtypes = [vp, C.c_int]
+    lib.qtts_set_batched_weight_format.argtypes = [vp, C.c_int]
+    lib.qtts_stream_logits.argtypes = [vp, C.c_int, vp, vp]
+    lib.qtts_batched_profile.argtypes = [vp, C.c_int, vp]
+    lib.qtts_debug_bgemm.argtypes = [C.c_int] * 8 + [vp] * 5 + [C.c_float, vp, vp]
     lib.qtts_debug_barrier_us.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.qtts_debug_barrier_us.restype = C.c_double
     lib.qtts_launch_count.argtypes = [vp]
@@ -104,6 +112,7 @@ class TTSTransformer:
         self._err = ""
         self.device, self.max_streams, self.max_ctx = device, max_streams, max_ctx
         self.config: dict = {}
+        self.batched_weight_format = BF16    # B operand of the batched kernel's GEMMs (applied at load)
 
     # -- error handling (bool + get_error(), like the reference) --------------------------------
     def get_error(self) -> str:
@@ -136,6 +145,8 @@ class TTSTransformer:
             self._err = self._lib.qtts_create_error().decode()
             return False
         self._h = h
+        if not self._lib.qtts_set_batched_weight_format(self._h, int(self.batched_weight_format)):
+            return False
         for name, code, dims, arr in tensors:
             d = (C.c_int64 * len(dims))(*dims)
             if not self._lib.qtts_upload_tensor(self._h, name.encode(), code, d, len(dims), _ptr(arr)):
@@ -166,6 +177,26 @@ class TTSTransformer:
     def set_ignore_eos(self, on: bool) -> bool:
         """Benchmark switch (fixed-length utterances); not reference behaviour."""
         return bool(self._lib.qtts_set_ignore_eos(self._h, 1 if on else 0))
+
+    def set_batched(self, on: bool) -> bool:
+        """step_frames: batched tcgen05 kernel (default) or the batch-1 kernel stream after stream."""
+        return bool(self._lib.qtts_set_batched(self._h, 1 if on else 0))
+
+    def stream_logits(self, slot: int, want_cp: bool = True):
+        """Parity hook: processed cb0 logits and (batched mode) code-predictor logits of the last frame."""
+        cb0 = np.zeros(self.config["codec_vocab_size"], np.float32)
+        cp = np.zeros((self.config["n_codebooks"] - 1, self.config["cp_vocab_size"]), np.float32) if want_cp else None
+        if not self._lib.qtts_stream_logits(self._h, slot, _ptr(cb0), _ptr(cp)):
+            return None
+        return cb0, cp
+
+    def batched_profile(self, on: bool):
+        out = np.zeros(64, np.uint64)
+        self._lib.qtts_batched_profile(self._h, 1 if on else 0, _ptr(out))
+        o = out.reshape(16, 4)
+        names = {0: "gemm_f32in", 8: "gemm_f16in", 2: "attn_cp", 4: "attn_talker", 6: "sample"}
+        return {n: {"count": int(o[i, 0]), "stage_cycles": int(o[i, 1]), "barrier_cycles": int(o[i, 2])}
+                for i, n in names.items()}
 
     def weight_stats(self) -> dict:
         out = (C.c_int64 * 4)()
@@ -291,3 +322,24 @@ class TTSTransformer:
         if not self._lib.qtts_step_frames(self._h, n_frames, _ptr(codes), _ptr(produced), _ptr(active)):
             return None
         return codes, produced, active
+
+
+def debug_bgemm(W, X, n_tok: int = 1, epi: int = EPI_STORE, in_f16: bool = False, norm_w=None, res=None, bias=None,
+                eps: float = 1e-6, weight_fmt: int = BF16, device: int = 0, want_ssq: bool = False):
+    """One projection stage of the batched tcgen05 kernel on caller-supplied operands (qtts_debug_bgemm)."""
+    lib = load_library()
+    W = np.ascontiguousarray(W, np.float32)
+    X = np.ascontiguousarray(X, np.float32)
+    rows, K = W.shape
+    rows_act = X.shape[0]
+    assert X.shape[1] == K and rows_act % n_tok == 0
+    outw = rows // 2 if epi == EPI_SWIGLU else rows
+    out = np.zeros((rows_act, outw), np.float32)
+    ssq = np.zeros((rows_act, rows // 16), np.float32) if want_ssq else None
+    f = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    nw, rs, bs = f(norm_w), f(res), f(bias)
+    ok = lib.qtts_debug_bgemm(device, weight_fmt, rows_act // n_tok, n_tok, rows, K, epi, 1 if in_f16 else 0,
+                              _ptr(W), _ptr(X), _ptr(nw), _ptr(rs), _ptr(bs), eps, _ptr(out), _ptr(ssq))
+    if not ok:
+        raise RuntimeError("qtts_debug_bgemm: " + lib.qtts_create_error().decode())
+    return (out, ssq) if want_ssq else out

@@ -1,0 +1,187 @@
+"""GPU tests of the BATCHED frame kernel (qtts_batched.cu, tcgen05 / TMEM): (1) one projection
+stage on caller-supplied operands against numpy (operand layouts, descriptors, epilogues, ring and
+barrier recycling), (2) whole frames: streams advanced in lock step by the batched kernel against
+the same streams advanced one by one by the batch-1 kernel (which is itself pinned to the
+reference's golden vectors in test_gpu_parity.py) and against the golden ids directly.
+
+Tolerances: a projection output is an FP32 tensor-core accumulation of exact F16 x BF16 products, so
+against a float64 dot product of the same rounded operands |d| <= 2e-5 * sum|terms|; whole-frame
+logits against the batch-1 kernel NMSE <= 1e-5 (the stated BF16-level tolerance of
+test_gpu_parity.py); greedy ids exact over the first frames.
+"""
+import numpy as np
+import pytest
+
+from conftest import nmse
+from test_oracle import load_gold
+
+pytestmark = pytest.mark.gpu
+
+
+def f16r(x):
+    return np.asarray(x, np.float32).astype(np.float16).astype(np.float32)
+
+
+def ref_gemm(pkg, W, X, n_tok, epi, in_f16, norm_w, res, bias, eps):
+    Wb = pkg.synth.bf16_round(W.copy()) if True else W
+    X = np.asarray(X, np.float32)
+    if norm_w is not None and not in_f16:
+        ss = (X.astype(np.float32) ** 2).astype(np.float64).sum(axis=1)
+        scale = (1.0 / np.sqrt((ss / X.shape[1]).astype(np.float32) + np.float32(eps))).astype(np.float32)
+        X = (X * scale[:, None]) * norm_w[None, :].astype(np.float32)
+    A = f16r(X).astype(np.float64)
+    out = A @ Wb.astype(np.float64).T
+    mag = np.abs(A) @ np.abs(Wb.astype(np.float64)).T
+    if epi == 1:
+        out = out + res
+    elif epi == 3:
+        out = out + bias[None, :]
+    elif epi == 2:
+        g, u = out[:, 0::2], out[:, 1::2]
+        out = f16r(g / (1.0 + np.exp(-g)) * u).astype(np.float64)
+    return out, mag
+
+
+CASES = [
+    # n_streams, n_tok, rows, K, epi, in_f16, norm
+    (64, 1, 1024, 512, 0, False, True),
+    (100, 2, 256, 1024, 0, False, True),      # two m-tiles (200 activation rows)
+    (64, 1, 512, 3072, 1, True, False),       # down-projection shape: F16 input, + residual, multi-piece tiles
+    (37, 1, 2048, 512, 2, False, True),       # gate/up with SwiGLU -> F16 output
+    (8, 2, 512, 256, 3, False, False),        # + bias (mtp_proj)
+    (128, 1, 4096, 1024, 0, False, True),     # QKV shape of the 0.6B model, full group
+]
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "f16"])
+@pytest.mark.parametrize("case", CASES, ids=[f"s{c[0]}x{c[1]}_r{c[2]}_k{c[3]}_e{c[4]}" for c in CASES])
+def test_bgemm_stage(pkg, case, fmt):
+    n_streams, n_tok, rows, K, epi, in_f16, norm = case
+    r = np.random.default_rng(rows + K + n_streams)
+    W = pkg.synth.bf16_round((0.05 * r.standard_normal((rows, K))).astype(np.float32))
+    X = r.standard_normal((n_streams * n_tok, K)).astype(np.float32)
+    if in_f16:
+        X = f16r(X)
+    norm_w = (1.0 + 0.1 * r.standard_normal(K)).astype(np.float32) if norm else None
+    res = r.standard_normal((n_streams * n_tok, rows)).astype(np.float32) if epi == 1 else None
+    bias = r.standard_normal(rows).astype(np.float32) if epi == 3 else None
+    out, ssq = pkg.debug_bgemm(W, X, n_tok=n_tok, epi=epi, in_f16=in_f16, norm_w=norm_w, res=res, bias=bias,
+                               eps=1e-6, weight_fmt=pkg.BF16 if fmt == "bf16" else pkg.F16, want_ssq=True)
+    want, mag = ref_gemm(pkg, W, X, n_tok, epi, in_f16, norm_w, res, bias, 1e-6)
+    if epi == 2:      # F16-rounded output of a product of two accumulations
+        assert np.allclose(out, want, rtol=3e-3, atol=3e-4), np.abs(out - want).max()
+        return
+    err = np.abs(out - want)
+    assert (err <= 2e-5 * mag + 1e-6).all(), f"max err {err.max():.3e} at {np.unravel_index(err.argmax(), err.shape)}"
+    if True:
+        want_ssq = (want.astype(np.float32) ** 2).reshape(want.shape[0], rows // 16, 16).sum(axis=2)
+        assert np.allclose(ssq, want_ssq, rtol=1e-3, atol=1e-4)
+
+
+@pytest.fixture(scope="module")
+def engines(pkg, make_gguf):
+    cache = {}
+
+    def get(preset, max_streams, max_ctx=256, fmt=None):
+        key = (preset, max_streams, max_ctx, fmt)
+        if key not in cache:
+            path, cfg = make_gguf(preset, 1234)
+            T = pkg.TTSTransformer(device=0, max_streams=max_streams, max_ctx=max_ctx)
+            if fmt is not None:
+                T.batched_weight_format = fmt
+            assert T.load_model(path), T.get_error()
+            cache[key] = (T, cfg)
+        return cache[key]
+
+    yield get
+    for T, _ in cache.values():
+        T.unload_model()
+
+
+def run_streams(T, toks, spk, max_len, temperature=0.0, seeds=None, chunk=4, logits_at=None):
+    n = len(toks)
+    for i in range(n):
+        assert T.stream_begin(i, toks[i], spk[i], max_len=max_len, temperature=temperature,
+                              seed=0 if seeds is None else seeds[i]), T.get_error()
+    got = [[] for _ in range(n)]
+    for _ in range(4 * max_len):
+        out = T.step_frames(chunk)
+        assert out is not None, T.get_error()
+        codes, produced, active = out
+        for i in range(n):
+            got[i].append(codes[i, :produced[i]])
+        if not active.any():
+            break
+    return [np.concatenate(g) for g in got]
+
+
+def first_diff(a, b):
+    m = min(len(a), len(b))
+    bad = (a[:m] != b[:m]).any(axis=1)
+    return int(np.argmax(bad)) if bad.any() else m
+
+
+@pytest.mark.parametrize("preset,n_streams,min_exact", [("tiny", 5, 4), ("tiny-mtp", 3, 4), ("0.6b", 4, 2)])
+def test_batched_matches_sequential(engines, pkg, preset, n_streams, min_exact):
+    T, cfg = engines(preset, n_streams)
+    texts = ["Hello, world!", "A second, longer utterance for slot one.", "Third", "Numbers 1 2 3 4 5 6 7 8 9",
+             "The quick brown fox jumps over the lazy dog."][:n_streams]
+    toks = [pkg.synth.synth_tokens(cfg, t) for t in texts]
+    spk = [pkg.synth.synth_speaker(cfg, seed=20 + i) for i in range(n_streams)]
+    T.set_numerics(1, 4)      # batch-1 kernel in FAST numerics: the batched kernel's attention arithmetic
+    T.set_batched(False)
+    seq = run_streams(T, toks, spk, 12)
+    T.set_batched(True)
+    bat = run_streams(T, toks, spk, 12)
+    T.set_numerics(0, 4)
+    for i in range(n_streams):
+        assert bat[i].shape[1] == 16 and len(bat[i]) > 0
+        assert (bat[i] >= 0).all() and (bat[i][:, 1:] < cfg.cp_vocab_size).all()
+        assert first_diff(bat[i], seq[i]) >= min_exact, (i, bat[i][:4], seq[i][:4])
+
+
+@pytest.mark.parametrize("preset,min_exact", [("tiny", 4), ("tiny-mtp", 4), ("0.6b", 2)])
+def test_batched_first_frame_logits_and_golden_ids(engines, pkg, preset, min_exact):
+    """The golden utterance in slot 1 of a 3-slot engine (other slots busy with other texts)."""
+    T, cfg = engines(preset, 3)
+    g = load_gold(preset)
+    toks = [pkg.synth.synth_tokens(cfg, "Other text"), g["tokens"], pkg.synth.synth_tokens(cfg, "x y z w")]
+    spk = [pkg.synth.synth_speaker(cfg, seed=3), g["speaker"], None]
+    T.set_batched(True)
+    for i in range(3):
+        assert T.stream_begin(i, toks[i], spk[i], max_len=int(g["max_len"]), temperature=0.0), T.get_error()
+    codes, produced, active = T.step_frames(1)
+    cb0, cp = T.stream_logits(1)
+    # frame 0: codebook-0 logits come from the (batch-1) prefill; the 15 code-predictor logit vectors
+    # are the batched kernel's, free-running == teacher-forced while the ids agree
+    ref_codes = g["codes"]
+    assert codes[1, 0, 0] == ref_codes[0, 0]
+    for s in range(15):
+        d = np.abs(cp[s] - g["cp_logits"][s]).max()
+        assert nmse(cp[s], g["cp_logits"][s]) <= 1e-5 and d <= 4e-3, (s, d)
+        if codes[1, 0, s + 1] != ref_codes[0, s + 1]:
+            top2 = np.sort(g["cp_logits"][s])[-2:]
+            assert top2[1] - top2[0] <= 2 * d
+            break
+    rest = [codes[1, :produced[1]]]
+    while active[1]:
+        codes, produced, active = T.step_frames(8)
+        rest.append(codes[1, :produced[1]])
+    out = np.concatenate(rest)
+    assert first_diff(out, ref_codes) >= min_exact
+
+
+def test_batched_sampling_reproducible_and_ragged(engines, pkg):
+    """temperature 0.9 / top-k 50 with per-stream seeds; ragged lengths; EOS by the ramp."""
+    T, cfg = engines("tiny", 5)
+    texts = ["Hi", "Hello, world!", "A somewhat longer sentence here.", "Hi", "Four"]
+    toks = [pkg.synth.synth_tokens(cfg, t) for t in texts]
+    spk = [None] * 5
+    T.set_batched(True)
+    a = run_streams(T, toks, spk, 120, temperature=0.9, seeds=[1, 2, 3, 1, 5], chunk=16)
+    b = run_streams(T, toks, spk, 120, temperature=0.9, seeds=[1, 2, 3, 1, 5], chunk=7)
+    for i in range(5):
+        assert np.array_equal(a[i], b[i])
+        assert 0 < len(a[i]) <= 120
+    assert np.array_equal(a[0], a[3])            # same text, same seed, different slot
+    assert not np.array_equal(a[0][:8], a[4][:8])

@@ -217,6 +217,7 @@ def test_concurrent_streams_match_single(engines, pkg):
     toks = [pkg.synth.synth_tokens(cfg, t) for t in texts]
     spk = [pkg.synth.synth_speaker(cfg, seed=20 + i) for i in range(3)]
     alone = [T.generate(toks[i], spk[i], max_len=12, temperature=0.0, slot=0) for i in range(3)]
+    T.set_batched(False)     # batch-1 kernel stream after stream (batched mode: test_gpu_batched.py)
     for i in range(3):
         assert T.stream_begin(i, toks[i], spk[i], max_len=12, temperature=0.0), T.get_error()
     got = [[] for _ in range(3)]
@@ -228,5 +229,6 @@ def test_concurrent_streams_match_single(engines, pkg):
             got[i].append(codes[i, :produced[i]])
         if not active.any():
             break
+    T.set_batched(True)
     for i in range(3):
         assert np.array_equal(np.concatenate(got[i]), alone[i])
