@@ -148,9 +148,11 @@ int qtts_step_frames(qtts_engine * e, int32_t n_frames, int32_t * codes_out,
 /* 1 (default): qtts_step_frames advances all active streams in lock step with the batched tcgen05
  * kernel (groups of <= 128 slots); 0: the batch-1 kernel, one stream after another. */
 int qtts_set_batched(qtts_engine * e, int on);
-/* B-operand (weight) element type of the batched kernel's tensor-core GEMMs: QTTS_BF16 (default) or
- * QTTS_F16 (the GGUF file's own type; activations are F16 either way, as in the reference's
- * ggml_mul_mat).  Must be called before qtts_finalize. */
+/* B-operand (weight) element type of the batched kernel's tensor-core GEMMs.  QTTS_F16 (default):
+ * the F16 image of the engine's BF16 weights (exact: BF16-exact values inside F16's range), so both
+ * kernels multiply the same real numbers; activations are F16 as in the reference's ggml_mul_mat.
+ * QTTS_BF16 is rejected: tcgen05.mma kind::f16 traps on mixed F16 x BF16 operands (measured on
+ * B200).  Must be called before qtts_finalize. */
 int qtts_set_batched_weight_format(qtts_engine * e, int fmt);
 /* parity hook: processed codebook-0 logits [V] (after suppress / penalty / EOS ramp) and, batched
  * mode only, the 15 code-predictor logit vectors [15*cp_vocab] of the LAST frame of `slot`. */

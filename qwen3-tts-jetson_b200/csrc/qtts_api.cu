@@ -374,8 +374,14 @@ int qtts_set_batched(qtts_engine * h, int on) { h->e.batched = on ? 1 : 0; retur
 int qtts_set_batched_weight_format(qtts_engine * h, int fmt) {
     Engine * e = &h->e;
     if (e->finalized) { e->err = "weight format must be chosen before qtts_finalize"; return 0; }
-    if (fmt != QTTS_F16 && fmt != QTTS_BF16) { e->err = "unknown weight format"; return 0; }
-    e->bfmt = (fmt == QTTS_BF16) ? 1 : 0;
+    if (fmt == QTTS_BF16) {
+        // measured on B200: tcgen05.mma kind::f16 with a_format = F16 and b_format = BF16 traps with
+        // "illegal instruction"; the activations must stay F16 (the reference's rounding point)
+        e->err = "batched kernel: BF16 weights cannot be mixed with F16 activations in one tcgen05.mma (kind::f16); use QTTS_F16";
+        return 0;
+    }
+    if (fmt != QTTS_F16) { e->err = "unknown weight format"; return 0; }
+    e->bfmt = 0;
     return 1;
 }
 

@@ -320,7 +320,7 @@ __device__ __noinline__ void bstage_gemm(const BOp & op, const BRun & run, BCtx 
                     for (int ks = 0; ks < kKc / 16; ++ks) {
                         const uint64_t ad = umma_smem_desc(a0 + ks * 2 * kALbo, kALbo, kASbo);
                         const uint64_t bd = umma_smem_desc(w0 + ks * 256, 128, (uint32_t) kp * 16u);
-                        umma_f16_ss(d, ad, bd, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+                        if (!(run.dbg & 1)) umma_f16_ss(d, ad, bd, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
                     }
                     umma_commit(cx.abar + buf);
                     if (mt == m_tiles - 1 && koff + kKc == kp) umma_commit(ring.empty + slot);
@@ -357,7 +357,8 @@ __device__ __noinline__ void bstage_gemm(const BOp & op, const BRun & run, BCtx 
                     if (!waited) { mbar_wait(cx.dbar, cx.d_use & 1u); tc_fence_after(); waited = true; }
                     __syncwarp();
                     float acc[16];
-                    tmem_ld16(cx.tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
+                    if (!(run.dbg & 2)) tmem_ld16(cx.tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
+                    else for (int i = 0; i < 16; ++i) acc[i] = 0.f;
                     if (valid) bepilogue16(op, r, n0, acc, side);
                 }
             }

@@ -268,6 +268,7 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
     run.n_streams = n_streams; run.n_frames = n_frames; run.check_done = check_done ? 1 : 0;
     run.idesc_base = batched_idesc(e);
     run.prof = e->prof_on ? e->prof + 2048 : nullptr;
+    { const char * d = getenv("QTTS_BDBG"); run.dbg = d ? atoi(d) : 0; }
     void * args[] = {(void *) &run};
     QTTS_CUDA(cudaLaunchCooperativeKernel((const void *) qtts_run_batched, dim3(e->n_sms), dim3(kThreads), args,
                                           kBSmemBytes, e->stream));

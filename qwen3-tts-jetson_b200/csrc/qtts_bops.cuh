@@ -98,6 +98,7 @@ struct BRun {
     int32_t n_streams, n_frames, check_done;
     uint32_t idesc_base;         // instruction descriptor without N (formats, M = 128)
     unsigned long long * prof;   // optional stage timers
+    int32_t dbg;                 // bring-up switches (env QTTS_BDBG): 1 skip MMA issue, 2 skip TMEM loads
 };
 
 }  // namespace qtts

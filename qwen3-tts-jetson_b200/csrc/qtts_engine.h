@@ -122,7 +122,7 @@ struct Engine {
     std::vector<const __half *> cp_embd;
     std::vector<Slot> slots;
     // batched (tcgen05) path
-    int bfmt = 1;                 // B-operand (weight) format: 1 = BF16, 0 = F16
+    int bfmt = 0;                 // B-operand (weight) format: 0 = F16 (1 = BF16 only for the bring-up test)
     int batched = 1;              // qtts_step_frames uses the batched kernel
     bool batched_ready = false;
     int64_t weight_bytes_batched = 0;

@@ -112,7 +112,7 @@ class TTSTransformer:
         self._err = ""
         self.device, self.max_streams, self.max_ctx = device, max_streams, max_ctx
         self.config: dict = {}
-        self.batched_weight_format = BF16    # B operand of the batched kernel's GEMMs (applied at load)
+        self.batched_weight_format = F16     # B operand of the batched kernel's GEMMs (applied at load)
 
     # -- error handling (bool + get_error(), like the reference) --------------------------------
     def get_error(self) -> str:
@@ -325,7 +325,7 @@ class TTSTransformer:
 
 
 def debug_bgemm(W, X, n_tok: int = 1, epi: int = EPI_STORE, in_f16: bool = False, norm_w=None, res=None, bias=None,
-                eps: float = 1e-6, weight_fmt: int = BF16, device: int = 0, want_ssq: bool = False):
+                eps: float = 1e-6, weight_fmt: int = F16, device: int = 0, want_ssq: bool = False):
     """One projection stage of the batched tcgen05 kernel on caller-supplied operands (qtts_debug_bgemm)."""
     lib = load_library()
     W = np.ascontiguousarray(W, np.float32)
