@@ -8,7 +8,7 @@ using namespace qtts;
 namespace qtts {
 extern "C" __global__ void qtts_run_program(const Op * ops, int n_ops, StreamState * st, GridBarrier * bar,
                                             int n_frames, RunCfg cfg);
-extern "C" __global__ void qtts_run_batched(BRun run);
+extern "C" __global__ void qtts_run_batched(const __grid_constant__ BRun run_param);
 }
 
 struct qtts_engine { Engine e; };

@@ -62,23 +62,42 @@ __device__ __forceinline__ bool mbar_test(uint64_t * bar, uint32_t parity) {
 }
 
 // ------------------------------------------------------------------------------------------
-// weight ring (one per CTA): piece number `seq` (counted from kernel start, in the CTA's own
-// consumption order) lives in slot seq % kBSlots; full[slot] completes by bytes (bulk copy),
-// empty[slot] by the tcgen05.commit that follows the last MMA reading the slot.
+// CTA state.  With ~222 KB of shared memory per CTA there is almost no L1 left, so anything the
+// compiler would put on the stack (structs passed by reference to the stage functions, spills)
+// turns into L2 round trips; every piece of CTA state therefore lives in ONE shared-memory block
+// at the start of dynamic shared memory, and the stage descriptor is copied there per stage.
+//
+// weight ring: piece number `seq` (counted from kernel start, in the CTA's own consumption order)
+// lives in slot seq % kBSlots; full[slot] completes by bytes (bulk copy), empty[slot] by the
+// tcgen05.commit that follows the last MMA reading the slot.
 // ------------------------------------------------------------------------------------------
-struct BRing {
-    unsigned char * base;
-    uint64_t * full, * empty;
-};
-
-struct BPrefetch {           // registers of the prefetcher thread
+struct BPrefetch {           // used by the prefetcher thread only
     int32_t idx, frame, t, p;
     int32_t n_tiles, n_pieces, tile_bytes, piece_bytes;
     const unsigned char * W;
     uint32_t seq;
+    int32_t exhausted;
     uint64_t policy;
-    bool exhausted;
 };
+
+struct BShared {
+    uint64_t full[kBSlots], empty[kBSlots], abar[2], dbar;
+    BRun run;                // copy of the kernel parameter
+    BOp op;                  // the stage being executed
+    Op item_op;              // Talker attention: per-item view for the batch-1 helpers
+    BPrefetch pf;
+    double red[kWarps];
+    float scale[kBMaxRows];
+    uint32_t tmem_base;
+    uint32_t cons_seq;       // ring pieces consumed so far
+    uint32_t a_use[2];       // commits issued on abar[i]
+    uint32_t d_use;          // commits issued on dbar
+    int32_t all_done;
+};
+constexpr size_t kBSharedBytes = (sizeof(BShared) + 127) & ~(size_t) 127;
+
+__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return reinterpret_cast<unsigned char *>(S) + kBSharedBytes; }
+__device__ __forceinline__ unsigned char * babuf_base(BShared * S) { return bring_base(S) + (size_t) kBSlots * kBSlotBytes; }
 
 __device__ __forceinline__ int first_tile(int cta_off) {
     const int G = (int) gridDim.x;
@@ -87,13 +106,14 @@ __device__ __forceinline__ int first_tile(int cta_off) {
 }
 
 // advance to the next piece of this CTA; false when the launch needs no more weights
-__device__ __forceinline__ bool bpf_advance(const BRun & run, BPrefetch & pf) {
+__device__ __forceinline__ bool bpf_advance(BShared * S) {
+    BPrefetch & pf = S->pf;
     if (pf.exhausted) return false;
     if (pf.p >= pf.n_pieces) { pf.t += (int) gridDim.x; pf.p = 0; }
     while (pf.t >= pf.n_tiles) {
-        if (++pf.idx >= run.n_sched) { pf.idx = 0; if (++pf.frame >= run.n_frames) { pf.exhausted = true; return false; } }
-        const int4 e0 = __ldg(reinterpret_cast<const int4 *>(run.sched + pf.idx));
-        const int4 e1 = __ldg(reinterpret_cast<const int4 *>(run.sched + pf.idx) + 1);
+        if (++pf.idx >= S->run.n_sched) { pf.idx = 0; if (++pf.frame >= S->run.n_frames) { pf.exhausted = 1; return false; } }
+        const int4 e0 = __ldg(reinterpret_cast<const int4 *>(S->run.sched + pf.idx));
+        const int4 e1 = __ldg(reinterpret_cast<const int4 *>(S->run.sched + pf.idx) + 1);
         pf.W = reinterpret_cast<const unsigned char *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
         pf.tile_bytes = e0.z; pf.piece_bytes = e0.w; pf.n_pieces = e1.x; pf.n_tiles = e1.y;
         pf.t = first_tile(e1.z); pf.p = 0;
@@ -102,40 +122,43 @@ __device__ __forceinline__ bool bpf_advance(const BRun & run, BPrefetch & pf) {
 }
 
 // issue the bulk copy of the next piece; blocking = wait for the slot to be recycled
-__device__ __forceinline__ bool bpf_issue(const BRun & run, BPrefetch & pf, const BRing & ring, bool blocking) {
-    if (!bpf_advance(run, pf)) return false;
+__device__ __forceinline__ bool bpf_issue(BShared * S, bool blocking) {
+    if (!bpf_advance(S)) return false;
+    BPrefetch & pf = S->pf;
     const int slot = (int) (pf.seq % (uint32_t) kBSlots);
     const uint32_t par = ((pf.seq / (uint32_t) kBSlots) & 1u) ^ 1u;
-    if (blocking) mbar_wait(ring.empty + slot, par);
-    else if (!mbar_test(ring.empty + slot, par)) return false;
+    if (blocking) mbar_wait(S->empty + slot, par);
+    else if (!mbar_test(S->empty + slot, par)) return false;
     const int off = pf.p * pf.piece_bytes;
     const uint32_t bytes = (uint32_t) min(pf.piece_bytes, pf.tile_bytes - off);
-    mbar_expect_tx(ring.full + slot, bytes);
-    bulk_g2s(ring.base + (size_t) slot * kBSlotBytes, pf.W + (size_t) pf.t * pf.tile_bytes + off, bytes,
-             ring.full + slot, pf.policy);
+    mbar_expect_tx(S->full + slot, bytes);
+    bulk_g2s(bring_base(S) + (size_t) slot * kBSlotBytes, pf.W + (size_t) pf.t * pf.tile_bytes + off, bytes,
+             S->full + slot, pf.policy);
     pf.p++; pf.seq++;
     return true;
 }
-__device__ __forceinline__ void bpf_poll(const BRun & run, BPrefetch & pf, const BRing & ring) {
-    while (bpf_issue(run, pf, ring, false)) {}
+__device__ __forceinline__ void bpf_poll(BShared * S) {
+    while (bpf_issue(S, false)) {}
 }
-__device__ __forceinline__ void bpf_ensure(const BRun & run, BPrefetch & pf, const BRing & ring, uint32_t seq_needed) {
-    while ((int32_t) (pf.seq - seq_needed) <= 0) if (!bpf_issue(run, pf, ring, true)) break;
+__device__ __forceinline__ void bpf_ensure(BShared * S, uint32_t seq_needed) {
+    while ((int32_t) (S->pf.seq - seq_needed) <= 0) if (!bpf_issue(S, true)) break;
 }
 
-__device__ __forceinline__ void bgrid_barrier(const BRun & run, unsigned int & epoch, BPrefetch & pf, const BRing & ring) {
+__device__ __forceinline__ void bgrid_barrier(BShared * S, unsigned int & epoch) {
     __syncthreads();
     if (threadIdx.x == 0) {
-        epoch += gridDim.x;
+        const unsigned int target = epoch + gridDim.x;
+        epoch = target;
+        unsigned int * cnt = &S->run.bar->count;
         __threadfence();
-        atomicAdd(&run.bar->count, 1u);
+        atomicAdd(cnt, 1u);
         unsigned int v;
         do {
-            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&run.bar->count) : "memory");
-        } while ((int) (v - epoch) < 0);
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&run.bar->count) : "memory");
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
+        } while ((int) (v - target) < 0);
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
     } else if (threadIdx.x == kPfThread) {
-        bpf_poll(run, pf, ring);
+        bpf_poll(S);
     }
     __syncthreads();
 }
@@ -143,33 +166,24 @@ __device__ __forceinline__ void bgrid_barrier(const BRun & run, unsigned int & e
 // ------------------------------------------------------------------------------------------
 // BOP_GEMM
 // ------------------------------------------------------------------------------------------
-struct BCtx {                // uniform across the CTA's threads
-    uint32_t cons_seq;       // ring pieces consumed so far
-    uint32_t a_use[2];       // commits issued on abar[i]
-    uint32_t d_use;          // commits issued on dbar
-    uint32_t tmem_base;
-    uint64_t * abar, * dbar;
-    unsigned char * abuf;    // 2 x kABufBytes
-    float * scale;           // [kBMaxRows]
-};
-
 __device__ __forceinline__ int row_off(int r, int B, int row_stride, int tok_stride) {
     const int t = (r >= B) ? 1 : 0;
     return (r - t * B) * row_stride + t * tok_stride;
 }
 
-template <int IN_KIND> struct BLoad { static constexpr int NV = (IN_KIND == BIN_F32) ? 8 : 4; };
-
-// global -> registers for chunk (kc, mt)
+// A "load unit" is what one pass of the 512 threads moves with 4 x 16-byte loads each:
+//   BIN_F32: 64 rows x 128 K-elements (unit u of a chunk = rows 64u .. 64u+63),
+//   BIN_F16: 128 rows x 128 K-elements.
+// global -> registers for unit (kc, mt, u)
 template <int IN_KIND>
-__device__ __forceinline__ void bload(const BOp & op, int kc, int mt, uint4 * v, float4 & nw) {
+__device__ __forceinline__ void bload(const BOp & op, int kc, int mt, int u, uint4 * v, float4 & nw) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (IN_KIND == BIN_F32) {
         const float * in = reinterpret_cast<const float *>(op.in);
         const int k = kc * kKc + lane * 4;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int r = mt * 128 + warp + 16 * i;
+        for (int i = 0; i < 4; ++i) {
+            const int r = mt * 128 + u * 64 + warp + 16 * i;
             if (r < op.rows_act)
                 v[i] = __ldcg(reinterpret_cast<const uint4 *>(in + row_off(r, op.n_streams, op.in_row_stride, op.in_tok_stride) + k));
         }
@@ -188,19 +202,18 @@ __device__ __forceinline__ void bload(const BOp & op, int kc, int mt, uint4 * v,
 
 // registers -> A buffer (F16, UMMA canonical K-major layout), RMSNorm applied for BIN_F32
 template <int IN_KIND>
-__device__ __forceinline__ void bstore(const BOp & op, const BCtx & cx, int kc, int mt, int buf, const uint4 * v, const float4 & nw,
-                                       bool write_hid) {
+__device__ __forceinline__ void bstore(const BOp & op, BShared * S, unsigned char * A, int kc, int mt, int u, const uint4 * v,
+                                       const float4 & nw, bool write_hid) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned char * A = cx.abuf + (size_t) buf * kABufBytes;
     if (IN_KIND == BIN_F32) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int rl = warp + 16 * i, r = mt * 128 + rl;
+        for (int i = 0; i < 4; ++i) {
+            const int rl = u * 64 + warp + 16 * i, r = mt * 128 + rl;
             if (r < op.rows_act) {
                 float x0 = __uint_as_float(v[i].x), x1 = __uint_as_float(v[i].y);
                 float x2 = __uint_as_float(v[i].z), x3 = __uint_as_float(v[i].w);
                 if (op.norm_w) {
-                    const float s = cx.scale[r];
+                    const float s = S->scale[r];
                     x0 = (x0 * s) * nw.x; x1 = (x1 * s) * nw.y; x2 = (x2 * s) * nw.z; x3 = (x3 * s) * nw.w;
                     if (write_hid)
                         *reinterpret_cast<float4 *>(op.hid_out + (size_t) r * op.K + kc * kKc + lane * 4) = make_float4(x0, x1, x2, x3);
@@ -237,29 +250,82 @@ __device__ __forceinline__ void bepilogue16(const BOp & op, int r, int n0, const
         *reinterpret_cast<uint4 *>(op.out16 + row_off(r, B, op.out_row_stride, op.out_tok_stride) + (n0 >> 1)) = pk;
         return;
     }
-    float o[16];
+    float * out = op.out32 + row_off(r, B, op.out_row_stride, op.out_tok_stride) + n0;
+    float ss = 0.f;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        o[4 * i] = acc[4 * i]; o[4 * i + 1] = acc[4 * i + 1]; o[4 * i + 2] = acc[4 * i + 2]; o[4 * i + 3] = acc[4 * i + 3];
-        if (op.epi == EPI_ADD || op.epi == EPI_BIAS) {
-            o[4 * i] += side[i].x; o[4 * i + 1] += side[i].y; o[4 * i + 2] += side[i].z; o[4 * i + 3] += side[i].w;
+        float4 o = make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
+        if (op.epi == EPI_ADD || op.epi == EPI_BIAS) { o.x += side[i].x; o.y += side[i].y; o.z += side[i].z; o.w += side[i].w; }
+        *reinterpret_cast<float4 *>(out + 4 * i) = o;
+        ss += o.x * o.x; ss += o.y * o.y; ss += o.z * o.z; ss += o.w * o.w;
+    }
+    if (op.flags & BF_SSQ_OUT) op.ssq_out[(size_t) r * (op.rows >> 4) + (n0 >> 4)] = ss;
+}
+
+// thread 0: the 8 MMAs (K = 16 each) of one activation chunk against the matching columns of the
+// weight piece in the ring, then the commits that recycle the A buffer / the ring slot / publish D
+__device__ __noinline__ void bgemm_issue(BShared * S, int kc, int mt, int buf, int piece, int koff, int kp, uint32_t cons_seq,
+                                         uint32_t idesc, int m_tiles, bool last) {
+    const BOp & op = S->op;
+    tc_fence_after();
+    const uint32_t seq = cons_seq + (uint32_t) piece;
+    const int slot = (int) (seq % (uint32_t) kBSlots);
+    if (mt == 0 && koff == 0) mbar_wait(S->full + slot, (seq / (uint32_t) kBSlots) & 1u);
+    const uint32_t a0 = smem_u32(babuf_base(S) + (size_t) buf * kABufBytes);
+    const uint32_t w0 = smem_u32(bring_base(S) + (size_t) slot * kBSlotBytes) + (uint32_t) (koff >> 3) * 128u;
+    const uint32_t d = S->tmem_base + (uint32_t) (mt * op.n_tile);
+    if (!(S->run.dbg & 1)) {
+#pragma unroll
+        for (int ks = 0; ks < kKc / 16; ++ks) {
+            const uint64_t ad = umma_smem_desc(a0 + ks * 2 * kALbo, kALbo, kASbo);
+            const uint64_t bd = umma_smem_desc(w0 + ks * 256, 128, (uint32_t) kp * 16u);
+            umma_f16_ss(d, ad, bd, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
         }
     }
-    float * out = op.out32 + row_off(r, B, op.out_row_stride, op.out_tok_stride) + n0;
+    umma_commit(S->abar + buf);
+    if (mt == m_tiles - 1 && koff + kKc == kp) umma_commit(S->empty + slot);
+    if (last) umma_commit(&S->dbar);
+}
+
+// epilogue of tile t: warp w reads TMEM lanes 32*(w%4).. (its sub-partition), 16 columns per pass
+__device__ __noinline__ void bgemm_epilogue(BShared * S, int t, int m_tiles, uint32_t d_use) {
+    const BOp & op = S->op;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tmem_base = S->tmem_base;
+    const int dbg = S->run.dbg;
+    const int q = warp & 3;
+    const int ncg = op.n_tile >> 4;
+    bool waited = false;
+    for (int cg = warp >> 2; cg < ncg; cg += 4) {
+        const int n0 = t * op.n_tile + cg * 16;
+        for (int mt = 0; mt < m_tiles; ++mt) {
+            const int r = mt * 128 + q * 32 + lane;
+            const bool valid = r < op.rows_act;
+            float4 side[4];
+            if (valid && op.epi == EPI_ADD) {
+                const float * rs = op.res + row_off(r, op.n_streams, op.out_row_stride, op.out_tok_stride) + n0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-        *reinterpret_cast<float4 *>(out + 4 * i) = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
-    if (op.flags & BF_SSQ_OUT) {
-        float ss = 0.f;
+                for (int i = 0; i < 4; ++i) side[i] = __ldcg(reinterpret_cast<const float4 *>(rs + 4 * i));
+            } else if (op.epi == EPI_BIAS) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) ss += o[i] * o[i];
-        op.ssq_out[(size_t) r * (op.rows >> 4) + (n0 >> 4)] = ss;
+                for (int i = 0; i < 4; ++i) side[i] = __ldg(reinterpret_cast<const float4 *>(op.bias + n0 + 4 * i));
+            }
+            if (!waited) { mbar_wait(&S->dbar, d_use & 1u); tc_fence_after(); waited = true; }
+            __syncwarp();
+            float acc[16];
+            if (!(dbg & 2)) tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
+            else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+            }
+            if (valid) bepilogue16(op, r, n0, acc, side);
+        }
     }
 }
 
 template <int IN_KIND>
-__device__ __noinline__ void bstage_gemm(const BOp & op, const BRun & run, BCtx & cx, BPrefetch & pf, const BRing & ring) {
-    constexpr int NV = BLoad<IN_KIND>::NV;
+__device__ __noinline__ void bstage_gemm(BShared * S) {
+    const BOp & op = S->op;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int G = (int) gridDim.x;
     const int t_first = first_tile(op.cta_off);
@@ -267,8 +333,15 @@ __device__ __noinline__ void bstage_gemm(const BOp & op, const BRun & run, BCtx 
         const int m_tiles = (op.rows_act + 127) >> 7;
         const int nkc = op.K / kKc;
         const int steps = nkc * m_tiles;
-        const uint32_t idesc = run.idesc_base | ((uint32_t) (op.n_tile >> 3) << 17);
+        const int upc = (IN_KIND == BIN_F32 && op.rows_act > 64) ? 2 : 1;     // load units per chunk
+        const int total = steps * upc;
+        const uint32_t idesc = S->run.idesc_base | ((uint32_t) (op.n_tile >> 3) << 17);
         const bool write_hid = (op.hid_out != nullptr) && (t_first == 0);
+        const uint32_t tmem_base = S->tmem_base;
+        uint32_t a_use0 = S->a_use[0], a_use1 = S->a_use[1], d_use = S->d_use, cons_seq = S->cons_seq;
+        unsigned char * abuf = babuf_base(S);
+        unsigned char * ring = bring_base(S);
+        const int dbg = S->run.dbg;
 
         // per-row RMSNorm scale from the producers' partial sums (double sum like ggml's rms_norm,
         // ops.cpp:3738-3747)
@@ -284,93 +357,61 @@ __device__ __noinline__ void bstage_gemm(const BOp & op, const BRun & run, BCtx 
                     for (int u = 0; u < 8; ++u) ss += (double) q[u];
                 }
                 const float mean = (float) (ss / (double) op.K);
-                cx.scale[tid] = 1.0f / sqrtf(mean + op.eps);
+                S->scale[tid] = 1.0f / sqrtf(mean + op.eps);
             }
             __syncthreads();
         }
 
         for (int t = t_first; t < op.n_tiles; t += G) {
-            uint4 cur[NV], nxt[NV];
-            float4 nwc = make_float4(1.f, 1.f, 1.f, 1.f), nwn = nwc;
-            bload<IN_KIND>(op, 0, 0, cur, nwc);
-            if (tid == kPfThread) bpf_ensure(run, pf, ring, cx.cons_seq);
-            for (int s = 0; s < steps; ++s) {
-                const int kc = s / m_tiles, mt = s - kc * m_tiles;
+            // one load unit in flight: the loads of unit j+1 are issued right after unit j went to
+            // shared memory and overlap the fence / barrier / MMA issue of unit j
+            uint4 cur[4];
+            float4 nwc = make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) cur[i] = make_uint4(0u, 0u, 0u, 0u);
+            bload<IN_KIND>(op, 0, 0, 0, cur, nwc);
+            if (tid == kPfThread) bpf_ensure(S, cons_seq);
+            int kc = 0, mt = 0, u = 0, s = 0;
+            for (int j = 0; j < total; ++j) {
                 const int buf = s & 1;
-                if (s + 1 < steps) {
-                    const int kc1 = (s + 1) / m_tiles, mt1 = (s + 1) - kc1 * m_tiles;
-                    bload<IN_KIND>(op, kc1, mt1, nxt, nwn);
+                if (u == 0) {       // the MMAs that read this buffer two chunks ago must be done
+                    const uint32_t au = buf ? a_use1 : a_use0;
+                    if (au > 0) mbar_wait(S->abar + buf, (au - 1) & 1u);
                 }
-                if (cx.a_use[buf] > 0) mbar_wait(cx.abar + buf, (cx.a_use[buf] - 1) & 1u);
-                bstore<IN_KIND>(op, cx, kc, mt, buf, cur, nwc, write_hid);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncthreads();
-                const int kin = kc * kKc;
-                const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
-                const int kp = min(op.kpp, op.K - piece * op.kpp);
-                if (tid == 0) {
-                    tc_fence_after();
-                    const uint32_t seq = cx.cons_seq + (uint32_t) piece;
-                    const int slot = (int) (seq % (uint32_t) kBSlots);
-                    if (mt == 0 && koff == 0) mbar_wait(ring.full + slot, (seq / (uint32_t) kBSlots) & 1u);
-                    const uint32_t a0 = smem_u32(cx.abuf + (size_t) buf * kABufBytes);
-                    const uint32_t w0 = smem_u32(ring.base + (size_t) slot * kBSlotBytes) + (uint32_t) (koff >> 3) * 128u;
-                    const uint32_t d = cx.tmem_base + (uint32_t) (mt * op.n_tile);
-#pragma unroll
-                    for (int ks = 0; ks < kKc / 16; ++ks) {
-                        const uint64_t ad = umma_smem_desc(a0 + ks * 2 * kALbo, kALbo, kASbo);
-                        const uint64_t bd = umma_smem_desc(w0 + ks * 256, 128, (uint32_t) kp * 16u);
-                        if (!(run.dbg & 1)) umma_f16_ss(d, ad, bd, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+                bstore<IN_KIND>(op, S, abuf + (size_t) buf * kABufBytes, kc, mt, u, cur, nwc, write_hid);
+                // position of unit j + 1
+                int kc1 = kc, mt1 = mt, u1 = u + 1, s1 = s;
+                if (u1 == upc) { u1 = 0; s1 = s + 1; if (++mt1 == m_tiles) { mt1 = 0; ++kc1; } }
+                if (j + 1 < total) bload<IN_KIND>(op, kc1, mt1, u1, cur, nwc);
+                if (u == upc - 1) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    __syncthreads();
+                    const int kin = kc * kKc;
+                    const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
+                    const int kp = min(op.kpp, op.K - piece * op.kpp);
+                    if (tid == 0) {
+                        bgemm_issue(S, kc, mt, buf, piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
+                    } else if (tid == kPfThread) {
+                        // the piece the NEXT chunk needs must be in flight before thread 0 waits for it
+                        const int kin1 = min(kin + kKc, op.K - kKc);
+                        bpf_ensure(S, cons_seq + (uint32_t) (kin1 / op.kpp));
+                        bpf_poll(S);
                     }
-                    umma_commit(cx.abar + buf);
-                    if (mt == m_tiles - 1 && koff + kKc == kp) umma_commit(ring.empty + slot);
-                    if (s == steps - 1) umma_commit(cx.dbar);
-                } else if (tid == kPfThread) {
-                    // the piece the NEXT step needs must be in flight before thread 0 waits for it
-                    const int kin1 = min(kin + kKc, op.K - kKc);
-                    bpf_ensure(run, pf, ring, cx.cons_seq + (uint32_t) (kin1 / op.kpp));
-                    bpf_poll(run, pf, ring);
+                    if (buf) a_use1++; else a_use0++;
                 }
-                cx.a_use[buf]++;
-#pragma unroll
-                for (int i = 0; i < NV; ++i) cur[i] = nxt[i];
-                nwc = nwn;
+                kc = kc1; mt = mt1; u = u1; s = s1;
             }
-            // ---- epilogue: warp w reads TMEM lanes 32*(w%4).. (its sub-partition), 16 columns per pass
-            const int q = warp & 3;
-            const int ncg = op.n_tile >> 4;
-            bool waited = false;
-            for (int cg = warp >> 2; cg < ncg; cg += 4) {
-                const int n0 = t * op.n_tile + cg * 16;
-                for (int mt = 0; mt < m_tiles; ++mt) {
-                    const int r = mt * 128 + q * 32 + lane;
-                    const bool valid = r < op.rows_act;
-                    float4 side[4];
-                    if (valid && op.epi == EPI_ADD) {
-                        const float * rs = op.res + row_off(r, op.n_streams, op.out_row_stride, op.out_tok_stride) + n0;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) side[i] = __ldcg(reinterpret_cast<const float4 *>(rs + 4 * i));
-                    } else if (op.epi == EPI_BIAS) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) side[i] = __ldg(reinterpret_cast<const float4 *>(op.bias + n0 + 4 * i));
-                    }
-                    if (!waited) { mbar_wait(cx.dbar, cx.d_use & 1u); tc_fence_after(); waited = true; }
-                    __syncwarp();
-                    float acc[16];
-                    if (!(run.dbg & 2)) tmem_ld16(cx.tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
-                    else for (int i = 0; i < 16; ++i) acc[i] = 0.f;
-                    if (valid) bepilogue16(op, r, n0, acc, side);
-                }
-            }
-            cx.d_use++;
+            bgemm_epilogue(S, t, m_tiles, d_use);
+            d_use++;
             tc_fence_before();
             __syncthreads();
-            cx.cons_seq += (uint32_t) op.n_pieces;
+            cons_seq += (uint32_t) op.n_pieces;
         }
+        if (tid == 0) { S->a_use[0] = a_use0; S->a_use[1] = a_use1; S->d_use = d_use; S->cons_seq = cons_seq; }
     }
     if ((op.flags & BF_INC_NPAST) && blockIdx.x == 0 && tid < op.n_streams) {
-        StreamState * st = run.st + tid;
-        if (run.active[tid] && !st->done) st->n_past += 1;
+        StreamState * st = S->run.st + tid;
+        if (S->run.active[tid] && !st->done) st->n_past += 1;
     }
 }
 
@@ -401,7 +442,8 @@ __device__ __forceinline__ void warp_norm_rope(float * x, const float * w, const
     }
 }
 
-__device__ __noinline__ void bstage_attn_cp(const BOp & op) {
+__device__ __noinline__ void bstage_attn_cp(BShared * S) {
+    const BOp & op = S->op;
     const int lane = threadIdx.x & 31;
     const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
     const int B = op.n_streams, nkv = op.n_kv_heads, rep = op.n_heads / nkv;
@@ -560,7 +602,11 @@ __device__ void battn_tk_item(const Op & iop, const float * qkv, __half * out16,
     __syncthreads();
 }
 
-__device__ __noinline__ void bstage_attn_tk(const BOp & op, const BRun & run, unsigned char * scratch, Op * iop) {
+__device__ __noinline__ void bstage_attn_tk(BShared * S) {
+    const BOp & op = S->op;
+    const BRun & run = S->run;
+    unsigned char * scratch = babuf_base(S);
+    Op * iop = &S->item_op;
     AttnSmem * sm = reinterpret_cast<AttnSmem *>(scratch);
     float * sc = reinterpret_cast<float *>(scratch + ((sizeof(AttnSmem) + 15) & ~(size_t) 15));
     const int B = op.n_streams, nkv = op.n_kv_heads, rep = op.n_heads / nkv;
@@ -591,7 +637,11 @@ __device__ __noinline__ void bstage_attn_tk(const BOp & op, const BRun & run, un
 // embedding rows of the NEXT pass, and for the last codebook the frame end (:2500-2527) and the
 // next Talker input sum (:2529-2553).
 // ------------------------------------------------------------------------------------------
-__device__ __noinline__ void bstage_sample(const BOp & op, const BRun & run, unsigned char * scratch, double * red) {
+__device__ __noinline__ void bstage_sample(BShared * S) {
+    const BOp & op = S->op;
+    const BRun & run = S->run;
+    unsigned char * scratch = babuf_base(S);
+    double * red = S->red;
     SampleSmem * sm = reinterpret_cast<SampleSmem *>(scratch);
     float * pbuf = reinterpret_cast<float *>(scratch + ((sizeof(SampleSmem) + 15) & ~(size_t) 15));
     const int B = op.n_streams, n = op.n_vocab, tid = threadIdx.x;
@@ -716,96 +766,88 @@ __device__ __noinline__ void bstage_sample(const BOp & op, const BRun & run, uns
 // ------------------------------------------------------------------------------------------
 // the batched program runner
 // ------------------------------------------------------------------------------------------
-constexpr size_t kBSmemBytes = (size_t) kBSlots * kBSlotBytes + 2 * (size_t) kABufBytes;
+constexpr size_t kBSmemBytes = kBSharedBytes + (size_t) kBSlots * kBSlotBytes + 2 * (size_t) kABufBytes;
+static_assert(kBSmemBytes <= 232448, "batched kernel exceeds the 227 KB of shared memory per CTA");
 static_assert(sizeof(AttnSmem) + 64 + 2 * kMaxScores * sizeof(float) <= 2 * (size_t) kABufBytes, "attention scratch overlays the A buffers");
 static_assert(sizeof(SampleSmem) + 64 + kMaxVocab * sizeof(float) <= 2 * (size_t) kABufBytes, "sampling scratch overlays the A buffers");
 
 extern "C" __global__ void __launch_bounds__(kThreads, 1)
-qtts_run_batched(BRun run) {
+qtts_run_batched(const __grid_constant__ BRun run_param) {
     extern __shared__ __align__(128) unsigned char bsm[];
-    __shared__ __align__(8) uint64_t full_bar[kBSlots], empty_bar[kBSlots], a_bar[2], d_bar;
-    __shared__ uint32_t tmem_slot;
-    __shared__ float scale_s[kBMaxRows];
-    __shared__ double red[kWarps];
-    __shared__ Op item_op;
-    __shared__ int all_done;
+    BShared * S = reinterpret_cast<BShared *>(bsm);
 
-    BRing ring;
-    ring.base = bsm; ring.full = full_bar; ring.empty = empty_bar;
-    BCtx cx;
-    cx.cons_seq = 0; cx.a_use[0] = cx.a_use[1] = 0; cx.d_use = 0;
-    cx.abar = a_bar; cx.dbar = &d_bar;
-    cx.abuf = bsm + (size_t) kBSlots * kBSlotBytes;
-    cx.scale = scale_s;
-    unsigned char * scratch = cx.abuf;
-
+    for (int i = threadIdx.x; i < (int) (sizeof(BRun) / 4); i += kThreads)
+        reinterpret_cast<uint32_t *>(&S->run)[i] = reinterpret_cast<const uint32_t *>(&run_param)[i];
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kBSlots; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); }
-        mbar_init(a_bar, 1); mbar_init(a_bar + 1, 1); mbar_init(&d_bar, 1);
+        for (int i = 0; i < kBSlots; ++i) { mbar_init(S->full + i, 1); mbar_init(S->empty + i, 1); }
+        mbar_init(S->abar, 1); mbar_init(S->abar + 1, 1); mbar_init(&S->dbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        S->cons_seq = 0; S->a_use[0] = 0; S->a_use[1] = 0; S->d_use = 0; S->all_done = 0;
+        BPrefetch & pf = S->pf;
+        pf.idx = -1; pf.frame = 0; pf.t = 0; pf.p = 0; pf.n_tiles = 0; pf.n_pieces = 0; pf.tile_bytes = 0; pf.piece_bytes = 0;
+        pf.W = nullptr; pf.seq = 0; pf.exhausted = (run_param.n_sched <= 0) ? 1 : 0;
+        pf.policy = policy_evict_first();
     }
     if (threadIdx.x < 32) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&tmem_slot)), "r"(512));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&S->tmem_base)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    cx.tmem_base = tmem_slot;
-
-    BPrefetch pf;
-    pf.idx = -1; pf.frame = 0; pf.t = 0; pf.p = 0; pf.n_tiles = 0; pf.n_pieces = 0; pf.tile_bytes = 0; pf.piece_bytes = 0;
-    pf.W = nullptr; pf.seq = 0; pf.policy = 0; pf.exhausted = (run.n_sched <= 0);
-    if (threadIdx.x == kPfThread) {
-        pf.policy = policy_evict_first();
-        bpf_poll(run, pf, ring);
-    }
+    if (threadIdx.x == kPfThread) bpf_poll(S);
     unsigned int epoch = 0;
+    const int n_frames = run_param.n_frames, n_ops = run_param.n_ops, n_streams = run_param.n_streams;
+    const bool prof = run_param.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
 
-    for (int f = 0; f < run.n_frames; ++f) {
-        if (run.check_done) {
+    for (int f = 0; f < n_frames; ++f) {
+        if (run_param.check_done) {
             // uniform across the grid: the states were published by the previous frame's barriers
-            if (threadIdx.x == 0) all_done = 1;
+            if (threadIdx.x == 0) S->all_done = 1;
             __syncthreads();
-            for (int b = threadIdx.x; b < run.n_streams; b += kThreads)
-                if (run.active[b] && !__ldcg(&run.st[b].done)) all_done = 0;
+            for (int b = threadIdx.x; b < n_streams; b += kThreads)
+                if (run_param.active[b] && !__ldcg(&run_param.st[b].done)) S->all_done = 0;
             __syncthreads();
-            if (all_done) break;
+            if (S->all_done) break;
         }
-        for (int i = 0; i < run.n_ops; ++i) {
-            const BOp & op = run.ops[i];
-            const long long t0 = (run.prof && threadIdx.x == 0) ? clock64() : 0;
-            switch (op.type) {
+        for (int i = 0; i < n_ops; ++i) {
+            // stage descriptor -> shared memory (the previous stage ended with a barrier)
+            for (int w = threadIdx.x; w < (int) (sizeof(BOp) / 4); w += kThreads)
+                reinterpret_cast<uint32_t *>(&S->op)[w] = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + i) + w);
+            __syncthreads();
+            const int type = S->op.type, in_kind = S->op.in_kind;
+            const long long t0 = prof ? clock64() : 0;
+            switch (type) {
                 case BOP_GEMM:
-                    if (op.in_kind == BIN_F32) bstage_gemm<BIN_F32>(op, run, cx, pf, ring);
-                    else                       bstage_gemm<BIN_F16>(op, run, cx, pf, ring);
+                    if (in_kind == BIN_F32) bstage_gemm<BIN_F32>(S);
+                    else                    bstage_gemm<BIN_F16>(S);
                     break;
-                case BOP_ATTN_CP: bstage_attn_cp(op); break;
-                case BOP_ATTN_TK: bstage_attn_tk(op, run, scratch, &item_op); break;
-                case BOP_SAMPLE:  bstage_sample(op, run, scratch, red); break;
+                case BOP_ATTN_CP: bstage_attn_cp(S); break;
+                case BOP_ATTN_TK: bstage_attn_tk(S); break;
+                case BOP_SAMPLE:  bstage_sample(S); break;
             }
-            const long long t1 = (run.prof && threadIdx.x == 0) ? clock64() : 0;
-            bgrid_barrier(run, epoch, pf, ring);
-            if (run.prof && threadIdx.x == 0 && blockIdx.x == 0) {
+            const long long t1 = prof ? clock64() : 0;
+            bgrid_barrier(S, epoch);
+            if (prof) {
                 const long long t2 = clock64();
-                const int slot = op.type * 2 + ((op.type == BOP_GEMM && op.in_kind == BIN_F16) ? 8 : 0);
-                run.prof[slot * 4 + 0] += 1;
-                run.prof[slot * 4 + 1] += (unsigned long long) (t1 - t0);
-                run.prof[slot * 4 + 2] += (unsigned long long) (t2 - t1);
+                const int slot = type * 2 + ((type == BOP_GEMM && in_kind == BIN_F16) ? 8 : 0);
+                run_param.prof[slot * 4 + 0] += 1;
+                run_param.prof[slot * 4 + 1] += (unsigned long long) (t1 - t0);
+                run_param.prof[slot * 4 + 2] += (unsigned long long) (t2 - t1);
             }
         }
     }
     // drain: every bulk copy issued into this CTA's shared memory must land before it exits
     __syncthreads();
     if (threadIdx.x == kPfThread) {
-        for (uint32_t s = cx.cons_seq; s != pf.seq; ++s)
-            mbar_wait(full_bar + (s % (uint32_t) kBSlots), (s / (uint32_t) kBSlots) & 1u);
+        for (uint32_t s = S->cons_seq; s != S->pf.seq; ++s)
+            mbar_wait(S->full + (s % (uint32_t) kBSlots), (s / (uint32_t) kBSlots) & 1u);
     }
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x < 32) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(cx.tmem_base), "r"(512));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(S->tmem_base), "r"(512));
     }
 }
 

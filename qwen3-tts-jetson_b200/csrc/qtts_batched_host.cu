@@ -7,7 +7,7 @@
 
 namespace qtts {
 
-extern "C" __global__ void qtts_run_batched(BRun run);
+extern "C" __global__ void qtts_run_batched(const __grid_constant__ BRun run_param);
 
 // src: BF16 [rows][K] row-major (the batch-1 kernel's fused layouts).  dst: for tile t (n_tile
 // rows) and piece p (kpp K-elements, the last one shorter), the piece is one contiguous block in
