@@ -1,6 +1,7 @@
 // qtts_api.cu — the extern "C" surface declared in include/qtts_b200.h.
 #include "qtts_engine.h"
 #include <cstring>
+#include <cstdio>
 #include <algorithm>
 
 using namespace qtts;
@@ -458,17 +459,22 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     if (!tile_matrix(e, dW, rows, K, T)) return cleanup(0);
     void * dX = nullptr;
     if (in_f16) {
-        std::vector<__half> xh(nX);
-        for (size_t i = 0; i < nX; ++i) xh[i] = __float2half_rn(X[i]);
-        dX = e->dalloc<__half>(nX, false);
-        cudaMemcpy(dX, xh.data(), nX * 2, cudaMemcpyHostToDevice);
+        // F16 activations live in global memory as UMMA-canonical 128-column chunks (qtts_batched.cu: canon_off)
+        const size_t cb = (size_t) ((rows_act + 7) / 8) * 2048, nXc = (size_t) (K / 128) * cb / 2;
+        std::vector<__half> xh(nXc);
+        for (int r = 0; r < rows_act; ++r)
+            for (int k = 0; k < K; ++k)
+                xh[((size_t) (k >> 7) * cb + (size_t) (r >> 3) * 2048 + (size_t) ((k & 127) >> 3) * 128 + (r & 7) * 16 + (k & 7) * 2) / 2] =
+                    __float2half_rn(X[(size_t) r * K + k]);
+        dX = e->dalloc<__half>(nXc, false);
+        cudaMemcpy(dX, xh.data(), nXc * 2, cudaMemcpyHostToDevice);
     } else {
         dX = e->dalloc<float>(nX, false);
         cudaMemcpy(dX, X, nX * 4, cudaMemcpyHostToDevice);
     }
     const int outw = (epi == EPI_SWIGLU) ? rows / 2 : rows;
     float * d_out = e->dalloc<float>((size_t) rows_act * rows);
-    __half * d_out16 = e->dalloc<__half>((size_t) rows_act * rows);
+    __half * d_out16 = e->dalloc<__half>((size_t) (rows_act + 8) * rows);
     float * d_res = nullptr, * d_bias = nullptr, * d_norm = nullptr, * d_ssq_in = nullptr;
     float * d_ssq = e->dalloc<float>((size_t) rows_act * (rows / 16));
     if (res) { d_res = e->dalloc<float>((size_t) rows_act * rows, false); cudaMemcpy(d_res, res, (size_t) rows_act * rows * 4, cudaMemcpyHostToDevice); }
@@ -485,12 +491,12 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     memset(&o, 0, sizeof(o));
     o.type = BOP_GEMM; o.n_streams = n_streams; o.rows_act = rows_act; o.n_tok = n_tok;
     o.flags = ssq_out ? BF_SSQ_OUT : 0;
-    o.Wt = T.p; o.rows = rows; o.K = K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = 5; o.kpp = T.kpp; o.n_pieces = T.n_pieces;
+    o.Wt = T.p; o.rows = rows; o.K = K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = 0; o.kpp = T.kpp; o.n_pieces = T.n_pieces;
     o.in_kind = in_f16 ? BIN_F16 : BIN_F32; o.in = dX; o.in_row_stride = K; o.in_tok_stride = n_streams * K;
     o.norm_w = d_norm; o.ssq_in = d_ssq_in; o.n_parts_in = 4; o.eps = eps;
     o.epi = epi; o.out32 = d_out; o.out16 = d_out16; o.res = d_res; o.bias = d_bias;
     o.out_row_stride = outw; o.out_tok_stride = n_streams * outw; o.ssq_out = d_ssq;
-    BSched sc{T.p, T.n_tile * K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles, 5, 0};
+    BSched sc{T.p, T.n_tile * K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles, 0, 0};
     BOp * d_ops = e->dalloc<BOp>(1, false);
     BSched * d_sc = e->dalloc<BSched>(1, false);
     StreamState * d_st = e->dalloc<StreamState>(n_streams);
@@ -498,13 +504,35 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     cudaMemcpy(d_ops, &o, sizeof(o), cudaMemcpyHostToDevice);
     cudaMemcpy(d_sc, &sc, sizeof(sc), cudaMemcpyHostToDevice);
     // two "frames": the second pass exercises ring slot / barrier phase recycling
-    if (!launch_batched(e, d_ops, 1, d_sc, 1, d_st, d_act, n_streams, epi == EPI_ADD && res == nullptr ? 1 : 2, false)) return cleanup(0);
+    int iters = 2;
+    if (const char * it = getenv("QTTS_BGEMM_ITERS")) iters = std::max(1, atoi(it));
+    cudaEvent_t t0, t1;
+    cudaEventCreate(&t0); cudaEventCreate(&t1);
+    cudaEventRecord(t0, e->stream);
+    if (iters > 2) { e->prof = e->dalloc<unsigned long long>(4096); e->prof_on = 1; }
+    if (!launch_batched(e, d_ops, 1, d_sc, 1, d_st, d_act, n_streams, iters, false)) return cleanup(0);
+    cudaEventRecord(t1, e->stream);
     cudaError_t r = cudaStreamSynchronize(e->stream);
+    if (iters > 2 && r == cudaSuccess) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, t0, t1);
+        fprintf(stderr, "[bgemm] rows_act=%d rows=%d K=%d n_tile=%d tiles=%d pieces=%d in_f16=%d epi=%d: %.2f us per stage (incl. grid barrier)\n",
+                rows_act, rows, K, T.n_tile, T.n_tiles, T.n_pieces, in_f16, epi, ms * 1e3 / iters);
+        unsigned long long pr[48];
+        cudaMemcpy(pr, e->prof + 2048, sizeof(pr), cudaMemcpyDeviceToHost);
+        if (pr[40]) fprintf(stderr, "[bgemm]   MMA thread per tile (cycles): wait weights %llu, wait A %llu, issue+commit %llu, loop %llu\n",
+                            pr[41] / pr[40], pr[42] / pr[40], pr[43] / pr[40], pr[44] / pr[40]);
+    }
+    cudaEventDestroy(t0); cudaEventDestroy(t1);
     if (r != cudaSuccess) { e->err = std::string("bgemm: ") + cudaGetErrorString(r); return cleanup(0); }
     if (epi == EPI_SWIGLU) {
-        std::vector<__half> oh((size_t) rows_act * outw);
-        cudaMemcpy(oh.data(), d_out16, oh.size() * 2, cudaMemcpyDeviceToHost);
-        for (size_t i = 0; i < oh.size(); ++i) out[i] = __half2float(oh[i]);
+        const size_t cb = (size_t) ((rows_act + 7) / 8) * 2048;
+        std::vector<__half> oh((size_t) (outw / 128 + 1) * cb / 2);
+        cudaMemcpy(oh.data(), d_out16, std::min(oh.size(), (size_t) (rows_act + 8) * rows) * 2, cudaMemcpyDeviceToHost);
+        for (int r = 0; r < rows_act; ++r)
+            for (int k = 0; k < outw; ++k)
+                out[(size_t) r * outw + k] = __half2float(oh[((size_t) (k >> 7) * cb + (size_t) (r >> 3) * 2048 +
+                                                               (size_t) ((k & 127) >> 3) * 128 + (r & 7) * 16 + (k & 7) * 2) / 2]);
     } else {
         cudaMemcpy(out, d_out, (size_t) rows_act * outw * 4, cudaMemcpyDeviceToHost);
     }

@@ -71,6 +71,7 @@ __device__ __forceinline__ bool mbar_test(uint64_t * bar, uint32_t parity) {
 // lives in slot seq % kBSlots; full[slot] completes by bytes (bulk copy), empty[slot] by the
 // tcgen05.commit that follows the last MMA reading the slot.
 // ------------------------------------------------------------------------------------------
+constexpr int kIssuersMax = 4;
 struct BPrefetch {           // used by the prefetcher thread only
     int32_t idx, frame, t, p;
     int32_t n_tiles, n_pieces, tile_bytes, piece_bytes;
@@ -82,6 +83,8 @@ struct BPrefetch {           // used by the prefetcher thread only
 
 struct BShared {
     uint64_t full[kBSlots], empty[kBSlots], abar[2], dbar;
+    uint64_t tfull[4], tempty[4];     // A pieces brought by bulk copies (F16-input stages)
+    uint32_t n_fill[4], n_cons[kIssuersMax][4];   // fills issued (producer) / consumptions done (per MMA issuer) per A buffer
     BRun run;                // copy of the kernel parameter
     BOp op;                  // the stage being executed
     Op item_op;              // Talker attention: per-item view for the batch-1 helpers
@@ -96,8 +99,16 @@ struct BShared {
 };
 constexpr size_t kBSharedBytes = (sizeof(BShared) + 127) & ~(size_t) 127;
 
-__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return reinterpret_cast<unsigned char *>(S) + kBSharedBytes; }
-__device__ __forceinline__ unsigned char * babuf_base(BShared * S) { return bring_base(S) + (size_t) kBSlots * kBSlotBytes; }
+// [BShared][A buffers 2 x kABufBytes][weight ring]: an M = 128 MMA reads 128 rows although a piece
+// may hold fewer; the over-read then falls into the ring (valid shared memory), never past the end
+__device__ __forceinline__ unsigned char * babuf_base(BShared * S) { return reinterpret_cast<unsigned char *>(S) + kBSharedBytes; }
+__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return babuf_base(S) + 2 * (size_t) kABufBytes; }
+// byte offset of element (row r, column col) of an F16 activation matrix stored in global memory
+// as UMMA-canonical chunks of 128 columns (chunk_bytes = ceil(rows / 8) * 2048): LBO 128, SBO 2048
+__device__ __forceinline__ size_t canon_off(int r, int col, int chunk_bytes) {
+    return (size_t) (col >> 7) * chunk_bytes + (size_t) (r >> 3) * 2048 + (size_t) ((col & 127) >> 3) * 128 + (r & 7) * 16 + (col & 7) * 2;
+}
+__device__ __forceinline__ int canon_chunk_bytes(int rows) { return ((rows + 7) >> 3) << 11; }
 
 __device__ __forceinline__ int first_tile(int cta_off) {
     const int G = (int) gridDim.x;
@@ -145,6 +156,7 @@ __device__ __forceinline__ void bpf_ensure(BShared * S, uint32_t seq_needed) {
 }
 
 __device__ __forceinline__ void bgrid_barrier(BShared * S, unsigned int & epoch) {
+    asm volatile("fence.proxy.async.global;" ::: "memory");   // F16 activations are re-read by bulk copies (async proxy)
     __syncthreads();
     if (threadIdx.x == 0) {
         const unsigned int target = epoch + gridDim.x;
@@ -247,7 +259,7 @@ __device__ __forceinline__ void bepilogue16(const BOp & op, int r, int n0, const
         uint4 pk;
         pk.x = *reinterpret_cast<const uint32_t *>(&h[0]); pk.y = *reinterpret_cast<const uint32_t *>(&h[1]);
         pk.z = *reinterpret_cast<const uint32_t *>(&h[2]); pk.w = *reinterpret_cast<const uint32_t *>(&h[3]);
-        *reinterpret_cast<uint4 *>(op.out16 + row_off(r, B, op.out_row_stride, op.out_tok_stride) + (n0 >> 1)) = pk;
+        *reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(op.out16) + canon_off(r, n0 >> 1, canon_chunk_bytes(op.rows_act))) = pk;
         return;
     }
     float * out = op.out32 + row_off(r, B, op.out_row_stride, op.out_tok_stride) + n0;
@@ -262,27 +274,39 @@ __device__ __forceinline__ void bepilogue16(const BOp & op, int r, int n0, const
     if (op.flags & BF_SSQ_OUT) op.ssq_out[(size_t) r * (op.rows >> 4) + (n0 >> 4)] = ss;
 }
 
-// thread 0: the 8 MMAs (K = 16 each) of one activation chunk against the matching columns of the
-// weight piece in the ring, then the commits that recycle the A buffer / the ring slot / publish D
-__device__ __noinline__ void bgemm_issue(BShared * S, int kc, int mt, int buf, int piece, int koff, int kp, uint32_t cons_seq,
-                                         uint32_t idesc, int m_tiles, bool last) {
+// MMA issue is spread over kIssuers threads (lane 0 of warps 0..3, one per SM sub-partition): issuing
+// one tcgen05.mma costs ~60 cycles of a thread's time while a 128 x 16..96 x 16 MMA occupies the
+// tensor pipe for far less, so a single issuer was the bottleneck of a stage (measured: 765 cycles
+// per 8-MMA chunk).  Issuer w takes K-steps [w * 8 / n_iss, (w + 1) * 8 / n_iss) of every chunk and
+// accumulates into its OWN TMEM accumulator (columns (w * m_tiles + mt) * n_tile ..); the epilogue
+// adds the n_iss accumulators in fixed order.  Every issuer commits to the same mbarriers (count
+// kIssuers): tcgen05.commit tracks the MMAs of the executing thread only.
+constexpr int kIssuers = 4;
+__device__ __forceinline__ int n_issuers(int n_tile, int m_tiles) {
+    int n = kIssuers;
+    while (n > 1 && n * m_tiles * n_tile > 512) n >>= 1;
+    return n;
+}
+
+__device__ __noinline__ void bgemm_issue(BShared * S, int w, int n_iss, int kc, int mt, uint32_t a0, uint32_t a_lbo, uint32_t a_sbo,
+                                         uint64_t * a_free, int piece, int koff, int kp, uint32_t cons_seq, uint32_t idesc,
+                                         int m_tiles, bool last) {
     const BOp & op = S->op;
     tc_fence_after();
     const uint32_t seq = cons_seq + (uint32_t) piece;
     const int slot = (int) (seq % (uint32_t) kBSlots);
     if (mt == 0 && koff == 0) mbar_wait(S->full + slot, (seq / (uint32_t) kBSlots) & 1u);
-    const uint32_t a0 = smem_u32(babuf_base(S) + (size_t) buf * kABufBytes);
-    const uint32_t w0 = smem_u32(bring_base(S) + (size_t) slot * kBSlotBytes) + (uint32_t) (koff >> 3) * 128u;
-    const uint32_t d = S->tmem_base + (uint32_t) (mt * op.n_tile);
-    if (!(S->run.dbg & 1)) {
-#pragma unroll
-        for (int ks = 0; ks < kKc / 16; ++ks) {
-            const uint64_t ad = umma_smem_desc(a0 + ks * 2 * kALbo, kALbo, kASbo);
-            const uint64_t bd = umma_smem_desc(w0 + ks * 256, 128, (uint32_t) kp * 16u);
-            umma_f16_ss(d, ad, bd, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+    if (w < n_iss && !(S->run.dbg & 1)) {
+        const uint32_t w0 = smem_u32(bring_base(S) + (size_t) slot * kBSlotBytes) + (uint32_t) (koff >> 3) * 128u;
+        const uint32_t d = S->tmem_base + (uint32_t) ((w * m_tiles + mt) * op.n_tile);
+        const int per = (kKc / 16) / n_iss;
+        const uint64_t ad0 = umma_smem_desc(a0, a_lbo, a_sbo), bd0 = umma_smem_desc(w0, 128, (uint32_t) kp * 16u);
+        for (int i = 0; i < per; ++i) {
+            const int ks = w * per + i;
+            umma_f16_ss(d, ad0 + (uint64_t) ((ks * 2 * a_lbo) >> 4), bd0 + (uint64_t) (ks * 16), idesc, (kc > 0 || i > 0) ? 1u : 0u);
         }
     }
-    umma_commit(S->abar + buf);
+    umma_commit(a_free);
     if (mt == m_tiles - 1 && koff + kKc == kp) umma_commit(S->empty + slot);
     if (last) umma_commit(&S->dbar);
 }
@@ -295,12 +319,16 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t, int m_tiles, uin
     const int dbg = S->run.dbg;
     const int q = warp & 3;
     const int ncg = op.n_tile >> 4;
+    const int n_iss = n_issuers(op.n_tile, m_tiles);
     bool waited = false;
     for (int cg = warp >> 2; cg < ncg; cg += 4) {
         const int n0 = t * op.n_tile + cg * 16;
         for (int mt = 0; mt < m_tiles; ++mt) {
-            const int r = mt * 128 + q * 32 + lane;
-            const bool valid = r < op.rows_act;
+            // M = 128: accumulator row i sits in TMEM lane i; M = 64 (rows_act <= 64): row i sits in lane
+            // (i % 16) + 32 * (i / 16), i.e. lanes 0..15 of each warp's sub-partition
+            const bool m64 = op.rows_act <= 64;
+            const int r = m64 ? q * 16 + lane : mt * 128 + q * 32 + lane;
+            const bool valid = r < op.rows_act && (!m64 || lane < 16);
             float4 side[4];
             if (valid && op.epi == EPI_ADD) {
                 const float * rs = op.res + row_off(r, op.n_streams, op.out_row_stride, op.out_tok_stride) + n0;
@@ -313,8 +341,15 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t, int m_tiles, uin
             if (!waited) { mbar_wait(&S->dbar, d_use & 1u); tc_fence_after(); waited = true; }
             __syncwarp();
             float acc[16];
-            if (!(dbg & 2)) tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
-            else {
+            if (!(dbg & 2)) {
+                tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
+                for (int w = 1; w < n_iss; ++w) {
+                    float more[16];
+                    tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) ((w * m_tiles + mt) * op.n_tile + cg * 16), more);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) acc[i] += more[i];
+                }
+            } else {
 #pragma unroll
                 for (int i = 0; i < 16; ++i) acc[i] = 0.f;
             }
@@ -334,8 +369,9 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
         const int nkc = op.K / kKc;
         const int steps = nkc * m_tiles;
         const int upc = (IN_KIND == BIN_F32 && op.rows_act > 64) ? 2 : 1;     // load units per chunk
+        const int n_iss = n_issuers(op.n_tile, m_tiles);
         const int total = steps * upc;
-        const uint32_t idesc = S->run.idesc_base | ((uint32_t) (op.n_tile >> 3) << 17);
+        const uint32_t idesc = (op.rows_act <= 64 ? (S->run.idesc_base & ~(0x1Fu << 24)) | (4u << 24) : S->run.idesc_base) | ((uint32_t) (op.n_tile >> 3) << 17);
         const bool write_hid = (op.hid_out != nullptr) && (t_first == 0);
         const uint32_t tmem_base = S->tmem_base;
         uint32_t a_use0 = S->a_use[0], a_use1 = S->a_use[1], d_use = S->d_use, cons_seq = S->cons_seq;
@@ -389,8 +425,9 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
                     const int kin = kc * kKc;
                     const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
                     const int kp = min(op.kpp, op.K - piece * op.kpp);
-                    if (tid == 0) {
-                        bgemm_issue(S, kc, mt, buf, piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
+                    if (lane == 0 && warp < kIssuers) {
+                        bgemm_issue(S, warp, n_iss, kc, mt, smem_u32(abuf + (size_t) buf * kABufBytes), kALbo, kASbo, S->abar + buf,
+                                    piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
                     } else if (tid == kPfThread) {
                         // the piece the NEXT chunk needs must be in flight before thread 0 waits for it
                         const int kin1 = min(kin + kKc, op.K - kKc);
@@ -408,6 +445,85 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
             cons_seq += (uint32_t) op.n_pieces;
         }
         if (tid == 0) { S->a_use[0] = a_use0; S->a_use[1] = a_use1; S->d_use = d_use; S->cons_seq = cons_seq; }
+    }
+    if ((op.flags & BF_INC_NPAST) && blockIdx.x == 0 && tid < op.n_streams) {
+        StreamState * st = S->run.st + tid;
+        if (S->run.active[tid] && !st->done) st->n_past += 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// BOP_GEMM with F16 input (O and down projections): the producing stage wrote the activations to
+// global memory already in UMMA-canonical 128-column chunks, so the whole stage is asynchronous:
+// thread kAProd bulk-copies (row block, chunk) pieces L2 -> shared memory (2 or 4 buffers), thread 0
+// waits on the pieces' mbarriers and issues the MMAs, tcgen05.commit recycles the buffers; the other
+// threads only run the epilogue.  No per-chunk CTA barrier, no register staging.
+// ------------------------------------------------------------------------------------------
+constexpr int kAProd = 4 * 32;      // lane 0 of warp 4 (warps 0..3 hold the MMA issuers)
+
+__device__ __noinline__ void bstage_gemm_tma(BShared * S) {
+    const BOp & op = S->op;
+    const int tid = threadIdx.x;
+    const int G = (int) gridDim.x;
+    const int t_first = first_tile(op.cta_off);
+    if (t_first < op.n_tiles) {
+        const int m_tiles = (op.rows_act + 127) >> 7;
+        const int nkc = op.K / kKc;
+        const int steps = nkc * m_tiles;
+        const int Rg = (op.rows_act + 7) >> 3, cb = Rg << 11;
+        const int nab = (Rg <= 8) ? 4 : 2, bstep = 4 / nab;          // buffers in use, barrier index step
+        const int n_iss = n_issuers(op.n_tile, m_tiles);
+        const int lane = tid & 31, warp = tid >> 5;
+        const int abstride = (nab == 4) ? kABufBytes / 2 : kABufBytes;
+        const uint32_t idesc = (op.rows_act <= 64 ? (S->run.idesc_base & ~(0x1Fu << 24)) | (4u << 24) : S->run.idesc_base) | ((uint32_t) (op.n_tile >> 3) << 17);
+        uint32_t d_use = S->d_use, cons_seq = S->cons_seq;
+        unsigned char * abuf = babuf_base(S);
+        for (int t = t_first; t < op.n_tiles; t += G) {
+            if (tid == kAProd) {
+                uint64_t pol;
+                asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+                asm volatile("fence.proxy.async.global;" ::: "memory");
+                const unsigned char * in = reinterpret_cast<const unsigned char *>(op.in);
+                for (int s = 0; s < steps; ++s) {
+                    const int kc = s / m_tiles, mt = s - kc * m_tiles;
+                    const int buf = s % nab, bi = buf * bstep;
+                    const uint32_t nf = S->n_fill[bi];
+                    mbar_wait(S->tempty + bi, (nf & 1u) ^ 1u);
+                    const uint32_t bytes = (uint32_t) min(16, Rg - 16 * mt) << 11;
+                    if (S->run.dbg & 4) {      // bring-up: pipeline overhead without the copy
+                        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->tfull + bi)) : "memory");
+                    } else {
+                        const int kcs = (S->run.dbg & 8) ? (kc + (int) blockIdx.x) % nkc : kc;   // bring-up: staggered chunk order
+                        mbar_expect_tx(S->tfull + bi, bytes);
+                        bulk_g2s(abuf + (size_t) buf * abstride, in + (size_t) kcs * cb + (size_t) mt * 32768, bytes, S->tfull + bi, pol);
+                    }
+                    S->n_fill[bi] = nf + 1;
+                }
+            } else if (lane == 0 && warp < kIssuers) {
+                for (int s = 0; s < steps; ++s) {
+                    const int kc = s / m_tiles, mt = s - kc * m_tiles;
+                    const int buf = s % nab, bi = buf * bstep;
+                    const int kin = kc * kKc;
+                    const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
+                    const int kp = min(op.kpp, op.K - piece * op.kpp);
+                    const uint32_t nc = S->n_cons[warp][bi];
+                    mbar_wait(S->tfull + bi, nc & 1u);
+                    S->n_cons[warp][bi] = nc + 1;
+                    bgemm_issue(S, warp, n_iss, kc, mt, smem_u32(abuf + (size_t) buf * abstride), 128, 2048, S->tempty + bi,
+                                piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
+                }
+            } else if (tid == kPfThread) {
+                bpf_ensure(S, cons_seq + (uint32_t) (op.n_pieces - 1));
+                bpf_poll(S);
+            }
+            __syncwarp();
+            bgemm_epilogue(S, t, m_tiles, d_use);
+            d_use++;
+            tc_fence_before();
+            __syncthreads();
+            cons_seq += (uint32_t) op.n_pieces;
+        }
+        if (tid == 0) { S->d_use = d_use; S->cons_seq = cons_seq; }
     }
     if ((op.flags & BF_INC_NPAST) && blockIdx.x == 0 && tid < op.n_streams) {
         StreamState * st = S->run.st + tid;
@@ -448,6 +564,7 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
     const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
     const int B = op.n_streams, nkv = op.n_kv_heads, rep = op.n_heads / nkv;
     const int kvw = nkv * kHeadDim;
+    float * scw = reinterpret_cast<float *>(babuf_base(S)) + (threadIdx.x >> 5) * 16;
     for (int item = gw; item < B * nkv; item += nw) {
         const int b = item / nkv, g = item - b * nkv;
         __half * kc = op.kc + (size_t) b * op.kv_stream_stride;
@@ -502,48 +619,48 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
 #pragma unroll
                     for (int j = 0; j < 4; ++j) qh[j] = f16r(q[j]);
                     const int n_kv = pos + 1;       // <= 16
-                    float sc[16];
+                    // scores through a per-warp shared-memory row (keeps the register count down: spills
+                    // would go to L2, there is no L1 left next to 222 KB of shared memory)
                     float mx = -CUDART_INF_F;
-#pragma unroll
-                    for (int jk = 0; jk < 16; ++jk) {
+                    for (int jk = 0; jk < n_kv; ++jk) {
                         float s = 0.f;
-                        if (jk < n_kv) {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                s = fmaf(__half2float(kc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), qh[j], s);
-                        }
+                        for (int j = 0; j < 4; ++j)
+                            s = fmaf(__half2float(kc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), qh[j], s);
                         s = warp_sum(s) * op.kq_scale;
-                        sc[jk] = s;
-                        if (jk < n_kv) mx = fmaxf(mx, s);
+                        if (lane == jk) scw[jk] = s;
+                        mx = fmaxf(mx, s);
                     }
+                    __syncwarp();
                     double sum = 0.0;
-#pragma unroll
-                    for (int jk = 0; jk < 16; ++jk) {
-                        const float e = (jk < n_kv) ? expf(sc[jk] - mx) : 0.f;
-                        sc[jk] = e;
-                        sum += (double) e;
-                    }
+                    for (int jk = 0; jk < n_kv; ++jk) sum += (double) expf(scw[jk] - mx);
                     const float inv = (float) (1.0 / sum);
                     float part[4][4];
 #pragma unroll
                     for (int pp = 0; pp < 4; ++pp)
 #pragma unroll
                         for (int j = 0; j < 4; ++j) part[pp][j] = 0.f;
+                    for (int j0 = 0; j0 < n_kv; j0 += 4) {
 #pragma unroll
-                    for (int jk = 0; jk < 16; ++jk) {
-                        if (jk < n_kv) {
-                            const float p = f16r(sc[jk] * inv);     // the P.V mul_mat rounds P to F16
+                        for (int pp = 0; pp < 4; ++pp) {
+                            const int jk = j0 + pp;
+                            if (jk < n_kv) {
+                                const float p = f16r(expf(scw[jk] - mx) * inv);     // the P.V mul_mat rounds P to F16
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                part[jk & 3][j] = fmaf(__half2float(vc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), p, part[jk & 3][j]);
+                                for (int j = 0; j < 4; ++j)
+                                    part[pp][j] = fmaf(__half2float(vc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), p, part[pp][j]);
+                            }
                         }
                     }
+                    __syncwarp();
 #pragma unroll
                     for (int j = 0; j < 4; ++j) o[j] = (part[0][j] + part[1][j]) + (part[2][j] + part[3][j]);
                 }
-                __half * out = op.attn16 + (size_t) (t * B + b) * op.attn_w + (size_t) h * kHeadDim;
+                unsigned char * out = reinterpret_cast<unsigned char *>(op.attn16);
+                const int cb = canon_chunk_bytes(op.rows_act);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) out[lane + 32 * j] = __float2half_rn(o[j]);
+                for (int j = 0; j < 4; ++j)
+                    *reinterpret_cast<__half *>(out + canon_off(t * B + b, h * kHeadDim + lane + 32 * j, cb)) = __float2half_rn(o[j]);
             }
         }
     }
@@ -554,7 +671,7 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
 // + F16 KV append, FP32 softmax and P.V over the F16 cache (ATTN_FAST numerics of qtts_kernels.cu).
 // ------------------------------------------------------------------------------------------
 template <int REP>
-__device__ void battn_tk_item(const Op & iop, const float * qkv, __half * out16, int pos, AttnSmem * sm, float * sc) {
+__device__ void battn_tk_item(const Op & iop, const float * qkv, unsigned char * out16, int row, int cb, int pos, AttnSmem * sm, float * sc) {
     const int tid = threadIdx.x;
     const int n_kv = pos + 1, kvw = iop.n_kv_heads * kHeadDim;
     const int g = iop.book;                      // KV group of this item (field reused)
@@ -597,7 +714,7 @@ __device__ void battn_tk_item(const Op & iop, const float * qkv, __half * out16,
         const int r = idx / kHeadDim, d = idx % kHeadDim;
         const float o = (sm->part[0][r][d] + sm->part[1][r][d]) + (sm->part[2][r][d] + sm->part[3][r][d]);
         const float lr = (r == 0) ? l[0] : l[REP - 1 < r ? REP - 1 : r];
-        out16[(size_t) (g * REP + r) * kHeadDim + d] = __float2half_rn(o / lr);
+        *reinterpret_cast<__half *>(out16 + canon_off(row, (g * REP + r) * kHeadDim + d, cb)) = __float2half_rn(o / lr);
     }
     __syncthreads();
 }
@@ -624,10 +741,11 @@ __device__ __noinline__ void bstage_attn_tk(BShared * S) {
         }
         __syncthreads();
         const float * qkv = op.qkv + (size_t) b * op.qkvw;
-        __half * out16 = op.attn16 + (size_t) b * op.attn_w;
-        if (rep == 1)      battn_tk_item<1>(*iop, qkv, out16, pos, sm, sc);
-        else if (rep == 2) battn_tk_item<2>(*iop, qkv, out16, pos, sm, sc);
-        else               battn_tk_item<4>(*iop, qkv, out16, pos, sm, sc);
+        unsigned char * out16 = reinterpret_cast<unsigned char *>(op.attn16);
+        const int cb = canon_chunk_bytes(op.rows_act);
+        if (rep == 1)      battn_tk_item<1>(*iop, qkv, out16, b, cb, pos, sm, sc);
+        else if (rep == 2) battn_tk_item<2>(*iop, qkv, out16, b, cb, pos, sm, sc);
+        else               battn_tk_item<4>(*iop, qkv, out16, b, cb, pos, sm, sc);
     }
 }
 
@@ -779,8 +897,12 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
     for (int i = threadIdx.x; i < (int) (sizeof(BRun) / 4); i += kThreads)
         reinterpret_cast<uint32_t *>(&S->run)[i] = reinterpret_cast<const uint32_t *>(&run_param)[i];
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kBSlots; ++i) { mbar_init(S->full + i, 1); mbar_init(S->empty + i, 1); }
-        mbar_init(S->abar, 1); mbar_init(S->abar + 1, 1); mbar_init(&S->dbar, 1);
+        for (int i = 0; i < kBSlots; ++i) { mbar_init(S->full + i, 1); mbar_init(S->empty + i, kIssuers); }
+        mbar_init(S->abar, kIssuers); mbar_init(S->abar + 1, kIssuers); mbar_init(&S->dbar, kIssuers);
+        for (int i = 0; i < 4; ++i) {
+            mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, kIssuers); S->n_fill[i] = 0;
+            for (int w = 0; w < kIssuersMax; ++w) S->n_cons[w][i] = 0;
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         S->cons_seq = 0; S->a_use[0] = 0; S->a_use[1] = 0; S->d_use = 0; S->all_done = 0;
@@ -821,7 +943,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
             switch (type) {
                 case BOP_GEMM:
                     if (in_kind == BIN_F32) bstage_gemm<BIN_F32>(S);
-                    else                    bstage_gemm<BIN_F16>(S);
+                    else                    bstage_gemm_tma(S);
                     break;
                 case BOP_ATTN_CP: bstage_attn_cp(S); break;
                 case BOP_ATTN_TK: bstage_attn_tk(S); break;

@@ -228,12 +228,13 @@ bool batched_init(Engine * e) {
         BGroup G;
         G.s0 = s0; G.n = std::min(128, e->max_streams - s0);
         const size_t B = (size_t) G.n;
+        const size_t B8 = (B + 7) & ~(size_t) 7, B28 = (2 * B + 7) & ~(size_t) 7;   // F16 activations: canonical chunks, rows padded to 8
         G.x = e->dalloc<float>(B * H); G.qkv = e->dalloc<float>(B * qkvw);
-        G.attn16 = e->dalloc<__half>(B * c.n_heads * kHeadDim); G.act16 = e->dalloc<__half>(B * c.intermediate_size);
+        G.attn16 = e->dalloc<__half>(B8 * c.n_heads * kHeadDim); G.act16 = e->dalloc<__half>(B8 * c.intermediate_size);
         G.ssq_e = e->dalloc<float>(B); G.ssq_p = e->dalloc<float>(B * (H / 16));
         G.emb = e->dalloc<float>(2 * B * H);
         G.cp_x = e->dalloc<float>(2 * B * std::max(H, cpH)); G.cp_qkv = e->dalloc<float>(2 * B * cqkvw);
-        G.cp_attn16 = e->dalloc<__half>(2 * B * c.cp_n_heads * kHeadDim); G.cp_act16 = e->dalloc<__half>(2 * B * c.cp_intermediate_size);
+        G.cp_attn16 = e->dalloc<__half>(B28 * c.cp_n_heads * kHeadDim); G.cp_act16 = e->dalloc<__half>(B28 * c.cp_intermediate_size);
         G.cp_ssq_e = e->dalloc<float>(2 * B); G.cp_ssq_p = e->dalloc<float>(2 * B * (cpH / 16));
         G.cp_logits = e->dalloc<float>(B * c.cp_vocab_size);
         G.cp_kc = e->dalloc<__half>(B * c.cp_layers * 16 * c.cp_n_kv_heads * kHeadDim);
