@@ -518,8 +518,13 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
         cudaEventElapsedTime(&ms, t0, t1);
         fprintf(stderr, "[bgemm] rows_act=%d rows=%d K=%d n_tile=%d tiles=%d pieces=%d in_f16=%d epi=%d: %.2f us per stage (incl. grid barrier)\n",
                 rows_act, rows, K, T.n_tile, T.n_tiles, T.n_pieces, in_f16, epi, ms * 1e3 / iters);
-        unsigned long long pr[48];
+        unsigned long long pr[64];
         cudaMemcpy(pr, e->prof + 2048, sizeof(pr), cudaMemcpyDeviceToHost);
+        if (pr[56]) fprintf(stderr, "[bgemm]   issuer 0 per call (cycles): fence + wait weights %llu, MMA issue %llu, commits %llu (calls %llu)\n",
+                            pr[57] / pr[56], pr[58] / pr[56], pr[59] / pr[56], pr[56]);
+        if (pr[48]) fprintf(stderr, "[bgemm]   F32 stage, thread 0 of tile 0's CTA (cycles per tile): prologue %llu, wait A buffer %llu, convert+store (incl. load latency) %llu, "
+                            "fence+sync %llu, issue %llu, epilogue+sync %llu, total %llu\n", pr[49] / pr[48], pr[50] / pr[48], pr[51] / pr[48],
+                            pr[52] / pr[48], pr[53] / pr[48], pr[54] / pr[48], pr[55] / pr[48]);
         if (pr[40]) fprintf(stderr, "[bgemm]   MMA thread per tile (cycles): wait weights %llu, wait A %llu, issue+commit %llu, loop %llu\n",
                             pr[41] / pr[40], pr[42] / pr[40], pr[43] / pr[40], pr[44] / pr[40]);
     }

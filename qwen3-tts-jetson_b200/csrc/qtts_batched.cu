@@ -382,43 +382,53 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
         // per-row RMSNorm scale from the producers' partial sums (double sum like ggml's rms_norm,
         // ops.cpp:3738-3747)
         if (IN_KIND == BIN_F32 && op.norm_w) {
-            if (tid < op.rows_act) {
+            // 4 threads per row, all partial loads of a thread in flight together (one L2 round trip per
+            // 128 partials instead of one per 8: this prologue was a quarter of the stage)
+            const int np = op.n_parts_in, sub = tid & 3;
+            for (int r0 = 0; r0 < op.rows_act; r0 += kThreads / 4) {
+                const int r = r0 + (tid >> 2);
                 double ss = 0.0;
-                const float * p = op.ssq_in + (size_t) tid * op.n_parts_in;
-                for (int i = 0; i < op.n_parts_in; i += 8) {
-                    float q[8];
+                if (r < op.rows_act) {
+                    const float * p = op.ssq_in + (size_t) r * np;
+                    for (int base = 0; base < np; base += 128) {
+                        float q[32];
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) q[u] = (i + u < op.n_parts_in) ? __ldcg(p + i + u) : 0.f;
+                        for (int u = 0; u < 32; ++u) { const int i = base + sub + 4 * u; q[u] = (i < np) ? __ldcg(p + i) : 0.f; }
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) ss += (double) q[u];
+                        for (int u = 0; u < 32; ++u) ss += (double) q[u];
+                    }
                 }
-                const float mean = (float) (ss / (double) op.K);
-                S->scale[tid] = 1.0f / sqrtf(mean + op.eps);
+                ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+                ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+                if (sub == 0 && r < op.rows_act) {
+                    const float mean = (float) (ss / (double) op.K);
+                    S->scale[r] = 1.0f / sqrtf(mean + op.eps);
+                }
             }
             __syncthreads();
         }
 
         for (int t = t_first; t < op.n_tiles; t += G) {
-            // one load unit in flight: the loads of unit j+1 are issued right after unit j went to
-            // shared memory and overlap the fence / barrier / MMA issue of unit j
-            uint4 cur[4];
-            float4 nwc = make_float4(1.f, 1.f, 1.f, 1.f);
+            // two load units in flight (two named register sets, loop unrolled by two): the loads of
+            // unit j+2 are issued as soon as unit j went to shared memory
+            uint4 v0[4], v1[4];
+            float4 nw0 = make_float4(1.f, 1.f, 1.f, 1.f), nw1 = nw0;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) cur[i] = make_uint4(0u, 0u, 0u, 0u);
-            bload<IN_KIND>(op, 0, 0, 0, cur, nwc);
-            if (tid == kPfThread) bpf_ensure(S, cons_seq);
-            int kc = 0, mt = 0, u = 0, s = 0;
-            for (int j = 0; j < total; ++j) {
+            for (int i = 0; i < 4; ++i) { v0[i] = make_uint4(0u, 0u, 0u, 0u); v1[i] = v0[i]; }
+            auto load_unit = [&](int j, uint4 * v, float4 & nw) {
+                const int s = j / upc, u = j - s * upc;
+                const int kc = s / m_tiles, mt = s - kc * m_tiles;
+                bload<IN_KIND>(op, kc, mt, u, v, nw);
+            };
+            auto process = [&](int j, const uint4 * v, const float4 & nw) {
+                const int s = j / upc, u = j - s * upc;
+                const int kc = s / m_tiles, mt = s - kc * m_tiles;
                 const int buf = s & 1;
                 if (u == 0) {       // the MMAs that read this buffer two chunks ago must be done
                     const uint32_t au = buf ? a_use1 : a_use0;
                     if (au > 0) mbar_wait(S->abar + buf, (au - 1) & 1u);
                 }
-                bstore<IN_KIND>(op, S, abuf + (size_t) buf * kABufBytes, kc, mt, u, cur, nwc, write_hid);
-                // position of unit j + 1
-                int kc1 = kc, mt1 = mt, u1 = u + 1, s1 = s;
-                if (u1 == upc) { u1 = 0; s1 = s + 1; if (++mt1 == m_tiles) { mt1 = 0; ++kc1; } }
-                if (j + 1 < total) bload<IN_KIND>(op, kc1, mt1, u1, cur, nwc);
+                bstore<IN_KIND>(op, S, abuf + (size_t) buf * kABufBytes, kc, mt, u, v, nw, write_hid);
                 if (u == upc - 1) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     __syncthreads();
@@ -429,14 +439,24 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
                         bgemm_issue(S, warp, n_iss, kc, mt, smem_u32(abuf + (size_t) buf * kABufBytes), kALbo, kASbo, S->abar + buf,
                                     piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
                     } else if (tid == kPfThread) {
-                        // the piece the NEXT chunk needs must be in flight before thread 0 waits for it
+                        // the piece the NEXT chunk needs must be in flight before the issuers wait for it
                         const int kin1 = min(kin + kKc, op.K - kKc);
                         bpf_ensure(S, cons_seq + (uint32_t) (kin1 / op.kpp));
                         bpf_poll(S);
                     }
                     if (buf) a_use1++; else a_use0++;
                 }
-                kc = kc1; mt = mt1; u = u1; s = s1;
+            };
+            load_unit(0, v0, nw0);
+            if (total > 1) load_unit(1, v1, nw1);
+            if (tid == kPfThread) bpf_ensure(S, cons_seq);
+            for (int j = 0; j < total; j += 2) {
+                process(j, v0, nw0);
+                if (j + 2 < total) load_unit(j + 2, v0, nw0);
+                if (j + 1 < total) {
+                    process(j + 1, v1, nw1);
+                    if (j + 3 < total) load_unit(j + 3, v1, nw1);
+                }
             }
             bgemm_epilogue(S, t, m_tiles, d_use);
             d_use++;
@@ -920,6 +940,8 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
     tc_fence_after();
     if (threadIdx.x == kPfThread) bpf_poll(S);
     unsigned int epoch = 0;
+    uint32_t next_word = 0;
+    bool have_next = false;
     const int n_frames = run_param.n_frames, n_ops = run_param.n_ops, n_streams = run_param.n_streams;
     const bool prof = run_param.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
 
@@ -934,9 +956,16 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
             if (S->all_done) break;
         }
         for (int i = 0; i < n_ops; ++i) {
-            // stage descriptor -> shared memory (the previous stage ended with a barrier)
-            for (int w = threadIdx.x; w < (int) (sizeof(BOp) / 4); w += kThreads)
-                reinterpret_cast<uint32_t *>(&S->op)[w] = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + i) + w);
+            // stage descriptor -> shared memory (the previous stage ended with a barrier); the descriptor
+            // of the NEXT stage is requested now and parked in a register during the stage
+            static_assert(sizeof(BOp) / 4 <= kThreads, "one word per thread");
+            if (threadIdx.x < (int) (sizeof(BOp) / 4)) {
+                if (!have_next) next_word = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + i) + threadIdx.x);
+                reinterpret_cast<uint32_t *>(&S->op)[threadIdx.x] = next_word;
+                const int ni = (i + 1 < n_ops) ? i + 1 : 0;
+                next_word = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + ni) + threadIdx.x);
+                have_next = true;
+            }
             __syncthreads();
             const int type = S->op.type, in_kind = S->op.in_kind;
             const long long t0 = prof ? clock64() : 0;
