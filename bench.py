@@ -36,6 +36,9 @@ N_TEXT = 200            # synthetic text ids: EOS ramp would start at frame 4*20
 PRESET, SEED = "0.6b", 1234
 TEMP, TOP_K, REP_PEN = 0.9, 50, 1.05
 REF_FRAMES = 24         # bounded CPU sample per step of the reference arm
+B_FRAMES = 64           # frames per stream of the batched legs (configs[2] / configs[3])
+B_TEXT = (32, 256)      # ragged text lengths of the batched legs
+B_TOTAL = 512           # configs[3]: 512 concurrent streams sharded by utterance over the GPUs
 METRIC, UNIT = "codec_frames_per_s", "frames/s"
 
 # algorithmic bytes per frame-step, 0.6B, BF16 weights (SURVEY.md §8d / DESIGN.md):
@@ -226,6 +229,13 @@ def run_ours(args, pkg):
         wall = time.perf_counter() - t0
     barrier()
     launches = T.launch_count() - l0
+    T.unload_model()
+    batched = []
+    if not args.no_batched:
+        for streams in sorted({64, max(1, B_TOTAL // world)}):
+            res = run_batched_leg(pkg, torch, dist, path, cfg, local, rank, world, streams, barrier)
+            res["streams_per_gpu"] = streams
+            batched.append(res)
     vals = torch.tensor([loop_ms, wall * 1e3, frames, float(launches)], dtype=torch.float64, device="cuda")
     if dist is not None:
         mx = vals.clone()
@@ -258,6 +268,28 @@ def run_ours(args, pkg):
                              "traffic": None, "kernel": "qtts_run_program", "peak_source": peak_src,
                              "algorithmic_bytes_per_frame": bytes_per_frame},
                 "clocks": clocks.summary()}
+        line["gpu_launches"] = launches + sum(b["launches"] for b in batched)
+        line["batched"] = []
+        for b in batched:
+            S = b["streams_per_gpu"]
+            fps = b["frames"] / (b["dev_ms"] / 1e3)
+            step_ms = b["dev_ms"] / (b["frames"] / (S * world))
+            # one frame-step of a group of <= 128 streams streams the weights once; KV per stream
+            groups = (S + 127) // 128
+            bytes_step = groups * WEIGHT_BYTES_PER_FRAME + S * KV_BYTES_PER_TOKEN * (b["n_kv_mean"] + 1)
+            ach = bytes_step / (step_ms / 1e3) / 1e9
+            line["batched"].append({
+                "workload": ("BASELINE configs[2]: 64 concurrent utterances on one GPU" if S == 64 and world == 1 else
+                             f"BASELINE configs[3]: {B_TOTAL} concurrent streams sharded by utterance over {world} GPU(s)") +
+                            f", ragged texts {B_TEXT[0]}-{B_TEXT[1]} tokens, cached speaker embeddings, temperature {TEMP} top-k {TOP_K}, "
+                            f"{B_FRAMES} frames per stream, batched tcgen05 kernel (groups of <= 128 streams in lock step)",
+                "streams_per_gpu": S, "streams_total": S * world, "value": fps, "unit": UNIT,
+                "ms_per_frame_step": step_ms, "rtf_per_stream": (step_ms / 1e3) * 12.5,
+                "e2e": {"value": b["frames"] / (b["wall_ms"] / 1e3), "unit": UNIT,
+                        "includes": "stream_begin (token/speaker H2D, prefill) + step_frames with codes D2H",
+                        "stream_begin_ms_total": b["begin_ms"]},
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                             "kernel": "qtts_run_batched", "algorithmic_bytes_per_frame_step": bytes_step}})
         if world == 1 and not args.no_cpu_baseline:
             try:
                 cores = host_cores()
@@ -267,11 +299,60 @@ def run_ours(args, pkg):
                                                   f"unmodified reference on ggml CPU backend ({ms[0] / 1e3:.1f} s)"}
             except Exception as ex:   # the checker is missing: say so instead of inventing a number
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
-        print(json.dumps(line), flush=True)
-    T.unload_model()
+            print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+def run_batched_leg(pkg, torch, dist, path, cfg, local, rank, world, streams, barrier):
+    """`streams` concurrent utterances on this GPU advanced in lock step by the batched tcgen05 kernel.
+    Returns (frames over all ranks, device ms max over ranks, wall ms max over ranks, launches, mean n_kv)."""
+    n_text_max = B_TEXT[1]
+    T = pkg.TTSTransformer(device=local, max_streams=streams, max_ctx=B_FRAMES + n_text_max + 32)
+    if not T.load_model(path):
+        raise RuntimeError("load_model (batched): " + T.get_error())
+    T.set_numerics(pkg.NUMERICS_FAST, 4)
+    T.set_ignore_eos(True)
+    r = np.random.default_rng(1000 + rank)
+    texts = [pkg.synth.synth_tokens(cfg, n_text=int(r.integers(B_TEXT[0], B_TEXT[1] + 1)), seed=rank * 4096 + i) for i in range(streams)]
+    spks = [pkg.synth.synth_speaker(cfg, seed=rank * 4096 + i) for i in range(streams)]
+
+    def one_pass(seed0):
+        t0 = time.perf_counter()
+        for i in range(streams):
+            if not T.stream_begin(i, texts[i], spks[i], max_len=B_FRAMES, temperature=TEMP, top_k=TOP_K,
+                                  repetition_penalty=REP_PEN, seed=seed0 + i):
+                raise RuntimeError("stream_begin: " + T.get_error())
+        t1 = time.perf_counter()
+        frames, dev_ms = 0, 0.0
+        while True:
+            out = T.step_frames(32)
+            if out is None:
+                raise RuntimeError("step_frames: " + T.get_error())
+            codes, produced, active = out
+            frames += int(produced.sum())
+            dev_ms += T.last_loop_ms()
+            if not active.any():
+                break
+        t2 = time.perf_counter()
+        return frames, dev_ms, (t2 - t0) * 1e3, (t1 - t0) * 1e3
+
+    one_pass(7)                                   # warm-up pass (also pages in the tiled weights)
+    barrier()
+    l0 = T.launch_count()
+    frames, dev_ms, wall_ms, begin_ms = one_pass(99)
+    barrier()
+    launches = T.launch_count() - l0
+    T.unload_model()
+    vals = torch.tensor([dev_ms, wall_ms, float(frames), float(launches), begin_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        mx = vals.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = vals.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dev_ms, wall_ms, frames, launches, begin_ms = float(mx[0]), float(mx[1]), float(sm[2]), int(sm[3]), float(mx[4])
+    # mean cached tokens per stream per frame: prefill (~10) + trailing grows one per frame
+    n_kv_mean = 10 + (B_FRAMES - 1) / 2.0 + 1
+    return {"frames": frames, "dev_ms": dev_ms, "wall_ms": wall_ms, "begin_ms": begin_ms, "launches": launches, "n_kv_mean": n_kv_mean}
 
 
 def main():
@@ -281,6 +362,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-batched", action="store_true", help="skip the batched (configs[2]/[3]) legs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     import qtts_pkg
