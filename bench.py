@@ -299,7 +299,7 @@ def run_ours(args, pkg):
                                                   f"unmodified reference on ggml CPU backend ({ms[0] / 1e3:.1f} s)"}
             except Exception as ex:   # the checker is missing: say so instead of inventing a number
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
-            print(json.dumps(line), flush=True)
+        print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
     return 0

@@ -264,7 +264,7 @@ __device__ __forceinline__ float dot8h(const uint4 w, const uint4 x) {
 // weights are read from the shared-memory ring (chunk = cons_seq + q / pairs_per_chunk), the
 // F16-rounded activations from xh.  Residual / bias values are requested before the dot products.
 template <int NT>
-__device__ void gemv_rows(const Op & op, const __half * xh, const Ring & ring, uint32_t cons_seq, int p0,
+__device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, const Ring ring, uint32_t cons_seq, int p0,
                           int q_begin, int q_end, unsigned long long * prof_wait) {
     const int K = op.K, kv = K >> 3;      // uint4 per row
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1145,6 +1145,10 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
     __shared__ __align__(8) uint64_t full_bar[kNumSlots];
     __shared__ double red[kWarps];
     __shared__ LocalState ls;
+    __shared__ Op sop;
+    static_assert(sizeof(Op) % 4 == 0 && sizeof(Op) / 4 <= kThreads, "one descriptor word per thread");
+    uint32_t next_word = 0;
+    bool have_next = false;
 
     Ring ring;
     ring.base = smem_raw;
@@ -1193,7 +1197,19 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
     for (int f = 0; f < n_frames && !stop; ++f) {
         if (cfg.check_done && ls.done) break;
         for (int i = 0; i < n_ops && !stop; ++i) {
-            const Op & op = ops[i];
+            // stage descriptor -> shared memory (with ~225 KB of shared memory per CTA there is no L1 left:
+            // every field read from the global descriptor was an L2 round trip); the NEXT stage's
+            // descriptor is requested now and parked in a register during the stage
+            __syncthreads();
+            if (threadIdx.x < (int) (sizeof(Op) / 4)) {
+                if (!have_next) next_word = __ldg(reinterpret_cast<const uint32_t *>(ops + i) + threadIdx.x);
+                reinterpret_cast<uint32_t *>(&sop)[threadIdx.x] = next_word;
+                const int ni = (i + 1 < n_ops) ? i + 1 : 0;
+                next_word = __ldg(reinterpret_cast<const uint32_t *>(ops + ni) + threadIdx.x);
+                have_next = true;
+            }
+            __syncthreads();
+            const Op & op = sop;
             bool all_to_all = true;
             const bool prof_on = cfg.prof && blockIdx.x == cfg.prof_cta && threadIdx.x == 0;
             const long long t0 = prof_on ? clock64() : 0;
