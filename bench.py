@@ -236,15 +236,10 @@ def run_ours(args, pkg):
             res = run_batched_leg(pkg, torch, dist, path, cfg, local, rank, world, streams, barrier)
             res["streams_per_gpu"] = streams
             batched.append(res)
-    vals = torch.tensor([loop_ms, wall * 1e3, frames, float(launches)], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        mx = vals.clone()
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = vals.clone()
-        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        loop_ms, wall_ms, frames, launches = float(mx[0]), float(mx[1]), float(sm[2]), int(sm[3])
-    else:
-        wall_ms = wall * 1e3
+    # job-level counters: device / wall time = max over ranks, frames / launches = sum over ranks
+    red = pkg.sharding.JobCounters(dist, "cuda").reduce({"loop_ms": loop_ms, "wall_ms": wall * 1e3},
+                                                        {"frames": frames, "launches": launches})
+    loop_ms, wall_ms, frames, launches = red["loop_ms"], red["wall_ms"], red["frames"], int(red["launches"])
     value = frames / (loop_ms / 1e3)
     e2e = frames / (wall_ms / 1e3)
 
@@ -345,11 +340,9 @@ def run_batched_leg(pkg, torch, dist, path, cfg, local, rank, world, streams, ba
     barrier()
     launches = T.launch_count() - l0
     T.unload_model()
-    vals = torch.tensor([dev_ms, wall_ms, float(frames), float(launches), begin_ms], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        mx = vals.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = vals.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        dev_ms, wall_ms, frames, launches, begin_ms = float(mx[0]), float(mx[1]), float(sm[2]), int(sm[3]), float(mx[4])
+    red = pkg.sharding.JobCounters(dist, "cuda").reduce({"dev_ms": dev_ms, "wall_ms": wall_ms, "begin_ms": begin_ms},
+                                                        {"frames": frames, "launches": launches})
+    dev_ms, wall_ms, begin_ms, frames, launches = red["dev_ms"], red["wall_ms"], red["begin_ms"], red["frames"], int(red["launches"])
     # mean cached tokens per stream per frame: prefill (~10) + trailing grows one per frame
     n_kv_mean = 10 + (B_FRAMES - 1) / 2.0 + 1
     return {"frames": frames, "dev_ms": dev_ms, "wall_ms": wall_ms, "begin_ms": begin_ms, "launches": launches, "n_kv_mean": n_kv_mean}

@@ -38,5 +38,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+CPP = os.path.join(HERE, "..", "cpp")
+ADAPTER_CHECK = os.path.join(CPP, "adapter_check")
+
+
+def build_adapter_check(force: bool = False) -> str:
+    """g++ build of the C++ host adapter's driver (cpp/adapter_check.cpp) against the C-ABI library."""
+    srcs = [os.path.join(CPP, f) for f in ("adapter_check.cpp", "qtts_transformer.hpp", "qtts_gguf.hpp")]
+    if not force and os.path.exists(ADAPTER_CHECK) and \
+            all(os.path.getmtime(s) <= os.path.getmtime(ADAPTER_CHECK) for s in srcs + [LIB]):
+        return ADAPTER_CHECK
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", srcs[0], "-o", ADAPTER_CHECK,
+           "-L" + HERE, "-lqtts_b200", "-Wl,-rpath,$ORIGIN/../" + os.path.basename(HERE)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
+    return ADAPTER_CHECK
+
+
 if __name__ == "__main__":
     print(build(force=True, verbose=True))
