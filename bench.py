@@ -163,6 +163,9 @@ def run_reference(args, pkg):
     return 0
 
 
+NCU_DRAM_BYTES_PER_LAUNCH = 130976350000 + 39054080
+
+
 def workload_config(world: int) -> dict:
     return {"workload": "BASELINE configs[1]: Qwen3-TTS-12Hz-0.6B random-init, batch 1 per GPU, temperature 0.9 top-k 50, "
                         f"{FRAMES} frames per utterance",
@@ -260,7 +263,11 @@ def run_ours(args, pkg):
                         "d2h_bytes_per_step": FRAMES * 16 * 4},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "kernel": "qtts_run_program", "peak_source": peak_src,
+                             # dram__bytes_read.sum + dram__bytes_write.sum of one 40-frame launch, from the
+                             # ncu --set full capture summarised in profiles/r01f_frame_ncu.md
+                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r01f_frame_ncu.md",
+                             "frames_per_launch": 40, "algorithmic_bytes_per_launch": bytes_per_frame * 40,
+                             "kernel": "qtts_run_program", "peak_source": peak_src,
                              "algorithmic_bytes_per_frame": bytes_per_frame},
                 "clocks": clocks.summary()}
         line["gpu_launches"] = launches + sum(b["launches"] for b in batched)
