@@ -48,6 +48,10 @@ int qtts_create(const qtts_config * cfg, int device, int max_streams, int max_ct
     e->max_ctx = max_ctx;
     e->max_text = std::max(max_ctx, 64);
     e->n_sms = prop.multiProcessorCount;
+    // flag-carrying activations need every CTA to own rows of every stage of a chain (a CTA that
+    // only reads could be overtaken by the next writer of the buffer)
+    if (const char * v = getenv("QTTS_LL")) e->ll = atoi(v) ? 1 : 0;
+    if (std::min(cfg->hidden_size, cfg->cp_hidden_size) / 2 < e->n_sms) e->ll = 0;
     int k_max = std::max({cfg->hidden_size, cfg->intermediate_size, cfg->cp_hidden_size, cfg->cp_intermediate_size,
                           cfg->text_embd_dim, cfg->n_heads * cfg->head_dim, cfg->cp_n_heads * cfg->cp_head_dim});
     // widest input of a two-token (merged code-predictor) stage

@@ -62,6 +62,8 @@ struct Slot {
     float * x = nullptr, * qkv = nullptr, * attn = nullptr, * act = nullptr;
     float * logits = nullptr, * hidden = nullptr, * in_embd = nullptr;
     float * cp_x = nullptr, * cp_qkv = nullptr, * cp_attn = nullptr, * cp_act = nullptr, * cp_logits = nullptr;
+    // flag-carrying copies of the residual stream and the SwiGLU output (Op::out_ll)
+    unsigned long long * x_ll = nullptr, * act_ll = nullptr, * cp_x_ll = nullptr, * cp_act_ll = nullptr;
     float * cp_hidden_in = nullptr;        // hidden handed to predict_codes by the API
     float * cp_dump = nullptr;             // [15][cp_vocab]
     float * cb0_dump = nullptr;            // [V]
@@ -105,6 +107,8 @@ struct Engine {
     int numerics = QTTS_NUMERICS_REFERENCE;
     int ref_threads = 4;          // ggml's default thread count (ggml/include/ggml.h:232)
     int persistent = 1;
+    int ll = 1;                    // flag-carrying activations between GEMV stages instead of grid barriers (env QTTS_LL=0: off)
+    uint32_t ll_seq = 0;           // stage tags handed out so far (monotonic across launches)
     int ignore_eos = 0;
     int64_t n_weights = 0, n_inexact = 0, weight_bytes = 0, kv_bytes = 0;
     int64_t launches = 0;

@@ -96,6 +96,7 @@ struct RunCfg {
     int32_t prof_cta;
     int32_t n_sched;        // GEMV stages per frame
     const WSched * sched;   // [n_sched]
+    uint32_t tag_base;      // stage tags of this launch are tag_base + 1 + (frame * n_ops + op index)
     unsigned long long * prof;   // optional [8 op types][8] cycle counters filled by CTA 0 (nullptr: off)
 };
 
@@ -146,15 +147,28 @@ struct Ring {
 
 constexpr int kPfThread = kThreads - 32;   // lane 0 of the last warp issues the bulk copies
 
-struct Prefetch {           // lives in the prefetcher thread's registers
+// Prefetcher state.  It lives in SHARED memory: only one thread uses it, and as a local variable of
+// the kernel it cost every thread ~20 registers (spilled around the stages; with ~225 KB of shared
+// memory there is no L1 to catch spills).  Upcoming schedule entries are pulled into `ent` by
+// cp.async two entries ahead, so advancing never waits for an L2 round trip.
+struct Prefetch {
     int32_t idx, frame;     // schedule entry, frame being prefetched
     int32_t q, p1;          // next row pair / end of this CTA's slice of the entry
     int32_t K, ppc, slot;
-    const __nv_bfloat16 * W;
     uint32_t seq;
+    const __nv_bfloat16 * W;
     uint64_t policy;
-    int4 n0, n1;            // schedule entry idx+1, requested one entry ahead (hides the L2 latency)
+    int4 ent[4][2];         // schedule entries idx .. idx+2 (slot = entry index & 3)
 };
+
+__device__ __forceinline__ void sched_fetch(Prefetch & pf, const WSched * __restrict__ sched, int n_sched, int k) {
+    // k = running entry counter; entry index = k % n_sched
+    const WSched * src = sched + (k % n_sched);
+    const uint32_t dst = smem_u32(&pf.ent[k & 3][0]);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(dst + 16), "l"(reinterpret_cast<const char *>(src) + 16) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
 
 __device__ __forceinline__ void cta_pairs(const Op & op, int & p0, int & p1) {
     const unsigned pairs = (unsigned) op.rows >> 1;
@@ -162,18 +176,17 @@ __device__ __forceinline__ void cta_pairs(const Op & op, int & p0, int & p1) {
     p1 = (int) (pairs * (blockIdx.x + 1) / gridDim.x);
 }
 
-// thread 0 only: issue bulk copies for upcoming chunks while ring slots are free
-__device__ __forceinline__ void prefetch_issue(const WSched * __restrict__ sched, int n_sched, int n_frames, Prefetch & pf,
-                                               uint32_t cons_seq, const Ring & ring) {
+// prefetcher thread only: issue bulk copies for upcoming chunks while ring slots are free.
+// pf.idx counts entries monotonically (entry = idx % n_sched, frame = idx / n_sched).
+__device__ __noinline__ void prefetch_issue(const WSched * __restrict__ sched, int n_sched, int n_frames, Prefetch & pf,
+                                            uint32_t cons_seq, const Ring ring) {
     while (pf.seq - cons_seq < (uint32_t) ring.n_slots && pf.frame < n_frames) {
         if (pf.q >= pf.p1) {
-            if (++pf.idx >= n_sched) { pf.idx = 0; if (++pf.frame >= n_frames) break; }
-            const int4 e0 = pf.n0, e1 = pf.n1;
-            {
-                const int nxt = (pf.idx + 1 < n_sched) ? pf.idx + 1 : 0;
-                pf.n0 = __ldg(reinterpret_cast<const int4 *>(sched + nxt));
-                pf.n1 = __ldg(reinterpret_cast<const int4 *>(sched + nxt) + 1);
-            }
+            const int k = ++pf.idx;
+            if (k >= (pf.frame + 1) * n_sched) { if (++pf.frame >= n_frames) break; }
+            asm volatile("cp.async.wait_group 1;" ::: "memory");      // entry k landed (k+1 may be in flight)
+            const int4 e0 = pf.ent[k & 3][0], e1 = pf.ent[k & 3][1];
+            sched_fetch(pf, sched, n_sched, k + 2);
             pf.W = reinterpret_cast<const __nv_bfloat16 *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
             pf.K = e0.z;
             const unsigned pairs = (unsigned) e0.w;
@@ -184,12 +197,13 @@ __device__ __forceinline__ void prefetch_issue(const WSched * __restrict__ sched
         }
         const int nq = min(pf.ppc, pf.p1 - pf.q);
         const uint32_t bytes = (uint32_t) nq * 4u * (uint32_t) pf.K;
-        mbar_expect_tx(ring.full + pf.slot, bytes);
-        bulk_g2s(ring.base + (size_t) pf.slot * ring.slot_bytes, pf.W + (size_t) 2 * pf.q * pf.K, bytes,
-                 ring.full + pf.slot, pf.policy);
+        const int slot = pf.slot;
+        mbar_expect_tx(ring.full + slot, bytes);
+        bulk_g2s(ring.base + (size_t) slot * ring.slot_bytes, pf.W + (size_t) 2 * pf.q * pf.K, bytes,
+                 ring.full + slot, pf.policy);
         pf.q += nq;
         pf.seq++;
-        if (++pf.slot == ring.n_slots) pf.slot = 0;
+        pf.slot = (slot + 1 == ring.n_slots) ? 0 : slot + 1;
     }
 }
 
@@ -204,7 +218,8 @@ __device__ __forceinline__ void grid_barrier(GridBarrier * bar, unsigned int & e
     __syncthreads();
     if (threadIdx.x == 0) {
         if (prof_sync) *prof_sync += (unsigned long long) (clock64() - ts);
-        epoch += gridDim.x;
+        const unsigned int target = epoch + gridDim.x;
+        epoch = target;
         __threadfence();
         atomicAdd(&bar->count, 1u);
         // relaxed polling (an acquire load invalidates L1 on every iteration), one acquire at the end;
@@ -212,7 +227,7 @@ __device__ __forceinline__ void grid_barrier(GridBarrier * bar, unsigned int & e
         unsigned int v;
         do {
             asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&bar->count) : "memory");
-        } while ((int) (v - epoch) < 0);
+        } while ((int) (v - target) < 0);
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&bar->count) : "memory");
     } else if (threadIdx.x == kPfThread) {
         prefetch_issue(sched, n_sched, n_frames, pf, cons_seq, ring);
@@ -224,6 +239,28 @@ __device__ __forceinline__ void grid_barrier(GridBarrier * bar, unsigned int & e
 // OP_GEMV
 // ------------------------------------------------------------------------------------------
 constexpr int kMaxPerThread = 12;     // input elements per thread: K <= kThreads * 12 = 6144
+
+// Flag-carrying activations: a single 64-bit relaxed store / load is single-copy atomic, so a
+// consumer that sees the producer stage's tag in the upper half has the value in the lower half.
+__device__ __forceinline__ void ll_store(unsigned long long * p, float v, uint32_t tag) {
+    const unsigned long long w = ((unsigned long long) tag << 32) | (unsigned long long) __float_as_uint(v);
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ unsigned long long ll_load(const unsigned long long * p) {
+    unsigned long long w;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    return w;
+}
+// a protocol error must not hang the device: ~2^22 polls (seconds) then trap
+__device__ __forceinline__ void ll_spin_guard(uint32_t & spins) {
+    if (++spins > (1u << 22)) __trap();
+}
+__device__ __forceinline__ float ll_wait(const unsigned long long * p, uint32_t tag) {
+    unsigned long long w = ll_load(p);
+    uint32_t spins = 0;
+    while ((uint32_t) (w >> 32) != tag) { ll_spin_guard(spins); w = ll_load(p); }
+    return __uint_as_float((uint32_t) w);
+}
 
 // raw input element i of token t (before the norm)
 __device__ __forceinline__ float gemv_input_elem(const Op & op, const LocalState * ls, const __half * row,
@@ -265,7 +302,7 @@ __device__ __forceinline__ float dot8h(const uint4 w, const uint4 x) {
 // F16-rounded activations from xh.  Residual / bias values are requested before the dot products.
 template <int NT>
 __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, const Ring ring, uint32_t cons_seq, int p0,
-                          int q_begin, int q_end, unsigned long long * prof_wait) {
+                          int q_begin, int q_end, unsigned long long * prof_wait, uint32_t tag, bool ll) {
     const int K = op.K, kv = K >> 3;      // uint4 per row
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ppc = ring.slot_bytes / (4 * K);
@@ -275,7 +312,10 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
         float side = 0.f;       // residual or bias of (token lane>>1, row 2p + (lane&1))
         if (lane < 2 * NT) {
             const int t = lane >> 1, r = 2 * p + (lane & 1);
-            if (op.epi == EPI_ADD) side = __ldcg(op.res + (size_t) t * op.out_stride + r);
+            if (op.epi == EPI_ADD) {
+                if (ll && op.res_ll) side = ll_wait(op.res_ll + (size_t) t * op.out_stride + r, tag - (uint32_t) op.res_dist);
+                else side = __ldcg(op.res + (size_t) t * op.out_stride + r);
+            }
             else if (op.epi == EPI_BIAS || op.epi == EPI_BIAS_SILU) side = __ldg(op.bias + r);
         }
         const int j = q / ppc;
@@ -319,7 +359,9 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
         if (op.epi == EPI_SWIGLU) {
             if (lane < NT) {
                 const float g = (lane == 0) ? a0[0] : a0[NT - 1], u = (lane == 0) ? a1[0] : a1[NT - 1];
-                op.out[(size_t) lane * op.out_stride + p] = silu_f(g) * u;
+                const float v = silu_f(g) * u;
+                op.out[(size_t) lane * op.out_stride + p] = v;
+                if (ll && op.out_ll) ll_store(op.out_ll + (size_t) lane * op.out_stride + p, v, tag);
             }
         } else if (lane < 2 * NT) {
             const int t = lane >> 1, r = 2 * p + (lane & 1);
@@ -327,6 +369,7 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
             acc += side;
             if (op.epi == EPI_BIAS_SILU) acc = silu_f(acc);
             op.out[(size_t) t * op.out_stride + r] = acc;
+            if (ll && op.out_ll) ll_store(op.out_ll + (size_t) t * op.out_stride + r, acc, tag);
         }
     }
 }
@@ -334,18 +377,51 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
 // input vector of token t -> F16-rounded activations in shared memory.  Every thread owns elements
 // tid + j*kThreads (j < NPER); the input and the norm weights are requested together (one L2
 // round trip) and the RMSNorm runs out of registers.
-template <int NPER>
+template <int NPER, bool LL>
 __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * ls, const __half * row, const float * trow,
-                                             int t, __half * xh, double * red) {
+                                             int t, __half * xh, double * red, uint32_t tag_in) {
     const int K = op.K;
     float xv[NPER], nw[NPER];
+    if (LL) {
+        // poll the producer stage's flag-carrying output: all of this thread's words are requested
+        // together, the round is repeated until every tag matches
+        const unsigned long long * src = op.in_ll + (size_t) t * op.in_stride;
 #pragma unroll
-    for (int j = 0; j < NPER; ++j) {
-        const int i = threadIdx.x + j * kThreads;
-        xv[j] = 0.f; nw[j] = 1.f;
-        if (i < K) {
-            xv[j] = gemv_input_elem(op, ls, row, trow, t, i);
-            if (op.norm_w) nw[j] = __ldg(op.norm_w + i);
+        for (int j = 0; j < NPER; ++j) {
+            const int i = threadIdx.x + j * kThreads;
+            nw[j] = (op.norm_w && i < K) ? __ldg(op.norm_w + i) : 1.f;
+            xv[j] = 0.f;
+        }
+        uint32_t spins = 0;
+        constexpr int kB = NPER < 6 ? NPER : 6;     // words in flight per polling round
+#pragma unroll
+        for (int j0 = 0; j0 < NPER; j0 += kB) {
+            bool ok;
+            do {
+                unsigned long long w[kB];
+#pragma unroll
+                for (int j = 0; j < kB; ++j) {
+                    const int i = threadIdx.x + (j0 + j) * kThreads;
+                    w[j] = (i < K) ? ll_load(src + i) : ((unsigned long long) tag_in << 32);
+                }
+                ok = true;
+#pragma unroll
+                for (int j = 0; j < kB; ++j) {
+                    ok = ok && ((uint32_t) (w[j] >> 32) == tag_in);
+                    xv[j0 + j] = __uint_as_float((uint32_t) w[j]);
+                }
+                if (!ok) ll_spin_guard(spins);
+            } while (!ok);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < NPER; ++j) {
+            const int i = threadIdx.x + j * kThreads;
+            xv[j] = 0.f; nw[j] = 1.f;
+            if (i < K) {
+                xv[j] = gemv_input_elem(op, ls, row, trow, t, i);
+                if (op.norm_w) nw[j] = __ldg(op.norm_w + i);
+            }
         }
     }
     if (op.x_out && blockIdx.x == 0) {
@@ -382,8 +458,11 @@ __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * l
 // returns the number of ring chunks this CTA consumed
 __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, LocalState * ls, float * xs, double * red,
                                const Ring & ring, uint32_t cons_seq,
-                               const WSched * sched, int n_sched, int n_frames, Prefetch & pf, unsigned long long * prof) {
+                               const WSched * sched, int n_sched, int n_frames, Prefetch & pf, unsigned long long * prof,
+                               uint32_t tag, bool ll) {
     const int K = op.K;
+    const bool ll_in = ll && op.in_ll != nullptr && op.in_kind == IN_VEC;
+    const uint32_t tag_in = tag - (uint32_t) op.in_dist;
     const bool prof_on = prof && threadIdx.x == 0;
     long long tA = prof_on ? clock64() : 0;
     __half * xh = reinterpret_cast<__half *>(xs);
@@ -402,10 +481,17 @@ __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, 
     }
     const int nper = (K + kThreads - 1) / kThreads;
     for (int t = 0; t < op.n_tok; ++t) {
-        if (nper <= 2)      gemv_prepare<2>(op, ls, row, trow, t, xh, red);
-        else if (nper <= 4) gemv_prepare<4>(op, ls, row, trow, t, xh, red);
-        else if (nper <= 6) gemv_prepare<6>(op, ls, row, trow, t, xh, red);
-        else                gemv_prepare<kMaxPerThread>(op, ls, row, trow, t, xh, red);
+        if (ll_in) {
+            if (nper <= 2)      gemv_prepare<2, true>(op, ls, row, trow, t, xh, red, tag_in);
+            else if (nper <= 4) gemv_prepare<4, true>(op, ls, row, trow, t, xh, red, tag_in);
+            else if (nper <= 6) gemv_prepare<6, true>(op, ls, row, trow, t, xh, red, tag_in);
+            else                gemv_prepare<kMaxPerThread, true>(op, ls, row, trow, t, xh, red, tag_in);
+        } else {
+            if (nper <= 2)      gemv_prepare<2, false>(op, ls, row, trow, t, xh, red, tag_in);
+            else if (nper <= 4) gemv_prepare<4, false>(op, ls, row, trow, t, xh, red, tag_in);
+            else if (nper <= 6) gemv_prepare<6, false>(op, ls, row, trow, t, xh, red, tag_in);
+            else                gemv_prepare<kMaxPerThread, false>(op, ls, row, trow, t, xh, red, tag_in);
+        }
     }
     __syncthreads();
     if (prof_on) { const long long t = clock64(); prof[OP_GEMV * 8 + 4] += (unsigned long long) (t - tA); tA = t; }
@@ -419,8 +505,8 @@ __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, 
     for (int c0 = 0; c0 < nch; c0 += ring.n_slots) {
         const int c1 = min(c0 + ring.n_slots, nch);
         const int qb = c0 * ppc, qe = min(c1 * ppc, p1 - p0);
-        if (op.n_tok == 2) gemv_rows<2>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr);
-        else               gemv_rows<1>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr);
+        if (op.n_tok == 2) gemv_rows<2>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr, tag, ll);
+        else               gemv_rows<1>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr, tag, ll);
         if (c1 < nch) {
             __syncthreads();
             if (threadIdx.x == kPfThread) prefetch_issue(sched, n_sched, n_frames, pf, cons_seq + (uint32_t) c1, ring);
@@ -1179,21 +1265,23 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
     }
     __syncthreads();
 
-    Prefetch pf;
-    pf.idx = -1; pf.frame = (cfg.n_sched > 0) ? 0 : n_frames; pf.q = 0; pf.p1 = 0; pf.K = 0; pf.ppc = 1; pf.slot = 0;
-    pf.W = nullptr; pf.seq = 0; pf.policy = 0; pf.n0 = make_int4(0, 0, 0, 0); pf.n1 = pf.n0;
+    __shared__ Prefetch pf;
     uint32_t cons_seq = 0;          // ring chunks consumed so far (uniform across the CTA)
-    unsigned int epoch = 0;         // bar->count is zeroed by the host before every persistent launch
+    __shared__ unsigned int epoch;  // thread 0 only; bar->count is zeroed by the host before every persistent launch
+    if (threadIdx.x == 0) epoch = 0;
     if (threadIdx.x == kPfThread) {
+        pf.idx = -1; pf.frame = (cfg.n_sched > 0) ? 0 : n_frames; pf.q = 0; pf.p1 = 0; pf.K = 0; pf.ppc = 1; pf.slot = 0;
+        pf.W = nullptr; pf.seq = 0;
         pf.policy = policy_evict_first();
         if (cfg.n_sched > 0) {
-            pf.n0 = __ldg(reinterpret_cast<const int4 *>(cfg.sched));
-            pf.n1 = __ldg(reinterpret_cast<const int4 *>(cfg.sched) + 1);
+            sched_fetch(pf, cfg.sched, cfg.n_sched, 0);
+            sched_fetch(pf, cfg.sched, cfg.n_sched, 1);
         }
         prefetch_issue(cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring);
     }
-
     bool stop = false;
+    bool pf_pending = false;        // a stage without a grid barrier leaves the ring refill to the next stage's entry
+    const bool ll = cfg.persistent != 0;
     for (int f = 0; f < n_frames && !stop; ++f) {
         if (cfg.check_done && ls.done) break;
         for (int i = 0; i < n_ops && !stop; ++i) {
@@ -1201,6 +1289,8 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
             // every field read from the global descriptor was an L2 round trip); the NEXT stage's
             // descriptor is requested now and parked in a register during the stage
             __syncthreads();
+            if (pf_pending && threadIdx.x == kPfThread) prefetch_issue(cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring);
+            pf_pending = false;
             if (threadIdx.x < (int) (sizeof(Op) / 4)) {
                 if (!have_next) next_word = __ldg(reinterpret_cast<const uint32_t *>(ops + i) + threadIdx.x);
                 reinterpret_cast<uint32_t *>(&sop)[threadIdx.x] = next_word;
@@ -1215,7 +1305,8 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
             const long long t0 = prof_on ? clock64() : 0;
             const long long t0p = (cfg.prof && threadIdx.x == 0) ? clock64() : 0;
             switch (op.type) {
-                case OP_GEMV:       cons_seq += stage_gemv(op, st, &ls, xs, red, ring, cons_seq, cfg.sched, cfg.n_sched, n_frames, pf, prof_on ? cfg.prof : nullptr); break;
+                case OP_GEMV:       cons_seq += stage_gemv(op, st, &ls, xs, red, ring, cons_seq, cfg.sched, cfg.n_sched, n_frames, pf, prof_on ? cfg.prof : nullptr,
+                                                           cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll); break;
                 case OP_ATTN:       stage_attn(op, &ls, scratch); break;
                 case OP_COPY:       stage_copy(op); break;
                 case OP_SAMPLE_CB0: stage_sample_cb0(op, st, &ls, scratch, xs); all_to_all = false; break;
@@ -1226,6 +1317,8 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
             const long long t1p = (cfg.prof && threadIdx.x == 0) ? clock64() : 0;
             if (!all_to_all) {
                 if (cfg.check_done && op.type != OP_SAMPLE_CP && ls.done) stop = true;
+            } else if (ll && (op.flags & F_LL_OUT)) {
+                pf_pending = true;      // consumers poll the flag-carrying output; no barrier
             } else if (cfg.persistent) {
                 grid_barrier(bar, epoch, cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring, prof_on ? cfg.prof + op.type * 8 + 7 : nullptr);
             } else {
@@ -1247,6 +1340,7 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
     // drain: every bulk copy issued into this CTA's shared memory must land before it exits
     __syncthreads();
     if (threadIdx.x == kPfThread) {
+        asm volatile("cp.async.wait_all;" ::: "memory");
         for (uint32_t s = cons_seq; s != pf.seq; ++s)
             mbar_wait(full_bar + (s % (uint32_t) cfg.n_slots), (s / (uint32_t) cfg.n_slots) & 1u);
     }

@@ -103,6 +103,12 @@ struct Op {
     const float * res;
     float * out;
     float eps;
+    // flag-carrying copies ("LL": one 64-bit word = f32 value | 32-bit stage tag << 32) that let the
+    // consumer stage poll the data itself instead of waiting at a grid barrier (see F_LL_OUT)
+    unsigned long long * out_ll;         // written next to `out` with this stage's tag
+    const unsigned long long * in_ll;    // IN_VEC read from here, tag = this stage's tag - in_dist
+    const unsigned long long * res_ll;   // EPI_ADD residual, tag = this stage's tag - res_dist
+    int32_t in_dist, res_dist;
     // ---- OP_ATTN ----
     const float * qkv;       // [(n_heads + 2 n_kv_heads) * 128] raw projections
     const float * q_norm_w, * k_norm_w;
@@ -136,6 +142,8 @@ struct Op {
 
 enum OpFlags : int32_t {
     F_INC_NPAST = 1,     // CTA 0 increments state.n_past when the stage completes
+    F_LL_OUT    = 2,     // persistent mode: no grid barrier after this stage; every consumer of its
+                         // output reads the flag-carrying copy (out_ll) and polls for this stage's tag
 };
 
 // Host-built list of the program's GEMV stages in execution order (one frame); the prefetcher

@@ -5,6 +5,7 @@
 //   -> FRAME_END -> Talker step (28 layers x 5 stages + head), whose first stage gathers the
 //   16 code embeddings + text row (src/tts_transformer.cpp:2529-2553).
 #include "qtts_engine.h"
+#include <algorithm>
 #include <cstring>
 
 namespace qtts {
@@ -29,12 +30,14 @@ static Op gemv(const __nv_bfloat16 * W, int rows, int K, const float * in, const
     return o;
 }
 
-struct LayerBuf { float * x, * qkv, * attn, * act; __half * kc, * vc; size_t kv_layer_stride; float * attn_part; unsigned int * attn_cnt; };
+struct LayerBuf { float * x, * qkv, * attn, * act; __half * kc, * vc; size_t kv_layer_stride; float * attn_part; unsigned int * attn_cnt;
+                  unsigned long long * x_ll, * act_ll; };
 
 // five stages of one decoder layer over n_tok tokens (2 only for the merged code-predictor
 // positions 0/1); `first` (if non-null) replaces the QKV stage's input setup
 static void emit_layer(Engine * e, std::vector<Op> & P, const LayerW & L, const Dims & D, const LayerBuf & B,
                        int layer, const Op * first, bool use_n_past, int pos_off, int mode, int n_tok = 1) {
+    const bool ll = e->ll != 0, ll_in = layer > 0;
     const float eps = e->cfg.rms_norm_eps;
     const int qkv_rows = (D.nh + 2 * D.nkv) * kHeadDim;
     const int aw = D.nh * kHeadDim;
@@ -43,6 +46,8 @@ static void emit_layer(Engine * e, std::vector<Op> & P, const LayerW & L, const 
     if (first) {
         q.in_kind = first->in_kind; q.in = first->in; q.table = first->table; q.tok_ptr = first->tok_ptr;
         q.tok_slot = first->tok_slot; q.es = first->es; q.x_out = first->x_out;
+    } else if (ll && ll_in) {
+        q.in_ll = B.x_ll; q.in_dist = 1;      // previous layer's down projection
     }
     P.push_back(q);
     Op a = blank();
@@ -57,12 +62,16 @@ static void emit_layer(Engine * e, std::vector<Op> & P, const LayerW & L, const 
     P.push_back(a);
     Op o = gemv(L.wo, D.H, aw, B.attn, nullptr, eps, EPI_ADD, B.x);
     o.res = B.x; o.n_tok = n_tok; o.in_stride = aw; o.out_stride = D.H;
+    if (ll) { o.out_ll = B.x_ll; o.flags |= F_LL_OUT; }
     P.push_back(o);
     Op gu = gemv(L.wgu, 2 * D.ffn, D.H, B.x, L.ffn_norm, eps, EPI_SWIGLU, B.act);
     gu.n_tok = n_tok; gu.in_stride = D.H; gu.out_stride = D.ffn;
+    if (ll) { gu.in_ll = B.x_ll; gu.in_dist = 1; gu.out_ll = B.act_ll; gu.flags |= F_LL_OUT; }
     P.push_back(gu);
     Op d = gemv(L.wdown, D.H, D.ffn, B.act, nullptr, eps, EPI_ADD, B.x);
     d.res = B.x; d.n_tok = n_tok; d.in_stride = D.ffn; d.out_stride = D.H;
+    // the stage after a layer's down projection is always a GEMV (next layer's QKV or the head)
+    if (ll) { d.in_ll = B.act_ll; d.in_dist = 1; d.res_ll = B.x_ll; d.res_dist = 2; d.out_ll = B.x_ll; d.flags |= F_LL_OUT; }
     P.push_back(d);
 }
 
@@ -71,7 +80,8 @@ void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, co
                       bool use_n_past, int pos_abs, int attn_mode, bool with_head, bool inc_npast) {
     const qtts_config & c = e->cfg;
     const Dims D{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
-    LayerBuf B{s.x, s.qkv, s.attn, s.act, s.kc, s.vc, (size_t) e->max_ctx * c.n_kv_heads * kHeadDim, s.attn_part, s.attn_cnt};
+    LayerBuf B{s.x, s.qkv, s.attn, s.act, s.kc, s.vc, (size_t) e->max_ctx * c.n_kv_heads * kHeadDim, s.attn_part, s.attn_cnt,
+               s.x_ll, s.act_ll};
     Op first = blank();
     first.in_kind = in_kind; first.in = in_vec; first.es = s.es; first.x_out = s.x;
     for (int l = 0; l < c.n_layers; ++l)
@@ -79,10 +89,13 @@ void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, co
     if (with_head) {
         Op h = gemv(e->codec_head, c.codec_vocab_size, c.hidden_size, s.x, e->output_norm, c.rms_norm_eps, EPI_STORE, s.logits);
         h.hid_out = s.hidden;
+        if (e->ll) { h.in_ll = s.x_ll; h.in_dist = 1; }
         if (inc_npast) h.flags |= F_INC_NPAST;
         P.push_back(h);
-    } else if (inc_npast) {
-        P.back().flags |= F_INC_NPAST;
+    } else {
+        // no head: nothing polls the last down projection, the stage ends with a grid barrier again
+        P.back().flags &= ~F_LL_OUT;
+        if (inc_npast) P.back().flags |= F_INC_NPAST;
     }
 }
 
@@ -96,7 +109,7 @@ void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float 
     const qtts_config & c = e->cfg;
     const Dims D{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
     LayerBuf B{s.cp_x, s.cp_qkv, s.cp_attn, s.cp_act, s.cp_kc, s.cp_vc, (size_t) 16 * c.cp_n_kv_heads * kHeadDim,
-               s.attn_part, s.attn_cnt};
+               s.attn_part, s.attn_cnt, s.cp_x_ll, s.cp_act_ll};
     const int n_pos = c.n_codebooks;   // 16 positions -> 15 sampled codes
     for (int p = 1; p < n_pos; ++p) {
         const int n_tok = (p == 1) ? 2 : 1;
@@ -118,9 +131,11 @@ void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float 
         for (int l = 0; l < c.cp_layers; ++l)
             emit_layer(e, P, e->cp[l], D, B, l, l == 0 ? &first : nullptr, false, p == 1 ? 0 : p, mode, n_tok);
         // the head reads the LAST token of the pass
-        P.push_back(gemv(e->lm_head[p - 1], c.cp_vocab_size, c.cp_hidden_size,
-                         s.cp_x + (size_t) (n_tok - 1) * c.cp_hidden_size, e->cp_output_norm,
-                         c.rms_norm_eps, EPI_STORE, s.cp_logits));
+        Op hd = gemv(e->lm_head[p - 1], c.cp_vocab_size, c.cp_hidden_size,
+                     s.cp_x + (size_t) (n_tok - 1) * c.cp_hidden_size, e->cp_output_norm,
+                     c.rms_norm_eps, EPI_STORE, s.cp_logits);
+        if (e->ll) { hd.in_ll = s.cp_x_ll + (size_t) (n_tok - 1) * c.cp_hidden_size; hd.in_dist = 1; }
+        P.push_back(hd);
         Op sp = blank();
         sp.type = OP_SAMPLE_CP; sp.logits = s.cp_logits; sp.n_vocab = c.cp_vocab_size; sp.book = p;
         sp.uniforms = uniforms; sp.forced = forced;
@@ -233,8 +248,23 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
     if (n_ops == 0) return true;
     if (e->persistent) {
         QTTS_CUDA(cudaMemsetAsync(&e->bar->count, 0, sizeof(unsigned int), e->stream));
+        // stage tags never repeat: a stale word of an earlier launch can not satisfy a poll
+        const uint64_t n_tags = (uint64_t) n_ops * (uint64_t) n_frames + 1;
+        if ((uint64_t) e->ll_seq + n_tags > 0xfff00000ull) {
+            QTTS_CUDA(cudaStreamSynchronize(e->stream));
+            for (Slot & t : e->slots) {
+                const qtts_config & c = e->cfg;
+                const size_t maxH = (size_t) std::max(c.hidden_size, c.cp_hidden_size);
+                QTTS_CUDA(cudaMemsetAsync(t.x_ll, 0, maxH * 8, e->stream));
+                QTTS_CUDA(cudaMemsetAsync(t.act_ll, 0, (size_t) c.intermediate_size * 8, e->stream));
+                QTTS_CUDA(cudaMemsetAsync(t.cp_x_ll, 0, 2 * maxH * 8, e->stream));
+                QTTS_CUDA(cudaMemsetAsync(t.cp_act_ll, 0, 2 * (size_t) c.cp_intermediate_size * 8, e->stream));
+            }
+            e->ll_seq = 0;
+        }
         RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 1, check_done ? 1 : 0, e->prof_on - 1, n_sched, d_sched,
-                   e->prof_on ? e->prof : nullptr};
+                   e->ll_seq, e->prof_on ? e->prof : nullptr};
+        e->ll_seq += (uint32_t) n_tags;
         StreamState * st = s.st;
         GridBarrier * bar = e->bar;
         void * args[] = {(void *) &d_ops, (void *) &n_ops, (void *) &st, (void *) &bar, (void *) &n_frames,
@@ -250,7 +280,7 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
         int si = 0;     // schedule entry of the i-th op when it is a GEMV
         for (int i = 0; i < n_ops; ++i) {
             const bool is_gemv = (*host_ops)[i].type == OP_GEMV;
-            RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 0, 0, 0, is_gemv ? 1 : 0, d_sched + si, nullptr};
+            RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 0, 0, 0, is_gemv ? 1 : 0, d_sched + si, 0u, nullptr};
             if (is_gemv) ++si;
             qtts_run_program<<<e->n_sms, kThreads, e->smem_bytes, e->stream>>>(d_ops + i, 1, s.st, e->bar, 1, cfg);
             e->launches += 1;

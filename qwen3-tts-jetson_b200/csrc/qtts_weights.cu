@@ -185,6 +185,10 @@ static bool alloc_slot(Engine * e, Slot & s, int index) {
     s.cp_attn = e->dalloc<float>(2 * (size_t) c.cp_n_heads * kHeadDim);
     s.cp_act = e->dalloc<float>(2 * (size_t) c.cp_intermediate_size);
     s.cp_logits = e->dalloc<float>(c.cp_vocab_size);
+    s.x_ll = e->dalloc<unsigned long long>(maxH);
+    s.act_ll = e->dalloc<unsigned long long>(c.intermediate_size);
+    s.cp_x_ll = e->dalloc<unsigned long long>(2 * (size_t) maxH);
+    s.cp_act_ll = e->dalloc<unsigned long long>(2 * (size_t) c.cp_intermediate_size);
     s.cp_hidden_in = e->dalloc<float>(H);
     s.cp_dump = e->dalloc<float>((size_t) 16 * c.cp_vocab_size);
     s.cb0_dump = e->dalloc<float>(c.codec_vocab_size);
