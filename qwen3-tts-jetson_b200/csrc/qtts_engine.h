@@ -64,6 +64,7 @@ struct Slot {
     float * cp_x = nullptr, * cp_qkv = nullptr, * cp_attn = nullptr, * cp_act = nullptr, * cp_logits = nullptr;
     // flag-carrying copies of the residual stream and the SwiGLU output (Op::out_ll)
     unsigned long long * x_ll = nullptr, * act_ll = nullptr, * cp_x_ll = nullptr, * cp_act_ll = nullptr;
+    unsigned long long * qkv_ll = nullptr, * attn_ll = nullptr, * cp_qkv_ll = nullptr, * cp_attn_ll = nullptr;
     float * cp_hidden_in = nullptr;        // hidden handed to predict_codes by the API
     float * cp_dump = nullptr;             // [15][cp_vocab]
     float * cb0_dump = nullptr;            // [V]

@@ -379,7 +379,7 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
 // round trip) and the RMSNorm runs out of registers.
 template <int NPER, bool LL>
 __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * ls, const __half * row, const float * trow,
-                                             int t, __half * xh, double * red, uint32_t tag_in) {
+                                             int t, __half * xh, double * red, uint32_t tag_in, uint32_t tag_x) {
     const int K = op.K;
     float xv[NPER], nw[NPER];
     if (LL) {
@@ -428,7 +428,10 @@ __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * l
 #pragma unroll
         for (int j = 0; j < NPER; ++j) {
             const int i = threadIdx.x + j * kThreads;
-            if (i < K) op.x_out[t * K + i] = xv[j];
+            if (i < K) {
+                op.x_out[t * K + i] = xv[j];
+                if (tag_x && op.x_out_ll) ll_store(op.x_out_ll + t * K + i, xv[j], tag_x);
+            }
         }
     }
     float scale = 1.0f;
@@ -482,15 +485,15 @@ __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, 
     const int nper = (K + kThreads - 1) / kThreads;
     for (int t = 0; t < op.n_tok; ++t) {
         if (ll_in) {
-            if (nper <= 2)      gemv_prepare<2, true>(op, ls, row, trow, t, xh, red, tag_in);
-            else if (nper <= 4) gemv_prepare<4, true>(op, ls, row, trow, t, xh, red, tag_in);
-            else if (nper <= 6) gemv_prepare<6, true>(op, ls, row, trow, t, xh, red, tag_in);
-            else                gemv_prepare<kMaxPerThread, true>(op, ls, row, trow, t, xh, red, tag_in);
+            if (nper <= 2)      gemv_prepare<2, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            else if (nper <= 4) gemv_prepare<4, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            else if (nper <= 6) gemv_prepare<6, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            else                gemv_prepare<kMaxPerThread, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
         } else {
-            if (nper <= 2)      gemv_prepare<2, false>(op, ls, row, trow, t, xh, red, tag_in);
-            else if (nper <= 4) gemv_prepare<4, false>(op, ls, row, trow, t, xh, red, tag_in);
-            else if (nper <= 6) gemv_prepare<6, false>(op, ls, row, trow, t, xh, red, tag_in);
-            else                gemv_prepare<kMaxPerThread, false>(op, ls, row, trow, t, xh, red, tag_in);
+            if (nper <= 2)      gemv_prepare<2, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            else if (nper <= 4) gemv_prepare<4, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            else if (nper <= 6) gemv_prepare<6, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            else                gemv_prepare<kMaxPerThread, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
         }
     }
     __syncthreads();
@@ -546,7 +549,8 @@ struct AttnSmem {
 };
 
 // q (nq heads from h_first), k, v of one token: per-head RMSNorm (double sum), NEOX RoPE at `pos`
-__device__ void attn_prepare(const Op & op, const float * qkv, int h_first, int nq, int g, int pos, AttnSmem * sm) {
+__device__ void attn_prepare(const Op & op, const float * qkv, int h_first, int nq, int g, int pos, AttnSmem * sm,
+                             const unsigned long long * qkv_ll = nullptr, uint32_t tag_in = 0) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int rows = nq + 2;
     __syncthreads();
@@ -555,7 +559,7 @@ __device__ void attn_prepare(const Op & op, const float * qkv, int h_first, int 
         const float * src = (row < nq)  ? qkv + (size_t) (h_first + row) * kHeadDim
                           : (row == nq) ? qkv + (size_t) (op.n_heads + g) * kHeadDim
                                         : qkv + (size_t) (op.n_heads + op.n_kv_heads + g) * kHeadDim;
-        sm->tmp[idx] = __ldcg(src + d);
+        sm->tmp[idx] = qkv_ll ? ll_wait(qkv_ll + (src - qkv) + d, tag_in) : __ldcg(src + d);
     }
     __syncthreads();
     if (warp <= nq) {       // rows 0..nq (queries and the key) are normalised
@@ -660,7 +664,8 @@ __device__ void attn_scores(const Op & op, const AttnSmem * sm, int g, int kvw, 
 // ---- ATTN_FAST: split-KV over (KV group, key range) CTAs, REP query heads per CTA; the last CTA
 // of a group to finish merges the partials (fixed order -> deterministic)
 template <int REP>
-__device__ __noinline__ void attn_fast(const Op & op, const float * qkv, float * out, int pos, AttnSmem * sm, float * sc) {
+__device__ __noinline__ void attn_fast(const Op & op, const float * qkv, float * out, int pos, AttnSmem * sm, float * sc,
+                                       const unsigned long long * qkv_ll, uint32_t tag_in) {
     const int tid = threadIdx.x;
     const int n_kv = pos + 1, kvw = op.n_kv_heads * kHeadDim;
     int S = (n_kv + kSplitKeys - 1) / kSplitKeys;
@@ -670,7 +675,7 @@ __device__ __noinline__ void attn_fast(const Op & op, const float * qkv, float *
     const int g = b / S, s = b % S;
     const int range = (n_kv + S - 1) / S;
     const int j0 = s * range, j1 = min(j0 + range, n_kv);
-    attn_prepare(op, qkv, g * REP, REP, g, pos, sm);
+    attn_prepare(op, qkv, g * REP, REP, g, pos, sm, qkv_ll, tag_in);
     if (s == S - 1) attn_append(op, g, pos, kvw, sm);
     const int cnt = max(j1 - j0, 0);
     attn_scores<REP>(op, sm, g, kvw, pos, j0, j1, sc, range);
@@ -745,7 +750,8 @@ __device__ __noinline__ void attn_fast(const Op & op, const float * qkv, float *
 
 // ---- ATTN_F32: code-predictor positions 0 and 1 in one stage (n_tok = 2), everything F32 with the
 // un-cached K/V, as the reference's 2-token prefill graph (src/tts_transformer.cpp:1613-1626)
-__device__ __noinline__ void attn_f32_pair(const Op & op, AttnSmem * sm, float * sc) {
+__device__ __noinline__ void attn_f32_pair(const Op & op, AttnSmem * sm, float * sc, const unsigned long long * qkv_ll,
+                                           uint32_t tag_in, unsigned long long * out_ll_base, uint32_t tag) {
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (b >= 2 * op.n_heads) return;
     const int t = b / op.n_heads, h = b % op.n_heads;
@@ -753,14 +759,18 @@ __device__ __noinline__ void attn_f32_pair(const Op & op, AttnSmem * sm, float *
     const int kvw = op.n_kv_heads * kHeadDim;
     const int pos = op.pos_off + t;
     float * out = op.out + (size_t) t * op.out_stride + (size_t) h * kHeadDim;
+    unsigned long long * out_ll = out_ll_base ? out_ll_base + (size_t) t * op.out_stride + (size_t) h * kHeadDim : nullptr;
     if (t == 1) {   // position 0's key / value, recomputed from token 0's projections
-        attn_prepare(op, op.qkv, h, 0, g, op.pos_off, sm);
+        attn_prepare(op, op.qkv, h, 0, g, op.pos_off, sm, qkv_ll, tag_in);
         if (tid < kHeadDim) { sm->k0f[tid] = sm->kf[tid]; sm->v0f[tid] = sm->vf[tid]; }
     }
-    attn_prepare(op, op.qkv + (size_t) t * op.qkv_stride, h, 1, g, pos, sm);
+    attn_prepare(op, op.qkv + (size_t) t * op.qkv_stride, h, 1, g, pos, sm, qkv_ll ? qkv_ll + (size_t) t * op.qkv_stride : nullptr, tag_in);
     if (h % rep == 0) attn_append(op, g, pos, kvw, sm);
     if (t == 0) {   // softmax over one key = 1.0 exactly
-        if (tid < kHeadDim) out[tid] = sm->vf[tid];
+        if (tid < kHeadDim) {
+            out[tid] = sm->vf[tid];
+            if (out_ll) ll_store(out_ll + tid, sm->vf[tid], tag);
+        }
         return;
     }
     if (warp < 2) {
@@ -778,13 +788,17 @@ __device__ __noinline__ void attn_f32_pair(const Op & op, AttnSmem * sm, float *
         const float e0 = expf(sc[0] - mx), e1 = expf(sc[1] - mx);
         const float inv = (float) (1.0 / ((double) e0 + (double) e1));
         const float p0 = e0 * inv, p1 = e1 * inv;
-        out[tid] = fmaf(sm->vf[tid], p1, sm->v0f[tid] * p0);
+        const float o = fmaf(sm->vf[tid], p1, sm->v0f[tid] * p0);
+        out[tid] = o;
+        if (out_ll) ll_store(out_ll + tid, o, tag);
     }
 }
 
 // ---- ATTN_SOFTMAX_P16 / ATTN_FLASH_F16SEQ: one CTA per query head, the reference's exact
 // rounding points (parity modes; the sequential F16 accumulator is inherently serial per dim)
-__device__ __noinline__ void attn_reference(const Op & op, const LocalState * ls, AttnSmem * sm, float * sc) {
+__device__ __noinline__ void attn_reference(const Op & op, const LocalState * ls, AttnSmem * sm, float * sc,
+                                            const unsigned long long * qkv_ll, uint32_t tag_in,
+                                            unsigned long long * out_ll_base, uint32_t tag) {
     const int h = blockIdx.x;
     if (h >= op.n_heads) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -795,8 +809,9 @@ __device__ __noinline__ void attn_reference(const Op & op, const LocalState * ls
     float * ms = sc + kMaxScores;
     float * vs = ms + kTile;
     float * out = op.out + (size_t) h * kHeadDim;
+    unsigned long long * out_ll = out_ll_base ? out_ll_base + (size_t) h * kHeadDim : nullptr;
 
-    attn_prepare(op, op.qkv, h, 1, g, pos, sm);
+    attn_prepare(op, op.qkv, h, 1, g, pos, sm, qkv_ll, tag_in);
     if (h % (op.n_heads / op.n_kv_heads) == 0) attn_append(op, g, pos, kvw, sm);
     attn_scores<1>(op, sm, g, kvw, pos, 0, n_kv, sc, 0);
     __syncthreads();
@@ -824,8 +839,11 @@ __device__ __noinline__ void attn_reference(const Op & op, const LocalState * ls
         }
         sm->part[part][0][d] = acc;
         __syncthreads();
-        if (tid < kHeadDim)
-            out[tid] = (sm->part[0][0][tid] + sm->part[1][0][tid]) + (sm->part[2][0][tid] + sm->part[3][0][tid]);
+        if (tid < kHeadDim) {
+            const float o = (sm->part[0][0][tid] + sm->part[1][0][tid]) + (sm->part[2][0][tid] + sm->part[3][0][tid]);
+            out[tid] = o;
+            if (out_ll) ll_store(out_ll + tid, o, tag);
+        }
         return;
     }
 
@@ -911,19 +929,26 @@ __device__ __noinline__ void attn_reference(const Op & op, const LocalState * ls
         }
     }
     if (n_chunks > 1 && Sf != 0.0f) outv = outv * (1.0f / Sf);
-    if (tid < kHeadDim) out[tid] = outv;
+    if (tid < kHeadDim) {
+        out[tid] = outv;
+        if (out_ll) ll_store(out_ll + tid, outv, tag);
+    }
 }
 
-__device__ __noinline__ void stage_attn(const Op & op, const LocalState * ls, float * scratch) {
+__device__ __noinline__ void stage_attn(const Op & op, const LocalState * ls, float * scratch, uint32_t tag, bool ll) {
     AttnSmem * sm = reinterpret_cast<AttnSmem *>(scratch);
     float * sc = scratch + (sizeof(AttnSmem) + 15) / 16 * 4;
-    if (op.mode == ATTN_F32) { attn_f32_pair(op, sm, sc); return; }
-    if (op.mode != ATTN_FAST) { attn_reference(op, ls, sm, sc); return; }
+    // flag-carrying input (the QKV stage's out_ll) / output (polled by the O projection)
+    const unsigned long long * qkv_ll = ll ? op.in_ll : nullptr;
+    unsigned long long * out_ll = ll ? op.out_ll : nullptr;
+    const uint32_t tag_in = tag - (uint32_t) op.in_dist;
+    if (op.mode == ATTN_F32) { attn_f32_pair(op, sm, sc, qkv_ll, tag_in, out_ll, tag); return; }
+    if (op.mode != ATTN_FAST) { attn_reference(op, ls, sm, sc, qkv_ll, tag_in, out_ll, tag); return; }
     const int pos = (op.use_n_past ? ls->n_past : 0) + op.pos_off;
     const int rep = op.n_heads / op.n_kv_heads;
-    if (rep == 1)      attn_fast<1>(op, op.qkv, op.out, pos, sm, sc);
-    else if (rep == 2) attn_fast<2>(op, op.qkv, op.out, pos, sm, sc);
-    else               attn_fast<4>(op, op.qkv, op.out, pos, sm, sc);
+    if (rep == 1)      attn_fast<1>(op, op.qkv, op.out, pos, sm, sc, qkv_ll, tag_in);
+    else if (rep == 2) attn_fast<2>(op, op.qkv, op.out, pos, sm, sc, qkv_ll, tag_in);
+    else               attn_fast<4>(op, op.qkv, op.out, pos, sm, sc, qkv_ll, tag_in);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1307,7 +1332,7 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
             switch (op.type) {
                 case OP_GEMV:       cons_seq += stage_gemv(op, st, &ls, xs, red, ring, cons_seq, cfg.sched, cfg.n_sched, n_frames, pf, prof_on ? cfg.prof : nullptr,
                                                            cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll); break;
-                case OP_ATTN:       stage_attn(op, &ls, scratch); break;
+                case OP_ATTN:       stage_attn(op, &ls, scratch, cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll); break;
                 case OP_COPY:       stage_copy(op); break;
                 case OP_SAMPLE_CB0: stage_sample_cb0(op, st, &ls, scratch, xs); all_to_all = false; break;
                 case OP_SAMPLE_CP:  stage_sample_cp(op, st, &ls, scratch, xs); all_to_all = false; break;

@@ -106,8 +106,9 @@ struct Op {
     // flag-carrying copies ("LL": one 64-bit word = f32 value | 32-bit stage tag << 32) that let the
     // consumer stage poll the data itself instead of waiting at a grid barrier (see F_LL_OUT)
     unsigned long long * out_ll;         // written next to `out` with this stage's tag
-    const unsigned long long * in_ll;    // IN_VEC read from here, tag = this stage's tag - in_dist
+    const unsigned long long * in_ll;    // IN_VEC (OP_ATTN: qkv) read from here, tag = this stage's tag - in_dist
     const unsigned long long * res_ll;   // EPI_ADD residual, tag = this stage's tag - res_dist
+    unsigned long long * x_out_ll;       // flag-carrying copy of x_out (this stage's tag)
     int32_t in_dist, res_dist;
     // ---- OP_ATTN ----
     const float * qkv;       // [(n_heads + 2 n_kv_heads) * 128] raw projections

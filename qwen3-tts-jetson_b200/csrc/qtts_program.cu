@@ -6,6 +6,7 @@
 //   16 code embeddings + text row (src/tts_transformer.cpp:2529-2553).
 #include "qtts_engine.h"
 #include <algorithm>
+#include <utility>
 #include <cstring>
 
 namespace qtts {
@@ -31,7 +32,7 @@ static Op gemv(const __nv_bfloat16 * W, int rows, int K, const float * in, const
 }
 
 struct LayerBuf { float * x, * qkv, * attn, * act; __half * kc, * vc; size_t kv_layer_stride; float * attn_part; unsigned int * attn_cnt;
-                  unsigned long long * x_ll, * act_ll; };
+                  unsigned long long * x_ll, * act_ll, * qkv_ll, * attn_ll; };
 
 // five stages of one decoder layer over n_tok tokens (2 only for the merged code-predictor
 // positions 0/1); `first` (if non-null) replaces the QKV stage's input setup
@@ -49,6 +50,17 @@ static void emit_layer(Engine * e, std::vector<Op> & P, const LayerW & L, const 
     } else if (ll && ll_in) {
         q.in_ll = B.x_ll; q.in_dist = 1;      // previous layer's down projection
     }
+    // the attention stage polls the projections; without a barrier in between, the residual the O
+    // projection adds must be flag-carrying too (x_out of a first layer, else the previous down projection)
+    const bool attn_ll_out = ll && mode != ATTN_FAST;     // ATTN_FAST merges split-KV partials across CTAs: barrier stays
+    int o_res_dist = 0;
+    if (ll) {
+        q.out_ll = B.qkv_ll; q.flags |= F_LL_OUT;
+        if (attn_ll_out) {
+            if (q.x_out) { q.x_out_ll = B.x_ll; o_res_dist = 2; }
+            else if (!first && ll_in) o_res_dist = 3;
+        }
+    }
     P.push_back(q);
     Op a = blank();
     a.type = OP_ATTN; a.qkv = B.qkv; a.q_norm_w = L.q_norm; a.k_norm_w = L.k_norm;
@@ -59,10 +71,15 @@ static void emit_layer(Engine * e, std::vector<Op> & P, const LayerW & L, const 
     a.eps = eps; a.out = B.attn;
     a.n_tok = n_tok; a.qkv_stride = qkv_rows; a.out_stride = aw;
     a.attn_part = B.attn_part; a.attn_cnt = B.attn_cnt;
+    if (ll) { a.in_ll = B.qkv_ll; a.in_dist = 1; }
+    // (a first layer fed by a plain vector without x_out - the mtp_proj case - keeps the barrier)
+    const bool a_ll_out = attn_ll_out && o_res_dist != 0;
+    if (a_ll_out) { a.out_ll = B.attn_ll; a.flags |= F_LL_OUT; }
     P.push_back(a);
     Op o = gemv(L.wo, D.H, aw, B.attn, nullptr, eps, EPI_ADD, B.x);
     o.res = B.x; o.n_tok = n_tok; o.in_stride = aw; o.out_stride = D.H;
     if (ll) { o.out_ll = B.x_ll; o.flags |= F_LL_OUT; }
+    if (a_ll_out) { o.in_ll = B.attn_ll; o.in_dist = 1; o.res_ll = B.x_ll; o.res_dist = o_res_dist; }
     P.push_back(o);
     Op gu = gemv(L.wgu, 2 * D.ffn, D.H, B.x, L.ffn_norm, eps, EPI_SWIGLU, B.act);
     gu.n_tok = n_tok; gu.in_stride = D.H; gu.out_stride = D.ffn;
@@ -81,7 +98,7 @@ void emit_talker_step(Engine * e, Slot & s, std::vector<Op> & P, int in_kind, co
     const qtts_config & c = e->cfg;
     const Dims D{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
     LayerBuf B{s.x, s.qkv, s.attn, s.act, s.kc, s.vc, (size_t) e->max_ctx * c.n_kv_heads * kHeadDim, s.attn_part, s.attn_cnt,
-               s.x_ll, s.act_ll};
+               s.x_ll, s.act_ll, s.qkv_ll, s.attn_ll};
     Op first = blank();
     first.in_kind = in_kind; first.in = in_vec; first.es = s.es; first.x_out = s.x;
     for (int l = 0; l < c.n_layers; ++l)
@@ -109,7 +126,7 @@ void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float 
     const qtts_config & c = e->cfg;
     const Dims D{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
     LayerBuf B{s.cp_x, s.cp_qkv, s.cp_attn, s.cp_act, s.cp_kc, s.cp_vc, (size_t) 16 * c.cp_n_kv_heads * kHeadDim,
-               s.attn_part, s.attn_cnt, s.cp_x_ll, s.cp_act_ll};
+               s.attn_part, s.attn_cnt, s.cp_x_ll, s.cp_act_ll, s.cp_qkv_ll, s.cp_attn_ll};
     const int n_pos = c.n_codebooks;   // 16 positions -> 15 sampled codes
     for (int p = 1; p < n_pos; ++p) {
         const int n_tok = (p == 1) ? 2 : 1;
@@ -255,10 +272,14 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
             for (Slot & t : e->slots) {
                 const qtts_config & c = e->cfg;
                 const size_t maxH = (size_t) std::max(c.hidden_size, c.cp_hidden_size);
-                QTTS_CUDA(cudaMemsetAsync(t.x_ll, 0, maxH * 8, e->stream));
-                QTTS_CUDA(cudaMemsetAsync(t.act_ll, 0, (size_t) c.intermediate_size * 8, e->stream));
-                QTTS_CUDA(cudaMemsetAsync(t.cp_x_ll, 0, 2 * maxH * 8, e->stream));
-                QTTS_CUDA(cudaMemsetAsync(t.cp_act_ll, 0, 2 * (size_t) c.cp_intermediate_size * 8, e->stream));
+                const size_t qkvw = (size_t) (c.n_heads + 2 * c.n_kv_heads) * kHeadDim;
+                const size_t cqkvw = (size_t) (c.cp_n_heads + 2 * c.cp_n_kv_heads) * kHeadDim;
+                const std::pair<unsigned long long *, size_t> bufs[] = {
+                    {t.x_ll, maxH}, {t.act_ll, (size_t) c.intermediate_size}, {t.cp_x_ll, 2 * maxH},
+                    {t.cp_act_ll, 2 * (size_t) c.cp_intermediate_size}, {t.qkv_ll, qkvw},
+                    {t.attn_ll, (size_t) c.n_heads * kHeadDim}, {t.cp_qkv_ll, 2 * cqkvw},
+                    {t.cp_attn_ll, 2 * (size_t) c.cp_n_heads * kHeadDim}};
+                for (const auto & b : bufs) QTTS_CUDA(cudaMemsetAsync(b.first, 0, b.second * 8, e->stream));
             }
             e->ll_seq = 0;
         }

@@ -189,6 +189,10 @@ static bool alloc_slot(Engine * e, Slot & s, int index) {
     s.act_ll = e->dalloc<unsigned long long>(c.intermediate_size);
     s.cp_x_ll = e->dalloc<unsigned long long>(2 * (size_t) maxH);
     s.cp_act_ll = e->dalloc<unsigned long long>(2 * (size_t) c.cp_intermediate_size);
+    s.qkv_ll = e->dalloc<unsigned long long>(qkvw);
+    s.attn_ll = e->dalloc<unsigned long long>((size_t) c.n_heads * kHeadDim);
+    s.cp_qkv_ll = e->dalloc<unsigned long long>(2 * (size_t) cqkvw);
+    s.cp_attn_ll = e->dalloc<unsigned long long>(2 * (size_t) c.cp_n_heads * kHeadDim);
     s.cp_hidden_in = e->dalloc<float>(H);
     s.cp_dump = e->dalloc<float>((size_t) 16 * c.cp_vocab_size);
     s.cb0_dump = e->dalloc<float>(c.codec_vocab_size);
