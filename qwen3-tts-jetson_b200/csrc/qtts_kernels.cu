@@ -19,6 +19,12 @@
 //                 :5224-5330 soft_max for the code-predictor / prefill variant).
 //   stage_sample_*: src/tts_transformer.cpp:2198-2236 and :2417-2499.
 #include "qtts_ops.cuh"
+#ifndef QTTS_OPT_RES
+#define QTTS_OPT_RES 1
+#endif
+#ifndef QTTS_OPT_ATTN
+#define QTTS_OPT_ATTN 1
+#endif
 #include <math_constants.h>
 
 namespace qtts {
@@ -310,10 +316,16 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
     for (int q = q_begin + warp; q < q_end; q += kWarps) {
         const int p = p0 + q;
         float side = 0.f;       // residual or bias of (token lane>>1, row 2p + (lane&1))
+        const unsigned long long * side_p = nullptr;     // flag-carrying residual: requested now, checked after the dots
+        unsigned long long side_w = 0;
         if (lane < 2 * NT) {
             const int t = lane >> 1, r = 2 * p + (lane & 1);
             if (op.epi == EPI_ADD) {
+#if QTTS_OPT_RES
+                if (ll && op.res_ll) { side_p = op.res_ll + (size_t) t * op.out_stride + r; side_w = ll_load(side_p); }
+#else
                 if (ll && op.res_ll) side = ll_wait(op.res_ll + (size_t) t * op.out_stride + r, tag - (uint32_t) op.res_dist);
+#endif
                 else side = __ldcg(op.res + (size_t) t * op.out_stride + r);
             }
             else if (op.epi == EPI_BIAS || op.epi == EPI_BIAS_SILU) side = __ldg(op.bias + r);
@@ -366,6 +378,12 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
         } else if (lane < 2 * NT) {
             const int t = lane >> 1, r = 2 * p + (lane & 1);
             float acc = (lane & 1) ? ((t == 0) ? a1[0] : a1[NT - 1]) : ((t == 0) ? a0[0] : a0[NT - 1]);
+            if (side_p) {
+                const uint32_t want = tag - (uint32_t) op.res_dist;
+                uint32_t spins = 0;
+                while ((uint32_t) (side_w >> 32) != want) { ll_spin_guard(spins); side_w = ll_load(side_p); }
+                side = __uint_as_float((uint32_t) side_w);
+            }
             acc += side;
             if (op.epi == EPI_BIAS_SILU) acc = silu_f(acc);
             op.out[(size_t) t * op.out_stride + r] = acc;
@@ -462,7 +480,7 @@ __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * l
 __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, LocalState * ls, float * xs, double * red,
                                const Ring & ring, uint32_t cons_seq,
                                const WSched * sched, int n_sched, int n_frames, Prefetch & pf, unsigned long long * prof,
-                               uint32_t tag, bool ll) {
+                               uint32_t tag, bool ll, bool pf_pending) {
     const int K = op.K;
     const bool ll_in = ll && op.in_ll != nullptr && op.in_kind == IN_VEC;
     const uint32_t tag_in = tag - (uint32_t) op.in_dist;
@@ -497,6 +515,7 @@ __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, 
         }
     }
     __syncthreads();
+    if (pf_pending && threadIdx.x == kPfThread) prefetch_issue(sched, n_sched, n_frames, pf, cons_seq, ring);
     if (prof_on) { const long long t = clock64(); prof[OP_GEMV * 8 + 4] += (unsigned long long) (t - tA); tA = t; }
 
     int p0, p1;
@@ -548,18 +567,40 @@ struct AttnSmem {
     int   flag;
 };
 
-// q (nq heads from h_first), k, v of one token: per-head RMSNorm (double sum), NEOX RoPE at `pos`
+// q (nq heads from h_first), k, v of one token: per-head RMSNorm (double sum), NEOX RoPE at `pos`.
+// A thread owns elements tid and tid + kThreads of the (nq + 2) x 128 staging block; its QK-norm
+// weights and RoPE factors are requested BEFORE the projections are read (polled), so the stage
+// has one L2 round trip on its critical path instead of three.
 __device__ void attn_prepare(const Op & op, const float * qkv, int h_first, int nq, int g, int pos, AttnSmem * sm,
                              const unsigned long long * qkv_ll = nullptr, uint32_t tag_in = 0) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int rows = nq + 2;
-    __syncthreads();
-    for (int idx = tid; idx < rows * kHeadDim; idx += kThreads) {
+    static_assert((kMaxRep + 2) * kHeadDim <= 2 * kThreads, "two staging elements per thread");
+    float nw[2], rc[2], rs[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int idx = tid + u * kThreads;
         const int row = idx / kHeadDim, d = idx % kHeadDim;
-        const float * src = (row < nq)  ? qkv + (size_t) (h_first + row) * kHeadDim
-                          : (row == nq) ? qkv + (size_t) (op.n_heads + g) * kHeadDim
-                                        : qkv + (size_t) (op.n_heads + op.n_kv_heads + g) * kHeadDim;
-        sm->tmp[idx] = qkv_ll ? ll_wait(qkv_ll + (src - qkv) + d, tag_in) : __ldcg(src + d);
+        nw[u] = 1.f; rc[u] = 1.f; rs[u] = 0.f;
+        if (QTTS_OPT_ATTN && row <= nq) {
+            // QK-norm only when the layer has the weight (src/tts_transformer.cpp:1424-1432)
+            const float * w = (row < nq) ? op.q_norm_w : op.k_norm_w;
+            if (w) nw[u] = __ldg(w + d);
+            const float2 cs = __ldg(reinterpret_cast<const float2 *>(op.rope) + (size_t) pos * 64 + (d & 63));
+            rc[u] = cs.x; rs[u] = cs.y;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int idx = tid + u * kThreads;
+        if (idx < rows * kHeadDim) {
+            const int row = idx / kHeadDim, d = idx % kHeadDim;
+            const float * src = (row < nq)  ? qkv + (size_t) (h_first + row) * kHeadDim
+                              : (row == nq) ? qkv + (size_t) (op.n_heads + g) * kHeadDim
+                                            : qkv + (size_t) (op.n_heads + op.n_kv_heads + g) * kHeadDim;
+            sm->tmp[idx] = qkv_ll ? ll_wait(qkv_ll + (src - qkv) + d, tag_in) : __ldcg(src + d);
+        }
     }
     __syncthreads();
     if (warp <= nq) {       // rows 0..nq (queries and the key) are normalised
@@ -570,30 +611,38 @@ __device__ void attn_prepare(const Op & op, const float * qkv, int h_first, int 
         if (lane == 0) sm->red[warp] = ss;
     }
     __syncthreads();
-    for (int idx = tid; idx < (nq + 1) * kHeadDim; idx += kThreads) {
-        const int row = idx / kHeadDim, d = idx % kHeadDim;
-        // QK-norm only when the layer has the weight (src/tts_transformer.cpp:1424-1432)
-        const float * w = (row < nq) ? op.q_norm_w : op.k_norm_w;
-        if (w) {
-            const float mean = (float) (sm->red[row] / (double) kHeadDim);
-            const float scale = 1.0f / sqrtf(mean + op.eps);
-            sm->tmp[idx] = (sm->tmp[idx] * scale) * w[d];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int idx = tid + u * kThreads;
+        if (idx < (nq + 1) * kHeadDim) {
+            const int row = idx / kHeadDim;
+            const float * w = (row < nq) ? op.q_norm_w : op.k_norm_w;
+            if (w) {
+                const float mean = (float) (sm->red[row] / (double) kHeadDim);
+                const float scale = 1.0f / sqrtf(mean + op.eps);
+                sm->tmp[idx] = (sm->tmp[idx] * scale) * (QTTS_OPT_ATTN ? nw[u] : w[idx % kHeadDim]);
+            }
         }
     }
     __syncthreads();
-    for (int idx = tid; idx < rows * kHeadDim; idx += kThreads) {
-        const int row = idx / kHeadDim, d = idx % kHeadDim;
-        if (row <= nq) {
-            const int i = d & 63;
-            const float c = op.rope[((size_t) pos * 64 + i) * 2], s = op.rope[((size_t) pos * 64 + i) * 2 + 1];
-            const float x0 = sm->tmp[row * kHeadDim + i], x1 = sm->tmp[row * kHeadDim + i + 64];
-            const float r = (d < 64) ? (x0 * c - x1 * s) : (x0 * s + x1 * c);
-            if (row < nq) sm->q[row][d] = (op.mode == ATTN_F32) ? r : f16r(r);
-            else { sm->kf[d] = r; sm->k16[d] = __float2half_rn(r); }
-        } else {
-            const float v = sm->tmp[idx];
-            sm->vf[d] = v;
-            sm->v16[d] = __float2half_rn(v);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int idx = tid + u * kThreads;
+        if (idx < rows * kHeadDim) {
+            const int row = idx / kHeadDim, d = idx % kHeadDim;
+            if (row <= nq) {
+                const int i = d & 63;
+                const float c = QTTS_OPT_ATTN ? rc[u] : op.rope[((size_t) pos * 64 + i) * 2];
+                const float sn = QTTS_OPT_ATTN ? rs[u] : op.rope[((size_t) pos * 64 + i) * 2 + 1];
+                const float x0 = sm->tmp[row * kHeadDim + i], x1 = sm->tmp[row * kHeadDim + i + 64];
+                const float r = (d < 64) ? (x0 * c - x1 * sn) : (x0 * sn + x1 * c);
+                if (row < nq) sm->q[row][d] = (op.mode == ATTN_F32) ? r : f16r(r);
+                else { sm->kf[d] = r; sm->k16[d] = __float2half_rn(r); }
+            } else {
+                const float v = sm->tmp[idx];
+                sm->vf[d] = v;
+                sm->v16[d] = __float2half_rn(v);
+            }
         }
     }
     __syncthreads();
@@ -1256,10 +1305,9 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
     __shared__ __align__(8) uint64_t full_bar[kNumSlots];
     __shared__ double red[kWarps];
     __shared__ LocalState ls;
-    __shared__ Op sop;
+    __shared__ Op sop2[2];         // stage descriptors, double buffered: [n & 1] is stage n's
     static_assert(sizeof(Op) % 4 == 0 && sizeof(Op) / 4 <= kThreads, "one descriptor word per thread");
     uint32_t next_word = 0;
-    bool have_next = false;
 
     Ring ring;
     ring.base = smem_raw;
@@ -1304,34 +1352,43 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
         }
         prefetch_issue(cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring);
     }
+    int cur = 0;
+    if (threadIdx.x < (int) (sizeof(Op) / 4)) {
+        reinterpret_cast<uint32_t *>(&sop2[0])[threadIdx.x] = __ldg(reinterpret_cast<const uint32_t *>(ops) + threadIdx.x);
+        next_word = __ldg(reinterpret_cast<const uint32_t *>(ops + (1 % n_ops)) + threadIdx.x);
+    }
     bool stop = false;
     bool pf_pending = false;        // a stage without a grid barrier leaves the ring refill to the next stage's entry
     const bool ll = cfg.persistent != 0;
     for (int f = 0; f < n_frames && !stop; ++f) {
         if (cfg.check_done && ls.done) break;
         for (int i = 0; i < n_ops && !stop; ++i) {
-            // stage descriptor -> shared memory (with ~225 KB of shared memory per CTA there is no L1 left:
-            // every field read from the global descriptor was an L2 round trip); the NEXT stage's
-            // descriptor is requested now and parked in a register during the stage
+            // stage descriptors live in shared memory (with ~225 KB of shared memory per CTA there is no
+            // L1 left: every field read from the global descriptor was an L2 round trip).  Stage n+1's
+            // descriptor is written to the other buffer now, from the register it was requested into
+            // one stage ago, and stage n+2's is requested: one __syncthreads per stage boundary.
             __syncthreads();
-            if (pf_pending && threadIdx.x == kPfThread) prefetch_issue(cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring);
-            pf_pending = false;
             if (threadIdx.x < (int) (sizeof(Op) / 4)) {
-                if (!have_next) next_word = __ldg(reinterpret_cast<const uint32_t *>(ops + i) + threadIdx.x);
-                reinterpret_cast<uint32_t *>(&sop)[threadIdx.x] = next_word;
-                const int ni = (i + 1 < n_ops) ? i + 1 : 0;
+                reinterpret_cast<uint32_t *>(&sop2[cur ^ 1])[threadIdx.x] = next_word;
+                const int ni = (i + 2) % n_ops;
                 next_word = __ldg(reinterpret_cast<const uint32_t *>(ops + ni) + threadIdx.x);
-                have_next = true;
             }
-            __syncthreads();
-            const Op & op = sop;
+            const Op & op = sop2[cur];
+            cur ^= 1;
+            // ring refill left over by a stage that ended without a grid barrier: a GEMV stage issues it
+            // after its input is staged (the prefetcher's warp is the one with the fewest rows), any
+            // other stage right here
+            if (pf_pending && op.type != OP_GEMV && threadIdx.x == kPfThread)
+                prefetch_issue(cfg.sched, cfg.n_sched, n_frames, pf, cons_seq, ring);
+            const bool pf_in_stage = pf_pending && op.type == OP_GEMV;
+            pf_pending = false;
             bool all_to_all = true;
             const bool prof_on = cfg.prof && blockIdx.x == cfg.prof_cta && threadIdx.x == 0;
             const long long t0 = prof_on ? clock64() : 0;
             const long long t0p = (cfg.prof && threadIdx.x == 0) ? clock64() : 0;
             switch (op.type) {
                 case OP_GEMV:       cons_seq += stage_gemv(op, st, &ls, xs, red, ring, cons_seq, cfg.sched, cfg.n_sched, n_frames, pf, prof_on ? cfg.prof : nullptr,
-                                                           cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll); break;
+                                                           cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll, pf_in_stage); break;
                 case OP_ATTN:       stage_attn(op, &ls, scratch, cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll); break;
                 case OP_COPY:       stage_copy(op); break;
                 case OP_SAMPLE_CB0: stage_sample_cb0(op, st, &ls, scratch, xs); all_to_all = false; break;
