@@ -288,7 +288,7 @@ __device__ __forceinline__ int n_issuers(int n_tile, int m_tiles) {
     return n;
 }
 
-__device__ __noinline__ void bgemm_issue(BShared * S, int w, int n_iss, int kc, int mt, uint32_t a0, uint32_t a_lbo, uint32_t a_sbo,
+__device__ __forceinline__ void bgemm_issue(BShared * S, int w, int n_iss, int kc, int mt, uint32_t a0, uint32_t a_lbo, uint32_t a_sbo,
                                          uint64_t * a_free, int piece, int koff, int kp, uint32_t cons_seq, uint32_t idesc,
                                          int m_tiles, bool last) {
     const BOp & op = S->op;
@@ -956,14 +956,13 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
             if (S->all_done) break;
         }
         for (int i = 0; i < n_ops; ++i) {
-            // stage descriptor -> shared memory (the previous stage ended with a barrier); the descriptor
-            // of the NEXT stage is requested now and parked in a register during the stage
+            // stage descriptor -> shared memory.  It was requested before the previous stage's grid
+            // barrier (see below), never across a call: a pending global load makes the first
+            // non-inlined call of the stage wait a full L2 round trip.
             static_assert(sizeof(BOp) / 4 <= kThreads, "one word per thread");
             if (threadIdx.x < (int) (sizeof(BOp) / 4)) {
                 if (!have_next) next_word = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + i) + threadIdx.x);
                 reinterpret_cast<uint32_t *>(&S->op)[threadIdx.x] = next_word;
-                const int ni = (i + 1 < n_ops) ? i + 1 : 0;
-                next_word = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + ni) + threadIdx.x);
                 have_next = true;
             }
             __syncthreads();
@@ -979,6 +978,10 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                 case BOP_SAMPLE:  bstage_sample(S); break;
             }
             const long long t1 = prof ? clock64() : 0;
+            if (threadIdx.x < (int) (sizeof(BOp) / 4)) {     // next stage's descriptor lands during the barrier
+                const int ni = (i + 1 < n_ops) ? i + 1 : 0;
+                next_word = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + ni) + threadIdx.x);
+            }
             bgrid_barrier(S, epoch);
             if (prof) {
                 const long long t2 = clock64();
