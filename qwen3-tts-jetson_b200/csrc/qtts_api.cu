@@ -460,7 +460,7 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     __nv_bfloat16 * dW = e->dalloc<__nv_bfloat16>(nW, false);
     cudaMemcpy(dW, wb.data(), nW * 2, cudaMemcpyHostToDevice);
     TiledW T;
-    if (!tile_matrix(e, dW, rows, K, T)) return cleanup(0);
+    if (!tile_matrix(e, dW, rows, K, T, in_f16 != 0 && epi == EPI_ADD)) return cleanup(0);
     void * dX = nullptr;
     if (in_f16) {
         // F16 activations live in global memory as UMMA-canonical 128-column chunks (qtts_batched.cu: canon_off)
@@ -495,12 +495,14 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     memset(&o, 0, sizeof(o));
     o.type = BOP_GEMM; o.n_streams = n_streams; o.rows_act = rows_act; o.n_tok = n_tok;
     o.flags = ssq_out ? BF_SSQ_OUT : 0;
-    o.Wt = T.p; o.rows = rows; o.K = K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = 0; o.kpp = T.kpp; o.n_pieces = T.n_pieces;
+    o.Wt = T.p; o.rows = rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = 0; o.kpp = T.kpp; o.n_pieces = T.n_pieces;
+    o.ksplit = T.ksplit;
+    if (T.ksplit > 1) o.part_ll = e->dalloc<unsigned long long>((size_t) rows * 256);
     o.in_kind = in_f16 ? BIN_F16 : BIN_F32; o.in = dX; o.in_row_stride = K; o.in_tok_stride = n_streams * K;
     o.norm_w = d_norm; o.ssq_in = d_ssq_in; o.n_parts_in = 4; o.eps = eps;
     o.epi = epi; o.out32 = d_out; o.out16 = d_out16; o.res = d_res; o.bias = d_bias;
     o.out_row_stride = outw; o.out_tok_stride = n_streams * outw; o.ssq_out = d_ssq;
-    BSched sc{T.p, T.n_tile * K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles, 0, 0};
+    BSched sc{T.p, T.n_tile * T.K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles, 0, 0};
     BOp * d_ops = e->dalloc<BOp>(1, false);
     BSched * d_sc = e->dalloc<BSched>(1, false);
     StreamState * d_st = e->dalloc<StreamState>(n_streams);
@@ -529,8 +531,9 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
         if (pr[48]) fprintf(stderr, "[bgemm]   F32 stage, thread 0 of tile 0's CTA (cycles per tile): prologue %llu, wait A buffer %llu, convert+store (incl. load latency) %llu, "
                             "fence+sync %llu, issue %llu, epilogue+sync %llu, total %llu\n", pr[49] / pr[48], pr[50] / pr[48], pr[51] / pr[48],
                             pr[52] / pr[48], pr[53] / pr[48], pr[54] / pr[48], pr[55] / pr[48]);
-        if (pr[40]) fprintf(stderr, "[bgemm]   MMA thread per tile (cycles): wait weights %llu, wait A %llu, issue+commit %llu, loop %llu\n",
-                            pr[41] / pr[40], pr[42] / pr[40], pr[43] / pr[40], pr[44] / pr[40]);
+        if (pr[40]) fprintf(stderr, "[bgemm]   F16 stage, issuer 0 of tile 0 (cycles per tile): first A chunk after %llu, waiting for A %llu, issue+commit+weights %llu, "
+                            "loop %llu; warp 1: epilogue (incl. wait for the MMAs) %llu, closing sync %llu\n",
+                            pr[41] / pr[40], pr[42] / pr[40], pr[43] / pr[40], pr[44] / pr[40], pr[45] / pr[40], pr[46] / pr[40]);
     }
     cudaEventDestroy(t0); cudaEventDestroy(t1);
     if (r != cudaSuccess) { e->err = std::string("bgemm: ") + cudaGetErrorString(r); return cleanup(0); }

@@ -84,7 +84,7 @@ struct BPrefetch {           // used by the prefetcher thread only
 struct BShared {
     uint64_t full[kBSlots], empty[kBSlots], abar[2], dbar;
     uint64_t tfull[4], tempty[4];     // A pieces brought by bulk copies (F16-input stages)
-    uint32_t n_fill[4], n_cons[kIssuersMax][4];   // fills issued (producer) / consumptions done (per MMA issuer) per A buffer
+    uint32_t n_fill[4], fill_base[4];  // fills issued per A buffer (producer's counter) / its value at the start of the stage
     BRun run;                // copy of the kernel parameter
     BOp op;                  // the stage being executed
     Op item_op;              // Talker attention: per-item view for the batch-1 helpers
@@ -95,6 +95,7 @@ struct BShared {
     uint32_t cons_seq;       // ring pieces consumed so far
     uint32_t a_use[2];       // commits issued on abar[i]
     uint32_t d_use;          // commits issued on dbar
+    uint32_t tag;            // this stage's tag (split-K hand-off)
     int32_t all_done;
 };
 constexpr size_t kBSharedBytes = (sizeof(BShared) + 127) & ~(size_t) 127;
@@ -312,14 +313,20 @@ __device__ __forceinline__ void bgemm_issue(BShared * S, int w, int n_iss, int k
 }
 
 // epilogue of tile t: warp w reads TMEM lanes 32*(w%4).. (its sub-partition), 16 columns per pass
-__device__ __noinline__ void bgemm_epilogue(BShared * S, int t, int m_tiles, uint32_t d_use) {
+__device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_tiles, uint32_t d_use, int n_acc = 0) {
     const BOp & op = S->op;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tmem_base = S->tmem_base;
     const int dbg = S->run.dbg;
     const int q = warp & 3;
     const int ncg = op.n_tile >> 4;
-    const int n_iss = n_issuers(op.n_tile, m_tiles);
+    // n_acc > 0: accumulators of issuers 0..n_acc-1 are summed; -1: m-tile mt has one accumulator, issuer mt's
+    const int n_iss = n_acc > 0 ? n_acc : (n_acc < 0 ? 1 : n_issuers(op.n_tile, m_tiles));
+    // split-K: virtual tile -> (row block t, K-half); half 1 only publishes its partial accumulator
+    const int ks = op.ksplit > 1 ? op.ksplit : 1;
+    const int t = t_virtual / ks, half = t_virtual - t * ks;
+    const int rows_pad = (op.rows_act + 31) & ~31;
+    const uint32_t tag = S->tag;
     bool waited = false;
     for (int cg = warp >> 2; cg < ncg; cg += 4) {
         const int n0 = t * op.n_tile + cg * 16;
@@ -330,7 +337,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t, int m_tiles, uin
             const int r = m64 ? q * 16 + lane : mt * 128 + q * 32 + lane;
             const bool valid = r < op.rows_act && (!m64 || lane < 16);
             float4 side[4];
-            if (valid && op.epi == EPI_ADD) {
+            if (valid && op.epi == EPI_ADD && half == 0) {
                 const float * rs = op.res + row_off(r, op.n_streams, op.out_row_stride, op.out_tok_stride) + n0;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) side[i] = __ldcg(reinterpret_cast<const float4 *>(rs + 4 * i));
@@ -342,7 +349,8 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t, int m_tiles, uin
             __syncwarp();
             float acc[16];
             if (!(dbg & 2)) {
-                tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) (mt * op.n_tile + cg * 16), acc);
+                const int wa = (n_acc < 0) ? mt : 0;
+                tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) ((wa * m_tiles + mt) * op.n_tile + cg * 16), acc);
                 for (int w = 1; w < n_iss; ++w) {
                     float more[16];
                     tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) ((w * m_tiles + mt) * op.n_tile + cg * 16), more);
@@ -352,6 +360,33 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t, int m_tiles, uin
             } else {
 #pragma unroll
                 for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+            }
+            if (ks > 1 && valid) {
+                unsigned long long * pp = op.part_ll + (((size_t) t * ncg + cg) * rows_pad + r) * 16;
+                if (half == 1) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const unsigned long long w = ((unsigned long long) tag << 32) | (unsigned long long) __float_as_uint(acc[i]);
+                        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(pp + i), "l"(w) : "memory");
+                    }
+                    continue;
+                }
+                // half 0: all 16 words requested together, repeated until every tag matches
+                uint32_t spins = 0;
+                bool ok;
+                do {
+                    unsigned long long w[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w[i]) : "l"(pp + i) : "memory");
+                    ok = true;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) ok = ok && ((uint32_t) (w[i] >> 32) == tag);
+                    if (ok) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) acc[i] += __uint_as_float((uint32_t) w[i]);
+                    } else if (++spins > (1u << 22)) __trap();
+                } while (!ok);
             }
             if (valid) bepilogue16(op, r, n0, acc, side);
         }
@@ -420,11 +455,12 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
                 const int kc = s / m_tiles, mt = s - kc * m_tiles;
                 bload<IN_KIND>(op, kc, mt, u, v, nw);
             };
-            auto process = [&](int j, const uint4 * v, const float4 & nw) {
+            // a load unit goes to shared memory (after the MMAs that read this buffer two chunks ago are done)
+            auto stage_unit = [&](int j, const uint4 * v, const float4 & nw) {
                 const int s = j / upc, u = j - s * upc;
                 const int kc = s / m_tiles, mt = s - kc * m_tiles;
                 const int buf = s & 1;
-                if (u == 0) {       // the MMAs that read this buffer two chunks ago must be done
+                if (u == 0) {
                     const uint32_t au = buf ? a_use1 : a_use0;
                     if (au > 0) mbar_wait(S->abar + buf, (au - 1) & 1u);
                 }
@@ -432,30 +468,40 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
                 if (u == upc - 1) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     __syncthreads();
-                    const int kin = kc * kKc;
-                    const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
-                    const int kp = min(op.kpp, op.K - piece * op.kpp);
-                    if (lane == 0 && warp < kIssuers) {
-                        bgemm_issue(S, warp, n_iss, kc, mt, smem_u32(abuf + (size_t) buf * kABufBytes), kALbo, kASbo, S->abar + buf,
-                                    piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
-                    } else if (tid == kPfThread) {
-                        // the piece the NEXT chunk needs must be in flight before the issuers wait for it
-                        const int kin1 = min(kin + kKc, op.K - kKc);
-                        bpf_ensure(S, cons_seq + (uint32_t) (kin1 / op.kpp));
-                        bpf_poll(S);
-                    }
-                    if (buf) a_use1++; else a_use0++;
                 }
+            };
+            // ... and its MMAs are issued AFTER the loads of the unit after next were requested, so the
+            // issuers' ~300 cycles per chunk overlap with the load latency instead of delaying it
+            auto issue_unit = [&](int j) {
+                const int s = j / upc, u = j - s * upc;
+                if (u != upc - 1) return;
+                const int kc = s / m_tiles, mt = s - kc * m_tiles;
+                const int buf = s & 1;
+                const int kin = kc * kKc;
+                const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
+                const int kp = min(op.kpp, op.K - piece * op.kpp);
+                if (lane == 0 && warp < kIssuers) {
+                    bgemm_issue(S, warp, n_iss, kc, mt, smem_u32(abuf + (size_t) buf * kABufBytes), kALbo, kASbo, S->abar + buf,
+                                piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
+                } else if (tid == kPfThread) {
+                    // the piece the NEXT chunk needs must be in flight before the issuers wait for it
+                    const int kin1 = min(kin + kKc, op.K - kKc);
+                    bpf_ensure(S, cons_seq + (uint32_t) (kin1 / op.kpp));
+                    bpf_poll(S);
+                }
+                if (buf) a_use1++; else a_use0++;
             };
             load_unit(0, v0, nw0);
             if (total > 1) load_unit(1, v1, nw1);
             if (tid == kPfThread) bpf_ensure(S, cons_seq);
             for (int j = 0; j < total; j += 2) {
-                process(j, v0, nw0);
+                stage_unit(j, v0, nw0);
                 if (j + 2 < total) load_unit(j + 2, v0, nw0);
+                issue_unit(j);
                 if (j + 1 < total) {
-                    process(j + 1, v1, nw1);
+                    stage_unit(j + 1, v1, nw1);
                     if (j + 3 < total) load_unit(j + 3, v1, nw1);
+                    issue_unit(j + 1);
                 }
             }
             bgemm_epilogue(S, t, m_tiles, d_use);
@@ -492,13 +538,18 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
         const int steps = nkc * m_tiles;
         const int Rg = (op.rows_act + 7) >> 3, cb = Rg << 11;
         const int nab = (Rg <= 8) ? 4 : 2, bstep = 4 / nab;          // buffers in use, barrier index step
-        const int n_iss = n_issuers(op.n_tile, m_tiles);
         const int lane = tid & 31, warp = tid >> 5;
         const int abstride = (nab == 4) ? kABufBytes / 2 : kABufBytes;
+        // accumulators: issuer w (< nab) writes (w, mt) for the steps that land in its buffer; with two
+        // buffers and two m-tiles step kc * 2 + mt lands in buffer mt, i.e. m-tile mt has ONE accumulator, issuer mt's
+        const int acc_mode = (m_tiles == 2 && nab == 2) ? -1 : min(nab, steps);
+        const uint32_t tmem_base = S->tmem_base;
         const uint32_t idesc = (op.rows_act <= 64 ? (S->run.idesc_base & ~(0x1Fu << 24)) | (4u << 24) : S->run.idesc_base) | ((uint32_t) (op.n_tile >> 3) << 17);
         uint32_t d_use = S->d_use, cons_seq = S->cons_seq;
         unsigned char * abuf = babuf_base(S);
         for (int t = t_first; t < op.n_tiles; t += G) {
+            // split-K: virtual tile t reads the activation chunks of its K-half
+            const int kc_base = (op.ksplit > 1) ? (t % op.ksplit) * nkc : 0;
             if (tid == kAProd) {
                 uint64_t pol;
                 asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
@@ -513,34 +564,86 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     if (S->run.dbg & 4) {      // bring-up: pipeline overhead without the copy
                         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->tfull + bi)) : "memory");
                     } else {
-                        const int kcs = (S->run.dbg & 8) ? (kc + (int) blockIdx.x) % nkc : kc;   // bring-up: staggered chunk order
+                        const int kcs = kc_base + ((S->run.dbg & 8) ? (kc + (int) blockIdx.x) % nkc : kc);   // (dbg 8: bring-up, staggered chunk order)
                         mbar_expect_tx(S->tfull + bi, bytes);
                         bulk_g2s(abuf + (size_t) buf * abstride, in + (size_t) kcs * cb + (size_t) mt * 32768, bytes, S->tfull + bi, pol);
                     }
                     S->n_fill[bi] = nf + 1;
                 }
             } else if (lane == 0 && warp < kIssuers) {
-                for (int s = 0; s < steps; ++s) {
-                    const int kc = s / m_tiles, mt = s - kc * m_tiles;
-                    const int buf = s % nab, bi = buf * bstep;
-                    const int kin = kc * kKc;
-                    const int piece = kin / op.kpp, koff = kin - piece * op.kpp;
+                // Chunk-alternating issue: issuer w takes the K-chunks kc = w, w + n_alt, ... and issues all
+                // 8 K-steps of each into its OWN accumulators (summed by the epilogue).  A tcgen05.mma costs
+                // its issuing thread ~60 cycles and a commit ~200; with the K-steps of every chunk spread
+                // over four issuers each of them paid wait + fence + commit per chunk for two MMAs (measured
+                // 1290 cycles per chunk); alternating whole chunks keeps the tensor pipe fed instead.
+                const bool pr = S->run.prof != nullptr && warp == 0 && t == 0;     // stage timers (tile 0's CTA)
+                long long c_wait = 0, c_issue = 0, c_first = 0;
+                const long long c0 = pr ? clock64() : 0;
+                const int w = warp;
+                const uint32_t ring0 = smem_u32(bring_base(S));
+                const uint32_t abuf0 = smem_u32(abuf);
+                const bool skip_mma = (S->run.dbg & 1) != 0;
+                const int nab_shift = (nab == 4) ? 2 : 1;
+                uint32_t started = 0;       // accumulators (w, mt) this issuer has written
+                int kc = 0;
+                for (int piece = 0; piece < op.n_pieces; ++piece) {
                     const int kp = min(op.kpp, op.K - piece * op.kpp);
-                    const uint32_t nc = S->n_cons[warp][bi];
-                    mbar_wait(S->tfull + bi, nc & 1u);
-                    S->n_cons[warp][bi] = nc + 1;
-                    bgemm_issue(S, warp, n_iss, kc, mt, smem_u32(abuf + (size_t) buf * abstride), 128, 2048, S->tempty + bi,
-                                piece, koff, kp, cons_seq, idesc, m_tiles, s == steps - 1);
+                    const int chunks = kp / kKc;
+                    const uint32_t seq = cons_seq + (uint32_t) piece;
+                    const int slot = (int) (seq % (uint32_t) kBSlots);
+                    mbar_wait(S->full + slot, (seq / (uint32_t) kBSlots) & 1u);     // every issuer: keeps the slot phases aligned
+                    const uint32_t w0 = ring0 + (uint32_t) slot * kBSlotBytes;
+                    bool mine = false;
+                    for (int c = 0; c < chunks; ++c, ++kc) {
+                        for (int mt = 0; mt < m_tiles; ++mt) {
+                            const int s = kc * m_tiles + mt;
+                            const int buf = s & (nab - 1), bi = buf * bstep;
+                            if (buf != w) continue;             // issuer w owns A buffer w: its fills are consumed in order by one thread
+                            mine = true;
+                            const uint32_t fill = S->fill_base[bi] + (uint32_t) (s >> nab_shift);
+                            const long long ca = pr ? clock64() : 0;
+                            mbar_wait(S->tfull + bi, fill & 1u);
+                            const long long cb2 = pr ? clock64() : 0;
+                            tc_fence_after();
+                            if (!skip_mma) {
+                                const uint32_t d = tmem_base + (uint32_t) ((w * m_tiles + mt) * op.n_tile);
+                                const uint64_t ad0 = umma_smem_desc(abuf0 + (uint32_t) buf * (uint32_t) abstride, 128, 2048);
+                                const uint64_t bd0 = umma_smem_desc(w0 + (uint32_t) c * 2048u, 128, (uint32_t) kp * 16u);
+                                const bool fresh = !((started >> mt) & 1u);
+                                started |= 1u << mt;
+#pragma unroll
+                                for (int i = 0; i < kKc / 16; ++i)
+                                    umma_f16_ss(d, ad0 + (uint64_t) (i * 16), bd0 + (uint64_t) (i * 16), idesc, (!fresh || i > 0) ? 1u : 0u);
+                            }
+                            umma_commit(S->tempty + bi);
+                            if (pr) { const long long cc = clock64(); c_wait += cb2 - ca; c_issue += cc - cb2; if (s == 0) c_first = cb2 - c0; }
+                        }
+                    }
+                    // release the weight slot: after my MMAs that read it, or at once when I had none in this piece
+                    if (mine) umma_commit(S->empty + slot);
+                    else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->empty + slot)) : "memory");
+                }
+                umma_commit(&S->dbar);
+                if (pr) {
+                    unsigned long long * P = S->run.prof;
+                    P[40] += 1; P[41] += (unsigned long long) c_first; P[42] += (unsigned long long) c_wait;
+                    P[43] += (unsigned long long) c_issue; P[44] += (unsigned long long) (clock64() - c0);
                 }
             } else if (tid == kPfThread) {
                 bpf_ensure(S, cons_seq + (uint32_t) (op.n_pieces - 1));
                 bpf_poll(S);
             }
             __syncwarp();
-            bgemm_epilogue(S, t, m_tiles, d_use);
+            const bool pr1 = S->run.prof != nullptr && tid == 32 && t == 0;      // a thread without issue duties
+            const long long e0 = pr1 ? clock64() : 0;
+            bgemm_epilogue(S, t, m_tiles, d_use, acc_mode);
+            const long long e1 = pr1 ? clock64() : 0;
             d_use++;
             tc_fence_before();
             __syncthreads();
+            if (pr1) { S->run.prof[45] += (unsigned long long) (e1 - e0); S->run.prof[46] += (unsigned long long) (clock64() - e1); }
+            if (tid < 4) S->fill_base[tid] = S->n_fill[tid];      // all fills of this tile were issued and consumed
+            if (t + G < op.n_tiles) __syncthreads();
             cons_seq += (uint32_t) op.n_pieces;
         }
         if (tid == 0) { S->d_use = d_use; S->cons_seq = cons_seq; }
@@ -920,8 +1023,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
         for (int i = 0; i < kBSlots; ++i) { mbar_init(S->full + i, 1); mbar_init(S->empty + i, kIssuers); }
         mbar_init(S->abar, kIssuers); mbar_init(S->abar + 1, kIssuers); mbar_init(&S->dbar, kIssuers);
         for (int i = 0; i < 4; ++i) {
-            mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, kIssuers); S->n_fill[i] = 0;
-            for (int w = 0; w < kIssuersMax; ++w) S->n_cons[w][i] = 0;
+            mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, 1); S->n_fill[i] = 0; S->fill_base[i] = 0;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -965,6 +1067,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                 reinterpret_cast<uint32_t *>(&S->op)[threadIdx.x] = next_word;
                 have_next = true;
             }
+            if (threadIdx.x == kThreads - 1) S->tag = run_param.tag_base + 1u + (uint32_t) (f * n_ops + i);
             __syncthreads();
             const int type = S->op.type, in_kind = S->op.in_kind;
             const long long t0 = prof ? clock64() : 0;

@@ -13,17 +13,21 @@ extern "C" __global__ void qtts_run_batched(const __grid_constant__ BRun run_par
 // rows) and piece p (kpp K-elements, the last one shorter), the piece is one contiguous block in
 // the K-major no-swizzle canonical layout: (row r, 8-element chunk c) at
 //   (r / 8) * (kp * 16) + c * 128 + (r % 8) * 16,  kp = K-extent of the piece.
+// With ksplit > 1 a row block is stored as ksplit virtual tiles, one per K-range of Kh = K / ksplit
+// columns (virtual tile index = row block * ksplit + K-half); kpp / pieces refer to the virtual tile.
 __global__ void k_tile_weights(const __nv_bfloat16 * __restrict__ src, unsigned char * __restrict__ dst,
-                               int rows, int K, int n_tile, int kpp, int to_f16) {
+                               int rows, int K, int n_tile, int kpp, int to_f16, int ksplit) {
     const size_t n_units = (size_t) rows * (K / 8);
+    const int Kh = K / ksplit;
     for (size_t u = (size_t) blockIdx.x * blockDim.x + threadIdx.x; u < n_units; u += (size_t) gridDim.x * blockDim.x) {
         const int r = (int) (u / (K / 8)), c = (int) (u % (K / 8));
         const int t = r / n_tile, rr = r % n_tile;
-        const int k = c * 8, p = k / kpp, kin = k - p * kpp;
-        const int kp = min(kpp, K - p * kpp);
-        const size_t off = (size_t) t * n_tile * K * 2 + (size_t) p * n_tile * kpp * 2 +
+        const int kfull = c * 8, h = kfull / Kh, k = kfull - h * Kh;
+        const int p = k / kpp, kin = k - p * kpp;
+        const int kp = min(kpp, Kh - p * kpp);
+        const size_t off = (size_t) (t * ksplit + h) * n_tile * Kh * 2 + (size_t) p * n_tile * kpp * 2 +
                            (size_t) (rr / 8) * (kp * 16) + (size_t) (kin / 8) * 128 + (size_t) (rr % 8) * 16;
-        uint4 v = *reinterpret_cast<const uint4 *>(src + (size_t) r * K + k);
+        uint4 v = *reinterpret_cast<const uint4 *>(src + (size_t) r * K + kfull);
         if (to_f16) {
             const __nv_bfloat16 * b = reinterpret_cast<const __nv_bfloat16 *>(&v);
             __half h[8];
@@ -47,18 +51,26 @@ static int pick_n_tile(int rows, int grid) {
     return best;
 }
 
-bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T) {
+bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T, bool allow_split) {
     if (rows % 16 || K % kKc) return e->fail("batched path: projection shape must be a multiple of 16 x 128");
-    T.rows = rows; T.K = K;
+    T.rows = rows;
     T.n_tile = pick_n_tile(rows, e->n_sms);
-    T.n_tiles = rows / T.n_tile;
+    // split-K: a narrow projection (O, down) has fewer row blocks than half the SMs; two CTAs per row
+    // block, each streaming half of K, double the bytes in flight of a latency-bound stage
+    const char * env = getenv("QTTS_KSPLIT");
+    // (measured after the chunk-alternating issue: the hand-off costs what the shorter loop saves - off unless QTTS_KSPLIT=1)
+    const bool want = allow_split && env && atoi(env) == 1;
+    T.ksplit = (want && 2 * (rows / T.n_tile) <= e->n_sms && K % (2 * kKc) == 0) ? 2 : 1;
+    const int Kh = K / T.ksplit;
+    T.K = Kh;
+    T.n_tiles = (rows / T.n_tile) * T.ksplit;
     int kpp = (kBSlotBytes / (T.n_tile * 2)) / kKc * kKc;
-    if (kpp > K) kpp = K;
+    if (kpp > Kh) kpp = Kh;
     T.kpp = kpp;
-    T.n_pieces = (K + kpp - 1) / kpp;
+    T.n_pieces = (Kh + kpp - 1) / kpp;
     T.p = e->dalloc<unsigned char>((size_t) rows * K * 2, false);
     if (!T.p) return e->fail("out of device memory for tiled weights");
-    k_tile_weights<<<1184, 256, 0, e->stream>>>(src, T.p, rows, K, T.n_tile, kpp, e->bfmt == 0 ? 1 : 0);
+    k_tile_weights<<<1184, 256, 0, e->stream>>>(src, T.p, rows, K, T.n_tile, kpp, e->bfmt == 0 ? 1 : 0, T.ksplit);
     QTTS_CUDA(cudaGetLastError());
     e->weight_bytes_batched += (int64_t) rows * K * 2;
     return true;
@@ -76,6 +88,7 @@ struct BEmit {
     std::vector<BOp> P;
     std::vector<BSched> S;
     int B, cta_off = 0;
+    unsigned long long * part_ll = nullptr;
 
     void gemm(const TiledW & T, int rows_act, int in_kind, const void * in, int in_row_stride, int in_tok_stride,
               const float * norm_w, const float * ssq_in, int n_parts_in, int epi, float * out32, __half * out16,
@@ -85,6 +98,7 @@ struct BEmit {
         o.type = BOP_GEMM; o.rows_act = rows_act; o.flags = flags | (ssq_out ? BF_SSQ_OUT : 0);
         o.Wt = T.p; o.rows = T.rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = cta_off;
         o.kpp = T.kpp; o.n_pieces = T.n_pieces;
+        o.ksplit = T.ksplit; o.part_ll = (T.ksplit > 1) ? part_ll : nullptr;
         o.in_kind = in_kind; o.in = in; o.in_row_stride = in_row_stride; o.in_tok_stride = in_tok_stride;
         o.norm_w = norm_w; o.ssq_in = ssq_in; o.n_parts_in = n_parts_in; o.eps = e->cfg.rms_norm_eps;
         o.epi = epi; o.out32 = out32; o.out16 = out16; o.res = res; o.bias = bias;
@@ -207,9 +221,9 @@ bool batched_init(Engine * e) {
     e->t_talker.resize(c.n_layers); e->t_cp.resize(c.cp_layers); e->t_lm_head.resize(c.n_codebooks - 1);
     auto layer = [&](const LayerW & W, const Dims & D, TiledLayer & L) {
         return tile_matrix(e, W.wqkv, (D.nh + 2 * D.nkv) * kHeadDim, D.H, L.qkv) &&
-               tile_matrix(e, W.wo, D.H, D.nh * kHeadDim, L.o) &&
+               tile_matrix(e, W.wo, D.H, D.nh * kHeadDim, L.o, true) &&
                tile_matrix(e, W.wgu, 2 * D.ffn, D.H, L.gu) &&
-               tile_matrix(e, W.wdown, D.H, D.ffn, L.down);
+               tile_matrix(e, W.wdown, D.H, D.ffn, L.down, true);
     };
     const Dims T{c.hidden_size, c.n_heads, c.n_kv_heads, c.intermediate_size};
     const Dims C{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
@@ -244,7 +258,11 @@ bool batched_init(Engine * e) {
         G.active = e->dalloc<int32_t>(B);
         if (!G.x || !G.qkv || !G.cp_x || !G.cp_qkv || !G.cp_logits || !G.cp_kc || !G.cp_vc || !G.cp_dump || !G.active)
             return e->fail("out of device memory for the batched activations");
-        BEmit E{e, {}, {}, G.n, 0};
+        // split-K partials: one flag-carrying word per accumulator element of the widest split projection
+        G.part_words = (size_t) std::max(H, cpH) * 256;
+        G.part_ll = e->dalloc<unsigned long long>(G.part_words);
+        if (!G.part_ll) return e->fail("out of device memory for the split-K partials");
+        BEmit E{e, {}, {}, G.n, 0, G.part_ll};
         emit_bframe(e, G, E);
         G.n_ops = (int) E.P.size(); G.n_sched = (int) E.S.size();
         G.ops = e->dalloc<BOp>(E.P.size(), false);
@@ -268,6 +286,16 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
     run.st = st; run.active = d_active; run.bar = e->bar;
     run.n_streams = n_streams; run.n_frames = n_frames; run.check_done = check_done ? 1 : 0;
     run.idesc_base = batched_idesc(e);
+    {   // stage tags never repeat across launches (stale partials can not satisfy a poll)
+        const uint64_t n_tags = (uint64_t) n_ops * (uint64_t) n_frames + 1;
+        if ((uint64_t) e->bll_seq + n_tags > 0xfff00000ull) {
+            QTTS_CUDA(cudaStreamSynchronize(e->stream));
+            for (BGroup & g : e->groups) QTTS_CUDA(cudaMemsetAsync(g.part_ll, 0, g.part_words * 8, e->stream));
+            e->bll_seq = 0;
+        }
+        run.tag_base = e->bll_seq;
+        e->bll_seq += (uint32_t) n_tags;
+    }
     run.prof = e->prof_on ? e->prof + 2048 : nullptr;
     { const char * d = getenv("QTTS_BDBG"); run.dbg = d ? atoi(d) : 0; }
     void * args[] = {(void *) &run};

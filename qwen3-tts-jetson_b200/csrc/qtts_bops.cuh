@@ -59,6 +59,12 @@ struct BOp {
     int32_t out_row_stride, out_tok_stride;
     float * ssq_out;             // [rows_act][rows / 16]
     float * hid_out;             // normalised, unrounded input rows [rows_act][K] (Talker hidden)
+    // split-K (F16-input stages with fewer tiles than half the SMs): the weight matrix is tiled as
+    // ksplit "virtual tiles" per row block (virtual tile v = row block v / ksplit, K-half v % ksplit;
+    // K above is the per-half extent).  Half 1 hands its partial accumulator to half 0 through
+    // flag-carrying words (f32 | stage tag << 32); half 0 adds it in fixed order and runs the epilogue.
+    int32_t ksplit;
+    unsigned long long * part_ll;    // [row blocks][n_tile / 16][rows_act padded to 32][16]
     // ---- attention ----
     const float * qkv; int32_t qkvw;
     const float * q_norm_w, * k_norm_w, * rope;
@@ -97,6 +103,7 @@ struct BRun {
     GridBarrier * bar;
     int32_t n_streams, n_frames, check_done;
     uint32_t idesc_base;         // instruction descriptor without N (formats, M = 128)
+    uint32_t tag_base;           // stage tag = tag_base + 1 + frame * n_ops + op index (never repeated)
     unsigned long long * prof;   // optional stage timers
     int32_t dbg;                 // bring-up switches (env QTTS_BDBG): 1 skip MMA issue, 2 skip TMEM loads
 };

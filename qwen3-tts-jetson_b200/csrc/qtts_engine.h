@@ -29,7 +29,8 @@ struct LayerW {
 struct Dims { int H, nh, nkv, ffn; };
 
 // projection matrix re-tiled for the batched (tcgen05) kernel, see qtts_batched_host.cu
-struct TiledW { unsigned char * p = nullptr; int rows = 0, K = 0, n_tile = 0, n_tiles = 0, kpp = 0, n_pieces = 0; };
+// K = K-extent of one (virtual) tile, n_tiles = number of virtual tiles = row blocks x ksplit
+struct TiledW { unsigned char * p = nullptr; int rows = 0, K = 0, n_tile = 0, n_tiles = 0, kpp = 0, n_pieces = 0, ksplit = 1; };
 struct TiledLayer { TiledW qkv, o, gu, down; };
 
 // per-stream buffers shared by the batch-1 and the batched kernels: one contiguous array over all
@@ -51,6 +52,8 @@ struct BGroup {
     __half * cp_attn16 = nullptr, * cp_act16 = nullptr, * cp_kc = nullptr, * cp_vc = nullptr;
     float * cb0_dump = nullptr, * cp_dump = nullptr;
     int32_t * active = nullptr;
+    unsigned long long * part_ll = nullptr;   // split-K partial accumulators (flag-carrying)
+    size_t part_words = 0;
     BOp * ops = nullptr; int n_ops = 0;
     BSched * sched = nullptr; int n_sched = 0;
     std::vector<BOp> host_ops;
@@ -110,6 +113,7 @@ struct Engine {
     int persistent = 1;
     int ll = 1;                    // flag-carrying activations between GEMV stages instead of grid barriers (env QTTS_LL=0: off)
     uint32_t ll_seq = 0;           // stage tags handed out so far (monotonic across launches)
+    uint32_t bll_seq = 0;          // same for the batched kernel's split-K hand-off
     int ignore_eos = 0;
     int64_t n_weights = 0, n_inexact = 0, weight_bytes = 0, kv_bytes = 0;
     int64_t launches = 0;
@@ -172,7 +176,7 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
 std::vector<WSched> build_sched(Engine * e, const std::vector<Op> & P);
 
 // qtts_batched_host.cu
-bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T);
+bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T, bool allow_split = false);
 bool batched_init(Engine * e);
 uint32_t batched_idesc(const Engine * e);
 bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_sched, int n_sched, StreamState * st,
