@@ -655,6 +655,53 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
 }
 
 // ------------------------------------------------------------------------------------------
+// BOP_NORM: x[r][:] (F32) -> f16( (x * scale_r) * w ) in the canonical chunk layout.  Doing this
+// once per row instead of inside every consumer CTA removes the dominant cost of the normalised
+// GEMM stages (every CTA re-read all rows as F32 from L2 and converted them: 38 MB of L2 traffic
+// per stage at 64 streams) and lets those stages run on the bulk-copy path.
+// Same arithmetic and rounding point as the in-stage prologue (ggml rms_norm, ops.cpp:3709-3758).
+// ------------------------------------------------------------------------------------------
+__device__ __noinline__ void bstage_norm(BShared * S) {
+    const BOp & op = S->op;
+    const int tid = threadIdx.x, K = op.K, np = op.n_parts_in;
+    const int cb = canon_chunk_bytes(op.rows_act);
+    for (int r = blockIdx.x; r < op.rows_act; r += (int) gridDim.x) {
+        const float * x = reinterpret_cast<const float *>(op.in) + row_off(r, op.n_streams, op.in_row_stride, op.in_tok_stride);
+        // everything this thread needs is requested before the reduction
+        const int k = tid * 8;
+        float4 xa = make_float4(0.f, 0.f, 0.f, 0.f), xb = xa, wa = xa, wb = xa;
+        if (k < K) {
+            xa = __ldcg(reinterpret_cast<const float4 *>(x + k)); xb = __ldcg(reinterpret_cast<const float4 *>(x + k + 4));
+            wa = __ldg(reinterpret_cast<const float4 *>(op.norm_w + k)); wb = __ldg(reinterpret_cast<const float4 *>(op.norm_w + k + 4));
+        }
+        double ss = 0.0;
+        for (int i = tid; i < np; i += kThreads) ss += (double) __ldcg(op.ssq_in + (size_t) r * np + i);
+        ss = block_sum_d(ss, S->red);
+        const float mean = (float) (ss / (double) K);
+        const float sc = 1.0f / sqrtf(mean + op.eps);
+        for (int kk = k; kk < K; kk += kThreads * 8) {
+            if (kk != k) {
+                xa = __ldcg(reinterpret_cast<const float4 *>(x + kk)); xb = __ldcg(reinterpret_cast<const float4 *>(x + kk + 4));
+                wa = __ldg(reinterpret_cast<const float4 *>(op.norm_w + kk)); wb = __ldg(reinterpret_cast<const float4 *>(op.norm_w + kk + 4));
+            }
+            const float v0 = (xa.x * sc) * wa.x, v1 = (xa.y * sc) * wa.y, v2 = (xa.z * sc) * wa.z, v3 = (xa.w * sc) * wa.w;
+            const float v4 = (xb.x * sc) * wb.x, v5 = (xb.y * sc) * wb.y, v6 = (xb.z * sc) * wb.z, v7 = (xb.w * sc) * wb.w;
+            if (op.hid_out) {
+                *reinterpret_cast<float4 *>(op.hid_out + (size_t) r * K + kk) = make_float4(v0, v1, v2, v3);
+                *reinterpret_cast<float4 *>(op.hid_out + (size_t) r * K + kk + 4) = make_float4(v4, v5, v6, v7);
+            }
+            const __half2 h0 = __floats2half2_rn(v0, v1), h1 = __floats2half2_rn(v2, v3);
+            const __half2 h2 = __floats2half2_rn(v4, v5), h3 = __floats2half2_rn(v6, v7);
+            uint4 pk;
+            pk.x = *reinterpret_cast<const uint32_t *>(&h0); pk.y = *reinterpret_cast<const uint32_t *>(&h1);
+            pk.z = *reinterpret_cast<const uint32_t *>(&h2); pk.w = *reinterpret_cast<const uint32_t *>(&h3);
+            *reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(op.out16) + canon_off(r, kk, cb)) = pk;
+        }
+        __syncthreads();        // S->red is reused by the next row of this CTA
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // BOP_ATTN_CP — one warp per (stream, KV group); lane holds dims lane + 32 j (j < 4), so the NEOX
 // pairs (i, i + 64) sit in one lane.  pair_f32: positions 0 and 1 in one pass with the all-F32
 // arithmetic of the reference's 2-token prefill graph (src/tts_transformer.cpp:1613-1626);
@@ -1079,6 +1126,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                 case BOP_ATTN_CP: bstage_attn_cp(S); break;
                 case BOP_ATTN_TK: bstage_attn_tk(S); break;
                 case BOP_SAMPLE:  bstage_sample(S); break;
+                case BOP_NORM:    bstage_norm(S); break;
             }
             const long long t1 = prof ? clock64() : 0;
             if (threadIdx.x < (int) (sizeof(BOp) / 4)) {     // next stage's descriptor lands during the barrier
@@ -1088,7 +1136,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
             bgrid_barrier(S, epoch);
             if (prof) {
                 const long long t2 = clock64();
-                const int slot = type * 2 + ((type == BOP_GEMM && in_kind == BIN_F16) ? 8 : 0);
+                const int slot = (type == BOP_NORM) ? 12 : type * 2 + ((type == BOP_GEMM && in_kind == BIN_F16) ? 8 : 0);
                 run_param.prof[slot * 4 + 0] += 1;
                 run_param.prof[slot * 4 + 1] += (unsigned long long) (t1 - t0);
                 run_param.prof[slot * 4 + 2] += (unsigned long long) (t2 - t1);

@@ -89,11 +89,23 @@ struct BEmit {
     std::vector<BSched> S;
     int B, cta_off = 0;
     unsigned long long * part_ll = nullptr;
+    __half * xn16 = nullptr;     // normalised F16 rows (canonical chunks) handed from a BOP_NORM stage to its GEMM
+    bool norm_stage = true;
 
     void gemm(const TiledW & T, int rows_act, int in_kind, const void * in, int in_row_stride, int in_tok_stride,
               const float * norm_w, const float * ssq_in, int n_parts_in, int epi, float * out32, __half * out16,
               const float * res, const float * bias, int out_row_stride, int out_tok_stride, float * ssq_out,
               float * hid_out = nullptr, int flags = 0) {
+        if (in_kind == BIN_F32 && norm_w && norm_stage && xn16) {
+            // RMSNorm once per row in its own small stage; the GEMM then takes F16 rows by bulk copy
+            BOp n = bblank(B);
+            n.type = BOP_NORM; n.rows_act = rows_act; n.K = T.K * T.ksplit;
+            n.in = in; n.in_row_stride = in_row_stride; n.in_tok_stride = in_tok_stride;
+            n.norm_w = norm_w; n.ssq_in = ssq_in; n.n_parts_in = n_parts_in; n.eps = e->cfg.rms_norm_eps;
+            n.out16 = xn16; n.hid_out = hid_out;
+            P.push_back(n);
+            in_kind = BIN_F16; in = xn16; norm_w = nullptr; ssq_in = nullptr; n_parts_in = 0; hid_out = nullptr;
+        }
         BOp o = bblank(B);
         o.type = BOP_GEMM; o.rows_act = rows_act; o.flags = flags | (ssq_out ? BF_SSQ_OUT : 0);
         o.Wt = T.p; o.rows = T.rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = cta_off;
@@ -262,7 +274,10 @@ bool batched_init(Engine * e) {
         G.part_words = (size_t) std::max(H, cpH) * 256;
         G.part_ll = e->dalloc<unsigned long long>(G.part_words);
         if (!G.part_ll) return e->fail("out of device memory for the split-K partials");
-        BEmit E{e, {}, {}, G.n, 0, G.part_ll};
+        G.xn16 = e->dalloc<__half>(B28 * (size_t) std::max(H, cpH));
+        if (!G.xn16) return e->fail("out of device memory for the normalised activations");
+        BEmit E{e, {}, {}, G.n, 0, G.part_ll, G.xn16};
+        if (const char * v = getenv("QTTS_BNORM")) E.norm_stage = atoi(v) != 0;
         emit_bframe(e, G, E);
         G.n_ops = (int) E.P.size(); G.n_sched = (int) E.S.size();
         G.ops = e->dalloc<BOp>(E.P.size(), false);

@@ -29,6 +29,8 @@ enum BOpType : int32_t {
     BOP_ATTN_CP = 1,   // code-predictor attention, one warp per (stream, KV group), <= 16 keys
     BOP_ATTN_TK = 2,   // Talker decode attention, one CTA pass per (stream, KV group)
     BOP_SAMPLE  = 3,   // per-stream sampling + embedding of the next input (+ frame end)
+    BOP_NORM    = 4,   // RMSNorm of F32 rows -> F16 rows in the canonical chunk layout (the next GEMM's A operand,
+                       // fetched by bulk copies); one row per CTA pass
 };
 
 enum BInKind : int32_t { BIN_F32 = 0, BIN_F16 = 1 };

@@ -194,7 +194,7 @@ class TTSTransformer:
         out = np.zeros(64, np.uint64)
         self._lib.qtts_batched_profile(self._h, 1 if on else 0, _ptr(out))
         o = out.reshape(16, 4)
-        names = {0: "gemm_f32in", 8: "gemm_f16in", 2: "attn_cp", 4: "attn_talker", 6: "sample"}
+        names = {0: "gemm_f32in", 8: "gemm_f16in", 12: "norm", 2: "attn_cp", 4: "attn_talker", 6: "sample"}
         return {n: {"count": int(o[i, 0]), "stage_cycles": int(o[i, 1]), "barrier_cycles": int(o[i, 2])}
                 for i, n in names.items()}
 
