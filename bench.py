@@ -163,7 +163,7 @@ def run_reference(args, pkg):
     return 0
 
 
-NCU_DRAM_BYTES_PER_LAUNCH = 130976350000 + 39054080
+NCU_DRAM_BYTES_PER_LAUNCH = 129936908000 + 29512448
 
 
 def workload_config(world: int) -> dict:
@@ -235,7 +235,8 @@ def run_ours(args, pkg):
     T.unload_model()
     batched = []
     if not args.no_batched:
-        for streams in sorted({64, max(1, B_TOTAL // world)}):
+        # 64 (configs[2]), 512 / world (configs[3]) and 128 = one full lock-step group per GPU
+        for streams in sorted({64, 128, max(1, B_TOTAL // world)}):
             res = run_batched_leg(pkg, torch, dist, path, cfg, local, rank, world, streams, barrier)
             res["streams_per_gpu"] = streams
             batched.append(res)
@@ -264,8 +265,8 @@ def run_ours(args, pkg):
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              # dram__bytes_read.sum + dram__bytes_write.sum of one 40-frame launch, from the
-                             # ncu --set full capture summarised in profiles/r01f_frame_ncu.md
-                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r01f_frame_ncu.md",
+                             # ncu --set full capture summarised in profiles/r01h_frame_ncu.md
+                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r01h_frame_ncu.md",
                              "frames_per_launch": 40, "algorithmic_bytes_per_launch": bytes_per_frame * 40,
                              "kernel": "qtts_run_program", "peak_source": peak_src,
                              "algorithmic_bytes_per_frame": bytes_per_frame},
@@ -282,7 +283,9 @@ def run_ours(args, pkg):
             ach = bytes_step / (step_ms / 1e3) / 1e9
             line["batched"].append({
                 "workload": ("BASELINE configs[2]: 64 concurrent utterances on one GPU" if S == 64 and world == 1 else
-                             f"BASELINE configs[3]: {B_TOTAL} concurrent streams sharded by utterance over {world} GPU(s)") +
+                             f"BASELINE configs[3]: {B_TOTAL} concurrent streams sharded by utterance over {world} GPU(s)"
+                             if S * world == B_TOTAL else
+                             f"one full lock-step group per GPU: {S} streams x {world} GPU(s), sharded by utterance") +
                             f", ragged texts {B_TEXT[0]}-{B_TEXT[1]} tokens, cached speaker embeddings, temperature {TEMP} top-k {TOP_K}, "
                             f"{B_FRAMES} frames per stream, batched tcgen05 kernel (groups of <= 128 streams in lock step)",
                 "streams_per_gpu": S, "streams_total": S * world, "value": fps, "unit": UNIT,
