@@ -728,13 +728,16 @@ __device__ __forceinline__ void warp_norm_rope(float * x, const float * w, const
     }
 }
 
+template <bool PAIR>
 __device__ __noinline__ void bstage_attn_cp(BShared * S) {
     const BOp & op = S->op;
     const int lane = threadIdx.x & 31;
     const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
     const int B = op.n_streams, nkv = op.n_kv_heads, rep = op.n_heads / nkv;
     const int kvw = nkv * kHeadDim;
-    float * scw = reinterpret_cast<float *>(babuf_base(S)) + (threadIdx.x >> 5) * 16;
+    // per-warp scratch in the (idle) A-buffer area: 16 scores + one query head (F16-rounded)
+    float * scw = reinterpret_cast<float *>(babuf_base(S)) + (threadIdx.x >> 5) * (16 + kHeadDim);
+    float * qs = scw + 16;
     for (int item = gw; item < B * nkv; item += nw) {
         const int b = item / nkv, g = item - b * nkv;
         __half * kc = op.kc + (size_t) b * op.kv_stream_stride;
@@ -755,7 +758,7 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
                 kc[(size_t) pos * kvw + g * kHeadDim + lane + 32 * j] = __float2half_rn(k[j]);
                 vc[(size_t) pos * kvw + g * kHeadDim + lane + 32 * j] = __float2half_rn(v[j]);
             }
-            if (op.pair_f32 && t == 0) {
+            if (PAIR && t == 0) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) { k0f[j] = k[j]; v0f[j] = v[j]; }
             }
@@ -767,7 +770,7 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
                 for (int j = 0; j < 4; ++j) q[j] = __ldcg(base + (size_t) h * kHeadDim + lane + 32 * j);
                 warp_norm_rope(q, op.q_norm_w, op.rope, pos, op.eps, lane, op.q_norm_w != nullptr);
                 float o[4];
-                if (op.pair_f32) {
+                if (PAIR) {
                     if (t == 0) {
 #pragma unroll
                         for (int j = 0; j < 4; ++j) o[j] = v[j];      // softmax over one key = 1
@@ -784,47 +787,90 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
                         for (int j = 0; j < 4; ++j) o[j] = fmaf(v[j], p1, v0f[j] * p0);
                     }
                 } else {
-                    // F16 Q, keys/values from the F16 cache (the current token included: just written)
-                    float qh[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) qh[j] = f16r(q[j]);
+                    // F16 Q, keys/values from the F16 cache (the current token included: just written).
+                    // All key rows are requested at once: half-warp `hw` takes the keys of its parity, lane
+                    // l16 of it 8 consecutive dims (one 16-byte load per key) - a key loop with a dependent
+                    // load + warp reduction per key was 16 L2 round trips per head.
                     const int n_kv = pos + 1;       // <= 16
-                    // scores through a per-warp shared-memory row (keeps the register count down: spills
-                    // would go to L2, there is no L1 left next to 222 KB of shared memory)
-                    float mx = -CUDART_INF_F;
-                    for (int jk = 0; jk < n_kv; ++jk) {
-                        float s = 0.f;
+                    const int hw = lane >> 4, l16 = lane & 15;
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            s = fmaf(__half2float(kc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), qh[j], s);
-                        s = warp_sum(s) * op.kq_scale;
-                        if (lane == jk) scw[jk] = s;
-                        mx = fmaxf(mx, s);
+                    for (int j = 0; j < 4; ++j) qs[lane + 32 * j] = f16r(q[j]);
+                    __syncwarp();
+                    float qa[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) qa[i] = qs[8 * l16 + i];
+                    const __half * kbase = kc + g * kHeadDim + 8 * l16;
+                    const __half * vbase = vc + g * kHeadDim + 8 * l16;
+                    uint4 kv[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int jk = 2 * i + hw;
+                        kv[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kbase + (size_t) jk * kvw) : make_uint4(0u, 0u, 0u, 0u);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const __half2 * hk = reinterpret_cast<const __half2 *>(&kv[i]);
+                        float sdot = 0.f;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float2 f = __half22float2(hk[u]);
+                            sdot = fmaf(f.x, qa[2 * u], sdot);
+                            sdot = fmaf(f.y, qa[2 * u + 1], sdot);
+                        }
+#pragma unroll
+                        for (int o2 = 8; o2 > 0; o2 >>= 1) sdot += __shfl_xor_sync(0xffffffffu, sdot, o2);
+                        if (l16 == 0 && 2 * i + hw < n_kv) scw[2 * i + hw] = sdot * op.kq_scale;
+                    }
+                    // the value rows are requested before the softmax needs the scores
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int jk = 2 * i + hw;
+                        kv[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(vbase + (size_t) jk * kvw) : make_uint4(0u, 0u, 0u, 0u);
                     }
                     __syncwarp();
+                    float mx = -CUDART_INF_F;
+                    for (int jk = 0; jk < n_kv; ++jk) mx = fmaxf(mx, scw[jk]);
                     double sum = 0.0;
                     for (int jk = 0; jk < n_kv; ++jk) sum += (double) expf(scw[jk] - mx);
                     const float inv = (float) (1.0 / sum);
-                    float part[4][4];
+                    // partial sums per key class jk mod 4, combined as (p0 + p1) + (p2 + p3) like the batch-1 kernel:
+                    // this half-warp holds classes hw (even i) and hw + 2 (odd i)
+                    float accA[8], accB[8];
 #pragma unroll
-                    for (int pp = 0; pp < 4; ++pp)
+                    for (int u = 0; u < 8; ++u) { accA[u] = 0.f; accB[u] = 0.f; }
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) part[pp][j] = 0.f;
-                    for (int j0 = 0; j0 < n_kv; j0 += 4) {
+                    for (int i = 0; i < 8; ++i) {
+                        const int jk = 2 * i + hw;
+                        if (jk < n_kv) {
+                            const float pk = f16r(expf(scw[jk] - mx) * inv);       // the P.V mul_mat rounds P to F16
+                            const __half2 * hv = reinterpret_cast<const __half2 *>(&kv[i]);
 #pragma unroll
-                        for (int pp = 0; pp < 4; ++pp) {
-                            const int jk = j0 + pp;
-                            if (jk < n_kv) {
-                                const float p = f16r(expf(scw[jk] - mx) * inv);     // the P.V mul_mat rounds P to F16
-#pragma unroll
-                                for (int j = 0; j < 4; ++j)
-                                    part[pp][j] = fmaf(__half2float(vc[(size_t) jk * kvw + g * kHeadDim + lane + 32 * j]), p, part[pp][j]);
+                            for (int u = 0; u < 4; ++u) {
+                                const float2 f = __half22float2(hv[u]);
+                                if (i & 1) { accB[2 * u] = fmaf(f.x, pk, accB[2 * u]); accB[2 * u + 1] = fmaf(f.y, pk, accB[2 * u + 1]); }
+                                else       { accA[2 * u] = fmaf(f.x, pk, accA[2 * u]); accA[2 * u + 1] = fmaf(f.y, pk, accA[2 * u + 1]); }
                             }
                         }
                     }
-                    __syncwarp();
+                    __half2 oh[4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) o[j] = (part[0][j] + part[1][j]) + (part[2][j] + part[3][j]);
+                    for (int u = 0; u < 8; u += 2) {
+                        // lanes of half-warp 0 end up with (p0 + p1) + (p2 + p3) of dims 8 * l16 + u, u + 1
+                        const float a0 = accA[u] + __shfl_xor_sync(0xffffffffu, accA[u], 16);
+                        const float b0 = accB[u] + __shfl_xor_sync(0xffffffffu, accB[u], 16);
+                        const float a1 = accA[u + 1] + __shfl_xor_sync(0xffffffffu, accA[u + 1], 16);
+                        const float b1 = accB[u + 1] + __shfl_xor_sync(0xffffffffu, accB[u + 1], 16);
+                        oh[u >> 1] = __floats2half2_rn(a0 + b0, a1 + b1);
+                    }
+                    if (hw == 0) {
+                        uint4 pk4;
+                        pk4.x = *reinterpret_cast<const uint32_t *>(&oh[0]); pk4.y = *reinterpret_cast<const uint32_t *>(&oh[1]);
+                        pk4.z = *reinterpret_cast<const uint32_t *>(&oh[2]); pk4.w = *reinterpret_cast<const uint32_t *>(&oh[3]);
+                        *reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(op.attn16) +
+                                                   canon_off(t * B + b, h * kHeadDim + 8 * l16, canon_chunk_bytes(op.rows_act))) = pk4;
+                    }
+                    __syncwarp();
+                    continue;
                 }
                 unsigned char * out = reinterpret_cast<unsigned char *>(op.attn16);
                 const int cb = canon_chunk_bytes(op.rows_act);
@@ -1123,7 +1169,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                     if (in_kind == BIN_F32) bstage_gemm<BIN_F32>(S);
                     else                    bstage_gemm_tma(S);
                     break;
-                case BOP_ATTN_CP: bstage_attn_cp(S); break;
+                case BOP_ATTN_CP: if (S->op.pair_f32) bstage_attn_cp<true>(S); else bstage_attn_cp<false>(S); break;
                 case BOP_ATTN_TK: bstage_attn_tk(S); break;
                 case BOP_SAMPLE:  bstage_sample(S); break;
                 case BOP_NORM:    bstage_norm(S); break;
