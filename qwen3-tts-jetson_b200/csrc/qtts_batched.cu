@@ -728,6 +728,26 @@ __device__ __forceinline__ void warp_norm_rope(float * x, const float * w, const
     }
 }
 
+// same arithmetic with the norm weights and the RoPE factors already in registers
+__device__ __forceinline__ void warp_norm_rope_pre(float * x, const float * w, const float * rc, const float * rs, float eps, bool do_norm) {
+    if (do_norm) {
+        double ss = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ss += (double) (x[j] * x[j]);
+        ss = warp_sum_d(ss);
+        const float mean = (float) (ss / (double) kHeadDim);
+        const float scale = 1.0f / sqrtf(mean + eps);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) x[j] = (x[j] * scale) * w[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const float x0 = x[j], x1 = x[j + 2];
+        x[j] = x0 * rc[j] - x1 * rs[j];
+        x[j + 2] = x0 * rs[j] + x1 * rc[j];
+    }
+}
+
 template <bool PAIR>
 __device__ __noinline__ void bstage_attn_cp(BShared * S) {
     const BOp & op = S->op;
@@ -738,6 +758,20 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
     // per-warp scratch in the (idle) A-buffer area: 16 scores + one query head (F16-rounded)
     float * scw = reinterpret_cast<float *>(babuf_base(S)) + (threadIdx.x >> 5) * (16 + kHeadDim);
     float * qs = scw + 16;
+    // single-token pass: position, norm weights and RoPE factors are the same for every item of the stage
+    float wq[4], wk[4], rc[2], rs[2];
+    if (!PAIR) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            wq[j] = op.q_norm_w ? __ldg(op.q_norm_w + lane + 32 * j) : 1.f;
+            wk[j] = op.k_norm_w ? __ldg(op.k_norm_w + lane + 32 * j) : 1.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const float2 cs = __ldg(reinterpret_cast<const float2 *>(op.rope) + (size_t) op.pos * 64 + lane + 32 * j);
+            rc[j] = cs.x; rs[j] = cs.y;
+        }
+    }
     for (int item = gw; item < B * nkv; item += nw) {
         const int b = item / nkv, g = item - b * nkv;
         __half * kc = op.kc + (size_t) b * op.kv_stream_stride;
@@ -746,13 +780,15 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
         for (int t = 0; t < op.n_tok; ++t) {
             const int pos = op.pos + t;
             const float * base = op.qkv + (size_t) (t * B + b) * op.qkvw;
-            float k[4], v[4];
+            float k[4], v[4], qn[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 k[j] = __ldcg(base + (size_t) (op.n_heads + g) * kHeadDim + lane + 32 * j);
                 v[j] = __ldcg(base + (size_t) (op.n_heads + nkv + g) * kHeadDim + lane + 32 * j);
+                qn[j] = __ldcg(base + (size_t) (g * rep) * kHeadDim + lane + 32 * j);       // first query head of the group
             }
-            warp_norm_rope(k, op.k_norm_w, op.rope, pos, op.eps, lane, op.k_norm_w != nullptr);
+            if (PAIR) warp_norm_rope(k, op.k_norm_w, op.rope, pos, op.eps, lane, op.k_norm_w != nullptr);
+            else      warp_norm_rope_pre(k, wk, rc, rs, op.eps, op.k_norm_w != nullptr);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 kc[(size_t) pos * kvw + g * kHeadDim + lane + 32 * j] = __float2half_rn(k[j]);
@@ -767,8 +803,13 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
                 const int h = g * rep + r;
                 float q[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) q[j] = __ldcg(base + (size_t) h * kHeadDim + lane + 32 * j);
-                warp_norm_rope(q, op.q_norm_w, op.rope, pos, op.eps, lane, op.q_norm_w != nullptr);
+                for (int j = 0; j < 4; ++j) q[j] = qn[j];
+                if (r + 1 < rep) {      // the next head's query is requested while this one is processed
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) qn[j] = __ldcg(base + (size_t) (h + 1) * kHeadDim + lane + 32 * j);
+                }
+                if (PAIR) warp_norm_rope(q, op.q_norm_w, op.rope, pos, op.eps, lane, op.q_norm_w != nullptr);
+                else      warp_norm_rope_pre(q, wq, rc, rs, op.eps, op.q_norm_w != nullptr);
                 float o[4];
                 if (PAIR) {
                     if (t == 0) {
