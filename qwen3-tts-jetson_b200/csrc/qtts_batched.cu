@@ -96,6 +96,7 @@ struct BShared {
     uint32_t a_use[2];       // commits issued on abar[i]
     uint32_t d_use;          // commits issued on dbar
     uint32_t tag;            // this stage's tag (split-K hand-off)
+    uint32_t rows_target;    // rows signalled by all BF_ROWS_SIGNAL stages of this launch so far (uniform over the grid)
     int32_t all_done;
 };
 constexpr size_t kBSharedBytes = (sizeof(BShared) + 127) & ~(size_t) 127;
@@ -553,6 +554,17 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
             if (tid == kAProd) {
                 uint64_t pol;
                 asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+                if (op.flags & BF_ROWS_WAIT) {
+                    // the rows come from a BOP_NORM stage that ended without a grid barrier: wait for its row counter
+                    const uint32_t target = S->rows_target;
+                    const unsigned int * ctr = &S->run.bar->pad[15];
+                    unsigned int v;
+                    uint32_t spins = 0;
+                    do {
+                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+                        if (++spins > (1u << 24)) __trap();
+                    } while ((int) (v - target) < 0);
+                }
                 asm volatile("fence.proxy.async.global;" ::: "memory");
                 const unsigned char * in = reinterpret_cast<const unsigned char *>(op.in);
                 for (int s = 0; s < steps; ++s) {
@@ -665,6 +677,8 @@ __device__ __noinline__ void bstage_norm(BShared * S) {
     const BOp & op = S->op;
     const int tid = threadIdx.x, K = op.K, np = op.n_parts_in;
     const int cb = canon_chunk_bytes(op.rows_act);
+    const bool signal = (op.flags & BF_ROWS_SIGNAL) != 0;
+    if (signal && tid == 0) S->rows_target += (uint32_t) op.rows_act;       // every CTA keeps the same running target
     for (int r = blockIdx.x; r < op.rows_act; r += (int) gridDim.x) {
         const float * x = reinterpret_cast<const float *>(op.in) + row_off(r, op.n_streams, op.in_row_stride, op.in_tok_stride);
         // everything this thread needs is requested before the reduction
@@ -697,7 +711,12 @@ __device__ __noinline__ void bstage_norm(BShared * S) {
             pk.z = *reinterpret_cast<const uint32_t *>(&h2); pk.w = *reinterpret_cast<const uint32_t *>(&h3);
             *reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(op.out16) + canon_off(r, kk, cb)) = pk;
         }
+        if (signal) asm volatile("fence.proxy.async.global;" ::: "memory");    // the row is read by bulk copies (async proxy)
         __syncthreads();        // S->red is reused by the next row of this CTA
+        if (signal && tid == 0) {
+            __threadfence();
+            atomicAdd(&S->run.bar->pad[15], 1u);
+        }
     }
 }
 
@@ -1161,7 +1180,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        S->cons_seq = 0; S->a_use[0] = 0; S->a_use[1] = 0; S->d_use = 0; S->all_done = 0;
+        S->cons_seq = 0; S->a_use[0] = 0; S->a_use[1] = 0; S->d_use = 0; S->all_done = 0; S->rows_target = 0;
         BPrefetch & pf = S->pf;
         pf.idx = -1; pf.frame = 0; pf.t = 0; pf.p = 0; pf.n_tiles = 0; pf.n_pieces = 0; pf.tile_bytes = 0; pf.piece_bytes = 0;
         pf.W = nullptr; pf.seq = 0; pf.exhausted = (run_param.n_sched <= 0) ? 1 : 0;
@@ -1220,7 +1239,12 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                 const int ni = (i + 1 < n_ops) ? i + 1 : 0;
                 next_word = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + ni) + threadIdx.x);
             }
-            bgrid_barrier(S, epoch);
+            if (type == BOP_NORM && (S->op.flags & BF_ROWS_SIGNAL)) {
+                if (threadIdx.x == kPfThread) bpf_poll(S);      // no barrier: the consumer waits for the row counter
+                __syncthreads();
+            } else {
+                bgrid_barrier(S, epoch);
+            }
             if (prof) {
                 const long long t2 = clock64();
                 const int slot = (type == BOP_NORM) ? 12 : type * 2 + ((type == BOP_GEMM && in_kind == BIN_F16) ? 8 : 0);

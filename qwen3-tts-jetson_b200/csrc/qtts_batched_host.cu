@@ -91,6 +91,7 @@ struct BEmit {
     unsigned long long * part_ll = nullptr;
     __half * xn16 = nullptr;     // normalised F16 rows (canonical chunks) handed from a BOP_NORM stage to its GEMM
     bool norm_stage = true;
+    bool rows_signal = true;     // norm -> GEMM hand-off through a row counter instead of a grid barrier
 
     void gemm(const TiledW & T, int rows_act, int in_kind, const void * in, int in_row_stride, int in_tok_stride,
               const float * norm_w, const float * ssq_in, int n_parts_in, int epi, float * out32, __half * out16,
@@ -103,6 +104,7 @@ struct BEmit {
             n.in = in; n.in_row_stride = in_row_stride; n.in_tok_stride = in_tok_stride;
             n.norm_w = norm_w; n.ssq_in = ssq_in; n.n_parts_in = n_parts_in; n.eps = e->cfg.rms_norm_eps;
             n.out16 = xn16; n.hid_out = hid_out;
+            if (rows_signal) { n.flags |= BF_ROWS_SIGNAL; flags |= BF_ROWS_WAIT; }
             P.push_back(n);
             in_kind = BIN_F16; in = xn16; norm_w = nullptr; ssq_in = nullptr; n_parts_in = 0; hid_out = nullptr;
         }
@@ -278,6 +280,7 @@ bool batched_init(Engine * e) {
         if (!G.xn16) return e->fail("out of device memory for the normalised activations");
         BEmit E{e, {}, {}, G.n, 0, G.part_ll, G.xn16};
         if (const char * v = getenv("QTTS_BNORM")) E.norm_stage = atoi(v) != 0;
+        if (const char * v = getenv("QTTS_BROWS")) E.rows_signal = atoi(v) != 0;
         emit_bframe(e, G, E);
         G.n_ops = (int) E.P.size(); G.n_sched = (int) E.S.size();
         G.ops = e->dalloc<BOp>(E.P.size(), false);
@@ -294,7 +297,7 @@ bool batched_init(Engine * e) {
 
 bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_sched, int n_sched, StreamState * st,
                     const int32_t * d_active, int n_streams, int n_frames, bool check_done) {
-    QTTS_CUDA(cudaMemsetAsync(&e->bar->count, 0, sizeof(unsigned int), e->stream));
+    QTTS_CUDA(cudaMemsetAsync(e->bar, 0, sizeof(GridBarrier), e->stream));     // arrival counter and row counter
     BRun run;
     memset(&run, 0, sizeof(run));
     run.ops = d_ops; run.n_ops = n_ops; run.sched = d_sched; run.n_sched = n_sched;

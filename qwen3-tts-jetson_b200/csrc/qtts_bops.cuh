@@ -38,6 +38,8 @@ enum BInKind : int32_t { BIN_F32 = 0, BIN_F16 = 1 };
 enum BFlags : int32_t {
     BF_INC_NPAST = 1,      // GEMM: CTA 0 advances n_past of every live stream at the end of the stage
     BF_SSQ_OUT   = 2,      // GEMM epilogue writes per-row sum-of-squares partials of its output
+    BF_ROWS_SIGNAL = 4,    // BOP_NORM: every finished row bumps the group's row counter; NO grid barrier after the stage
+    BF_ROWS_WAIT   = 8,    // GEMM fed by such a stage: the A-operand producer waits for the row counter instead
 };
 
 struct BOp {
