@@ -235,8 +235,8 @@ def run_ours(args, pkg):
     T.unload_model()
     batched = []
     if not args.no_batched:
-        # 64 (configs[2]), 512 / world (configs[3]) and 128 = one full lock-step group per GPU
-        for streams in sorted({64, 128, max(1, B_TOTAL // world)}):
+        # 64 (configs[2]), 512 / world (configs[3]) and 256 = one full lock-step group per GPU
+        for streams in sorted({64, 256, max(1, B_TOTAL // world)}):
             res = run_batched_leg(pkg, torch, dist, path, cfg, local, rank, world, streams, barrier)
             res["streams_per_gpu"] = streams
             batched.append(res)
@@ -287,7 +287,7 @@ def run_ours(args, pkg):
                              if S * world == B_TOTAL else
                              f"one full lock-step group per GPU: {S} streams x {world} GPU(s), sharded by utterance") +
                             f", ragged texts {B_TEXT[0]}-{B_TEXT[1]} tokens, cached speaker embeddings, temperature {TEMP} top-k {TOP_K}, "
-                            f"{B_FRAMES} frames per stream, batched tcgen05 kernel (groups of <= 128 streams in lock step)",
+                            f"{B_FRAMES} frames per stream, batched tcgen05 kernel (groups of <= 256 streams in lock step)",
                 "streams_per_gpu": S, "streams_total": S * world, "value": fps, "unit": UNIT,
                 "ms_per_frame_step": step_ms, "rtf_per_stream": (step_ms / 1e3) * 12.5,
                 "e2e": {"value": b["frames"] / (b["wall_ms"] / 1e3), "unit": UNIT,

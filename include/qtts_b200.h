@@ -146,7 +146,7 @@ int qtts_step_frames(qtts_engine * e, int32_t n_frames, int32_t * codes_out,
                      int32_t * produced, int32_t * active);
 
 /* 1 (default): qtts_step_frames advances all active streams in lock step with the batched tcgen05
- * kernel (groups of <= 128 slots); 0: the batch-1 kernel, one stream after another. */
+ * kernel (groups of <= 256 slots, env QTTS_BGROUP lowers it); 0: the batch-1 kernel, one stream after another. */
 int qtts_set_batched(qtts_engine * e, int on);
 /* B-operand (weight) element type of the batched kernel's tensor-core GEMMs.  QTTS_F16 (default):
  * the F16 image of the engine's BF16 weights (exact: BF16-exact values inside F16's range), so both

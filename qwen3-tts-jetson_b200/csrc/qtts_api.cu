@@ -398,7 +398,7 @@ int qtts_stream_logits(qtts_engine * h, int slot, float * cb0_out, float * cp_ou
     cudaStreamSynchronize(e->stream);
     const qtts_config & c = e->cfg;
     if (e->batched && e->batched_ready) {
-        BGroup & G = e->groups[slot / 128];
+        BGroup & G = e->groups[slot / e->bgroup];
         const int b = slot - G.s0;
         if (cb0_out) cudaMemcpy(cb0_out, G.cb0_dump + (size_t) b * c.codec_vocab_size, c.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
         if (cp_out)
@@ -497,7 +497,7 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     o.flags = ssq_out ? BF_SSQ_OUT : 0;
     o.Wt = T.p; o.rows = rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = 0; o.kpp = T.kpp; o.n_pieces = T.n_pieces;
     o.ksplit = T.ksplit;
-    if (T.ksplit > 1) o.part_ll = e->dalloc<unsigned long long>((size_t) rows * 256);
+    if (T.ksplit > 1) o.part_ll = e->dalloc<unsigned long long>((size_t) rows * kBMaxRows);
     o.in_kind = in_f16 ? BIN_F16 : BIN_F32; o.in = dX; o.in_row_stride = K; o.in_tok_stride = n_streams * K;
     o.norm_w = d_norm; o.ssq_in = d_ssq_in; o.n_parts_in = 4; o.eps = eps;
     o.epi = epi; o.out32 = d_out; o.out16 = d_out16; o.res = d_res; o.bias = d_bias;

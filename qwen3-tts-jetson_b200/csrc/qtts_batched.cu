@@ -321,7 +321,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
     const int dbg = S->run.dbg;
     const int q = warp & 3;
     const int ncg = op.n_tile >> 4;
-    // n_acc > 0: accumulators of issuers 0..n_acc-1 are summed; -1: m-tile mt has one accumulator, issuer mt's
+    // n_acc > 0: accumulators of issuers 0..n_acc-1 are summed; -nab: m-tile mt has one accumulator, issuer (mt % nab)'s
     const int n_iss = n_acc > 0 ? n_acc : (n_acc < 0 ? 1 : n_issuers(op.n_tile, m_tiles));
     // split-K: virtual tile -> (row block t, K-half); half 1 only publishes its partial accumulator
     const int ks = op.ksplit > 1 ? op.ksplit : 1;
@@ -350,7 +350,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
             __syncwarp();
             float acc[16];
             if (!(dbg & 2)) {
-                const int wa = (n_acc < 0) ? mt : 0;
+                const int wa = (n_acc < 0) ? (mt & (-n_acc - 1)) : 0;
                 tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) ((wa * m_tiles + mt) * op.n_tile + cg * 16), acc);
                 for (int w = 1; w < n_iss; ++w) {
                     float more[16];
@@ -543,7 +543,8 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
         const int abstride = (nab == 4) ? kABufBytes / 2 : kABufBytes;
         // accumulators: issuer w (< nab) writes (w, mt) for the steps that land in its buffer; with two
         // buffers and two m-tiles step kc * 2 + mt lands in buffer mt, i.e. m-tile mt has ONE accumulator, issuer mt's
-        const int acc_mode = (m_tiles == 2 && nab == 2) ? -1 : min(nab, steps);
+        // (generally: with m_tiles a multiple of the buffer count, m-tile mt always lands in buffer mt % nab)
+        const int acc_mode = (m_tiles >= nab && m_tiles % nab == 0) ? -nab : min(nab, steps);
         const uint32_t tmem_base = S->tmem_base;
         const uint32_t idesc = (op.rows_act <= 64 ? (S->run.idesc_base & ~(0x1Fu << 24)) | (4u << 24) : S->run.idesc_base) | ((uint32_t) (op.n_tile >> 3) << 17);
         uint32_t d_use = S->d_use, cons_seq = S->cons_seq;

@@ -252,9 +252,10 @@ bool batched_init(Engine * e) {
     // stream groups of at most 128 streams (the merged code-predictor pass has 2 rows per stream)
     const int H = c.hidden_size, cpH = c.cp_hidden_size;
     const int qkvw = (c.n_heads + 2 * c.n_kv_heads) * kHeadDim, cqkvw = (c.cp_n_heads + 2 * c.cp_n_kv_heads) * kHeadDim;
-    for (int s0 = 0; s0 < e->max_streams; s0 += 128) {
+    if (const char * v = getenv("QTTS_BGROUP")) e->bgroup = std::max(8, std::min(atoi(v), kBMaxGroup));
+    for (int s0 = 0; s0 < e->max_streams; s0 += e->bgroup) {
         BGroup G;
-        G.s0 = s0; G.n = std::min(128, e->max_streams - s0);
+        G.s0 = s0; G.n = std::min(e->bgroup, e->max_streams - s0);
         const size_t B = (size_t) G.n;
         const size_t B8 = (B + 7) & ~(size_t) 7, B28 = (2 * B + 7) & ~(size_t) 7;   // F16 activations: canonical chunks, rows padded to 8
         G.x = e->dalloc<float>(B * H); G.qkv = e->dalloc<float>(B * qkvw);
@@ -273,7 +274,7 @@ bool batched_init(Engine * e) {
         if (!G.x || !G.qkv || !G.cp_x || !G.cp_qkv || !G.cp_logits || !G.cp_kc || !G.cp_vc || !G.cp_dump || !G.active)
             return e->fail("out of device memory for the batched activations");
         // split-K partials: one flag-carrying word per accumulator element of the widest split projection
-        G.part_words = (size_t) std::max(H, cpH) * 256;
+        G.part_words = (size_t) std::max(H, cpH) * kBMaxRows;
         G.part_ll = e->dalloc<unsigned long long>(G.part_words);
         if (!G.part_ll) return e->fail("out of device memory for the split-K partials");
         G.xn16 = e->dalloc<__half>(B28 * (size_t) std::max(H, cpH));

@@ -21,7 +21,8 @@ constexpr int kASbo       = (kKc / 8) * kALbo;   // 2304
 constexpr int kABufBytes  = 16 * kASbo;          // 128 rows -> 36864 B
 constexpr int kBSlots     = 6;                   // weight ring slots
 constexpr int kBSlotBytes = 24576;
-constexpr int kBMaxRows   = 256;                 // activation rows per GEMM (streams x tokens)
+constexpr int kBMaxRows   = 512;                 // activation rows per GEMM (streams x tokens)
+constexpr int kBMaxGroup  = 256;                 // streams advanced in lock step by one launch
 constexpr int kBMaxParts  = 256;                 // sum-of-squares partials per row (= out rows / 16)
 
 enum BOpType : int32_t {

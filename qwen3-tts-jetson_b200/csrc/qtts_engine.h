@@ -115,6 +115,7 @@ struct Engine {
     int ll = 1;                    // flag-carrying activations between GEMV stages instead of grid barriers (env QTTS_LL=0: off)
     uint32_t ll_seq = 0;           // stage tags handed out so far (monotonic across launches)
     uint32_t bll_seq = 0;          // same for the batched kernel's split-K hand-off
+    int bgroup = 256;              // streams per lock-step group of the batched kernel (env QTTS_BGROUP, <= kBMaxGroup)
     int ignore_eos = 0;
     int64_t n_weights = 0, n_inexact = 0, weight_bytes = 0, kv_bytes = 0;
     int64_t launches = 0;

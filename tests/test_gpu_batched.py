@@ -190,3 +190,33 @@ def test_batched_sampling_reproducible_and_ragged(engines, pkg):
         assert 0 < len(a[i]) <= 120
     assert np.array_equal(a[0], a[3])            # same text, same seed, different slot
     assert not np.array_equal(a[0][:8], a[4][:8])
+
+
+@pytest.mark.gpu
+def test_batched_large_group_matches_batch1(pkg, make_gguf):
+    """More than 128 streams in ONE lock-step group (two 128-row M tiles per GEMM, four in the merged
+    code-predictor pass): first-frame logits of slots on both sides of the M-tile boundary against the
+    batch-1 kernel, and greedy ids of all streams over the first frames."""
+    path, cfg = make_gguf("tiny", 1234)
+    n = 140
+    toks = [pkg.synth.synth_tokens(cfg, n_text=8 + (i % 5), seed=i) for i in range(n)]
+    spks = [pkg.synth.synth_speaker(cfg, seed=i) for i in range(n)]
+    T = pkg.TTSTransformer(device=0, max_streams=n, max_ctx=128)
+    assert T.load_model(path), T.get_error()
+    res = {}
+    for batched in (True, False):
+        assert T.set_batched(batched)
+        for i in range(n):
+            assert T.stream_begin(i, toks[i], spks[i], max_len=3, temperature=0.0, seed=i), T.get_error()
+        codes, produced, active = T.step_frames(1)
+        assert (produced == 1).all()
+        logits = {i: T.stream_logits(i, want_cp=False)[0].copy() for i in (0, 63, 127, 128, 139)}
+        codes2, produced2, _ = T.step_frames(2)
+        res[batched] = (codes[:, 0].copy(), logits, codes2[:, :2].copy())
+    for i, l in res[True][1].items():
+        ref = res[False][1][i]
+        keep = np.isfinite(ref)
+        assert nmse(l[keep], ref[keep]) <= 1e-5, i
+    same0 = (res[True][0] == res[False][0]).all(axis=1)
+    assert same0.mean() >= 0.95, f"only {same0.sum()} of {n} streams agree on the first frame"
+    T.unload_model()
