@@ -996,6 +996,152 @@ __device__ void battn_tk_item(const Op & iop, const float * qkv, unsigned char *
     __syncthreads();
 }
 
+// Talker attention, one WARP per (stream, KV group) - the form the code-predictor attention has, with
+// an online softmax over blocks of 16 keys so that any context length fits: half-warp `hw` takes the
+// keys of its parity, lane l16 of it 8 consecutive dims (one 16-byte load per key and operand).
+// ATTN_FAST numerics: F16 Q / K / V, FP32 scores, softmax and P.V.  All (stream, group) items of the
+// stage run concurrently (2048 warps at 256 streams) instead of 14 CTA-wide items in sequence per SM.
+__device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
+    constexpr int REP = 2;
+    const BOp & op = S->op;
+    const BRun & run = S->run;
+    const int lane = threadIdx.x & 31, hw = lane >> 4, l16 = lane & 15;
+    const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
+    const int B = op.n_streams, nkv = op.n_kv_heads, kvw = nkv * kHeadDim;
+    float * qs = reinterpret_cast<float *>(babuf_base(S)) + (threadIdx.x >> 5) * (REP * kHeadDim);
+    const int cb = canon_chunk_bytes(op.rows_act);
+    float wq[4], wk[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        wq[j] = op.q_norm_w ? __ldg(op.q_norm_w + lane + 32 * j) : 1.f;
+        wk[j] = op.k_norm_w ? __ldg(op.k_norm_w + lane + 32 * j) : 1.f;
+    }
+    for (int item = gw; item < B * nkv; item += nw) {
+        const int b = item / nkv, g = item - b * nkv;
+        const int pos = __ldcg(&run.st[b].n_past), n_kv = pos + 1;
+        __half * kc = op.kc + (size_t) b * op.kv_stream_stride + g * kHeadDim;
+        __half * vc = op.vc + (size_t) b * op.kv_stream_stride + g * kHeadDim;
+        const float * base = op.qkv + (size_t) b * op.qkvw;
+        float k[4], v[4], q0[4], q1[4], rc[2], rs[2];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            k[j] = __ldcg(base + (size_t) (op.n_heads + g) * kHeadDim + lane + 32 * j);
+            v[j] = __ldcg(base + (size_t) (op.n_heads + nkv + g) * kHeadDim + lane + 32 * j);
+            q0[j] = __ldcg(base + (size_t) (g * REP) * kHeadDim + lane + 32 * j);
+            q1[j] = __ldcg(base + (size_t) (g * REP + 1) * kHeadDim + lane + 32 * j);
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const float2 cs = __ldg(reinterpret_cast<const float2 *>(op.rope) + (size_t) pos * 64 + lane + 32 * j);
+            rc[j] = cs.x; rs[j] = cs.y;
+        }
+        warp_norm_rope_pre(k, wk, rc, rs, op.eps, op.k_norm_w != nullptr);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            kc[(size_t) pos * kvw + lane + 32 * j] = __float2half_rn(k[j]);
+            vc[(size_t) pos * kvw + lane + 32 * j] = __float2half_rn(v[j]);
+        }
+        warp_norm_rope_pre(q0, wq, rc, rs, op.eps, op.q_norm_w != nullptr);
+        warp_norm_rope_pre(q1, wq, rc, rs, op.eps, op.q_norm_w != nullptr);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { qs[lane + 32 * j] = f16r(q0[j]); qs[kHeadDim + lane + 32 * j] = f16r(q1[j]); }
+        __syncwarp();
+        float qa[REP][8];
+#pragma unroll
+        for (int r = 0; r < REP; ++r)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) qa[r][i] = qs[r * kHeadDim + 8 * l16 + i];
+        float m[REP], l[REP], acc[REP][8];
+#pragma unroll
+        for (int r = 0; r < REP; ++r) {
+            m[r] = -CUDART_INF_F; l[r] = 0.f;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc[r][u] = 0.f;
+        }
+        const __half * kb = kc + 8 * l16, * vb = vc + 8 * l16;
+        for (int jb = 0; jb < n_kv; jb += 16) {
+            uint4 kv[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int jk = jb + 2 * i + hw;
+                kv[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : make_uint4(0u, 0u, 0u, 0u);
+            }
+            float sc[REP][8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const __half2 * hk = reinterpret_cast<const __half2 *>(&kv[i]);
+                float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float2 f = __half22float2(hk[u]);
+                    d0 = fmaf(f.x, qa[0][2 * u], d0); d0 = fmaf(f.y, qa[0][2 * u + 1], d0);
+                    d1 = fmaf(f.x, qa[1][2 * u], d1); d1 = fmaf(f.y, qa[1][2 * u + 1], d1);
+                }
+#pragma unroll
+                for (int o2 = 8; o2 > 0; o2 >>= 1) {
+                    d0 += __shfl_xor_sync(0xffffffffu, d0, o2);
+                    d1 += __shfl_xor_sync(0xffffffffu, d1, o2);
+                }
+                const bool ok = jb + 2 * i + hw < n_kv;
+                sc[0][i] = ok ? d0 * op.kq_scale : -CUDART_INF_F;
+                sc[1][i] = ok ? d1 * op.kq_scale : -CUDART_INF_F;
+            }
+            // the value rows are requested before the softmax update needs the scores
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int jk = jb + 2 * i + hw;
+                kv[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(vb + (size_t) jk * kvw) : make_uint4(0u, 0u, 0u, 0u);
+            }
+#pragma unroll
+            for (int r = 0; r < REP; ++r) {
+                float mb = sc[r][0];
+#pragma unroll
+                for (int i = 1; i < 8; ++i) mb = fmaxf(mb, sc[r][i]);
+                mb = fmaxf(mb, __shfl_xor_sync(0xffffffffu, mb, 16));
+                const float mn = fmaxf(m[r], mb);                   // finite: key jb exists
+                const float scale = __expf(m[r] - mn);              // 0 on the first block
+                float ls = 0.f;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { sc[r][i] = __expf(sc[r][i] - mn); ls += sc[r][i]; }
+                ls += __shfl_xor_sync(0xffffffffu, ls, 16);
+                l[r] = fmaf(l[r], scale, ls);
+                m[r] = mn;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) acc[r][u] *= scale;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const __half2 * hv = reinterpret_cast<const __half2 *>(&kv[i]);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float2 f = __half22float2(hv[u]);
+                    acc[0][2 * u] = fmaf(f.x, sc[0][i], acc[0][2 * u]); acc[0][2 * u + 1] = fmaf(f.y, sc[0][i], acc[0][2 * u + 1]);
+                    acc[1][2 * u] = fmaf(f.x, sc[1][i], acc[1][2 * u]); acc[1][2 * u + 1] = fmaf(f.y, sc[1][i], acc[1][2 * u + 1]);
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < REP; ++r) {
+            __half2 oh[4];
+            const float inv = 1.0f / l[r];
+#pragma unroll
+            for (int u = 0; u < 8; u += 2) {
+                const float a0 = acc[r][u] + __shfl_xor_sync(0xffffffffu, acc[r][u], 16);
+                const float a1 = acc[r][u + 1] + __shfl_xor_sync(0xffffffffu, acc[r][u + 1], 16);
+                oh[u >> 1] = __floats2half2_rn(a0 * inv, a1 * inv);
+            }
+            if (hw == 0) {
+                uint4 pk4;
+                pk4.x = *reinterpret_cast<const uint32_t *>(&oh[0]); pk4.y = *reinterpret_cast<const uint32_t *>(&oh[1]);
+                pk4.z = *reinterpret_cast<const uint32_t *>(&oh[2]); pk4.w = *reinterpret_cast<const uint32_t *>(&oh[3]);
+                *reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(op.attn16) +
+                                           canon_off(b, (g * REP + r) * kHeadDim + 8 * l16, cb)) = pk4;
+            }
+        }
+        __syncwarp();
+    }
+}
+
 __device__ __noinline__ void bstage_attn_tk(BShared * S) {
     const BOp & op = S->op;
     const BRun & run = S->run;
@@ -1231,7 +1377,10 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                     else                    bstage_gemm_tma(S);
                     break;
                 case BOP_ATTN_CP: if (S->op.pair_f32) bstage_attn_cp<true>(S); else bstage_attn_cp<false>(S); break;
-                case BOP_ATTN_TK: bstage_attn_tk(S); break;
+                case BOP_ATTN_TK:
+                    if (S->op.pair_f32 == 2 && S->op.n_heads == 2 * S->op.n_kv_heads) bstage_attn_tk_warp(S);
+                    else bstage_attn_tk(S);
+                    break;
                 case BOP_SAMPLE:  bstage_sample(S); break;
                 case BOP_NORM:    bstage_norm(S); break;
             }

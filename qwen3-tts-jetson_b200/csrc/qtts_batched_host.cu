@@ -205,6 +205,8 @@ static void emit_bframe(Engine * e, BGroup & G, BEmit & E) {
     for (int l = 0; l < c.n_layers; ++l) {
         BOp a = bblank(B);
         a.type = BOP_ATTN_TK; a.rope = e->rope; a.eps = eps; a.kq_scale = kq;
+        // warp-per-(stream, group) form (field reused as a switch: 2 = on); QTTS_BATTN=0 keeps the CTA-per-item form
+        { const char * v = getenv("QTTS_BATTN"); a.pair_f32 = (v && atoi(v) == 0) ? 0 : 2; }
         a.kc = bb.kc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
         a.vc = bb.vc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
         a.kv_stream_stride = (int64_t) bb.kv_slab;
