@@ -74,7 +74,7 @@ __device__ __forceinline__ bool mbar_test(uint64_t * bar, uint32_t parity) {
 constexpr int kIssuersMax = 4;
 struct BPrefetch {           // used by the prefetcher thread only
     int32_t idx, frame, t, p;
-    int32_t n_tiles, n_pieces, tile_bytes, piece_bytes;
+    int32_t n_tiles, n_pieces, tile_bytes, piece_bytes, msplit;
     const unsigned char * W;
     uint32_t seq;
     int32_t exhausted;
@@ -128,7 +128,7 @@ __device__ __forceinline__ bool bpf_advance(BShared * S) {
         const int4 e0 = __ldg(reinterpret_cast<const int4 *>(S->run.sched + pf.idx));
         const int4 e1 = __ldg(reinterpret_cast<const int4 *>(S->run.sched + pf.idx) + 1);
         pf.W = reinterpret_cast<const unsigned char *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
-        pf.tile_bytes = e0.z; pf.piece_bytes = e0.w; pf.n_pieces = e1.x; pf.n_tiles = e1.y;
+        pf.tile_bytes = e0.z; pf.piece_bytes = e0.w; pf.n_pieces = e1.x; pf.n_tiles = e1.y; pf.msplit = e1.w > 1 ? e1.w : 1;
         pf.t = first_tile(e1.z); pf.p = 0;
     }
     return true;
@@ -145,7 +145,7 @@ __device__ __forceinline__ bool bpf_issue(BShared * S, bool blocking) {
     const int off = pf.p * pf.piece_bytes;
     const uint32_t bytes = (uint32_t) min(pf.piece_bytes, pf.tile_bytes - off);
     mbar_expect_tx(S->full + slot, bytes);
-    bulk_g2s(bring_base(S) + (size_t) slot * kBSlotBytes, pf.W + (size_t) pf.t * pf.tile_bytes + off, bytes,
+    bulk_g2s(bring_base(S) + (size_t) slot * kBSlotBytes, pf.W + (size_t) (pf.t / pf.msplit) * pf.tile_bytes + off, bytes,
              S->full + slot, pf.policy);
     pf.p++; pf.seq++;
     return true;
@@ -314,7 +314,7 @@ __device__ __forceinline__ void bgemm_issue(BShared * S, int w, int n_iss, int k
 }
 
 // epilogue of tile t: warp w reads TMEM lanes 32*(w%4).. (its sub-partition), 16 columns per pass
-__device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_tiles, uint32_t d_use, int n_acc = 0) {
+__device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_tiles, uint32_t d_use, int n_acc = 0, int mt0 = 0) {
     const BOp & op = S->op;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tmem_base = S->tmem_base;
@@ -325,7 +325,8 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
     const int n_iss = n_acc > 0 ? n_acc : (n_acc < 0 ? 1 : n_issuers(op.n_tile, m_tiles));
     // split-K: virtual tile -> (row block t, K-half); half 1 only publishes its partial accumulator
     const int ks = op.ksplit > 1 ? op.ksplit : 1;
-    const int t = t_virtual / ks, half = t_virtual - t * ks;
+    const int ms = op.msplit > 1 ? op.msplit : 1;       // split-M: m_tiles / mt below are local, rows start at M tile mt0
+    const int t = t_virtual / (ks * ms), half = (ks > 1) ? t_virtual - t * ks : 0;
     const int rows_pad = (op.rows_act + 31) & ~31;
     const uint32_t tag = S->tag;
     bool waited = false;
@@ -335,7 +336,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
             // M = 128: accumulator row i sits in TMEM lane i; M = 64 (rows_act <= 64): row i sits in lane
             // (i % 16) + 32 * (i / 16), i.e. lanes 0..15 of each warp's sub-partition
             const bool m64 = op.rows_act <= 64;
-            const int r = m64 ? q * 16 + lane : mt * 128 + q * 32 + lane;
+            const int r = m64 ? q * 16 + lane : (mt0 + mt) * 128 + q * 32 + lane;
             const bool valid = r < op.rows_act && (!m64 || lane < 16);
             float4 side[4];
             if (valid && op.epi == EPI_ADD && half == 0) {
@@ -534,7 +535,8 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
     const int G = (int) gridDim.x;
     const int t_first = first_tile(op.cta_off);
     if (t_first < op.n_tiles) {
-        const int m_tiles = (op.rows_act + 127) >> 7;
+        const int msplit = op.msplit > 1 ? op.msplit : 1;
+        const int m_tiles = ((op.rows_act + 127) >> 7) / msplit;     // M tiles of ONE work item
         const int nkc = op.K / kKc;
         const int steps = nkc * m_tiles;
         const int Rg = (op.rows_act + 7) >> 3, cb = Rg << 11;
@@ -552,6 +554,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
         for (int t = t_first; t < op.n_tiles; t += G) {
             // split-K: virtual tile t reads the activation chunks of its K-half
             const int kc_base = (op.ksplit > 1) ? (t % op.ksplit) * nkc : 0;
+            const int mt0 = (t % msplit) * m_tiles;                 // split-M: first M tile of this work item
             if (tid == kAProd) {
                 uint64_t pol;
                 asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
@@ -573,13 +576,13 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     const int buf = s % nab, bi = buf * bstep;
                     const uint32_t nf = S->n_fill[bi];
                     mbar_wait(S->tempty + bi, (nf & 1u) ^ 1u);
-                    const uint32_t bytes = (uint32_t) min(16, Rg - 16 * mt) << 11;
+                    const uint32_t bytes = (uint32_t) min(16, Rg - 16 * (mt0 + mt)) << 11;
                     if (S->run.dbg & 4) {      // bring-up: pipeline overhead without the copy
                         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->tfull + bi)) : "memory");
                     } else {
                         const int kcs = kc_base + ((S->run.dbg & 8) ? (kc + (int) blockIdx.x) % nkc : kc);   // (dbg 8: bring-up, staggered chunk order)
                         mbar_expect_tx(S->tfull + bi, bytes);
-                        bulk_g2s(abuf + (size_t) buf * abstride, in + (size_t) kcs * cb + (size_t) mt * 32768, bytes, S->tfull + bi, pol);
+                        bulk_g2s(abuf + (size_t) buf * abstride, in + (size_t) kcs * cb + (size_t) (mt0 + mt) * 32768, bytes, S->tfull + bi, pol);
                     }
                     S->n_fill[bi] = nf + 1;
                 }
@@ -649,7 +652,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
             __syncwarp();
             const bool pr1 = S->run.prof != nullptr && tid == 32 && t == 0;      // a thread without issue duties
             const long long e0 = pr1 ? clock64() : 0;
-            bgemm_epilogue(S, t, m_tiles, d_use, acc_mode);
+            bgemm_epilogue(S, t, m_tiles, d_use, acc_mode, mt0);
             const long long e1 = pr1 ? clock64() : 0;
             d_use++;
             tc_fence_before();
@@ -1329,7 +1332,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         S->cons_seq = 0; S->a_use[0] = 0; S->a_use[1] = 0; S->d_use = 0; S->all_done = 0; S->rows_target = 0;
         BPrefetch & pf = S->pf;
-        pf.idx = -1; pf.frame = 0; pf.t = 0; pf.p = 0; pf.n_tiles = 0; pf.n_pieces = 0; pf.tile_bytes = 0; pf.piece_bytes = 0;
+        pf.idx = -1; pf.frame = 0; pf.t = 0; pf.p = 0; pf.n_tiles = 0; pf.n_pieces = 0; pf.tile_bytes = 0; pf.piece_bytes = 0; pf.msplit = 1;
         pf.W = nullptr; pf.seq = 0; pf.exhausted = (run_param.n_sched <= 0) ? 1 : 0;
         pf.policy = policy_evict_first();
     }

@@ -92,6 +92,7 @@ struct BEmit {
     __half * xn16 = nullptr;     // normalised F16 rows (canonical chunks) handed from a BOP_NORM stage to its GEMM
     bool norm_stage = true;
     bool rows_signal = true;     // norm -> GEMM hand-off through a row counter instead of a grid barrier
+    bool msplit_on = true;
 
     void gemm(const TiledW & T, int rows_act, int in_kind, const void * in, int in_row_stride, int in_tok_stride,
               const float * norm_w, const float * ssq_in, int n_parts_in, int epi, float * out32, __half * out16,
@@ -113,13 +114,17 @@ struct BEmit {
         o.Wt = T.p; o.rows = T.rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = cta_off;
         o.kpp = T.kpp; o.n_pieces = T.n_pieces;
         o.ksplit = T.ksplit; o.part_ll = (T.ksplit > 1) ? part_ll : nullptr;
+        // split-M: a narrow projection over >= 2 M tiles gives each (N tile, M half) its own CTA
+        const int m_total = (rows_act + 127) / 128;
+        const int msplit = (msplit_on && in_kind == BIN_F16 && T.ksplit == 1 && m_total % 2 == 0 && 2 * T.n_tiles <= e->n_sms) ? 2 : 1;
+        o.msplit = msplit; o.n_tiles = T.n_tiles * msplit;
         o.in_kind = in_kind; o.in = in; o.in_row_stride = in_row_stride; o.in_tok_stride = in_tok_stride;
         o.norm_w = norm_w; o.ssq_in = ssq_in; o.n_parts_in = n_parts_in; o.eps = e->cfg.rms_norm_eps;
         o.epi = epi; o.out32 = out32; o.out16 = out16; o.res = res; o.bias = bias;
         o.out_row_stride = out_row_stride; o.out_tok_stride = out_tok_stride; o.ssq_out = ssq_out; o.hid_out = hid_out;
         P.push_back(o);
-        S.push_back(BSched{T.p, T.n_tile * T.K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles, cta_off, 0});
-        cta_off = (cta_off + T.n_tiles) % e->n_sms;
+        S.push_back(BSched{T.p, T.n_tile * T.K * 2, T.n_tile * T.kpp * 2, T.n_pieces, T.n_tiles * msplit, cta_off, msplit});
+        cta_off = (cta_off + T.n_tiles * msplit) % e->n_sms;
     }
 };
 
@@ -284,6 +289,7 @@ bool batched_init(Engine * e) {
         BEmit E{e, {}, {}, G.n, 0, G.part_ll, G.xn16};
         if (const char * v = getenv("QTTS_BNORM")) E.norm_stage = atoi(v) != 0;
         if (const char * v = getenv("QTTS_BROWS")) E.rows_signal = atoi(v) != 0;
+        if (const char * v = getenv("QTTS_MSPLIT")) E.msplit_on = atoi(v) != 0;
         emit_bframe(e, G, E);
         G.n_ops = (int) E.P.size(); G.n_sched = (int) E.S.size();
         G.ops = e->dalloc<BOp>(E.P.size(), false);

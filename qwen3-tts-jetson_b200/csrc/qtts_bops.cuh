@@ -69,6 +69,9 @@ struct BOp {
     // K above is the per-half extent).  Half 1 hands its partial accumulator to half 0 through
     // flag-carrying words (f32 | stage tag << 32); half 0 adds it in fixed order and runs the epilogue.
     int32_t ksplit;
+    // split-M (stages with at least two M tiles and fewer N tiles than half the SMs): virtual tile v =
+    // (N tile v / msplit, M-tile range v % msplit); both CTAs stream the same weight tile, each its own rows
+    int32_t msplit;
     unsigned long long * part_ll;    // [row blocks][n_tile / 16][rows_act padded to 32][16]
     // ---- attention ----
     const float * qkv; int32_t qkvw;
@@ -96,7 +99,7 @@ struct BOp {
 // prefetcher schedule: the GEMM stages of one frame in execution order
 struct BSched {
     const unsigned char * W;
-    int32_t tile_bytes, piece_bytes, n_pieces, n_tiles, cta_off, pad;
+    int32_t tile_bytes, piece_bytes, n_pieces, n_tiles, cta_off, msplit;     // n_tiles counts virtual tiles; weight tile = virtual tile / msplit
 };
 static_assert(sizeof(BSched) == 32, "BSched is read as two int4");
 
