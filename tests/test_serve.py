@@ -1,0 +1,98 @@
+"""Batching front door (qwen3-tts-jetson_b200/serve.py): line protocol, continuous
+batching into free slots, the 40-frame chunk callback contract of the reference
+(src/tts_transformer.cpp:2517-2523, 2563-2570).  CPU: against a deterministic stand-in engine; GPU:
+the real engine must hand out what generate() returns for the same request."""
+import io
+
+import numpy as np
+import pytest
+
+import qtts_pkg
+from test_sharding import FakeEngine, NB
+
+
+def test_parse_lines():
+    P = qtts_pkg.load().serve.BatchingServer.parse
+    assert P("\n") is None
+    assert P("quit\n") == ("quit",) and P("exit") == ("quit",)
+    assert P("a\t1,2, 3\tout.bin\t7\n") == ("req", "a", [1, 2, 3], "out.bin", 7)
+    assert P("b\t4,5") == ("req", "b", [4, 5], None, None)
+    assert P("only-id")[0] == "err" and P("c\t1,x")[0] == "err"
+
+
+def test_continuous_batching_and_chunks(tmp_path):
+    serve = qtts_pkg.load().serve
+    eng = FakeEngine(max_streams=2, ms_per_call=1.0)
+    chunks = {}
+    srv = serve.BatchingServer(eng, max_len=50, frames_per_call=3, chunk_frames=4,
+                               on_chunk=lambda rid, c: chunks.setdefault(rid, []).append(c.copy()))
+    r = np.random.default_rng(3)
+    reqs = {f"r{i}": r.integers(0, 4000, size=5 + i).astype(np.int32) for i in range(5)}
+    lines = [f"{rid}\t{','.join(map(str, t))}\t{tmp_path / (rid + '.i32')}\n" for rid, t in reqs.items()]
+    lines.insert(2, "bad line without tab\n")
+    lines.append("quit\n")
+    lines.append("late\t1,2,3,4\n")                      # after quit: never served
+    out, err = io.StringIO(), io.StringIO()
+    assert srv.serve(lines, out=out, err=err) == 0
+    answers = [l.split("\t") for l in out.getvalue().splitlines()]
+    ok = {a[1]: a for a in answers if a[0] == "OK"}
+    assert sorted(ok) == sorted(reqs) and sum(a[0] == "ERR" for a in answers) == 1
+    assert "late" not in ok
+    for rid, toks in reqs.items():
+        n = FakeEngine.n_frames(toks, 50)
+        want = np.stack([FakeEngine.frame(toks, 0, f) for f in range(n)]).astype(np.int32)
+        got = np.fromfile(tmp_path / (rid + ".i32"), "<i4").reshape(-1, NB)
+        assert np.array_equal(got, want) and int(ok[rid][2]) == n
+        # chunk contract: full blocks of 4 frames, then the remainder; together the whole utterance
+        sizes = [len(c) for c in chunks[rid]]
+        assert all(s == 4 for s in sizes[:-1]) and 1 <= sizes[-1] <= 4
+        assert np.array_equal(np.concatenate(chunks[rid]), want)
+    # two slots, five requests: slots were reused while other streams were still running
+    assert srv.idle() and sorted(srv.free) == [0, 1]
+
+
+def test_engine_errors_are_answers():
+    serve = qtts_pkg.load().serve
+
+    class Failing(FakeEngine):
+        def stream_begin(self, slot, tokens, speaker, max_len, seed, **kw):
+            return len(tokens) >= 4 and super().stream_begin(slot, tokens, speaker, max_len, seed, **kw)
+
+        def get_error(self):
+            return "Need at least 4 text tokens for generation"
+
+    srv = serve.BatchingServer(Failing(2, 1.0), max_len=8)
+    out = io.StringIO()
+    srv.serve(["x\t1,2\n", "y\t1,2,3,4,5\n"], out=out, err=io.StringIO())
+    lines = out.getvalue().splitlines()
+    assert lines[0].startswith("ERR\tx\tNeed at least 4 text tokens") and lines[1].startswith("OK\ty\t")
+
+
+@pytest.mark.gpu
+def test_server_hands_out_what_generate_returns(make_gguf, tmp_path):
+    pkg = qtts_pkg.load()
+    path, cfg = make_gguf("tiny", 1234)
+    T = pkg.TTSTransformer(device=0, max_streams=3, max_ctx=256)
+    assert T.load_model(path), T.get_error()
+    T.set_batched(False)                     # batch-1 kernel per stream: bit-equal to generate()
+    reqs = {f"u{i}": pkg.synth.synth_tokens(cfg, n_text=6 + 2 * i, seed=i) for i in range(7)}
+    chunks = {}
+    srv = pkg.serve.BatchingServer(T, max_len=11, frames_per_call=4, chunk_frames=4, temperature=0.0, top_k=0,
+                                   on_chunk=lambda rid, c: chunks.setdefault(rid, []).append(c.copy()))
+    lines = [f"{rid}\t{','.join(map(str, t))}\t{tmp_path / rid}\n" for rid, t in reqs.items()]
+    out = io.StringIO()
+    srv.serve(lines, out=out, err=io.StringIO())
+    assert sum(l.startswith("OK\t") for l in out.getvalue().splitlines()) == len(reqs)
+    for rid, toks in reqs.items():
+        want = T.generate(toks, None, max_len=11, temperature=0.0, top_k=0)
+        got = np.fromfile(tmp_path / rid, "<i4").reshape(-1, 16)
+        assert np.array_equal(got, want), rid
+        assert np.array_equal(np.concatenate(chunks[rid]), want)
+    # and on the batched kernel: every request answered, frame counts within range
+    T.set_batched(True)
+    out = io.StringIO()
+    pkg.serve.BatchingServer(T, max_len=9, temperature=0.9, top_k=50).serve(
+        [f"{rid}\t{','.join(map(str, t))}\n" for rid, t in reqs.items()], out=out, err=io.StringIO())
+    ans = [l.split("\t") for l in out.getvalue().splitlines()]
+    assert len(ans) == len(reqs) and all(a[0] == "OK" and 1 <= int(a[2]) <= 9 for a in ans)
+    T.unload_model()
