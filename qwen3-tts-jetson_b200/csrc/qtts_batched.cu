@@ -363,7 +363,15 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
 #pragma unroll
                 for (int i = 0; i < 16; ++i) acc[i] = 0.f;
             }
-            if (ks > 1 && valid) {
+            if (ks > 1 && valid && op.part32) {
+                if (half == 1) {        // deferred combine: the following norm stage adds this partial
+                    float * pd = op.part32 + row_off(r, op.n_streams, op.out_row_stride, op.out_tok_stride) + n0;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        *reinterpret_cast<float4 *>(pd + 4 * i) = make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
+                    continue;
+                }
+            } else if (ks > 1 && valid) {
                 unsigned long long * pp = op.part_ll + (((size_t) t * ncg + cg) * rows_pad + r) * 16;
                 if (half == 1) {
 #pragma unroll
@@ -693,7 +701,24 @@ __device__ __noinline__ void bstage_norm(BShared * S) {
             wa = __ldg(reinterpret_cast<const float4 *>(op.norm_w + k)); wb = __ldg(reinterpret_cast<const float4 *>(op.norm_w + k + 4));
         }
         double ss = 0.0;
-        for (int i = tid; i < np; i += kThreads) ss += (double) __ldcg(op.ssq_in + (size_t) r * np + i);
+        if (op.part32) {
+            // the producing projection was split over K: x = x + (second half's partial), in this fixed order;
+            // the row is written back (it is the residual of the next projection) and squared here
+            const float * pr = op.part32 + (x - reinterpret_cast<const float *>(op.in));
+            float * xw = const_cast<float *>(x);
+            for (int kk = k; kk < K; kk += kThreads * 8) {
+                float4 a = xa, b = xb;
+                if (kk != k) { a = __ldcg(reinterpret_cast<const float4 *>(x + kk)); b = __ldcg(reinterpret_cast<const float4 *>(x + kk + 4)); }
+                const float4 pa = __ldcg(reinterpret_cast<const float4 *>(pr + kk)), pb = __ldcg(reinterpret_cast<const float4 *>(pr + kk + 4));
+                a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w; b.x += pb.x; b.y += pb.y; b.z += pb.z; b.w += pb.w;
+                *reinterpret_cast<float4 *>(xw + kk) = a; *reinterpret_cast<float4 *>(xw + kk + 4) = b;
+                if (kk == k) { xa = a; xb = b; }
+                ss += (double) (a.x * a.x); ss += (double) (a.y * a.y); ss += (double) (a.z * a.z); ss += (double) (a.w * a.w);
+                ss += (double) (b.x * b.x); ss += (double) (b.y * b.y); ss += (double) (b.z * b.z); ss += (double) (b.w * b.w);
+            }
+        } else {
+            for (int i = tid; i < np; i += kThreads) ss += (double) __ldcg(op.ssq_in + (size_t) r * np + i);
+        }
         ss = block_sum_d(ss, S->red);
         const float mean = (float) (ss / (double) K);
         const float sc = 1.0f / sqrtf(mean + op.eps);

@@ -58,8 +58,11 @@ bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW 
     // split-K: a narrow projection (O, down) has fewer row blocks than half the SMs; two CTAs per row
     // block, each streaming half of K, double the bytes in flight of a latency-bound stage
     const char * env = getenv("QTTS_KSPLIT");
-    // (measured after the chunk-alternating issue: the hand-off costs what the shorter loop saves - off unless QTTS_KSPLIT=1)
-    const bool want = allow_split && env && atoi(env) == 1;
+    // QTTS_KSPLIT=1: half 0 waits for half 1's partial (flag-carrying words) - measured: the hand-off costs what the
+    // shorter loop saves.  QTTS_KSPLIT=2: deferred combine, the following norm stage adds the partial (BEmit::defer).
+    // Only for groups of one M tile: wider groups use split-M, which needs unsplit weights.
+    const int mode = env ? atoi(env) : 2;       // default: deferred combine (+9% at 64 streams, +12% at 128); 0 = off
+    const bool want = allow_split && (mode == 1 || (mode == 2 && std::min(e->bgroup, e->max_streams) <= 128));
     T.ksplit = (want && 2 * (rows / T.n_tile) <= e->n_sms && K % (2 * kKc) == 0) ? 2 : 1;
     const int Kh = K / T.ksplit;
     T.K = Kh;
@@ -93,6 +96,9 @@ struct BEmit {
     bool norm_stage = true;
     bool rows_signal = true;     // norm -> GEMM hand-off through a row counter instead of a grid barrier
     bool msplit_on = true;
+    float * part32 = nullptr;            // deferred split-K: second half's partial sums, laid out like the output
+    bool defer = false;
+    const float * pending_x = nullptr;   // output of a deferred-split projection whose partial has not been added yet
 
     void gemm(const TiledW & T, int rows_act, int in_kind, const void * in, int in_row_stride, int in_tok_stride,
               const float * norm_w, const float * ssq_in, int n_parts_in, int epi, float * out32, __half * out16,
@@ -105,6 +111,11 @@ struct BEmit {
             n.in = in; n.in_row_stride = in_row_stride; n.in_tok_stride = in_tok_stride;
             n.norm_w = norm_w; n.ssq_in = ssq_in; n.n_parts_in = n_parts_in; n.eps = e->cfg.rms_norm_eps;
             n.out16 = xn16; n.hid_out = hid_out;
+            if (pending_x) {
+                // this stage reads (a suffix of) the rows the split projection wrote: same strides, same offsets
+                n.part32 = part32 + (reinterpret_cast<const float *>(in) - pending_x);
+                pending_x = nullptr;
+            }
             if (rows_signal) { n.flags |= BF_ROWS_SIGNAL; flags |= BF_ROWS_WAIT; }
             P.push_back(n);
             in_kind = BIN_F16; in = xn16; norm_w = nullptr; ssq_in = nullptr; n_parts_in = 0; hid_out = nullptr;
@@ -114,6 +125,11 @@ struct BEmit {
         o.Wt = T.p; o.rows = T.rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = cta_off;
         o.kpp = T.kpp; o.n_pieces = T.n_pieces;
         o.ksplit = T.ksplit; o.part_ll = (T.ksplit > 1) ? part_ll : nullptr;
+        if (pending_x) { fprintf(stderr, "qtts: deferred split-K output consumed by a stage without a norm\n"); abort(); }
+        if (T.ksplit > 1 && defer && epi == EPI_ADD && out32 && norm_stage && xn16) {
+            o.part32 = part32; pending_x = out32;
+            o.flags &= ~BF_SSQ_OUT;      // the norm stage squares the combined row itself
+        }
         // split-M: a narrow projection over >= 2 M tiles gives each (N tile, M half) its own CTA
         const int m_total = (rows_act + 127) / 128;
         const int msplit = (msplit_on && in_kind == BIN_F16 && T.ksplit == 1 && m_total % 2 == 0 && 2 * T.n_tiles <= e->n_sms) ? 2 : 1;
@@ -238,6 +254,7 @@ bool batched_init(Engine * e) {
     if (occ < 1) return e->fail("batched kernel does not fit one CTA per SM");
     const int rep = c.n_heads / c.n_kv_heads;
     if (rep > kMaxRep || e->max_ctx * rep > 2 * kMaxScores) return e->fail("batched path: context too long for the attention scratch");
+    if (const char * v = getenv("QTTS_BGROUP")) e->bgroup = std::max(8, std::min(atoi(v), kBMaxGroup));
     // tiled weights
     e->t_talker.resize(c.n_layers); e->t_cp.resize(c.cp_layers); e->t_lm_head.resize(c.n_codebooks - 1);
     auto layer = [&](const LayerW & W, const Dims & D, TiledLayer & L) {
@@ -259,7 +276,6 @@ bool batched_init(Engine * e) {
     // stream groups of at most 128 streams (the merged code-predictor pass has 2 rows per stream)
     const int H = c.hidden_size, cpH = c.cp_hidden_size;
     const int qkvw = (c.n_heads + 2 * c.n_kv_heads) * kHeadDim, cqkvw = (c.cp_n_heads + 2 * c.cp_n_kv_heads) * kHeadDim;
-    if (const char * v = getenv("QTTS_BGROUP")) e->bgroup = std::max(8, std::min(atoi(v), kBMaxGroup));
     for (int s0 = 0; s0 < e->max_streams; s0 += e->bgroup) {
         BGroup G;
         G.s0 = s0; G.n = std::min(e->bgroup, e->max_streams - s0);
@@ -286,7 +302,11 @@ bool batched_init(Engine * e) {
         if (!G.part_ll) return e->fail("out of device memory for the split-K partials");
         G.xn16 = e->dalloc<__half>(B28 * (size_t) std::max(H, cpH));
         if (!G.xn16) return e->fail("out of device memory for the normalised activations");
+        G.part32 = e->dalloc<float>(2 * B * (size_t) std::max(H, cpH));
+        if (!G.part32) return e->fail("out of device memory for the split-K partials");
         BEmit E{e, {}, {}, G.n, 0, G.part_ll, G.xn16};
+        E.part32 = G.part32;
+        { const char * v = getenv("QTTS_KSPLIT"); E.defer = !v || atoi(v) == 2; }
         if (const char * v = getenv("QTTS_BNORM")) E.norm_stage = atoi(v) != 0;
         if (const char * v = getenv("QTTS_BROWS")) E.rows_signal = atoi(v) != 0;
         if (const char * v = getenv("QTTS_MSPLIT")) E.msplit_on = atoi(v) != 0;

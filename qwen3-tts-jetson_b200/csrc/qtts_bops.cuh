@@ -73,6 +73,10 @@ struct BOp {
     // (N tile v / msplit, M-tile range v % msplit); both CTAs stream the same weight tile, each its own rows
     int32_t msplit;
     unsigned long long * part_ll;    // [row blocks][n_tile / 16][rows_act padded to 32][16]
+    // deferred combine (ksplit with part32 set): half 0 runs the epilogue on its own partial sum, half 1 stores its
+    // partial to part32 (layout of out32); the BOP_NORM stage that follows adds it (x = x + part, written back) and
+    // computes the row's sum of squares itself - no CTA ever waits for its partner
+    float * part32;
     // ---- attention ----
     const float * qkv; int32_t qkvw;
     const float * q_norm_w, * k_norm_w, * rope;

@@ -53,6 +53,7 @@ struct BGroup {
     float * cb0_dump = nullptr, * cp_dump = nullptr;
     int32_t * active = nullptr;
     unsigned long long * part_ll = nullptr;   // split-K partial accumulators (flag-carrying)
+    float * part32 = nullptr;                 // split-K, deferred combine: second half's partial sums (layout of x)
     __half * xn16 = nullptr;                  // BOP_NORM output (canonical F16 rows)
     size_t part_words = 0;
     BOp * ops = nullptr; int n_ops = 0;

@@ -193,12 +193,14 @@ def test_batched_sampling_reproducible_and_ragged(engines, pkg):
 
 
 @pytest.mark.gpu
-def test_batched_large_group_matches_batch1(pkg, make_gguf):
-    """More than 128 streams in ONE lock-step group (two 128-row M tiles per GEMM, four in the merged
-    code-predictor pass): first-frame logits of slots on both sides of the M-tile boundary against the
+@pytest.mark.parametrize("n,probe", [(140, (0, 63, 127, 128, 139)), (128, (0, 64, 127)), (72, (0, 31, 71))])
+def test_batched_large_group_matches_batch1(pkg, make_gguf, n, probe):
+    """140: more than 128 streams in ONE lock-step group (two 128-row M tiles per GEMM, four in the merged
+    code-predictor pass, split-M on the narrow projections).  128 / 72: one M tile, the O and down projections
+    split over K with the second half's partial added by the following norm stage (two M tiles in the merged
+    code-predictor pass).  First-frame logits of slots on both sides of the tile boundaries against the
     batch-1 kernel, and greedy ids of all streams over the first frames."""
     path, cfg = make_gguf("tiny", 1234)
-    n = 140
     toks = [pkg.synth.synth_tokens(cfg, n_text=8 + (i % 5), seed=i) for i in range(n)]
     spks = [pkg.synth.synth_speaker(cfg, seed=i) for i in range(n)]
     T = pkg.TTSTransformer(device=0, max_streams=n, max_ctx=128)
@@ -210,7 +212,7 @@ def test_batched_large_group_matches_batch1(pkg, make_gguf):
             assert T.stream_begin(i, toks[i], spks[i], max_len=3, temperature=0.0, seed=i), T.get_error()
         codes, produced, active = T.step_frames(1)
         assert (produced == 1).all()
-        logits = {i: T.stream_logits(i, want_cp=False)[0].copy() for i in (0, 63, 127, 128, 139)}
+        logits = {i: T.stream_logits(i, want_cp=False)[0].copy() for i in probe}
         codes2, produced2, _ = T.step_frames(2)
         res[batched] = (codes[:, 0].copy(), logits, codes2[:, :2].copy())
     for i, l in res[True][1].items():
