@@ -315,6 +315,25 @@ public:
         return true;
     }
 
+    // begin() in two phases: prepare() many slots, then prefill() once - the Talker prefill of all of them is one
+    // batched pass (step() also runs it for slots still pending)
+    bool prepare(int slot, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd, int32_t max_len,
+                 int32_t language_id = 2050, float repetition_penalty = 1.05f, float temperature = 0.9f,
+                 int32_t top_k = 50, uint64_t seed = 0) {
+        if (!tr_.engine()) { err_ = "Model not loaded"; return false; }
+        if (qtts_stream_prepare(tr_.engine(), slot, text_tokens, n_tokens, speaker_embd, max_len, language_id,
+                                repetition_penalty, temperature, top_k, seed) == 0) {
+            err_ = qtts_last_error(tr_.engine());
+            return false;
+        }
+        return true;
+    }
+    bool prefill() {
+        if (!tr_.engine()) { err_ = "Model not loaded"; return false; }
+        if (qtts_prefill_pending(tr_.engine()) == 0) { err_ = qtts_last_error(tr_.engine()); return false; }
+        return true;
+    }
+
     // codes: [max_streams][n_frames][n_codebooks]; produced / active: [max_streams]
     bool step(int32_t n_frames, std::vector<int32_t> & codes, std::vector<int32_t> & produced,
               std::vector<int32_t> & active) {

@@ -139,6 +139,16 @@ int qtts_generate(qtts_engine * e, int slot, const int32_t * text_tokens, int32_
 int qtts_stream_begin(qtts_engine * e, int slot, const int32_t * text_tokens, int32_t n_tokens,
                       const float * speaker_embd, int32_t max_len, int32_t language_id,
                       float repetition_penalty, float temperature, int32_t top_k, uint64_t seed);
+/* The same in two phases, so that the prefill of MANY utterances is one batched pass:
+ * qtts_stream_prepare = build_prefill_graph (src/tts_transformer.cpp:1093-1231) + per-stream state, the stream is
+ * "pending"; qtts_prefill_pending = forward_prefill (:1829-1920) of every pending stream, per lock-step group all
+ * together on the batched kernel (one weight pass per prefill position for the group; FAST attention numerics),
+ * after which they are active.  qtts_step_frames runs it implicitly for streams still pending.
+ * qtts_last_loop_ms afterwards = device time of the batched prefill. */
+int qtts_stream_prepare(qtts_engine * e, int slot, const int32_t * text_tokens, int32_t n_tokens,
+                        const float * speaker_embd, int32_t max_len, int32_t language_id,
+                        float repetition_penalty, float temperature, int32_t top_k, uint64_t seed);
+int qtts_prefill_pending(qtts_engine * e);
 /* Advance every active stream by up to n_frames frames.  codes_out is
  * [max_streams][n_frames][n_codebooks]; produced[slot] = frames written for that slot;
  * active[slot] = 1 while the stream has neither hit EOS nor max_len. */

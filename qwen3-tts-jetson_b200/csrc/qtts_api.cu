@@ -249,10 +249,12 @@ int qtts_predict_codes(qtts_engine * h, int slot, const float * hidden, int32_t 
     return 1;
 }
 
-static bool stream_begin(Engine * e, Slot & s, const int32_t * tokens, int32_t n, const float * speaker, int32_t max_len,
-                         int32_t language_id, float rep_pen, float temperature, int32_t top_k, uint64_t seed) {
+// embeddings (A12) + per-stream state; the Talker prefill (A3) is left to the caller
+static bool stream_prepare(Engine * e, Slot & s, const int32_t * tokens, int32_t n, const float * speaker, int32_t max_len,
+                           int32_t language_id, float rep_pen, float temperature, int32_t top_k, uint64_t seed) {
     if (!tokens) return e->fail("text_tokens is null");
     if (n < 4) return e->fail("Need at least 4 text tokens for generation");
+    s.active = false; s.pending = false;
     if (!do_build_prefill(e, s, tokens, n, speaker, language_id)) return false;
     // required context as in the reference (src/tts_transformer.cpp:2383)
     if (s.prefill_len + max_len + 8 > e->max_ctx) return e->fail("max_len does not fit the engine's max_ctx");
@@ -262,8 +264,41 @@ static bool stream_begin(Engine * e, Slot & s, const int32_t * tokens, int32_t n
     st.ignore_eos = e->ignore_eos;
     QTTS_CUDA(cudaMemcpyAsync(s.st, &st, sizeof(st), cudaMemcpyHostToDevice, e->stream));
     QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    return true;
+}
+
+static bool stream_begin(Engine * e, Slot & s, const int32_t * tokens, int32_t n, const float * speaker, int32_t max_len,
+                         int32_t language_id, float rep_pen, float temperature, int32_t top_k, uint64_t seed) {
+    if (!stream_prepare(e, s, tokens, n, speaker, max_len, language_id, rep_pen, temperature, top_k, seed)) return false;
     if (!do_forward_prefill(e, s, s.prefill_len, 0)) return false;
     s.active = true;
+    return true;
+}
+
+// Talker prefill of every prepared stream: per lock-step group, all of them together on the batched kernel (one
+// weight pass per prefill position for the whole group); the batch-1 kernel, stream after stream, when the batched
+// path is switched off.  The streams become active.
+static bool prefill_pending(Engine * e) {
+    bool any = false;
+    for (const Slot & s : e->slots) any |= s.pending;
+    if (!any) return true;
+    if (e->batched && e->batched_ready) {
+        for (BGroup & G : e->groups) {
+            std::vector<const float *> rows(G.n, nullptr);
+            std::vector<int32_t> plen(G.n, 0);
+            bool some = false;
+            for (int i = 0; i < G.n; ++i) {
+                const Slot & s = e->slots[G.s0 + i];
+                if (s.pending) { rows[i] = s.prefill; plen[i] = s.prefill_len; some = true; }
+            }
+            if (some && !run_batched_prefill(e, G, rows, plen)) return false;
+        }
+        QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    } else {
+        for (Slot & s : e->slots)
+            if (s.pending && !do_forward_prefill(e, s, s.prefill_len, 0)) return false;
+    }
+    for (Slot & s : e->slots) if (s.pending) { s.pending = false; s.active = true; }
     return true;
 }
 
@@ -326,6 +361,31 @@ int qtts_stream_begin(qtts_engine * h, int slot, const int32_t * tokens, int32_t
     return stream_begin(e, *s, tokens, n, speaker, max_len, language_id, rep_pen, temperature, top_k, seed) ? 1 : 0;
 }
 
+int qtts_stream_prepare(qtts_engine * h, int slot, const int32_t * tokens, int32_t n, const float * speaker, int32_t max_len,
+                        int32_t language_id, float rep_pen, float temperature, int32_t top_k, uint64_t seed) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    if (!stream_prepare(e, *s, tokens, n, speaker, max_len, language_id, rep_pen, temperature, top_k, seed)) return 0;
+    s->pending = true;
+    return 1;
+}
+
+int qtts_prefill_pending(qtts_engine * h) {
+    Engine * e = &h->e;
+    if (!e->finalized) { e->err = "engine not finalized"; return 0; }
+    cudaSetDevice(e->device);
+    cudaEventRecord(e->ev0, e->stream);
+    if (!prefill_pending(e)) return 0;
+    cudaEventRecord(e->ev1, e->stream);
+    if (cudaEventSynchronize(e->ev1) != cudaSuccess) { e->err = std::string("prefill_pending: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e->ev0, e->ev1);
+    e->last_loop_ms = ms;
+    return 1;
+}
+
 // Batched mode (default): all active streams of a group of <= 128 slots advance in lock step inside
 // ONE launch of the tcgen05 frame kernel (qtts_batched.cu), weights streamed once per frame for the
 // whole group.  Sequential mode (qtts_set_batched(e, 0)): the batch-1 kernel, one stream after
@@ -334,6 +394,7 @@ int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int
     Engine * e = &h->e;
     if (!e->finalized) { e->err = "engine not finalized"; return 0; }
     cudaSetDevice(e->device);
+    if (!prefill_pending(e)) return 0;        // streams prepared since the last call join here
     const int nb = e->cfg.n_codebooks;
     const size_t ns = e->slots.size();
     std::vector<StreamState> hs0(ns), hs1(ns);

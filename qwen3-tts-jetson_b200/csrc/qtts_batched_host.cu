@@ -164,6 +164,29 @@ static void emit_blayer(BEmit & E, const TiledLayer & L, const LayerW & W, const
            x, nullptr, x, nullptr, D.H, B * D.H, ssq_p);
 }
 
+// one Talker decode step of the group: 28 layers over the residual rows x (complete sums of squares in ssq_e),
+// output_norm -> hidden_out, codec_head -> logits_out, n_past advanced for the launch's active streams
+static void emit_btalker(Engine * e, BGroup & G, BEmit & E, float * x, float * ssq_e, float * logits_out, float * hidden_out) {
+    const qtts_config & c = e->cfg;
+    BatchBufs & bb = e->bb;
+    const int B = G.n, s0 = G.s0, H = c.hidden_size;
+    const Dims T{H, c.n_heads, c.n_kv_heads, c.intermediate_size};
+    const float kq = 1.0f / sqrtf((float) kHeadDim);
+    for (int l = 0; l < c.n_layers; ++l) {
+        BOp a = bblank(B);
+        a.type = BOP_ATTN_TK; a.rope = e->rope; a.eps = c.rms_norm_eps; a.kq_scale = kq;
+        // warp-per-(stream, group) form (field reused as a switch: 2 = on); QTTS_BATTN=0 keeps the CTA-per-item form
+        { const char * v = getenv("QTTS_BATTN"); a.pair_f32 = (v && atoi(v) == 0) ? 0 : 2; }
+        a.kc = bb.kc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
+        a.vc = bb.vc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
+        a.kv_stream_stride = (int64_t) bb.kv_slab;
+        emit_blayer(E, e->t_talker[l], e->talker[l], T, B, 1, x, G.qkv, G.attn16, G.act16,
+                    l == 0 ? ssq_e : G.ssq_p, l == 0 ? 1 : H / 16, G.ssq_p, a);
+    }
+    E.gemm(e->t_codec_head, B, BIN_F32, x, H, 0, e->output_norm, G.ssq_p, H / 16, EPI_STORE,
+           logits_out, nullptr, nullptr, nullptr, c.codec_vocab_size, 0, nullptr, hidden_out, BF_INC_NPAST);
+}
+
 // frame program of the stream group [s0, s0 + B)
 static void emit_bframe(Engine * e, BGroup & G, BEmit & E) {
     const qtts_config & c = e->cfg;
@@ -223,20 +246,7 @@ static void emit_bframe(Engine * e, BGroup & G, BEmit & E) {
         }
         E.P.push_back(sp);
     }
-    for (int l = 0; l < c.n_layers; ++l) {
-        BOp a = bblank(B);
-        a.type = BOP_ATTN_TK; a.rope = e->rope; a.eps = eps; a.kq_scale = kq;
-        // warp-per-(stream, group) form (field reused as a switch: 2 = on); QTTS_BATTN=0 keeps the CTA-per-item form
-        { const char * v = getenv("QTTS_BATTN"); a.pair_f32 = (v && atoi(v) == 0) ? 0 : 2; }
-        a.kc = bb.kc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
-        a.vc = bb.vc + (size_t) s0 * bb.kv_slab + (size_t) l * e->max_ctx * T.nkv * kHeadDim;
-        a.kv_stream_stride = (int64_t) bb.kv_slab;
-        emit_blayer(E, e->t_talker[l], e->talker[l], T, B, 1, G.x, G.qkv, G.attn16, G.act16,
-                    l == 0 ? G.ssq_e : G.ssq_p, l == 0 ? 1 : H / 16, G.ssq_p, a);
-    }
-    E.gemm(e->t_codec_head, B, BIN_F32, G.x, H, 0, e->output_norm, G.ssq_p, H / 16, EPI_STORE,
-           bb.logits + (size_t) s0 * c.codec_vocab_size, nullptr, nullptr, nullptr, c.codec_vocab_size, 0, nullptr,
-           bb.hidden + (size_t) s0 * H, BF_INC_NPAST);
+    emit_btalker(e, G, E, G.x, G.ssq_e, bb.logits + (size_t) s0 * c.codec_vocab_size, bb.hidden + (size_t) s0 * H);
 }
 
 uint32_t batched_idesc(const Engine * e) {
@@ -318,6 +328,21 @@ bool batched_init(Engine * e) {
         QTTS_CUDA(cudaMemcpy(G.ops, E.P.data(), E.P.size() * sizeof(BOp), cudaMemcpyHostToDevice));
         QTTS_CUDA(cudaMemcpy(G.sched, E.S.data(), E.S.size() * sizeof(BSched), cudaMemcpyHostToDevice));
         G.host_ops = E.P;
+        // batched prefill program: one Talker step over private residual rows / outputs
+        G.pf_x = e->dalloc<float>(B * H); G.pf_ssq_e = e->dalloc<float>(B);
+        G.pf_logits = e->dalloc<float>(B * c.codec_vocab_size); G.pf_hidden = e->dalloc<float>(B * H);
+        G.pf_rows = e->dalloc<const float *>(B); G.pf_plen = e->dalloc<int32_t>(B); G.pf_active = e->dalloc<int32_t>(B);
+        if (!G.pf_x || !G.pf_ssq_e || !G.pf_logits || !G.pf_hidden || !G.pf_rows || !G.pf_plen || !G.pf_active)
+            return e->fail("out of device memory for the batched prefill");
+        BEmit F{e, {}, {}, G.n, 0, G.part_ll, G.xn16};
+        F.part32 = G.part32; F.defer = E.defer; F.norm_stage = E.norm_stage; F.rows_signal = E.rows_signal; F.msplit_on = E.msplit_on;
+        emit_btalker(e, G, F, G.pf_x, G.pf_ssq_e, G.pf_logits, G.pf_hidden);
+        G.pf_n_ops = (int) F.P.size(); G.pf_n_sched = (int) F.S.size();
+        G.pf_ops = e->dalloc<BOp>(F.P.size(), false);
+        G.pf_sched = e->dalloc<BSched>(F.S.size(), false);
+        if (!G.pf_ops || !G.pf_sched) return e->fail("out of device memory for the batched prefill program");
+        QTTS_CUDA(cudaMemcpy(G.pf_ops, F.P.data(), F.P.size() * sizeof(BOp), cudaMemcpyHostToDevice));
+        QTTS_CUDA(cudaMemcpy(G.pf_sched, F.S.data(), F.S.size() * sizeof(BSched), cudaMemcpyHostToDevice));
         e->groups.push_back(G);
     }
     e->batched_ready = true;
@@ -360,6 +385,69 @@ bool run_batched_group(Engine * e, BGroup & G, int n_frames) {
     QTTS_CUDA(cudaMemcpyAsync(G.active, act.data(), act.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
     QTTS_CUDA(cudaStreamSynchronize(e->stream));
     return launch_batched(e, G.ops, G.n_ops, G.sched, G.n_sched, e->bb.st + G.s0, G.active, G.n, n_frames, true);
+}
+
+// ------------------------------------------------------------------------------------------
+// Batched prefill (forward_prefill, src/tts_transformer.cpp:1829-1920, for many utterances at once): position t of
+// every stream being prefilled is one lock-step Talker step of the tcgen05 kernel (weights streamed once per position
+// for the whole group instead of once per stream and position).  Causality comes from the KV cache exactly as in the
+// token-by-token batch-1 prefill: position t attends to the F16 K/V rows 0..t written so far.
+// Streams of the group that are mid-utterance are untouched: the program works on pf_x / pf_logits / pf_hidden, the
+// launch's active mask covers only (stream being prefilled, t < its prefill length), and the K/V row a masked stream
+// gets written at its own n_past is overwritten by that stream's next real step before anything reads it.
+// ------------------------------------------------------------------------------------------
+__global__ void k_prefill_gather(const float * const * __restrict__ rows, const int32_t * __restrict__ plen, int t,
+                                 float * __restrict__ x, float * __restrict__ ssq_e, int32_t * __restrict__ active, int H) {
+    __shared__ double red[32];
+    const int b = blockIdx.x;
+    const bool on = rows[b] != nullptr && t < plen[b];
+    if (threadIdx.x == 0) active[b] = on ? 1 : 0;
+    if (!on) return;
+    const float * src = rows[b] + (size_t) t * H;
+    double ss = 0.0;
+    for (int i = threadIdx.x; i < H; i += blockDim.x) {
+        const float v = src[i];
+        x[(size_t) b * H + i] = v;
+        ss += (double) (v * v);
+    }
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int w = 0; w < (int) (blockDim.x >> 5); ++w) tot += red[w];
+        ssq_e[b] = (float) tot;
+    }
+}
+
+// logits / hidden of the streams whose LAST prefill position was t -> their rows of the per-stream slabs
+__global__ void k_prefill_scatter(const float * const * __restrict__ rows, const int32_t * __restrict__ plen, int t,
+                                  const float * __restrict__ lg, float * __restrict__ logits, int V,
+                                  const float * __restrict__ hid, float * __restrict__ hidden, int H) {
+    const int b = blockIdx.x;
+    if (rows[b] == nullptr || plen[b] - 1 != t) return;
+    for (int i = threadIdx.x; i < V; i += blockDim.x) logits[(size_t) b * V + i] = lg[(size_t) b * V + i];
+    for (int i = threadIdx.x; i < H; i += blockDim.x) hidden[(size_t) b * H + i] = hid[(size_t) b * H + i];
+}
+
+bool run_batched_prefill(Engine * e, BGroup & G, const std::vector<const float *> & rows, const std::vector<int32_t> & plen) {
+    const qtts_config & c = e->cfg;
+    const int H = c.hidden_size, V = c.codec_vocab_size;
+    int max_len = 0;
+    for (int i = 0; i < G.n; ++i) if (rows[i]) max_len = std::max(max_len, (int) plen[i]);
+    if (max_len == 0) return true;
+    QTTS_CUDA(cudaMemcpyAsync(G.pf_rows, rows.data(), G.n * sizeof(const float *), cudaMemcpyHostToDevice, e->stream));
+    QTTS_CUDA(cudaMemcpyAsync(G.pf_plen, plen.data(), G.n * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));      // rows / plen are caller-owned host vectors
+    for (int t = 0; t < max_len; ++t) {
+        k_prefill_gather<<<G.n, 256, 0, e->stream>>>(G.pf_rows, G.pf_plen, t, G.pf_x, G.pf_ssq_e, G.pf_active, H);
+        if (!launch_batched(e, G.pf_ops, G.pf_n_ops, G.pf_sched, G.pf_n_sched, e->bb.st + G.s0, G.pf_active, G.n, 1, false)) return false;
+        k_prefill_scatter<<<G.n, 256, 0, e->stream>>>(G.pf_rows, G.pf_plen, t, G.pf_logits, e->bb.logits + (size_t) G.s0 * V, V,
+                                                       G.pf_hidden, e->bb.hidden + (size_t) G.s0 * H, H);
+        e->launches += 2;
+    }
+    QTTS_CUDA(cudaGetLastError());
+    return true;
 }
 
 }  // namespace qtts

@@ -59,6 +59,13 @@ struct BGroup {
     BOp * ops = nullptr; int n_ops = 0;
     BSched * sched = nullptr; int n_sched = 0;
     std::vector<BOp> host_ops;
+    // batched prefill (run_batched_prefill): the Talker half of the frame program over its own residual rows, so
+    // streams of the group that are mid-utterance keep their pending input / logits / hidden
+    float * pf_x = nullptr, * pf_ssq_e = nullptr, * pf_logits = nullptr, * pf_hidden = nullptr;
+    const float ** pf_rows = nullptr;         // [n] prefill embedding rows of the streams being prefilled (else null)
+    int32_t * pf_plen = nullptr, * pf_active = nullptr;
+    BOp * pf_ops = nullptr; int pf_n_ops = 0;
+    BSched * pf_sched = nullptr; int pf_n_sched = 0;
 };
 
 // per-slot device buffers
@@ -96,6 +103,7 @@ struct Slot {
     // host mirrors
     int32_t prefill_len = 0, trailing_len = 0, n_text_tokens = 0;
     bool active = false;
+    bool pending = false;                  // prepared (embeddings + state) but the Talker prefill has not run yet
 };
 
 struct Engine {
@@ -131,6 +139,7 @@ struct Engine {
     std::vector<__nv_bfloat16 *> lm_head;
     float * output_norm = nullptr, * cp_output_norm = nullptr, * fc1_b = nullptr, * fc2_b = nullptr, * mtp_b = nullptr;
     const __half * codec_embd = nullptr, * text_embd = nullptr;
+    float * text_tab = nullptr;    // folded text table [text_vocab][H] (fold_text_table), nullptr: per-token projection
     std::vector<const __half *> cp_embd;
     std::vector<Slot> slots;
     // batched (tcgen05) path
@@ -177,6 +186,7 @@ bool run_program(Engine * e, Slot & s, const std::vector<Op> & P, int n_frames, 
 bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vector<Op> * host_ops, int n_ops,
                         const WSched * d_sched, int n_sched, int n_frames, bool check_done);
 std::vector<WSched> build_sched(Engine * e, const std::vector<Op> & P);
+bool fold_text_table(Engine * e);
 
 // qtts_batched_host.cu
 bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T, bool allow_split = false);
@@ -185,6 +195,7 @@ uint32_t batched_idesc(const Engine * e);
 bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_sched, int n_sched, StreamState * st,
                     const int32_t * d_active, int n_streams, int n_frames, bool check_done);
 bool run_batched_group(Engine * e, BGroup & G, int n_frames);
+bool run_batched_prefill(Engine * e, BGroup & G, const std::vector<const float *> & rows, const std::vector<int32_t> & plen);
 
 #define QTTS_CUDA(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
     e->err = std::string(#call) + ": " + cudaGetErrorString(_e); return false; } } while (0)

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <utility>
 #include <cstring>
+#include <cstdlib>
 
 namespace qtts {
 
@@ -188,6 +189,11 @@ static Op row_op(float * out, const __half * table, const int32_t * tok_ptr, con
     return o;
 }
 
+__global__ void k_assemble_prefill(const float * __restrict__ tab, const __half * __restrict__ codec_embd,
+                                   const int32_t * __restrict__ ids, int n, int n_codec, int has_speaker,
+                                   const float * __restrict__ speaker, int H, int plen, int trailing_len,
+                                   float * __restrict__ prefill, float * __restrict__ trailing, float * __restrict__ pad);
+
 // build_prefill_graph (src/tts_transformer.cpp:1093-1231) on the device.  Token ids are staged in
 // s.tokens: [0..n) the text tokens, then the 3 special text ids, then the codec ids.
 bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t * tokens, int n_tokens,
@@ -211,6 +217,16 @@ bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t
     ids.insert(ids.end(), codec.begin(), codec.end());
     QTTS_CUDA(cudaMemcpyAsync(s.tokens, ids.data(), ids.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
     QTTS_CUDA(cudaStreamSynchronize(e->stream));   // ids is a stack-lifetime host buffer
+    if (e->text_tab) {
+        const int plen = 3 + (n_codec_prefill + (has_speaker ? 1 : 0) + 1) + 1;
+        const int trailing_tokens = n_tokens - 9 > 0 ? n_tokens - 9 : 0;
+        k_assemble_prefill<<<plen + trailing_tokens + 2, 256, 0, e->stream>>>(
+            e->text_tab, e->codec_embd, s.tokens, n_tokens, n_codec_prefill, has_speaker ? 1 : 0, s.speaker, H,
+            plen, trailing_tokens + 1, s.prefill, s.trailing, s.pad);
+        QTTS_CUDA(cudaGetLastError());
+        s.prefill_len = plen; s.trailing_len = trailing_tokens + 1; s.n_text_tokens = n_tokens;
+        return true;            // P stays empty: nothing left for the stage program
+    }
 
     auto text_proj = [&](int tok_index, float * dst) {   // project_text_tokens (:1026-1091)
         Op f1 = gemv(e->fc1, E, E, nullptr, nullptr, c.rms_norm_eps, EPI_BIAS_SILU, s.tp_tmp);
@@ -253,6 +269,83 @@ bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t
     return true;
 }
 
+// ------------------------------------------------------------------------------------------
+// Folded text table: project_text_tokens (src/tts_transformer.cpp:1026-1091) is a pure function of the token id
+// (text_embd row -> fc1 + bias, SiLU -> fc2 + bias), so it is evaluated ONCE per vocabulary entry at load time, by
+// the same two GEMV stages the per-token path runs (bit-identical rows), into an F32 table [text_vocab][H].
+// build_prefill_graph (:1093-1231) then is one gather kernel per utterance instead of two dependent GEMV
+// stages per text token.  QTTS_FOLD_TEXT=0 keeps the per-token path.
+// ------------------------------------------------------------------------------------------
+bool fold_text_table(Engine * e) {
+    if (const char * v = getenv("QTTS_FOLD_TEXT")) if (atoi(v) == 0) return true;
+    const qtts_config & c = e->cfg;
+    if (!e->fc1 || !e->fc2 || !e->text_embd || e->slots.empty()) return true;
+    const int H = c.hidden_size, E = c.text_embd_dim, V = c.text_vocab_size;
+    e->text_tab = e->dalloc<float>((size_t) V * H, false);
+    int32_t * ids = e->dalloc<int32_t>(V, false);
+    if (!e->text_tab || !ids) { e->text_tab = nullptr; return e->fail("out of device memory for the folded text table"); }
+    std::vector<int32_t> iota(V);
+    for (int i = 0; i < V; ++i) iota[i] = i;
+    QTTS_CUDA(cudaMemcpy(ids, iota.data(), (size_t) V * sizeof(int32_t), cudaMemcpyHostToDevice));
+    Slot & s = e->slots[0];
+    const int chunk = 2048;
+    std::vector<Op> P;
+    for (int t0 = 0; t0 < V; t0 += chunk) {
+        P.clear();
+        for (int t = t0; t < std::min(V, t0 + chunk); ++t) {
+            Op f1 = gemv(e->fc1, E, E, nullptr, nullptr, c.rms_norm_eps, EPI_BIAS_SILU, s.tp_tmp);
+            f1.in_kind = IN_EMBED_ROW; f1.table = e->text_embd; f1.tok_ptr = ids + t; f1.bias = e->fc1_b;
+            P.push_back(f1);
+            Op f2 = gemv(e->fc2, H, E, s.tp_tmp, nullptr, c.rms_norm_eps, EPI_BIAS, e->text_tab + (size_t) t * H);
+            f2.bias = e->fc2_b;
+            P.push_back(f2);
+        }
+        if (!run_program(e, s, P, 1, false)) { e->text_tab = nullptr; return false; }
+    }
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    return true;
+}
+
+// rows of one utterance out of the folded table.  ids: [0, n) text tokens, then tts_bos / tts_eos / tts_pad, then
+// the codec prefill ids (n_codec of them), codec_pad, codec_bos.  Row r of the grid:
+//   [0, plen)            prefill rows        [plen, plen + trailing_len)  trailing text rows        last: the pad row
+__global__ void k_assemble_prefill(const float * __restrict__ tab, const __half * __restrict__ codec_embd,
+                                   const int32_t * __restrict__ ids, int n, int n_codec, int has_speaker,
+                                   const float * __restrict__ speaker, int H, int plen, int trailing_len,
+                                   float * __restrict__ prefill, float * __restrict__ trailing, float * __restrict__ pad) {
+    const int r = blockIdx.x;
+    const int sp0 = n, cd0 = n + 3;
+    const float * bos = tab + (size_t) ids[sp0] * H, * eos = tab + (size_t) ids[sp0 + 1] * H, * padr = tab + (size_t) ids[sp0 + 2] * H;
+    const float * a = nullptr, * b = nullptr;
+    const __half * hrow = nullptr;
+    float * dst;
+    if (r < plen) {
+        dst = prefill + (size_t) r * H;
+        const int overlay_len = plen - 4;
+        if (r < 3) a = tab + (size_t) ids[r] * H;                               // role rows
+        else if (r < plen - 1) {                                                // codec rows + tts_pad / tts_bos overlay
+            const int t = r - 3;
+            b = (t == overlay_len - 1) ? bos : padr;
+            if (has_speaker && t == n_codec) a = speaker;
+            else hrow = codec_embd + (size_t) ids[cd0 + ((t < n_codec) ? t : t - has_speaker)] * H;
+        } else {                                                                // text_proj(tokens[3]) + codec_embd(codec_bos)
+            hrow = codec_embd + (size_t) ids[cd0 + n_codec + 1] * H;
+            b = tab + (size_t) ids[3] * H;
+        }
+    } else if (r < plen + trailing_len) {
+        const int t = r - plen;
+        dst = trailing + (size_t) t * H;
+        a = (t == trailing_len - 1) ? eos : tab + (size_t) ids[4 + t] * H;
+    } else {
+        dst = pad; a = padr;
+    }
+    for (int i = threadIdx.x; i < H; i += blockDim.x) {
+        // operand order of the program path: (codec row | overlay) + (overlay | speaker); F32 addition commutes
+        const float x = hrow ? __half2float(hrow[i]) : a[i];
+        dst[i] = b ? x + b[i] : x;
+    }
+}
+
 std::vector<WSched> build_sched(Engine * e, const std::vector<Op> & P) {
     std::vector<WSched> S;
     for (const Op & op : P)
@@ -290,6 +383,8 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
         GridBarrier * bar = e->bar;
         void * args[] = {(void *) &d_ops, (void *) &n_ops, (void *) &st, (void *) &bar, (void *) &n_frames,
                          (void *) &cfg};
+        // the attribute is per function, not per engine: another engine (other K -> other ring size) may have changed it
+        QTTS_CUDA(cudaFuncSetAttribute(qtts_run_program, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) e->smem_bytes));
         QTTS_CUDA(cudaLaunchCooperativeKernel((const void *) qtts_run_program, dim3(e->n_sms), dim3(kThreads),
                                               args, e->smem_bytes, e->stream));
         e->launches += 1;
@@ -297,6 +392,7 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
     }
     // debug path: one launch per stage; needs the host copy of the program to find sampling stages
     if (!host_ops) return e->fail("stage-by-stage mode needs the host copy of the program");
+    QTTS_CUDA(cudaFuncSetAttribute(qtts_run_program, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) e->smem_bytes));
     for (int f = 0; f < n_frames; ++f) {
         int si = 0;     // schedule entry of the i-th op when it is a GEMV
         for (int i = 0; i < n_ops; ++i) {

@@ -329,6 +329,7 @@ bool engine_finalize(Engine * e) {
     e->slots.resize(e->max_streams);
     for (int i = 0; i < e->max_streams; ++i) if (!alloc_slot(e, e->slots[i], i)) return false;
     if (!batched_init(e)) return false;
+    if (!fold_text_table(e)) return false;
     e->finalized = true;
     return true;
 }

@@ -41,7 +41,8 @@ FRAME_CB = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_
 EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error", "qtts_upload_tensor",
            "qtts_finalize", "qtts_weight_stats", "qtts_set_numerics", "qtts_set_persistent", "qtts_set_ignore_eos",
            "qtts_clear_kv_cache", "qtts_build_prefill", "qtts_forward_prefill", "qtts_forward_step",
-           "qtts_predict_codes", "qtts_generate", "qtts_stream_begin", "qtts_step_frames",
+           "qtts_predict_codes", "qtts_generate", "qtts_stream_begin", "qtts_stream_prepare", "qtts_prefill_pending",
+           "qtts_step_frames",
            "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
            "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
 
@@ -79,6 +80,8 @@ def load_library(path: str | None = None):
     lib.qtts_generate.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64,
                                   vp, i32p, FRAME_CB, i32, vp]
     lib.qtts_stream_begin.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64]
+    lib.qtts_stream_prepare.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64]
+    lib.qtts_prefill_pending.argtypes = [vp]
     lib.qtts_step_frames.argtypes = [vp, i32, vp, vp, vp]
     lib.qtts_profile.argtypes = [vp, C.c_int, vp]
     lib.qtts_set_batched.argtypes = [vp, C.c_int]
@@ -313,6 +316,18 @@ class TTSTransformer:
         spk = None if speaker_embd is None else np.ascontiguousarray(speaker_embd, dtype=np.float32)
         return bool(self._lib.qtts_stream_begin(self._h, slot, _ptr(toks), len(toks), _ptr(spk), max_len, language_id,
                                                 repetition_penalty, temperature, top_k, seed))
+
+    def stream_prepare(self, slot: int, text_tokens, speaker_embd=None, max_len: int = 4096, language_id: int = 2050,
+                       repetition_penalty: float = 1.05, temperature: float = 0.9, top_k: int = 50, seed: int = 0) -> bool:
+        """Phase 1 of stream_begin (embeddings + state); the Talker prefill runs in prefill_pending()."""
+        toks = np.ascontiguousarray(text_tokens, dtype=np.int32)
+        spk = None if speaker_embd is None else np.ascontiguousarray(speaker_embd, dtype=np.float32)
+        return bool(self._lib.qtts_stream_prepare(self._h, slot, _ptr(toks), len(toks), _ptr(spk), max_len, language_id,
+                                                  repetition_penalty, temperature, top_k, seed))
+
+    def prefill_pending(self) -> bool:
+        """Batched Talker prefill of every prepared stream (forward_prefill for many utterances at once)."""
+        return bool(self._lib.qtts_prefill_pending(self._h))
 
     def step_frames(self, n_frames: int):
         nb = self.config["n_codebooks"]

@@ -222,3 +222,106 @@ def test_batched_large_group_matches_batch1(pkg, make_gguf, n, probe):
     same0 = (res[True][0] == res[False][0]).all(axis=1)
     assert same0.mean() >= 0.95, f"only {same0.sum()} of {n} streams agree on the first frame"
     T.unload_model()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("preset,n", [("tiny", 7), ("tiny-mtp", 4), ("0.6b", 5), ("tiny", 140)])
+def test_batched_prefill_matches_batch1_prefill(pkg, make_gguf, preset, n):
+    """stream_prepare + prefill_pending (forward_prefill of all streams as lock-step passes of the batched kernel)
+    against stream_begin (the batch-1 kernel's token-by-token prefill): codebook-0 logits of the first frame
+    (they are the prefill's output) and greedy ids.  Ragged prefill lengths: every third stream has no speaker
+    row (9 instead of 10 positions)."""
+    path, cfg = make_gguf(preset, 1234)
+    toks = [pkg.synth.synth_tokens(cfg, n_text=8 + (i % 5), seed=i) for i in range(n)]
+    spks = [None if i % 3 == 2 else pkg.synth.synth_speaker(cfg, seed=i) for i in range(n)]
+    T = pkg.TTSTransformer(device=0, max_streams=n, max_ctx=128)
+    assert T.load_model(path), T.get_error()
+    T.set_numerics(1, 4)
+    res = {}
+    for mode in ("batch1", "batched"):
+        for i in range(n):
+            if mode == "batch1":
+                assert T.stream_begin(i, toks[i], spks[i], max_len=4, temperature=0.0, seed=i), T.get_error()
+            else:
+                assert T.stream_prepare(i, toks[i], spks[i], max_len=4, temperature=0.0, seed=i), T.get_error()
+        if mode == "batched":
+            assert T.prefill_pending(), T.get_error()
+        codes, produced, active = T.step_frames(4)
+        assert (produced == 4).all() and not active.any()
+        res[mode] = (codes.copy(), [T.stream_logits(i, want_cp=False)[0].copy() for i in range(min(n, 8))])
+    T.unload_model()
+    ca, la = res["batch1"]
+    cb, lb = res["batched"]
+    for a, b in zip(la, lb):
+        assert not np.isnan(b).any() and (np.isfinite(a) == np.isfinite(b)).all()
+    # stream_logits holds the LAST frame's processed codebook-0 logits; compare where both runs took the same path
+    same_first = (ca[:, 0, :] == cb[:, 0, :]).all(axis=1)
+    print("streams equal on frame 0:", int(same_first.sum()), "of", n)
+    assert same_first.mean() >= 0.8
+    assert (ca[:, 0, 0] == cb[:, 0, 0]).mean() >= 0.9
+
+
+@pytest.mark.gpu
+def test_batched_prefill_first_frame_logits(pkg, make_gguf):
+    """Prefill logits themselves: one frame only, so stream_logits is the prefill's codebook-0 logit vector after
+    the suppress / repetition stage, equal processing on both paths."""
+    path, cfg = make_gguf("0.6b", 1234)
+    n = 3
+    toks = [pkg.synth.synth_tokens(cfg, n_text=12 + 7 * i, seed=i) for i in range(n)]
+    spks = [pkg.synth.synth_speaker(cfg, seed=i) for i in range(n)]
+    T = pkg.TTSTransformer(device=0, max_streams=n, max_ctx=128)
+    assert T.load_model(path), T.get_error()
+    T.set_numerics(1, 4)
+    out = {}
+    for mode in ("batch1", "batched"):
+        for i in range(n):
+            fn = T.stream_begin if mode == "batch1" else T.stream_prepare
+            assert fn(i, toks[i], spks[i], max_len=2, temperature=0.0, seed=i), T.get_error()
+        codes, produced, active = T.step_frames(1)      # pending streams are prefilled implicitly
+        assert (produced == 1).all()
+        out[mode] = [T.stream_logits(i, want_cp=False)[0].copy() for i in range(n)]
+    T.unload_model()
+    for a, b in zip(out["batch1"], out["batched"]):
+        fin = np.isfinite(a) & np.isfinite(b)
+        assert (np.isfinite(a) == np.isfinite(b)).all()
+        assert nmse(b[fin], a[fin]) <= 1e-5 and np.abs(a[fin] - b[fin]).max() <= 4e-3
+
+
+@pytest.mark.gpu
+def test_batched_prefill_joins_running_group(pkg, make_gguf):
+    """Continuous batching: streams prepared while others of the same lock-step group are mid-utterance.  The
+    running streams' ids must not change (the prefill works on private rows), the joiner's ids equal a solo run."""
+    path, cfg = make_gguf("tiny", 1234)
+    toks = [pkg.synth.synth_tokens(cfg, n_text=9 + i, seed=i) for i in range(4)]
+    spks = [pkg.synth.synth_speaker(cfg, seed=i) for i in range(4)]
+    T = pkg.TTSTransformer(device=0, max_streams=4, max_ctx=128)
+    assert T.load_model(path), T.get_error()
+    T.set_numerics(1, 4)
+
+    def drain(got):
+        while True:
+            codes, produced, active = T.step_frames(5)
+            for i in range(4):
+                got[i].append(codes[i, :produced[i]])
+            if not active.any():
+                break
+
+    # A: slots 0, 1 alone; B: slot 3 alone; C: 0, 1 start, slot 3 (+2) join after 6 frames
+    runs = {}
+    for name, first, late in (("A", (0, 1), ()), ("B", (3,), ()), ("C", (0, 1), (3, 2))):
+        got = [[] for _ in range(4)]
+        for i in first:
+            assert T.stream_prepare(i, toks[i], spks[i], max_len=20, temperature=0.0, seed=i), T.get_error()
+        assert T.prefill_pending(), T.get_error()
+        codes, produced, active = T.step_frames(6)
+        for i in range(4):
+            got[i].append(codes[i, :produced[i]])
+        for i in late:
+            assert T.stream_prepare(i, toks[i], spks[i], max_len=20, temperature=0.0, seed=i), T.get_error()
+        drain(got)
+        runs[name] = [np.concatenate(g) for g in got]
+    T.unload_model()
+    for i in (0, 1):
+        assert len(runs["A"][i]) == 20 and np.array_equal(runs["A"][i], runs["C"][i])
+    assert len(runs["B"][3]) == 20 and np.array_equal(runs["B"][3], runs["C"][3])
+    assert len(runs["C"][2]) == 20

@@ -18,7 +18,7 @@ from test_oracle import load_gold, NMSE_TOL, ABS_TOL
 
 pytestmark = pytest.mark.gpu
 
-EXACT_FRAMES = {"tiny": 4, "tiny-mtp": 4, "0.6b": 2}
+EXACT_FRAMES = {"tiny": 4, "tiny-mtp": 4, "0.6b": 2, "1.7b": 1}
 
 
 @pytest.fixture(scope="module")
@@ -39,14 +39,14 @@ def engines(pkg, make_gguf):
         T.unload_model()
 
 
-@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b"])
+@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b", "1.7b"])
 def test_weights_bf16_exact(engines, preset):
     T, cfg, _ = engines(preset)
     st = T.weight_stats()
     assert st["n_weights"] > 0 and st["n_not_bf16_exact"] == 0
 
 
-@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b"])
+@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b", "1.7b"])
 def test_build_prefill_vs_golden(engines, preset):
     T, cfg, _ = engines(preset)
     g = load_gold(preset)
@@ -56,25 +56,28 @@ def test_build_prefill_vs_golden(engines, preset):
         assert np.abs(a - b).max() <= 1e-6
 
 
-@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b"])
+@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b", "1.7b"])
 def test_talker_teacher_forced_vs_golden(engines, preset):
     T, cfg, _ = engines(preset)
     g = load_gold(preset)
     T.set_numerics(0, int(g["threads"]))
     T.clear_kv_cache()
     hid, logits = T.forward_prefill(g["prefill"])
-    assert nmse(logits, g["pre_logits"]) <= NMSE_TOL and np.abs(logits - g["pre_logits"]).max() <= ABS_TOL
+    # max|d| is stated for Talker logits of the 0.6B scale; with the same N(0, 0.02) init they grow as sqrt(hidden),
+    # so the absolute bound scales with it (1.7b preset: hidden 2048 -> 5.7e-3); the NMSE bound is scale-free
+    abs_tol = ABS_TOL * max(1.0, (cfg.hidden_size / 1024.0) ** 0.5)
+    assert nmse(logits, g["pre_logits"]) <= NMSE_TOL and np.abs(logits - g["pre_logits"]).max() <= abs_tol
     assert nmse(hid, g["pre_hidden"]) <= NMSE_TOL
     assert int(logits[:2048].argmax()) == int(g["cp_cb0"])
     n_past = g["prefill"].shape[0]
     for i in range(g["step_embd"].shape[0]):
         lg, hd = T.forward_step(g["step_embd"][i], n_past + i)
         assert nmse(lg, g["step_logits"][i]) <= NMSE_TOL
-        assert np.abs(lg - g["step_logits"][i]).max() <= ABS_TOL
+        assert np.abs(lg - g["step_logits"][i]).max() <= abs_tol
         assert nmse(hd, g["step_hidden"][i]) <= NMSE_TOL
 
 
-@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b"])
+@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b", "1.7b"])
 def test_code_predictor_teacher_forced_vs_golden(engines, preset):
     T, cfg, _ = engines(preset)
     g = load_gold(preset)
@@ -88,7 +91,7 @@ def test_code_predictor_teacher_forced_vs_golden(engines, preset):
             assert codes[s] == g["cp_codes"][s]
 
 
-@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b"])
+@pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b", "1.7b"])
 @pytest.mark.parametrize("persistent", [True, False])
 def test_generate_greedy_vs_golden(engines, preset, persistent):
     if preset == "0.6b" and not persistent:

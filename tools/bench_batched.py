@@ -26,7 +26,11 @@ for rep in range(2):
     t0 = time.time()
     for i in range(B):
         toks = pkg.synth.synth_tokens(cfg, n_text=int(r.integers(max(8, n_text // 2), n_text + 1)), seed=i)
-        assert T.stream_begin(i, toks, pkg.synth.synth_speaker(cfg, seed=i), max_len=frames, temperature=0.9, top_k=50, seed=i), T.get_error()
+        fn = T.stream_begin if os.environ.get("QTTS_SEQ_PREFILL") else T.stream_prepare
+        assert fn(i, toks, pkg.synth.synth_speaker(cfg, seed=i), max_len=frames, temperature=0.9, top_k=50, seed=i), T.get_error()
+    t_prep = time.time() - t0
+    assert T.prefill_pending(), T.get_error()
+    print(f"  prepare {t_prep / B * 1e3:.2f} ms/stream, batched prefill {T.last_loop_ms():.1f} ms device for {B} streams", flush=True)
     t_begin = time.time() - t0
     if prof and rep == 1:
         T.batched_profile(True)
