@@ -1044,7 +1044,18 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
         wq[j] = op.q_norm_w ? __ldg(op.q_norm_w + lane + 32 * j) : 1.f;
         wk[j] = op.k_norm_w ? __ldg(op.k_norm_w + lane + 32 * j) : 1.f;
     }
-    for (int item = gw; item < B * nkv; item += nw) {
+    // split-KV over `spl` adjacent warps of the CTA when there are fewer items than warps (<= 128 streams: 2, <= 64: 4):
+    // the key range is dealt in blocks of 16, the LAST warp of the group owns the tail (and the new K/V row), the
+    // others hand (m, l, acc) over through shared memory and it merges them in fixed order.  A long context is
+    // latency-bound per warp (two dependent L2/DRAM round trips per 16 keys), so bytes in flight scale with the warps.
+    const int wib = threadIdx.x >> 5;
+    int spl = 1;
+    if (4 * B * nkv <= nw) spl = 4; else if (2 * B * nkv <= nw) spl = 2;
+    if (S->run.dbg & 16) spl = 1;      // A/B switch (QTTS_BDBG=16): one warp per item
+    const int part = gw % spl, ngrp = nw / spl;
+    const bool tail = part == spl - 1;
+    float * pbuf = reinterpret_cast<float *>(babuf_base(S) + kWarps * REP * kHeadDim * sizeof(float));   // [warp][20][32]
+    for (int item = gw / spl; item < B * nkv; item += ngrp) {
         const int b = item / nkv, g = item - b * nkv;
         const int pos = __ldcg(&run.st[b].n_past), n_kv = pos + 1;
         __half * kc = op.kc + (size_t) b * op.kv_stream_stride + g * kHeadDim;
@@ -1063,11 +1074,13 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
             const float2 cs = __ldg(reinterpret_cast<const float2 *>(op.rope) + (size_t) pos * 64 + lane + 32 * j);
             rc[j] = cs.x; rs[j] = cs.y;
         }
-        warp_norm_rope_pre(k, wk, rc, rs, op.eps, op.k_norm_w != nullptr);
+        if (tail) {
+            warp_norm_rope_pre(k, wk, rc, rs, op.eps, op.k_norm_w != nullptr);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            kc[(size_t) pos * kvw + lane + 32 * j] = __float2half_rn(k[j]);
-            vc[(size_t) pos * kvw + lane + 32 * j] = __float2half_rn(v[j]);
+            for (int j = 0; j < 4; ++j) {
+                kc[(size_t) pos * kvw + lane + 32 * j] = __float2half_rn(k[j]);
+                vc[(size_t) pos * kvw + lane + 32 * j] = __float2half_rn(v[j]);
+            }
         }
         warp_norm_rope_pre(q0, wq, rc, rs, op.eps, op.q_norm_w != nullptr);
         warp_norm_rope_pre(q1, wq, rc, rs, op.eps, op.q_norm_w != nullptr);
@@ -1087,7 +1100,9 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
             for (int u = 0; u < 8; ++u) acc[r][u] = 0.f;
         }
         const __half * kb = kc + 8 * l16, * vb = vc + 8 * l16;
-        for (int jb = 0; jb < n_kv; jb += 16) {
+        const int per = ((n_kv + 15) / 16) / spl;                   // 16-key blocks of every warp but the last
+        const int jb0 = part * per * 16, jb1 = tail ? n_kv : (part + 1) * per * 16;
+        for (int jb = jb0; jb < jb1; jb += 16) {
             uint4 kv[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -1148,8 +1163,37 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
                 }
             }
         }
+        if (spl > 1) {
+            if (!tail) {
+                float * pw = pbuf + wib * (20 * 32) + lane;
+#pragma unroll
+                for (int r = 0; r < REP; ++r) {
+                    pw[(r * 10 + 0) * 32] = m[r]; pw[(r * 10 + 1) * 32] = l[r];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) pw[(r * 10 + 2 + u) * 32] = acc[r][u];
+                }
+            }
+            asm volatile("bar.sync %0, %1;" :: "r"(1 + wib / spl), "r"(32 * spl) : "memory");
+            if (tail) {
+                for (int p = 0; p < spl - 1; ++p) {
+                    const float * pw = pbuf + (wib - (spl - 1) + p) * (20 * 32) + lane;
+#pragma unroll
+                    for (int r = 0; r < REP; ++r) {
+                        const float mp = pw[(r * 10 + 0) * 32], lp = pw[(r * 10 + 1) * 32];
+                        const float mn = fmaxf(m[r], mp);            // finite: the tail warp always has a block
+                        const float st = __expf(m[r] - mn), sp = __expf(mp - mn);     // an empty part has m = -inf -> 0
+                        l[r] = fmaf(l[r], st, lp * sp);
+                        m[r] = mn;
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) acc[r][u] = fmaf(acc[r][u], st, pw[(r * 10 + 2 + u) * 32] * sp);
+                    }
+                }
+            }
+            asm volatile("bar.sync %0, %1;" :: "r"(1 + wib / spl), "r"(32 * spl) : "memory");
+        }
 #pragma unroll
         for (int r = 0; r < REP; ++r) {
+            if (!tail) break;
             __half2 oh[4];
             const float inv = 1.0f / l[r];
 #pragma unroll

@@ -63,7 +63,10 @@ class BatchingServer:
         while self.queue and self.free:
             req_id, tokens, out, speaker, max_len, seed = self.queue.popleft()
             slot = self.free.pop()
-            if not self.engine.stream_begin(slot, tokens, speaker, max_len=max_len, seed=seed, **self.sampling):
+            # two-phase begin: the Talker prefill of everything admitted in this round is ONE batched pass, run by
+            # the next step_frames (engines without stream_prepare, e.g. the CPU test double, use stream_begin)
+            begin = getattr(self.engine, "stream_prepare", None) or self.engine.stream_begin
+            if not begin(slot, tokens, speaker, max_len=max_len, seed=seed, **self.sampling):
                 done.append(("ERR", req_id, self.engine.get_error()))
                 self.free.append(slot)
                 continue

@@ -93,7 +93,8 @@ def serve_sharded(engine, utterances: Sequence[dict], rank: int, world: int, cou
         wave = list(range(w0, min(w0 + engine.max_streams, hi)))
         for slot, u in enumerate(wave):
             utt = utterances[u]
-            if not engine.stream_begin(slot, utt["tokens"], utt.get("speaker"), max_len=max_len,
+            begin = getattr(engine, "stream_prepare", None) or engine.stream_begin    # batched prefill at the first step
+            if not begin(slot, utt["tokens"], utt.get("speaker"), max_len=max_len,
                                        seed=int(utt.get("seed", u)), **sampling):
                 raise RuntimeError(f"stream_begin(utterance {u}): {engine.get_error()}")
         parts = {u: [] for u in wave}
