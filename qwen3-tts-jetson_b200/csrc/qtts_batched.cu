@@ -20,6 +20,9 @@
 //   * sampling / embedding / frame end run per stream, distributed over CTAs.
 // Reference behaviour reproduced: src/tts_transformer.cpp:2416-2560 (frame loop), :2153-2340 (code
 // predictor), :1376-1512 (Talker step), :2417-2499 (CB0 post-processing and sampling).
+#ifndef QTTS_BAR_RED
+#define QTTS_BAR_RED 0
+#endif
 #include "qtts_bops.cuh"
 
 namespace qtts {
@@ -164,8 +167,13 @@ __device__ __forceinline__ void bgrid_barrier(BShared * S, unsigned int & epoch)
         const unsigned int target = epoch + gridDim.x;
         epoch = target;
         unsigned int * cnt = &S->run.bar->count;
+#if QTTS_BAR_RED
+        // release-reduction: no return value to wait for; cumulative over the CTA's writes ordered by the bar.sync above
+        asm volatile("red.release.gpu.global.add.u32 [%0], %1;" :: "l"(cnt), "r"(1u) : "memory");
+#else
         __threadfence();
         atomicAdd(cnt, 1u);
+#endif
         unsigned int v;
         do {
             asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
