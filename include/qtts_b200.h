@@ -43,9 +43,14 @@ enum { QTTS_F32 = 0, QTTS_F16 = 1, QTTS_BF16 = 2 };
 
 /* numerics modes (see DESIGN.md "Numerics"):
  *   REFERENCE: reproduces the rounding points of the reference's ggml-cpu execution, including
- *              the sequential F16 V-accumulator of its flash attention (ops.cpp:8108-8344);
+ *              the sequential F16 V-accumulator of its flash attention (ops.cpp:8108-8344), and
+ *              the reference's codebook-0 top-k threshold = scored_idx[top_k - 1] after
+ *              std::nth_element (src/tts_transformer.cpp:2464-2466): whichever member of the top-k
+ *              set libstdc++'s introselect leaves there, so fewer than top_k candidates may survive;
  *   FAST:      same rounding points for every projection, KV cache and Q, but the Talker's
- *              decode attention accumulates P.V in FP32 with a parallel split-KV reduction. */
+ *              decode attention accumulates P.V in FP32 with a parallel split-KV reduction, and the
+ *              codebook-0 threshold is the exact top_k-th largest logit (what the reference's
+ *              code-predictor sampler does with std::partial_sort, :2211-2218). */
 enum { QTTS_NUMERICS_REFERENCE = 0, QTTS_NUMERICS_FAST = 1 };
 
 /* ---- life cycle ------------------------------------------------------------------------- */
@@ -99,9 +104,22 @@ int qtts_build_prefill(qtts_engine * e, int slot, const int32_t * text_tokens, i
                        float * prefill_out, float * trailing_out, float * pad_out);
 
 /* forward_prefill (src/tts_transformer.cpp:1829-1920): n_tokens rows of embeddings at
- * positions n_past.. ; hidden_out [H] = normalised hidden of the LAST token, logits_out [V]. */
+ * positions n_past.. ; hidden_out [n_tokens*H] = normalised hidden of EVERY token like the
+ * reference's `output` (:1893; the last row is what feeds the code predictor), logits_out [V] =
+ * logits of the last token.  Either may be NULL. */
 int qtts_forward_prefill(qtts_engine * e, int slot, const float * embd, int32_t n_tokens,
                          int32_t n_past, float * hidden_out, float * logits_out);
+
+/* forward_text (src/tts_transformer.cpp:1922-1950): project_text_tokens (+ speaker_embd on every row, may
+ * be NULL) then forward_prefill; hidden_out [n_tokens*H]. */
+int qtts_forward_text(qtts_engine * e, int slot, const int32_t * text_tokens, int32_t n_tokens,
+                      const float * speaker_embd, int32_t n_past, float * hidden_out);
+/* forward_codec (src/tts_transformer.cpp:2030-2040): codec_embd row of one token -> forward_step. */
+int qtts_forward_codec(qtts_engine * e, int slot, int32_t codec_token, int32_t n_past, float * logits_out);
+
+/* get_hidden_states (src/tts_transformer.cpp:2042-2048): normalised hidden [H] of the last forward call of `slot`
+ * (last_hidden_, what predict_codes_autoregressive is fed). */
+int qtts_get_hidden_states(qtts_engine * e, int slot, float * hidden_out);
 
 /* forward_step (src/tts_transformer.cpp:1952-2028). */
 int qtts_forward_step(qtts_engine * e, int slot, const float * step_embd, int32_t n_past,
@@ -154,6 +172,33 @@ int qtts_prefill_pending(qtts_engine * e);
  * active[slot] = 1 while the stream has neither hit EOS nor max_len. */
 int qtts_step_frames(qtts_engine * e, int32_t n_frames, int32_t * codes_out,
                      int32_t * produced, int32_t * active);
+
+/* Parity hooks for a stream begun / prepared but not yet stepped (all arrays are host memory, copied):
+ *   forced_codes [n_forced][n_codebooks]: teacher forcing - in frames [0, n_forced) the codes fed back (code-predictor
+ *     inputs, next Talker input, repetition-penalty set) are these, while the codes the engine emits stay its own choice;
+ *     an own EOS inside the forced range does not end the stream.
+ *   uniforms [n_uniform][n_codebooks]: the uniform in [0,1) each sampled code consumes ([f][0] codebook 0, [f][c] code
+ *     c) instead of the engine's counter-based generator - TRTCodePredictor::run_sampling_loop's rand_vals
+ *     (src/trt_code_predictor.cpp:602-726, src/tts_transformer.cpp:2663-2665) extended to codebook 0.
+ * Either pointer may be NULL.  n_* <= max_ctx. */
+int qtts_stream_force(qtts_engine * e, int slot, const int32_t * forced_codes, int32_t n_forced,
+                      const float * uniforms, int32_t n_uniform);
+/* Codebook-0 post-processing + sampling of ONE frame on caller-supplied raw Talker logits [V]
+ * (src/tts_transformer.cpp:2417-2499, the block generate() runs inline): seen_tokens = the distinct
+ * codebook-0 tokens emitted so far, u = the uniform draw (ignored for temperature <= 0).
+ * token_out = chosen id (codec_eos_id = stop); processed_out (may be NULL) [V] = logits after
+ * suppress / repetition penalty / EOS ramp.  Uses the engine's numerics mode for the top-k threshold. */
+int qtts_sample_cb0(qtts_engine * e, int slot, const float * raw_logits, int32_t frame, int32_t n_text_tokens,
+                    const int32_t * seen_tokens, int32_t n_seen, float repetition_penalty, float temperature,
+                    int32_t top_k, float u, int32_t * token_out, float * processed_out);
+/* debug switches: bit 0 = the batch-1 frame kernel also keeps the 15 code-predictor logit vectors of the last frame
+ * (qtts_stream_logits; the batched kernel always does). */
+int qtts_set_debug(qtts_engine * e, int flags);
+/* KV capacity per stream without touching the weights (init_kv_cache, src/tts_transformer.cpp:794-842, which the
+ * reference calls from generate() whenever prefill_len + max_len + 8 outgrows the cache, :2383-2388).  max_text =
+ * longest utterance in text tokens (trailing-row capacity; <= 0 keeps the current one).  Streams in flight are
+ * dropped.  n_ctx is capped at 4608 KV slots per stream (the attention scratch; the reference has no cap). */
+int qtts_resize_kv(qtts_engine * e, int32_t n_ctx, int32_t max_text);
 
 /* 1 (default): qtts_step_frames advances all active streams in lock step with the batched tcgen05
  * kernel (groups of <= 256 slots, env QTTS_BGROUP lowers it); 0: the batch-1 kernel, one stream after another. */

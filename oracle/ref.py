@@ -46,8 +46,30 @@ def _load():
     lib.ref_predict_codes_logits.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_void_p, _i32p, _f32p]
     lib.ref_generate.argtypes = [C.c_void_p, _i32p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float,
                                  C.c_float, C.c_int, _i32p, C.POINTER(C.c_double)]
+    lib.ref_seed_rng.argtypes = [C.c_void_p, C.c_uint32]
+    lib.ref_sample_cb0.argtypes = [_f32p, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, C.POINTER(C.c_int)]
+    lib.ref_generate_trace.argtypes = [C.c_void_p, _i32p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float,
+                                       C.c_int] + [C.c_void_p] * 7 + [C.POINTER(C.c_int)]
+    lib.ref_nth_check.argtypes = [_f32p, C.c_int, C.c_int, _i32p, _i32p]
     _lib = lib
     return lib
+
+
+def nth_check(vals, k: int):
+    """(std::nth_element's arrangement, csrc/qtts_nth.cuh's arrangement) of the ids 0..n-1 by descending value."""
+    v = np.ascontiguousarray(vals, dtype=np.float32)
+    a = np.zeros(v.shape[0], np.int32); b = np.zeros(v.shape[0], np.int32)
+    _load().ref_nth_check(v, v.shape[0], int(k), a, b)
+    return a, b
+
+
+def sample_cb0(processed_logits, eos_id: int, temperature: float, top_k: int, u: float):
+    """src/tts_transformer.cpp:2451-2494 with the reference's own libstdc++ calls (std::nth_element
+    threshold included) on post-processed codebook-0 logits.  Returns (token, candidates kept)."""
+    lg = np.ascontiguousarray(processed_logits, dtype=np.float32)
+    kept = C.c_int()
+    tok = _load().ref_sample_cb0(lg, lg.shape[0], int(eos_id), float(temperature), int(top_k), float(u), C.byref(kept))
+    return int(tok), int(kept.value)
 
 
 class Reference:
@@ -135,6 +157,33 @@ class Reference:
         if not self.lib.ref_predict_codes_logits(self.h, hidden, int(cb0), self._opt(f), out, logits):
             raise RuntimeError(self.error())
         return out, logits
+
+    def seed_rng(self, seed: int):
+        """Re-seed the reference's sampler (it seeds from std::random_device otherwise)."""
+        self.lib.ref_seed_rng(self.h, int(seed) & 0xffffffff)
+
+    def generate_trace(self, tokens, speaker=None, max_len=64, language_id=2050, rep_pen=1.05,
+                       temperature=0.0, top_k=50):
+        """generate() replayed through the reference's own methods with per-frame dumps
+        (oracle/ref_harness.cpp:ref_generate_trace).  Returns a dict; rows = frames (+1 if EOS ended it)."""
+        tokens = np.ascontiguousarray(tokens, dtype=np.int32)
+        spk = None if speaker is None else np.ascontiguousarray(speaker, dtype=np.float32)
+        H, V, rows = self.cfg["hidden"], self.cfg["codec_vocab"], max_len + 1
+        raw = np.zeros((rows, V), np.float32); proc = np.zeros((rows, V), np.float32)
+        hid = np.zeros((rows, H), np.float32); emb = np.zeros((rows, H), np.float32)
+        u0 = np.zeros(rows, np.float32); ucp = np.zeros((rows, 15), np.float64)
+        codes = np.zeros((rows, 16), np.int32)
+        eos = C.c_int()
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        n = self.lib.ref_generate_trace(self.h, tokens, len(tokens), self._opt(spk), max_len, language_id, rep_pen,
+                                        temperature, top_k, p(raw), p(proc), p(hid), p(emb), p(u0), p(ucp), p(codes),
+                                        C.byref(eos))
+        if n < 0:
+            raise RuntimeError(self.error() or "ref_generate_trace failed")
+        r = n + (1 if eos.value >= 0 else 0)
+        return {"n_frames": n, "eos_frame": eos.value, "raw": raw[:r].copy(), "proc": proc[:r].copy(),
+                "hidden": hid[:n].copy(), "step_embd": emb[:max(n - 1, 0)].copy(), "u_cb0": u0[:r].copy(),
+                "u_cp": ucp[:n].copy(), "codes": codes[:n].copy()}
 
     def generate(self, tokens, speaker=None, max_len=4096, language_id=2050, rep_pen=1.05,
                  temperature=0.0, top_k=50):

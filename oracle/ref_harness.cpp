@@ -35,6 +35,10 @@
 #undef private
 #include "text_tokenizer.h"
 
+// the product's restatement of libstdc++'s introselect (header-only, host + device), checked below
+// against std::nth_element itself
+#include "../qwen3-tts-jetson_b200/csrc/qtts_nth.cuh"
+
 using qwen3_tts::TTSTransformer;
 
 namespace {
@@ -238,6 +242,148 @@ int ref_generate(void * h, const int32_t * tokens, int n_tokens, const float * s
     if (ms_out) ms_out[0] = t1 - t0;
     memcpy(codes_out, out.data(), out.size() * sizeof(int32_t));
     return (int) (out.size() / r->tts.get_config().n_codebooks);
+}
+
+// ---- sampled runs made reproducible -------------------------------------------------------
+// The reference seeds its sampler from std::random_device (src/tts_transformer.h:298), so its
+// sampled streams differ from run to run.  The harness re-seeds that very member (private,
+// reached through the re-declaration above), which changes nothing else of the reference.
+void ref_seed_rng(void * h, uint32_t seed) {
+    static_cast<RefHandle *>(h)->tts.rng_.seed(seed);
+}
+
+// Codebook-0 sampling on already post-processed logits: a line-by-line restatement of
+// src/tts_transformer.cpp:2451-2494 with the SAME libstdc++ calls (std::nth_element on an index
+// vector with the value comparator, std::max_element, expf, double sum, float CDF scan), so the
+// threshold it picks is the one the reference picks for these logits: scored_idx[top_k - 1] after
+// nth_element(begin, begin + top_k, end) is SOME member of the top-k set, not necessarily the
+// k-th largest.  `u` stands for the reference's uniform_real_distribution<float> draw.
+// kept_out (may be null) receives the number of candidates that survived the mask.
+int ref_sample_cb0(const float * processed, int vocab, int eos_id, float temperature, int top_k,
+                   float u, int * kept_out) {
+    std::vector<float> logits(processed, processed + vocab), probs(vocab), scored_vals(vocab);
+    std::vector<int32_t> scored_idx(vocab);
+    for (int32_t i = 0; i < vocab; ++i) logits[i] /= temperature;
+    float eos_logit = logits[eos_id];
+    if (top_k > 0 && top_k < vocab) {
+        for (int32_t i = 0; i < vocab; ++i) { scored_vals[i] = logits[i]; scored_idx[i] = i; }
+        std::nth_element(scored_idx.begin(), scored_idx.begin() + top_k, scored_idx.end(),
+            [&](int32_t a, int32_t b) { return scored_vals[a] > scored_vals[b]; });
+        float threshold = scored_vals[scored_idx[top_k - 1]];
+        for (int32_t i = 0; i < vocab; ++i) if (logits[i] < threshold) logits[i] = -INFINITY;
+    }
+    logits[eos_id] = eos_logit;
+    if (kept_out) { int k = 0; for (int32_t i = 0; i < vocab; ++i) k += std::isfinite(logits[i]) ? 1 : 0; *kept_out = k; }
+    float max_logit = *std::max_element(logits.data(), logits.data() + vocab);
+    double sum = 0.0;
+    for (int32_t i = 0; i < vocab; ++i) { probs[i] = expf(logits[i] - max_logit); sum += probs[i]; }
+    for (int32_t i = 0; i < vocab; ++i) probs[i] = (float) (probs[i] / sum);
+    float cumsum = 0.0f;
+    int32_t next_token = vocab - 1;
+    for (int32_t i = 0; i < vocab; ++i) { cumsum += probs[i]; if (cumsum >= u) { next_token = i; break; } }
+    return next_token;
+}
+
+// std::nth_element as the reference calls it (index vector, value-descending comparator,
+// src/tts_transformer.cpp:2458-2465) next to the product's restatement (csrc/qtts_nth.cuh) on the
+// same values: both index arrays are returned so the test can require them to be IDENTICAL.
+void ref_nth_check(const float * vals, int n, int k, int32_t * idx_std, int32_t * idx_ours) {
+    std::vector<int32_t> a(n);
+    for (int i = 0; i < n; ++i) { a[i] = i; idx_ours[i] = i; }
+    std::nth_element(a.begin(), a.begin() + k, a.end(), [&](int32_t x, int32_t y) { return vals[x] > vals[y]; });
+    memcpy(idx_std, a.data(), n * sizeof(int32_t));
+    qtts::nth::nth_element_desc(idx_ours, k, n, vals);
+}
+
+// generate() replayed frame by frame through the reference's OWN methods (forward_prefill,
+// predict_codes_autoregressive, lookup_single_embedding_row, forward_step, rng_) with the inline
+// codebook-0 block of src/tts_transformer.cpp:2417-2499 restated between them, so that the
+// per-frame intermediates the real generate() never exposes can be dumped.  The caller checks the
+// codes against ref_generate() on the same inputs (and seed): equal codes = faithful replay.
+//   raw_out       [rows][V]   Talker logits as forward_prefill / forward_step returned them
+//   proc_out      [rows][V]   after suppress / repetition penalty / EOS ramp (before temperature)
+//   hidden_out    [rows][H]   last_hidden_ handed to the code predictor
+//   step_embd_out [rows][H]   next Talker input assembled after the frame (:2529-2553)
+//   u_cb0_out     [rows]      the uniform_real_distribution<float> draw of the frame (temperature > 0)
+//   u_cp_out      [rows][15]  the generate_canonical<double,53> draws std::discrete_distribution
+//                             consumes for the frame's 15 codes (taken from a COPY of rng_ before the call)
+//   codes_out     [rows][16]
+// rows = frames produced (+1 when the loop ended by EOS: that frame's raw / proc / u_cb0 are
+// filled too, *eos_frame_out = its index, else -1).  Any output pointer may be null.  Returns the
+// number of frames produced, or -1.
+int ref_generate_trace(void * h, const int32_t * tokens, int n_tokens, const float * speaker, int max_len,
+                       int language_id, float rep_pen, float temperature, int top_k,
+                       float * raw_out, float * proc_out, float * hidden_out, float * step_embd_out,
+                       float * u_cb0_out, double * u_cp_out, int32_t * codes_out, int * eos_frame_out) {
+    auto * r = static_cast<RefHandle *>(h);
+    auto & t = r->tts;
+    const auto & cfg = t.get_config();
+    const int H = cfg.hidden_size, V = cfg.codec_vocab_size, NB = cfg.n_codebooks;
+    if (eos_frame_out) *eos_frame_out = -1;
+    if (n_tokens < 4 || max_len <= 0) return -1;
+    std::vector<float> prefill, trailing, pad;
+    if (!t.build_prefill_graph(tokens, n_tokens, speaker, language_id, prefill, trailing, pad)) return -1;
+    const int prefill_len = (int) (prefill.size() / H), trailing_len = (int) (trailing.size() / H);
+    const int required_ctx = prefill_len + max_len + 8;
+    if (t.state_.cache.n_ctx < required_ctx || t.state_.cache.n_ctx > std::max<int32_t>(required_ctx * 2, 512))
+        if (!t.init_kv_cache(required_ctx)) return -1;
+    t.clear_kv_cache();
+    std::vector<float> hidden_all, logits;
+    if (!t.forward_prefill(prefill.data(), prefill_len, 0, hidden_all, &logits)) return -1;
+    int n_past = prefill_len, produced = 0;
+    std::unordered_set<int32_t> seen;
+    std::vector<float> step_embd(H), row(H);
+    std::vector<int32_t> codes;
+    for (int frame = 0; frame < max_len; ++frame) {
+        if (raw_out) memcpy(raw_out + (size_t) frame * V, logits.data(), V * sizeof(float));
+        for (int32_t i = V - 1024; i < V; ++i) if (i != cfg.codec_eos_id) logits[i] = -INFINITY;
+        if (rep_pen != 1.0f)
+            for (int32_t tok : seen) { if (logits[tok] > 0.0f) logits[tok] /= rep_pen; else logits[tok] *= rep_pen; }
+        const int32_t expected = std::max(20, n_tokens * 4);
+        if (frame >= expected) {
+            float ramp = std::min(1.0f, (float) (frame - expected) / (float) expected);
+            float max_lg = *std::max_element(logits.data(), logits.data() + V);
+            float target = max_lg + 5.0f;
+            logits[cfg.codec_eos_id] += ramp * (target - logits[cfg.codec_eos_id]);
+        }
+        if (proc_out) memcpy(proc_out + (size_t) frame * V, logits.data(), V * sizeof(float));
+        int32_t next;
+        if (temperature <= 0.0f) {
+            next = 0;
+            for (int32_t i = 1; i < V; ++i) if (logits[i] > logits[next]) next = i;
+        } else {
+            std::uniform_real_distribution<float> udist(0.0f, 1.0f);
+            const float u = udist(t.rng_);
+            if (u_cb0_out) u_cb0_out[frame] = u;
+            next = ref_sample_cb0(logits.data(), V, cfg.codec_eos_id, temperature, top_k, u, nullptr);
+        }
+        if (next == cfg.codec_eos_id) { if (eos_frame_out) *eos_frame_out = frame; break; }
+        seen.insert(next);
+        if (hidden_out) memcpy(hidden_out + (size_t) frame * H, t.last_hidden_.data(), H * sizeof(float));
+        if (u_cp_out && temperature > 0.0f) {
+            std::mt19937 peek = t.rng_;
+            for (int s = 0; s < 15; ++s) u_cp_out[(size_t) frame * 15 + s] = std::generate_canonical<double, 53>(peek);
+        }
+        if (!t.predict_codes_autoregressive(t.last_hidden_.data(), next, codes, temperature, top_k)) return -1;
+        if (codes_out) {
+            codes_out[(size_t) frame * NB] = next;
+            for (int cb = 1; cb < NB; ++cb) codes_out[(size_t) frame * NB + cb] = codes[cb - 1];
+        }
+        produced = frame + 1;
+        if (frame + 1 >= max_len) break;
+        if (!t.lookup_single_embedding_row(t.model_.codec_embd, next, row.data())) return -1;
+        for (int i = 0; i < H; ++i) step_embd[i] = row[i];
+        for (int cb = 1; cb < NB; ++cb) {
+            if (!t.lookup_single_embedding_row(t.model_.code_pred_embd[cb - 1], codes[cb - 1], row.data())) return -1;
+            for (int i = 0; i < H; ++i) step_embd[i] += row[i];
+        }
+        const float * tr = (frame < trailing_len) ? trailing.data() + (size_t) frame * H : pad.data();
+        for (int i = 0; i < H; ++i) step_embd[i] += tr[i];
+        if (step_embd_out) memcpy(step_embd_out + (size_t) frame * H, step_embd.data(), H * sizeof(float));
+        if (!t.forward_step(step_embd.data(), n_past, logits)) return -1;
+        n_past++;
+    }
+    return produced;
 }
 
 }  // extern "C"

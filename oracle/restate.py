@@ -426,7 +426,10 @@ def cb0_postprocess(logits, seen, frame, n_text_tokens, rep_pen, eos_id, vocab):
     if frame >= expected:
         ramp = min(F32(1.0), F32(frame - expected) / F32(expected))
         target = F32(lg.max() + F32(5.0))
-        lg[eos_id] = F32(lg[eos_id] + F32(ramp) * F32(target - lg[eos_id]))
+        # `logits[eos] += ramp * (target - logits[eos])`: GCC contracts this into one FMA wherever the ISA has it
+        # (-ffp-contract=fast is its default; the reference builds with -march=native, the oracle with -mfma), so the
+        # product is not rounded.  float32 x float32 is exact in float64; the sum is rounded once.
+        lg[eos_id] = F32(np.float64(F32(ramp)) * np.float64(F32(target - lg[eos_id])) + np.float64(lg[eos_id]))
     return lg
 
 

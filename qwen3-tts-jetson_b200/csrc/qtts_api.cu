@@ -82,6 +82,7 @@ void qtts_destroy(qtts_engine * h) {
     cudaSetDevice(e->device);
     cudaStreamSynchronize(e->stream);
     for (void * p : e->allocs) cudaFree(p);
+    for (void * p : e->stream_allocs) cudaFree(p);
     for (auto & kv : e->tensors) if (kv.second.raw) cudaFree(kv.second.raw);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
@@ -170,13 +171,24 @@ int qtts_build_prefill(qtts_engine * h, int slot, const int32_t * tokens, int32_
 
 // prefill over rows already resident in s.prefill (token by token; identical arithmetic to the
 // reference's causal prefill graph because every K/V it attends to is the F16 cache copy)
-static bool do_forward_prefill(Engine * e, Slot & s, int n_tokens, int n_past) {
-    if (n_tokens <= 0 || n_tokens > 64) return e->fail("forward_prefill: n_tokens must be in 1..64");
-    if (n_past + n_tokens > e->max_ctx) return e->fail("forward_prefill: KV cache too small");
+static bool do_forward_prefill(Engine * e, Slot & s, int n_tokens, int n_past, bool all_hidden = false) {
+    if (n_tokens <= 0) return e->fail("n_tokens must be > 0");                       // src/tts_transformer.cpp:1840-1843
+    if (n_tokens > 64) return e->fail("forward_prefill: at most 64 tokens per call");
+    if (n_past < 0) return e->fail("forward_prefill: n_past must be >= 0");
+    if (n_past + n_tokens > e->max_ctx) return e->fail("Context length exceeded");   // :1852-1855
     std::vector<Op> P;
     const size_t H = e->cfg.hidden_size;
-    for (int t = 0; t < n_tokens; ++t)
-        emit_talker_step(e, s, P, IN_VEC, s.prefill + t * H, false, n_past + t, ATTN_SOFTMAX_P16, t == n_tokens - 1, false);
+    if (all_hidden && !s.prefill_hidden) {
+        s.prefill_hidden = e->dalloc<float>((size_t) 64 * H);
+        if (!s.prefill_hidden) return e->fail("out of device memory for the prefill hidden rows");
+    }
+    for (int t = 0; t < n_tokens; ++t) {
+        // the reference returns the normalised hidden of EVERY row (:1893): with all_hidden the head stage (whose
+        // prologue is the output norm) runs for every token and leaves its row in prefill_hidden
+        const bool head = all_hidden || t == n_tokens - 1;
+        emit_talker_step(e, s, P, IN_VEC, s.prefill + t * H, false, n_past + t, ATTN_SOFTMAX_P16, head, false);
+        if (all_hidden && t < n_tokens - 1) P.back().hid_out = s.prefill_hidden + t * H;
+    }
     if (!run_program(e, s, P, 1, false)) return false;
     const int np = n_past + n_tokens;
     QTTS_CUDA(cudaMemcpyAsync(&s.st->n_past, &np, sizeof(int), cudaMemcpyHostToDevice, e->stream));
@@ -190,11 +202,16 @@ int qtts_forward_prefill(qtts_engine * h, int slot, const float * embd, int32_t 
     Slot * s = get_slot(e, slot);
     if (!s) return 0;
     cudaSetDevice(e->device);
-    if (n_tokens <= 0 || n_tokens > 64) { e->err = "forward_prefill: n_tokens must be in 1..64"; return 0; }
+    if (!embd) { e->err = "prefill_embd is null"; return 0; }
+    if (n_tokens <= 0) { e->err = "n_tokens must be > 0"; return 0; }
+    if (n_tokens > 64) { e->err = "forward_prefill: at most 64 tokens per call"; return 0; }
     const size_t H = e->cfg.hidden_size;
     if (cudaMemcpyAsync(s->prefill, embd, n_tokens * H * sizeof(float), cudaMemcpyHostToDevice, e->stream) != cudaSuccess) { e->err = "H2D failed"; return 0; }
-    if (!do_forward_prefill(e, *s, n_tokens, n_past)) return 0;
-    if (hidden_out) cudaMemcpy(hidden_out, s->hidden, H * sizeof(float), cudaMemcpyDeviceToHost);
+    if (!do_forward_prefill(e, *s, n_tokens, n_past, hidden_out != nullptr && n_tokens > 1)) return 0;
+    if (hidden_out) {
+        if (n_tokens > 1) cudaMemcpy(hidden_out, s->prefill_hidden, (size_t) (n_tokens - 1) * H * sizeof(float), cudaMemcpyDeviceToHost);
+        cudaMemcpy(hidden_out + (size_t) (n_tokens - 1) * H, s->hidden, H * sizeof(float), cudaMemcpyDeviceToHost);
+    }
     if (logits_out) cudaMemcpy(logits_out, s->logits, e->cfg.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
     cudaError_t r = cudaGetLastError();
     if (r != cudaSuccess) { e->err = std::string("forward_prefill: ") + cudaGetErrorString(r); return 0; }
@@ -206,7 +223,9 @@ int qtts_forward_step(qtts_engine * h, int slot, const float * step_embd, int32_
     Slot * s = get_slot(e, slot);
     if (!s) return 0;
     cudaSetDevice(e->device);
-    if (n_past + 1 > e->max_ctx) { e->err = "forward_step: KV cache too small"; return 0; }
+    if (!step_embd) { e->err = "step_embd is null"; return 0; }
+    if (n_past < 0) { e->err = "forward_step: n_past must be >= 0"; return 0; }
+    if (n_past + 1 > e->max_ctx) { e->err = "Context length exceeded"; return 0; }       // src/tts_transformer.cpp:1972-1975
     const size_t H = e->cfg.hidden_size;
     if (cudaMemcpyAsync(s->in_embd, step_embd, H * sizeof(float), cudaMemcpyHostToDevice, e->stream) != cudaSuccess) { e->err = "H2D failed"; return 0; }
     std::vector<Op> P;
@@ -219,6 +238,85 @@ int qtts_forward_step(qtts_engine * h, int slot, const float * step_embd, int32_
     if (r != cudaSuccess) { e->err = std::string("forward_step: ") + cudaGetErrorString(r); return 0; }
     if (logits_out) cudaMemcpy(logits_out, s->logits, e->cfg.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
     if (hidden_out) cudaMemcpy(hidden_out, s->hidden, H * sizeof(float), cudaMemcpyDeviceToHost);
+    return 1;
+}
+
+// forward_text (src/tts_transformer.cpp:1922-1950): rows of the folded text-projection table (project_text_tokens,
+// :1026-1091) + the speaker row, then the prefill pass
+int qtts_forward_text(qtts_engine * h, int slot, const int32_t * tokens, int32_t n_tokens, const float * speaker,
+                      int32_t n_past, float * hidden_out) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    if (!tokens) { e->err = "text_tokens is null"; return 0; }
+    if (n_tokens <= 0) { e->err = "n_tokens must be > 0"; return 0; }
+    if (n_tokens > 64) { e->err = "forward_text: at most 64 tokens per call"; return 0; }
+    const qtts_config & c = e->cfg;
+    const size_t H = c.hidden_size;
+    for (int i = 0; i < n_tokens; ++i)
+        if (tokens[i] < 0 || tokens[i] >= c.text_vocab_size) { e->err = "text token id out of range"; return 0; }
+    if (cudaMemcpyAsync(s->tokens, tokens, n_tokens * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream) != cudaSuccess) { e->err = "H2D failed"; return 0; }
+    if (speaker) cudaMemcpyAsync(s->speaker, speaker, H * sizeof(float), cudaMemcpyHostToDevice, e->stream);
+    cudaStreamSynchronize(e->stream);
+    std::vector<Op> P;
+    for (int t = 0; t < n_tokens; ++t) {
+        float * dst = s->prefill + (size_t) t * H;
+        if (e->text_tab) {
+            // row of the F32 table selected on the host (ids were validated above) + the speaker row
+            Op o;
+            memset(&o, 0, sizeof(o));
+            o.type = OP_COPY; o.tok_slot = -1; o.n_tok = 1; o.temperature_override = -1e30f;
+            o.out = dst; o.n = (int) H;
+            o.a = e->text_tab + (size_t) tokens[t] * H; o.b = speaker ? s->speaker : nullptr;
+            P.push_back(o);
+        } else {
+            e->err = "forward_text needs the folded text table (QTTS_FOLD_TEXT=0 disables it)"; return 0;
+        }
+    }
+    if (!run_program(e, *s, P, 1, false)) return 0;
+    if (!do_forward_prefill(e, *s, n_tokens, n_past, hidden_out != nullptr && n_tokens > 1)) return 0;
+    if (hidden_out) {
+        if (n_tokens > 1) cudaMemcpy(hidden_out, s->prefill_hidden, (size_t) (n_tokens - 1) * H * sizeof(float), cudaMemcpyDeviceToHost);
+        cudaMemcpy(hidden_out + (size_t) (n_tokens - 1) * H, s->hidden, H * sizeof(float), cudaMemcpyDeviceToHost);
+    }
+    cudaError_t r = cudaGetLastError();
+    if (r != cudaSuccess) { e->err = std::string("forward_text: ") + cudaGetErrorString(r); return 0; }
+    return 1;
+}
+
+int qtts_get_hidden_states(qtts_engine * h, int slot, float * hidden_out) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s || !hidden_out) return 0;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    if (cudaMemcpy(hidden_out, s->hidden, e->cfg.hidden_size * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess) { e->err = "get_hidden_states: copy failed"; return 0; }
+    return 1;
+}
+
+// forward_codec (src/tts_transformer.cpp:2030-2040)
+int qtts_forward_codec(qtts_engine * h, int slot, int32_t codec_token, int32_t n_past, float * logits_out) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    const qtts_config & c = e->cfg;
+    if (codec_token < 0 || codec_token >= c.codec_vocab_size) { e->err = "forward_codec: token out of range"; return 0; }
+    if (n_past < 0) { e->err = "forward_codec: n_past must be >= 0"; return 0; }
+    if (n_past + 1 > e->max_ctx) { e->err = "Context length exceeded"; return 0; }
+    cudaMemcpyAsync(&s->tokens[0], &codec_token, sizeof(int32_t), cudaMemcpyHostToDevice, e->stream);
+    cudaStreamSynchronize(e->stream);
+    std::vector<Op> P;
+    const int mode = (e->numerics == QTTS_NUMERICS_REFERENCE) ? ATTN_FLASH_F16SEQ : ATTN_FAST;
+    emit_talker_step(e, *s, P, IN_EMBED_ROW, nullptr, false, n_past, mode, true, false);
+    P[0].table = e->codec_embd; P[0].tok_ptr = s->tokens; P[0].tok_slot = -1;
+    if (!run_program(e, *s, P, 1, false)) return 0;
+    const int np = n_past + 1;
+    cudaMemcpyAsync(&s->st->n_past, &np, sizeof(int), cudaMemcpyHostToDevice, e->stream);
+    cudaError_t r = cudaStreamSynchronize(e->stream);
+    if (r != cudaSuccess) { e->err = std::string("forward_codec: ") + cudaGetErrorString(r); return 0; }
+    if (logits_out) cudaMemcpy(logits_out, s->logits, c.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
     return 1;
 }
 
@@ -255,6 +353,15 @@ static bool stream_prepare(Engine * e, Slot & s, const int32_t * tokens, int32_t
     if (!tokens) return e->fail("text_tokens is null");
     if (n < 4) return e->fail("Need at least 4 text tokens for generation");
     s.active = false; s.pending = false;
+    if (max_len <= 0) {
+        // generate() returns an empty output for max_len <= 0 (src/tts_transformer.cpp:2364-2367): the stream is born done
+        StreamState st{};
+        st.done = 1;
+        QTTS_CUDA(cudaMemcpyAsync(s.st, &st, sizeof(st), cudaMemcpyHostToDevice, e->stream));
+        QTTS_CUDA(cudaStreamSynchronize(e->stream));
+        s.prefill_len = 0;
+        return true;
+    }
     if (!do_build_prefill(e, s, tokens, n, speaker, language_id)) return false;
     // required context as in the reference (src/tts_transformer.cpp:2383)
     if (s.prefill_len + max_len + 8 > e->max_ctx) return e->fail("max_len does not fit the engine's max_ctx");
@@ -262,6 +369,7 @@ static bool stream_prepare(Engine * e, Slot & s, const int32_t * tokens, int32_t
     st.max_len = max_len; st.n_text_tokens = n; st.trailing_len = s.trailing_len;
     st.top_k = top_k; st.rep_pen = rep_pen; st.temperature = temperature; st.seed = seed;
     st.ignore_eos = e->ignore_eos;
+    st.sample_mode = (e->numerics == QTTS_NUMERICS_REFERENCE) ? 1 : 0;
     QTTS_CUDA(cudaMemcpyAsync(s.st, &st, sizeof(st), cudaMemcpyHostToDevice, e->stream));
     QTTS_CUDA(cudaStreamSynchronize(e->stream));
     return true;
@@ -270,6 +378,7 @@ static bool stream_prepare(Engine * e, Slot & s, const int32_t * tokens, int32_t
 static bool stream_begin(Engine * e, Slot & s, const int32_t * tokens, int32_t n, const float * speaker, int32_t max_len,
                          int32_t language_id, float rep_pen, float temperature, int32_t top_k, uint64_t seed) {
     if (!stream_prepare(e, s, tokens, n, speaker, max_len, language_id, rep_pen, temperature, top_k, seed)) return false;
+    if (max_len <= 0) return true;
     if (!do_forward_prefill(e, s, s.prefill_len, 0)) return false;
     s.active = true;
     return true;
@@ -368,7 +477,7 @@ int qtts_stream_prepare(qtts_engine * h, int slot, const int32_t * tokens, int32
     if (!s) return 0;
     cudaSetDevice(e->device);
     if (!stream_prepare(e, *s, tokens, n, speaker, max_len, language_id, rep_pen, temperature, top_k, seed)) return 0;
-    s->pending = true;
+    s->pending = max_len > 0;
     return 1;
 }
 
@@ -435,6 +544,88 @@ int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int
     return 1;
 }
 
+int qtts_stream_force(qtts_engine * h, int slot, const int32_t * forced, int32_t n_forced, const float * uniforms, int32_t n_uniform) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    if (!s->active && !s->pending) { e->err = "stream_force: the stream has not been begun / prepared"; return 0; }
+    const int nb = e->cfg.n_codebooks;
+    if (n_forced < 0 || n_uniform < 0 || n_forced > e->max_ctx || n_uniform > e->max_ctx) { e->err = "stream_force: frame count out of range"; return 0; }
+    if (forced && n_forced > 0) {
+        for (int i = 0; i < n_forced * nb; ++i) {
+            const int lim = (i % nb == 0) ? e->cfg.codec_vocab_size : e->cfg.cp_vocab_size;
+            if (forced[i] < 0 || forced[i] >= lim) { e->err = "stream_force: code out of range"; return 0; }
+        }
+        if (!s->force_codes) s->force_codes = e->dalloc<int32_t>((size_t) e->max_ctx * nb);
+        if (!s->force_codes) { e->err = "out of device memory for the forced codes"; return 0; }
+        cudaMemcpyAsync(s->force_codes, forced, (size_t) n_forced * nb * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream);
+    }
+    if (uniforms && n_uniform > 0) {
+        if (!s->force_u) s->force_u = e->dalloc<float>((size_t) e->max_ctx * nb);
+        if (!s->force_u) { e->err = "out of device memory for the uniforms"; return 0; }
+        cudaMemcpyAsync(s->force_u, uniforms, (size_t) n_uniform * nb * sizeof(float), cudaMemcpyHostToDevice, e->stream);
+    }
+    StreamState hs;
+    cudaMemcpyAsync(&hs, s->st, sizeof(hs), cudaMemcpyDeviceToHost, e->stream);
+    cudaStreamSynchronize(e->stream);
+    hs.forced = (forced && n_forced > 0) ? s->force_codes : nullptr; hs.forced_frames = hs.forced ? n_forced : 0;
+    hs.uniforms = (uniforms && n_uniform > 0) ? s->force_u : nullptr; hs.uniform_frames = hs.uniforms ? n_uniform : 0;
+    cudaMemcpyAsync(s->st, &hs, sizeof(hs), cudaMemcpyHostToDevice, e->stream);
+    if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("stream_force: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
+    return 1;
+}
+
+int qtts_sample_cb0(qtts_engine * h, int slot, const float * raw, int32_t frame, int32_t n_text_tokens, const int32_t * seen,
+                    int32_t n_seen, float rep_pen, float temperature, int32_t top_k, float u, int32_t * token_out,
+                    float * processed_out) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    const qtts_config & c = e->cfg;
+    if (!raw || !token_out) { e->err = "sample_cb0: null argument"; return 0; }
+    if (frame < 0 || frame >= e->max_ctx) { e->err = "sample_cb0: frame out of range"; return 0; }
+    StreamState st{};
+    st.frame = frame; st.max_len = frame + 2; st.n_text_tokens = n_text_tokens; st.top_k = top_k; st.rep_pen = rep_pen;
+    st.temperature = temperature; st.sample_mode = (e->numerics == QTTS_NUMERICS_REFERENCE) ? 1 : 0;
+    for (int i = 0; i < n_seen; ++i) {
+        if (seen[i] < 0 || seen[i] >= c.codec_vocab_size) { e->err = "sample_cb0: seen token out of range"; return 0; }
+        st.seen[seen[i] >> 5] |= 1u << (seen[i] & 31);
+    }
+    s->active = false; s->pending = false;
+    cudaMemcpyAsync(s->st, &st, sizeof(st), cudaMemcpyHostToDevice, e->stream);
+    cudaMemcpyAsync(s->logits, raw, c.codec_vocab_size * sizeof(float), cudaMemcpyHostToDevice, e->stream);
+    cudaMemcpyAsync(s->uniforms + frame, &u, sizeof(float), cudaMemcpyHostToDevice, e->stream);
+    cudaStreamSynchronize(e->stream);
+    Op o;
+    memset(&o, 0, sizeof(o));
+    o.type = OP_SAMPLE_CB0; o.n_tok = 1; o.tok_slot = -1; o.temperature_override = -1e30f;
+    o.logits = s->logits; o.n_vocab = c.codec_vocab_size; o.eos_id = c.codec_eos_id; o.suppress_start = c.codec_vocab_size - 1024;
+    o.dump = s->cb0_dump; o.uniforms = s->uniforms; o.n_books = c.n_codebooks;
+    std::vector<Op> P{o};
+    if (!run_program(e, *s, P, 1, false)) return 0;
+    StreamState hs;
+    cudaMemcpyAsync(&hs, s->st, sizeof(hs), cudaMemcpyDeviceToHost, e->stream);
+    if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("sample_cb0: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
+    *token_out = hs.eos ? c.codec_eos_id : hs.cur_codes[0];
+    if (processed_out) cudaMemcpy(processed_out, s->cb0_dump, c.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
+    return 1;
+}
+
+int qtts_set_debug(qtts_engine * h, int flags) {
+    Engine * e = &h->e;
+    e->debug_flags = flags;
+    if (e->finalized) { cudaSetDevice(e->device); cudaStreamSynchronize(e->stream); if (!rebuild_frame_programs(e)) return 0; }
+    return 1;
+}
+
+int qtts_resize_kv(qtts_engine * h, int32_t n_ctx, int32_t max_text) {
+    Engine * e = &h->e;
+    cudaSetDevice(e->device);
+    return engine_resize(e, n_ctx, max_text) ? 1 : 0;
+}
+
 int qtts_set_batched(qtts_engine * h, int on) { h->e.batched = on ? 1 : 0; return 1; }
 
 int qtts_set_batched_weight_format(qtts_engine * h, int fmt) {
@@ -468,7 +659,10 @@ int qtts_stream_logits(qtts_engine * h, int slot, float * cb0_out, float * cp_ou
                            c.cp_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
     } else {
         if (cb0_out) cudaMemcpy(cb0_out, s->cb0_dump, c.codec_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
-        if (cp_out) { e->err = "code-predictor logits of the last frame are only kept by the batched kernel"; return 0; }
+        if (cp_out) {
+            if (!(e->debug_flags & 1)) { e->err = "code-predictor logits of the last frame: batch-1 kernel keeps them only with qtts_set_debug(e, 1)"; return 0; }
+            cudaMemcpy(cp_out, s->cp_dump, (size_t) (c.n_codebooks - 1) * c.cp_vocab_size * sizeof(float), cudaMemcpyDeviceToHost);
+        }
     }
     if (cudaGetLastError() != cudaSuccess) { e->err = "stream_logits: copy failed"; return 0; }
     return 1;
@@ -507,6 +701,7 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     auto cleanup = [&](int rc) {
         cudaStreamSynchronize(e->stream);
         for (void * p : e->allocs) cudaFree(p);
+        for (void * p : e->stream_allocs) cudaFree(p);
         cudaStreamDestroy(e->stream);
         if (!rc) g_create_err = e->err;
         return rc;

@@ -1292,7 +1292,8 @@ __device__ __noinline__ void bstage_sample(BShared * S) {
                 if (tid == 0) {
                     const float ramp = fminf(1.0f, (float) (frame - expected) / (float) expected);
                     const float target = mx + 5.0f;
-                    sm->l[op.eos_id] += ramp * (target - sm->l[op.eos_id]);
+                    // one FMA, like the reference as compiled (GCC contracts `l += ramp * (target - l)`)
+                    sm->l[op.eos_id] = __fmaf_rn(ramp, target - sm->l[op.eos_id], sm->l[op.eos_id]);
                 }
                 __syncthreads();
             }
@@ -1303,18 +1304,26 @@ __device__ __noinline__ void bstage_sample(BShared * S) {
                 __syncthreads();
             }
             if (temperature <= 0.0f) tok = block_argmax(sm->l, n, sm);
-            else tok = block_sample(n, temperature, top_k, philox_uniform(st->seed, (uint32_t) frame, 0u, 0x0cb0u),
-                                    ignore_eos ? -1 : op.eos_id, sm, pbuf);
+            else {
+                const float * su = st->uniforms;
+                const float u = (su && frame < st->uniform_frames) ? __ldcg(su + (size_t) frame * op.n_books)
+                                                                   : philox_uniform(st->seed, (uint32_t) frame, 0u, 0x0cb0u);
+                tok = block_sample(n, temperature, top_k, u, ignore_eos ? -1 : op.eos_id, sm, pbuf, st->sample_mode);
+            }
             __syncthreads();
+            // teacher forcing (parity hook): the own choice is emitted, the forced code is fed back
+            const int32_t * fc = st->forced;
+            const bool forcing = fc != nullptr && frame < st->forced_frames;
+            const int fed = forcing ? __ldcg(fc + (size_t) frame * op.n_books) : tok;
             if (tid == 0 && live) {
-                if (tok == op.eos_id) { st->done = 1; st->eos = 1; }
+                if (tok == op.eos_id && !forcing) { st->done = 1; st->eos = 1; }
                 else {
-                    st->cur_codes[0] = tok; st->feed_codes[0] = tok;
-                    st->seen[tok >> 5] |= 1u << (tok & 31);
+                    st->cur_codes[0] = tok; st->feed_codes[0] = fed;
+                    st->seen[fed >> 5] |= 1u << (fed & 31);
                 }
             }
             // code-predictor input rows: token 0 = Talker hidden, token 1 = codec_embd[cb0]
-            const int feed = (live && tok != op.eos_id) ? tok : __ldcg(&st->feed_codes[0]);
+            const int feed = (live && (tok != op.eos_id || forcing)) ? fed : __ldcg(&st->feed_codes[0]);
             const __half * row = op.table + (size_t) feed * op.xw;
             double s0 = 0.0, s1 = 0.0;
             for (int i = tid; i < op.xw; i += kThreads) {
@@ -1335,12 +1344,18 @@ __device__ __noinline__ void bstage_sample(BShared * S) {
             }
             __syncthreads();
             if (temperature <= 0.0f) tok = block_argmax(sm->l, n, sm);
-            else tok = block_sample(n, temperature, top_k, philox_uniform(st->seed, (uint32_t) frame, (uint32_t) op.book, 0x0c9du),
-                                    -1, sm, pbuf);
+            else {
+                const float * su = st->uniforms;
+                const float u = (su && frame < st->uniform_frames) ? __ldcg(su + (size_t) frame * op.n_books + op.book)
+                                                                   : philox_uniform(st->seed, (uint32_t) frame, (uint32_t) op.book, 0x0c9du);
+                tok = block_sample(n, temperature, top_k, u, -1, sm, pbuf, 0);
+            }
             __syncthreads();
-            if (tid == 0) { st->cur_codes[op.book] = tok; st->feed_codes[op.book] = tok; }
+            const int32_t * fc = st->forced;
+            const int fed = (fc && frame < st->forced_frames) ? __ldcg(fc + (size_t) frame * op.n_books + op.book) : tok;
+            if (tid == 0) { st->cur_codes[op.book] = tok; st->feed_codes[op.book] = fed; }
             if (op.book < op.n_books - 1) {
-                const __half * row = op.table + (size_t) tok * op.xw;
+                const __half * row = op.table + (size_t) fed * op.xw;
                 double s0 = 0.0;
                 for (int i = tid; i < op.xw; i += kThreads) {
                     const float e = __half2float(row[i]);
@@ -1352,7 +1367,11 @@ __device__ __noinline__ void bstage_sample(BShared * S) {
             } else {
                 // frame end + next Talker input
                 __syncthreads();
-                if (tid < op.n_books) sm->idx[tid] = (unsigned short) ((tid == op.book) ? tok : __ldcg(&st->cur_codes[tid]));
+                // idx[0..n_books): the frame's own codes (emitted); idx[kMaxBooks..): the fed-back codes (next Talker input)
+                if (tid < op.n_books) {
+                    sm->idx[tid] = (unsigned short) ((tid == op.book) ? tok : __ldcg(&st->cur_codes[tid]));
+                    sm->idx[kMaxBooks + tid] = (unsigned short) ((tid == op.book) ? fed : __ldcg(&st->feed_codes[tid]));
+                }
                 __syncthreads();
                 int f1 = frame;
                 if (live) {
@@ -1370,9 +1389,9 @@ __device__ __noinline__ void bstage_sample(BShared * S) {
                 const EmbedSumArgs * es = op.es;
                 double s0 = 0.0;
                 for (int i = tid; i < op.xw; i += kThreads) {
-                    float acc = __half2float(es->tables[0][(size_t) sm->idx[0] * op.xw + i]);
+                    float acc = __half2float(es->tables[0][(size_t) sm->idx[kMaxBooks] * op.xw + i]);
                     for (int c = 1; c < es->n_books; ++c)
-                        acc += __half2float(es->tables[c][(size_t) sm->idx[c] * op.xw + i]);
+                        acc += __half2float(es->tables[c][(size_t) sm->idx[kMaxBooks + c] * op.xw + i]);
                     acc += __ldcg(trow + i);
                     op.x_out[(size_t) b * op.xw + i] = acc;
                     s0 += (double) (acc * acc);

@@ -282,8 +282,16 @@ bool batched_init(Engine * e) {
     if (!tile_matrix(e, e->codec_head, c.codec_vocab_size, c.hidden_size, e->t_codec_head)) return false;
     if (e->mtp && !tile_matrix(e, e->mtp, c.cp_hidden_size, c.hidden_size, e->t_mtp)) return false;
     QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    return true;
+}
 
-    // stream groups of at most 128 streams (the merged code-predictor pass has 2 rows per stream)
+// lock-step groups of at most e->bgroup (<= 256) streams over the current slots (the merged code-predictor pass has
+// 2 rows per stream: kBMaxRows = 512)
+bool batched_build_groups(Engine * e) {
+    const qtts_config & c = e->cfg;
+    const int rep = c.n_heads / c.n_kv_heads;
+    if (rep > kMaxRep || e->max_ctx * rep > 2 * kMaxScores) return e->fail("batched path: context too long for the attention scratch");
+    e->groups.clear();
     const int H = c.hidden_size, cpH = c.cp_hidden_size;
     const int qkvw = (c.n_heads + 2 * c.n_kv_heads) * kHeadDim, cqkvw = (c.cp_n_heads + 2 * c.cp_n_kv_heads) * kHeadDim;
     for (int s0 = 0; s0 < e->max_streams; s0 += e->bgroup) {

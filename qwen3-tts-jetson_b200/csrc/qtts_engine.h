@@ -43,7 +43,7 @@ struct BatchBufs {
     size_t kv_slab = 0, trailing_stride = 0, codes_stride = 0;
 };
 
-// one group of <= 128 streams advanced by one batched launch
+// one lock-step group (<= e->bgroup = 256 streams) advanced by one batched launch
 struct BGroup {
     int s0 = 0, n = 0;
     float * x = nullptr, * qkv = nullptr, * ssq_e = nullptr, * ssq_p = nullptr, * emb = nullptr;
@@ -82,6 +82,9 @@ struct Slot {
     float * cb0_dump = nullptr;            // [V]
     float * uniforms = nullptr;            // [max(16, max_len)]
     int32_t * forced = nullptr;            // [15]
+    int32_t * force_codes = nullptr;       // [max_ctx][n_books] teacher-forcing codes (qtts_stream_force), allocated on first use
+    float * force_u = nullptr;             // [max_ctx][n_books] host-supplied uniforms
+    float * prefill_hidden = nullptr;      // [64][H] normalised hidden of every prefill row (forward_prefill's `output`), on first use
     __half * kc = nullptr, * vc = nullptr;           // [n_layers][max_ctx][kvw]
     __half * cp_kc = nullptr, * cp_vc = nullptr;     // [cp_layers][16][cp_kvw]
     float * attn_part = nullptr;                     // ATTN_FAST partials [n_heads][kMaxSplits][kPartStride]
@@ -116,8 +119,11 @@ struct Engine {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     std::map<std::string, DevTensor> tensors;
-    std::vector<void *> allocs;
+    std::vector<void *> allocs;          // weights, tiled weights, folded text table: live as long as the engine
+    std::vector<void *> stream_allocs;   // everything sized by max_streams / max_ctx / max_text: rebuilt by qtts_resize_kv
+    bool stream_phase = false;           // which of the two lists dalloc appends to
     bool finalized = false;
+    int debug_flags = 0;                 // qtts_set_debug
     int numerics = QTTS_NUMERICS_REFERENCE;
     int ref_threads = 4;          // ggml's default thread count (ggml/include/ggml.h:232)
     int persistent = 1;
@@ -158,7 +164,7 @@ struct Engine {
         void * p = nullptr;
         if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
         if (zero) cudaMemset(p, 0, n * sizeof(T));
-        allocs.push_back(p);
+        (stream_phase ? stream_allocs : allocs).push_back(p);
         return (T *) p;
     }
 };
@@ -166,6 +172,8 @@ struct Engine {
 // qtts_weights.cu
 bool engine_upload(Engine * e, const char * name, int dtype, const int64_t * dims, int n_dims, const void * host);
 bool engine_finalize(Engine * e);
+bool engine_build_streams(Engine * e);      // per-stream buffers, frame programs, lock-step groups (after the weights)
+bool engine_resize(Engine * e, int n_ctx, int max_text);
 
 // qtts_kernels.cu
 size_t slot_bytes_for(int k_max);
@@ -190,7 +198,8 @@ bool fold_text_table(Engine * e);
 
 // qtts_batched_host.cu
 bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T, bool allow_split = false);
-bool batched_init(Engine * e);
+bool batched_init(Engine * e);              // tiles the weights (once)
+bool batched_build_groups(Engine * e);      // lock-step groups over the current slots
 uint32_t batched_idesc(const Engine * e);
 bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_sched, int n_sched, StreamState * st,
                     const int32_t * d_active, int n_streams, int n_frames, bool check_done);

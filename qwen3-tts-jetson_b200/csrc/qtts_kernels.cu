@@ -19,6 +19,7 @@
 //                 :5224-5330 soft_max for the code-predictor / prefill variant).
 //   stage_sample_*: src/tts_transformer.cpp:2198-2236 and :2417-2499.
 #include "qtts_ops.cuh"
+#include "qtts_nth.cuh"
 #ifndef QTTS_OPT_RES
 #define QTTS_OPT_RES 1
 #endif
@@ -279,9 +280,9 @@ __device__ __forceinline__ float gemv_input_elem(const Op & op, const LocalState
         default: {
             // next Talker input (src/tts_transformer.cpp:2529-2553): sequential f32 sum, same order
             const EmbedSumArgs * es = op.es;
-            float acc = __half2float(es->tables[0][(size_t) ls->cur_codes[0] * K + i]);
+            float acc = __half2float(es->tables[0][(size_t) ls->feed_codes[0] * K + i]);
             for (int c = 1; c < es->n_books; ++c)
-                acc += __half2float(es->tables[c][(size_t) ls->cur_codes[c] * K + i]);
+                acc += __half2float(es->tables[c][(size_t) ls->feed_codes[c] * K + i]);
             return acc + __ldcg(trow + i);
         }
     }
@@ -1112,13 +1113,30 @@ __device__ float philox_uniform(uint64_t seed, uint32_t c0, uint32_t c1, uint32_
 // eos_id >= 0: EOS survives top-k (src/tts_transformer.cpp:2451-2494); eos_id < 0: code-predictor
 // rule (:2202-2232) with the CDF scan of the TRT sampler (src/trt_cuda_kernels.cu:160-180) in
 // place of std::discrete_distribution.
-__device__ __noinline__ int block_sample(int n, float temperature, int top_k, float u, int eos_id, SampleSmem * sm, float * p) {
+__device__ __noinline__ int block_sample(int n, float temperature, int top_k, float u, int eos_id, SampleSmem * sm, float * p,
+                                         int ref_nth) {
     float * l = sm->l;
     for (int i = threadIdx.x; i < n; i += kThreads) l[i] = l[i] / temperature;
     __syncthreads();
     const float eos_logit = (eos_id >= 0) ? l[eos_id] : 0.f;
     if (top_k > 0 && top_k < n) {
-        const float thr = block_kth_largest(l, n, top_k, sm);
+        float thr;
+        if (ref_nth) {
+            // the reference's codebook-0 threshold: scored_vals[scored_idx[top_k - 1]] after std::nth_element
+            // (src/tts_transformer.cpp:2464-2466) - SOME member of the top-k set, whichever libstdc++'s introselect
+            // leaves there; reproduced by running the same algorithm (qtts_nth.cuh) on one thread
+            if (threadIdx.x == 0) {
+                unsigned short * ix = reinterpret_cast<unsigned short *>(p);       // p is rewritten below
+                for (int i = 0; i < n; ++i) ix[i] = (unsigned short) i;
+                nth::nth_element_desc(ix, top_k, n, l);
+                sm->redf[0] = l[ix[top_k - 1]];
+            }
+            __syncthreads();
+            thr = sm->redf[0];
+            __syncthreads();
+        } else {
+            thr = block_kth_largest(l, n, top_k, sm);
+        }
         for (int i = threadIdx.x; i < n; i += kThreads) if (l[i] < thr) l[i] = -CUDART_INF_F;
         __syncthreads();
     }
@@ -1159,9 +1177,11 @@ __device__ __noinline__ int block_sample(int n, float temperature, int top_k, fl
     if (threadIdx.x == kThreads - 1) sm->count = base + incl;
     __syncthreads();
     if (threadIdx.x == 0) {
+        // src/tts_transformer.cpp:2487-2494: the scan starts at index 0 with cumsum = probs[0], so a draw of
+        // exactly 0 selects index 0 even when its probability is 0 (zeros are skipped below)
         float cum = 0.f;
-        int tok = n - 1;
-        const int m = sm->count;
+        int tok = (u <= 0.0f) ? 0 : n - 1;
+        const int m = (u <= 0.0f) ? 0 : sm->count;
         for (int t = 0; t < m; ++t) {
             const int i = sm->idx[t];
             cum += p[i];
@@ -1199,7 +1219,8 @@ __device__ __noinline__ void stage_sample_cb0(const Op & op, StreamState * st, L
         if (threadIdx.x == 0) {
             const float ramp = fminf(1.0f, (float) (frame - expected) / (float) expected);
             const float target = mx + 5.0f;
-            sm->l[op.eos_id] += ramp * (target - sm->l[op.eos_id]);
+            // one FMA, like the reference as compiled (GCC contracts `l += ramp * (target - l)` wherever the ISA has FMA)
+            sm->l[op.eos_id] = __fmaf_rn(ramp, target - sm->l[op.eos_id], sm->l[op.eos_id]);
         }
         __syncthreads();
     }
@@ -1213,20 +1234,26 @@ __device__ __noinline__ void stage_sample_cb0(const Op & op, StreamState * st, L
     if (temperature <= 0.0f) {
         tok = block_argmax(sm->l, n, sm);
     } else {
+        const float * su = st->uniforms;
         const float u = op.uniforms ? __ldcg(op.uniforms + frame)
-                                    : philox_uniform(st->seed, (uint32_t) frame, 0u, 0x0cb0u);
-        tok = block_sample(n, temperature, top_k, u, ignore_eos ? -1 : op.eos_id, sm, xs);
+                      : (su && frame < st->uniform_frames) ? __ldcg(su + (size_t) frame * op.n_books)
+                      : philox_uniform(st->seed, (uint32_t) frame, 0u, 0x0cb0u);
+        tok = block_sample(n, temperature, top_k, u, ignore_eos ? -1 : op.eos_id, sm, xs, st->sample_mode);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        if (tok == op.eos_id) {
+        // teacher forcing (parity hook): the engine's own choice is still what the frame emits
+        const int32_t * fc = st->forced;
+        const bool forcing = fc != nullptr && frame < st->forced_frames;
+        if (tok == op.eos_id && !forcing) {
             ls->done = 1; ls->eos = 1;
             if (lead) { st->done = 1; st->eos = 1; }
         } else {
+            const int feed = forcing ? __ldcg(fc + (size_t) frame * op.n_books) : tok;
             ls->cur_codes[0] = tok;
-            ls->feed_codes[0] = tok;
-            ls->seen[tok >> 5] |= 1u << (tok & 31);
-            if (lead) { st->cur_codes[0] = tok; st->feed_codes[0] = tok; st->seen[tok >> 5] = ls->seen[tok >> 5]; }
+            ls->feed_codes[0] = feed;
+            ls->seen[feed >> 5] |= 1u << (feed & 31);
+            if (lead) { st->cur_codes[0] = tok; st->feed_codes[0] = feed; st->seen[feed >> 5] = ls->seen[feed >> 5]; }
         }
     }
     __syncthreads();
@@ -1249,13 +1276,17 @@ __device__ __noinline__ void stage_sample_cp(const Op & op, StreamState * st, Lo
     if (temperature <= 0.0f) {
         tok = block_argmax(sm->l, n, sm);
     } else {
+        const float * su = (op.temperature_override < -1e29f) ? st->uniforms : nullptr;   // (not in qtts_predict_codes)
         const float u = op.uniforms ? __ldcg(op.uniforms + (op.book - 1))
-                                    : philox_uniform(st->seed, (uint32_t) ls->frame, (uint32_t) op.book, 0x0c9du);
-        tok = block_sample(n, temperature, top_k, u, -1, sm, xs);
+                      : (su && ls->frame < st->uniform_frames) ? __ldcg(su + (size_t) ls->frame * op.n_books + op.book)
+                      : philox_uniform(st->seed, (uint32_t) ls->frame, (uint32_t) op.book, 0x0c9du);
+        tok = block_sample(n, temperature, top_k, u, -1, sm, xs, 0);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        const int feed = op.forced ? __ldcg(op.forced + (op.book - 1)) : tok;
+        const int32_t * fc = (op.temperature_override < -1e29f) ? st->forced : nullptr;
+        const int feed = op.forced ? __ldcg(op.forced + (op.book - 1))
+                       : (fc && ls->frame < st->forced_frames) ? __ldcg(fc + (size_t) ls->frame * op.n_books + op.book) : tok;
         ls->cur_codes[op.book] = tok;
         ls->feed_codes[op.book] = feed;
         if (lead) { st->cur_codes[op.book] = tok; st->feed_codes[op.book] = feed; }

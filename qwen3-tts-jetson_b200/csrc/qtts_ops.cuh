@@ -69,9 +69,14 @@ struct StreamState {
     float   temperature;
     uint64_t seed;
     int32_t ignore_eos;      // benchmark switch: EOS can never be chosen (fixed-length utterances)
-    int32_t pad0;
-    int32_t cur_codes[kMaxBooks];   // codes of the frame being produced (cb0..cb15)
-    int32_t feed_codes[kMaxBooks];  // codes fed back inside the code predictor (forced or own)
+    int32_t forced_frames;   // teacher forcing (parity hook, qtts_stream_force): frames [0, forced_frames) feed back
+    const int32_t * forced;  //   forced[frame][n_books] instead of the engine's own choice (which is still what is emitted)
+    const float * uniforms;  // host-supplied uniforms [frame][n_books] (TRTCodePredictor::run_sampling_loop's rand_vals,
+                             //   src/trt_code_predictor.cpp:602-726, extended to codebook 0); nullptr: Philox
+    int32_t uniform_frames;  // rows of `uniforms`; later frames fall back to Philox
+    int32_t sample_mode;     // 0: codebook-0 top-k threshold = exact k-th largest; 1: the reference's std::nth_element pick
+    int32_t cur_codes[kMaxBooks];   // codes of the frame being produced (cb0..cb15): the engine's own choice, emitted
+    int32_t feed_codes[kMaxBooks];  // codes fed back (code-predictor inputs, next Talker input, repetition set): forced or own
     uint32_t seen[kMaxVocab / 32];  // bitmap of distinct cb0 tokens emitted so far
 };
 

@@ -156,7 +156,7 @@ void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float 
         P.push_back(hd);
         Op sp = blank();
         sp.type = OP_SAMPLE_CP; sp.logits = s.cp_logits; sp.n_vocab = c.cp_vocab_size; sp.book = p;
-        sp.uniforms = uniforms; sp.forced = forced;
+        sp.uniforms = uniforms; sp.forced = forced; sp.n_books = c.n_codebooks;
         sp.dump = dump ? dump + (size_t) (p - 1) * c.cp_vocab_size : nullptr;
         if (override_sampling) { sp.temperature_override = temperature; sp.top_k_override = top_k; }
         P.push_back(sp);
@@ -168,9 +168,9 @@ void emit_frame(Engine * e, Slot & s, std::vector<Op> & P) {
     Op s0 = blank();
     s0.type = OP_SAMPLE_CB0; s0.logits = s.logits; s0.n_vocab = c.codec_vocab_size;
     s0.eos_id = c.codec_eos_id; s0.suppress_start = c.codec_vocab_size - 1024;
-    s0.dump = s.cb0_dump;
+    s0.dump = s.cb0_dump; s0.n_books = c.n_codebooks;
     P.push_back(s0);
-    emit_code_predictor(e, s, P, s.hidden, nullptr, nullptr, nullptr, false, 0.f, 0);
+    emit_code_predictor(e, s, P, s.hidden, (e->debug_flags & 1) ? s.cp_dump : nullptr, nullptr, nullptr, false, 0.f, 0);
     Op fe = blank();
     fe.type = OP_FRAME_END; fe.codes_out = s.codes; fe.n_books = c.n_codebooks;
     P.push_back(fe);
@@ -281,8 +281,10 @@ bool fold_text_table(Engine * e) {
     const qtts_config & c = e->cfg;
     if (!e->fc1 || !e->fc2 || !e->text_embd || e->slots.empty()) return true;
     const int H = c.hidden_size, E = c.text_embd_dim, V = c.text_vocab_size;
+    e->stream_phase = false;            // the table belongs to the weights: it survives qtts_resize_kv
     e->text_tab = e->dalloc<float>((size_t) V * H, false);
     int32_t * ids = e->dalloc<int32_t>(V, false);
+    e->stream_phase = true;
     if (!e->text_tab || !ids) { e->text_tab = nullptr; return e->fail("out of device memory for the folded text table"); }
     std::vector<int32_t> iota(V);
     for (int i = 0; i < V; ++i) iota[i] = i;

@@ -290,6 +290,20 @@ bool engine_finalize(Engine * e) {
     QTTS_CUDA(cudaMemcpy(&bad, e->d_inexact, sizeof(bad), cudaMemcpyDeviceToHost));
     e->n_inexact = (int64_t) bad;
 
+    if (!batched_init(e)) return false;
+    if (!engine_build_streams(e)) return false;
+    if (!fold_text_table(e)) return false;
+    e->finalized = true;
+    return true;
+}
+
+// Everything whose size depends on max_streams / max_ctx / max_text.  Runs at the end of
+// qtts_finalize and again from qtts_resize_kv (the reference's init_kv_cache, src/tts_transformer.cpp:794-842),
+// which frees e->stream_allocs first; the weights are not touched.
+bool engine_build_streams(Engine * e) {
+    const qtts_config & c = e->cfg;
+    e->stream_phase = true;
+    e->kv_bytes = 0;
     // RoPE table exactly as ggml_rope_cache_init computes it (ops.cpp:5612-5627): theta starts at
     // the position and is multiplied by theta_scale = powf(base, -2/n_dims) pair after pair, in
     // float; cosf/sinf from the host libm.
@@ -311,6 +325,7 @@ bool engine_finalize(Engine * e) {
     }
     {   // per-stream buffers shared with the batched kernel: contiguous over the slots
         BatchBufs & bb = e->bb;
+        bb = BatchBufs{};
         const size_t n = (size_t) e->max_streams;
         bb.kv_slab = (size_t) c.n_layers * e->max_ctx * c.n_kv_heads * kHeadDim;
         bb.trailing_stride = (size_t) (e->max_text + 1) * c.hidden_size;
@@ -326,12 +341,30 @@ bool engine_finalize(Engine * e) {
         if (!bb.st || !bb.logits || !bb.hidden || !bb.kc || !bb.vc || !bb.trailing || !bb.pad || !bb.codes)
             return e->fail("out of device memory for stream slots");
     }
+    e->slots.clear();
     e->slots.resize(e->max_streams);
     for (int i = 0; i < e->max_streams; ++i) if (!alloc_slot(e, e->slots[i], i)) return false;
-    if (!batched_init(e)) return false;
-    if (!fold_text_table(e)) return false;
-    e->finalized = true;
+    if (!batched_build_groups(e)) return false;
     return true;
+}
+
+bool engine_resize(Engine * e, int n_ctx, int max_text) {
+    if (!e->finalized) return e->fail("engine not finalized");
+    if (n_ctx < 32) return e->fail("resize_kv: n_ctx must be >= 32");
+    if (n_ctx > kMaxScores) return e->fail("resize_kv: n_ctx exceeds the engine limit of " + std::to_string(kMaxScores) + " KV slots per stream");
+    const int rep = e->cfg.n_heads / e->cfg.n_kv_heads;
+    if (n_ctx * rep > 2 * kMaxScores) return e->fail("resize_kv: context too long for the attention scratch");
+    if (max_text <= 0) max_text = e->max_text;
+    if (n_ctx == e->max_ctx && max_text == e->max_text) return true;
+    QTTS_CUDA(cudaStreamSynchronize(e->stream));
+    for (void * p : e->stream_allocs) cudaFree(p);
+    e->stream_allocs.clear();
+    e->slots.clear();
+    e->groups.clear();
+    e->batched_ready = false;
+    e->max_ctx = n_ctx;
+    e->max_text = max_text;
+    return engine_build_streams(e);
 }
 
 }  // namespace qtts

@@ -44,7 +44,8 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_predict_codes", "qtts_generate", "qtts_stream_begin", "qtts_stream_prepare", "qtts_prefill_pending",
            "qtts_step_frames",
            "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
-           "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle"]
+           "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle",
+           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states"]
 
 _lib = None
 
@@ -76,6 +77,13 @@ def load_library(path: str | None = None):
     lib.qtts_build_prefill.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32p, i32p, vp, vp, vp]
     lib.qtts_forward_prefill.argtypes = [vp, C.c_int, vp, i32, i32, vp, vp]
     lib.qtts_forward_step.argtypes = [vp, C.c_int, vp, i32, vp, vp]
+    lib.qtts_forward_text.argtypes = [vp, C.c_int, vp, i32, vp, i32, vp]
+    lib.qtts_forward_codec.argtypes = [vp, C.c_int, i32, i32, vp]
+    lib.qtts_stream_force.argtypes = [vp, C.c_int, vp, i32, vp, i32]
+    lib.qtts_sample_cb0.argtypes = [vp, C.c_int, vp, i32, i32, vp, i32, C.c_float, C.c_float, i32, C.c_float, i32p, vp]
+    lib.qtts_set_debug.argtypes = [vp, C.c_int]
+    lib.qtts_resize_kv.argtypes = [vp, i32, i32]
+    lib.qtts_get_hidden_states.argtypes = [vp, C.c_int, vp]
     lib.qtts_predict_codes.argtypes = [vp, C.c_int, vp, i32, C.c_float, i32, vp, vp, vp, vp]
     lib.qtts_generate.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64,
                                   vp, i32p, FRAME_CB, i32, vp]
@@ -222,11 +230,15 @@ class TTSTransformer:
         return float(self._lib.qtts_last_loop_ms(self._h))
 
     # -- KV cache (src/tts_transformer.cpp:794-900) -------------------------------------------------
-    def init_kv_cache(self, n_ctx: int) -> bool:
-        if n_ctx > self.max_ctx:
-            self._err = "init_kv_cache: n_ctx exceeds the engine's max_ctx"
+    def init_kv_cache(self, n_ctx: int, max_text: int = 0) -> bool:
+        """Re-size the per-stream KV slabs (weights stay resident); streams in flight are dropped."""
+        if not self._lib.qtts_resize_kv(self._h, n_ctx, max_text):
             return False
-        return True   # KV slabs are allocated once per slot at load time (max_ctx entries)
+        self.max_ctx = n_ctx
+        return True
+
+    def set_debug(self, flags: int) -> bool:
+        return bool(self._lib.qtts_set_debug(self._h, flags))
 
     def clear_kv_cache(self, slot: int = 0) -> bool:
         return bool(self._lib.qtts_clear_kv_cache(self._h, slot))
@@ -247,13 +259,62 @@ class TTSTransformer:
         return pre[:pl.value].copy(), trail[:tl.value].copy(), pad
 
     # -- forward_prefill / forward_step (src/tts_transformer.cpp:1829-2028) -------------------------
-    def forward_prefill(self, prefill_embd, n_past: int = 0, slot: int = 0):
-        e = np.ascontiguousarray(prefill_embd, dtype=np.float32)
-        hid = np.zeros(self.config["hidden_size"], np.float32)
+    def forward_prefill(self, prefill_embd, n_past: int = 0, slot: int = 0, all_rows: bool = True):
+        """Returns (hidden [n_tokens, H] like the reference's `output`, logits [V] of the last token);
+        all_rows=False skips the per-row hidden states (hidden = [1, H], the last row)."""
+        e = np.ascontiguousarray(prefill_embd, dtype=np.float32).reshape(-1, self.config["hidden_size"])
+        n = e.shape[0]
         logits = np.zeros(self.config["codec_vocab_size"], np.float32)
-        if not self._lib.qtts_forward_prefill(self._h, slot, _ptr(e), e.shape[0], n_past, _ptr(hid), _ptr(logits)):
+        if all_rows:
+            hid = np.zeros((max(n, 1), self.config["hidden_size"]), np.float32)
+            ok = self._lib.qtts_forward_prefill(self._h, slot, _ptr(e), n, n_past, _ptr(hid), _ptr(logits))
+            return (hid, logits) if ok else None
+        ok = self._lib.qtts_forward_prefill(self._h, slot, _ptr(e), n, n_past, None, _ptr(logits))
+        if not ok:
             return None
-        return hid, logits
+        return self.get_hidden_states(slot)[None, :], logits
+
+    def get_hidden_states(self, slot: int = 0):
+        """get_hidden_states (src/tts_transformer.cpp:2042-2048): the normalised hidden of the last forward call."""
+        hid = np.zeros(self.config["hidden_size"], np.float32)
+        if not self._lib.qtts_get_hidden_states(self._h, slot, _ptr(hid)):
+            return None
+        return hid
+
+    def forward_text(self, text_tokens, speaker_embd=None, n_past: int = 0, slot: int = 0):
+        toks = np.ascontiguousarray(text_tokens, dtype=np.int32)
+        spk = None if speaker_embd is None else np.ascontiguousarray(speaker_embd, dtype=np.float32)
+        hid = np.zeros((max(len(toks), 1), self.config["hidden_size"]), np.float32)
+        if not self._lib.qtts_forward_text(self._h, slot, _ptr(toks), len(toks), _ptr(spk), n_past, _ptr(hid)):
+            return None
+        return hid
+
+    def forward_codec(self, codec_token: int, n_past: int, slot: int = 0):
+        logits = np.zeros(self.config["codec_vocab_size"], np.float32)
+        if not self._lib.qtts_forward_codec(self._h, slot, int(codec_token), n_past, _ptr(logits)):
+            return None
+        return logits
+
+    # -- parity hooks ------------------------------------------------------------------------------------
+    def stream_force(self, slot: int, forced_codes=None, uniforms=None) -> bool:
+        """Teacher forcing / host-supplied uniforms for a begun or prepared stream (qtts_stream_force)."""
+        f = None if forced_codes is None else np.ascontiguousarray(forced_codes, dtype=np.int32)
+        u = None if uniforms is None else np.ascontiguousarray(uniforms, dtype=np.float32)
+        return bool(self._lib.qtts_stream_force(self._h, slot, _ptr(f), 0 if f is None else f.shape[0],
+                                                _ptr(u), 0 if u is None else u.shape[0]))
+
+    def sample_cb0(self, raw_logits, frame: int, n_text_tokens: int, seen_tokens=(), repetition_penalty: float = 1.05,
+                   temperature: float = 0.0, top_k: int = 50, u: float = 0.5, slot: int = 0):
+        """Codebook-0 post-processing + sampling of one frame (src/tts_transformer.cpp:2417-2499) on raw logits.
+        Returns (token, processed logits)."""
+        lg = np.ascontiguousarray(raw_logits, dtype=np.float32)
+        seen = np.ascontiguousarray(sorted(int(t) for t in seen_tokens), dtype=np.int32)
+        tok = C.c_int32()
+        proc = np.zeros(self.config["codec_vocab_size"], np.float32)
+        if not self._lib.qtts_sample_cb0(self._h, slot, _ptr(lg), frame, n_text_tokens, _ptr(seen) if len(seen) else None,
+                                         len(seen), repetition_penalty, temperature, top_k, u, C.byref(tok), _ptr(proc)):
+            return None
+        return int(tok.value), proc
 
     def forward_step(self, step_embd, n_past: int, slot: int = 0):
         e = np.ascontiguousarray(step_embd, dtype=np.float32)

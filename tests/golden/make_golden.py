@@ -63,6 +63,82 @@ def make(preset: str, gguf_dir: str = "/tmp"):
     R.close()
 
 
+# ----------------------------------------------------------------------------------------------
+# round 2: per-frame fixtures.  ref_<preset>_seed1234_frames.npz holds what the reference's
+# generate() computes INSIDE its frame loop, dumped by replaying the loop through the reference's
+# own methods (oracle/ref_harness.cpp:ref_generate_trace; the replay is accepted only if its codes
+# equal the real generate()'s):
+#   g_*   greedy "Hello, world!" run of the base fixture: raw Talker logits, hidden and next-input
+#         embedding of the first G_FRAMES frames, code-predictor logits of frames 1..2
+#   e_*   greedy "Hi" (10 tokens: EOS ramp from frame 40, src/tts_transformer.cpp:2439-2445) run
+#         until the reference stops: all codes, the stop frame, raw + processed logits around the ramp
+#   s_*   sampled run (temperature 0.9, top-k 50) with the reference's rng_ re-seeded to S_SEED:
+#         codes and the uniforms each sampled code consumed (codebook 0: uniform_real_distribution<float>;
+#         codes 1..15: the generate_canonical<double,53> draw of std::discrete_distribution)
+# ----------------------------------------------------------------------------------------------
+G_FRAMES = {"tiny": 12, "tiny-mtp": 12, "0.6b": 12, "1.7b": 6}
+S_FRAMES = {"tiny": 24, "tiny-mtp": 24, "0.6b": 24, "1.7b": 8}
+S_SEED = 3
+
+
+def make_frames(preset: str, gguf_dir: str = "/tmp"):
+    m = qtts_pkg.load()
+    synth = m.synth
+    cfg = synth.PRESETS[preset]
+    path = os.path.join(gguf_dir, f"synth-{preset}-{SEED}.gguf")
+    if not os.path.exists(path):
+        synth.write_gguf(path, preset, SEED)
+    toks = synth.synth_tokens(cfg, TEXT)
+    spk = synth.synth_speaker(cfg)
+    R = ref.Reference(path)
+    out = {}
+    # greedy base run
+    n = FRAMES[preset]
+    codes, _ = R.generate(toks, spk, max_len=n, temperature=0.0)
+    tr = R.generate_trace(toks, spk, max_len=n, temperature=0.0)
+    assert np.array_equal(tr["codes"], codes), "trace replay differs from generate()"
+    g = G_FRAMES[preset]
+    out.update(g_codes=codes, g_raw=tr["raw"][:g], g_hidden=tr["hidden"][:g], g_step_embd=tr["step_embd"][:g])
+    cpl = []
+    for f in (1, 2):
+        c15, lg = R.predict_codes_logits(tr["hidden"][f], int(codes[f, 0]))
+        assert np.array_equal(c15, codes[f, 1:])
+        cpl.append(lg)
+    out["g_cp_logits"] = np.stack(cpl)
+    # run to EOS
+    toks_e = synth.synth_tokens(cfg, "Hi")
+    codes_e, _ = R.generate(toks_e, None, max_len=400, temperature=0.0)
+    te = R.generate_trace(toks_e, None, max_len=400, temperature=0.0)
+    assert np.array_equal(te["codes"], codes_e) and te["eos_frame"] == len(codes_e), "EOS trace differs from generate()"
+    expected = max(20, 4 * len(toks_e))
+    fr = sorted({expected - 1, expected, expected + 1, (expected + te["eos_frame"]) // 2, te["eos_frame"] - 1, te["eos_frame"]})
+    fr = [f for f in fr if 0 <= f < te["raw"].shape[0]]
+    out.update(e_tokens=toks_e, e_codes=codes_e, e_eos_frame=np.int32(te["eos_frame"]), e_frames=np.asarray(fr, np.int32),
+               e_raw=te["raw"][fr], e_proc=te["proc"][fr])
+    # sampled run, seeded
+    ns = S_FRAMES[preset]
+    R.seed_rng(S_SEED)
+    codes_s, _ = R.generate(toks, spk, max_len=ns, temperature=0.9, top_k=50)
+    R.seed_rng(S_SEED)
+    ts = R.generate_trace(toks, spk, max_len=ns, temperature=0.9, top_k=50)
+    assert np.array_equal(ts["codes"], codes_s), "sampled trace differs from generate()"
+    u = np.zeros((ts["raw"].shape[0], 16), np.float64)
+    u[:, 0] = ts["u_cb0"]
+    u[:ts["n_frames"], 1:] = ts["u_cp"]
+    out.update(s_codes=codes_s, s_u=u, s_eos_frame=np.int32(ts["eos_frame"]), s_seed=np.int32(S_SEED),
+               s_proc=ts["proc"][:4], s_temperature=np.float32(0.9), s_top_k=np.int32(50))
+    dst = os.path.join(ROOT, "tests", "golden", f"ref_{preset}_seed{SEED}_frames.npz")
+    np.savez_compressed(dst, **out)
+    print(f"{dst}: greedy {len(codes)} frames, EOS run stops at {te['eos_frame']}, sampled {len(codes_s)} frames "
+          f"(eos {ts['eos_frame']}), {os.path.getsize(dst) / 1e3:.0f} kB")
+    R.close()
+
+
 if __name__ == "__main__":
-    for p in (sys.argv[1:] or ["tiny", "tiny-mtp"]):
-        make(p)
+    args = sys.argv[1:]
+    if args and args[0] == "frames":
+        for p in (args[1:] or ["tiny", "tiny-mtp", "0.6b", "1.7b"]):
+            make_frames(p)
+    else:
+        for p in (args or ["tiny", "tiny-mtp"]):
+            make(p)

@@ -18,7 +18,9 @@ from test_oracle import load_gold, NMSE_TOL, ABS_TOL
 
 pytestmark = pytest.mark.gpu
 
-EXACT_FRAMES = {"tiny": 4, "tiny-mtp": 4, "0.6b": 2, "1.7b": 1}
+# free-running greedy ids equal to the reference's over at least this many leading frames (measured on B200 in
+# round 2, REFERENCE numerics: see DESIGN.md section 2); the first differing id must be a near-tie of the reference
+EXACT_FRAMES = {"tiny": 8, "tiny-mtp": 8, "0.6b": 32, "1.7b": 4}
 
 
 @pytest.fixture(scope="module")
@@ -57,12 +59,17 @@ def test_build_prefill_vs_golden(engines, preset):
 
 
 @pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b", "1.7b"])
-def test_talker_teacher_forced_vs_golden(engines, preset):
+@pytest.mark.parametrize("mode", [0, 1], ids=["reference", "fast"])
+def test_talker_teacher_forced_vs_golden(engines, preset, mode):
+    """forward_prefill + 3 forward_step calls against the reference's goldens, in BOTH numerics modes (FAST is what
+    bench.py runs: same rounding points, FP32 P.V accumulation in the decode attention)."""
     T, cfg, _ = engines(preset)
     g = load_gold(preset)
-    T.set_numerics(0, int(g["threads"]))
+    T.set_numerics(mode, int(g["threads"]))
     T.clear_kv_cache()
-    hid, logits = T.forward_prefill(g["prefill"])
+    hid_all, logits = T.forward_prefill(g["prefill"])
+    assert hid_all.shape == (g["prefill"].shape[0], cfg.hidden_size)      # every row, like the reference (:1893)
+    hid = hid_all[-1]
     # max|d| is stated for Talker logits of the 0.6B scale; with the same N(0, 0.02) init they grow as sqrt(hidden),
     # so the absolute bound scales with it (1.7b preset: hidden 2048 -> 5.7e-3); the NMSE bound is scale-free
     abs_tol = ABS_TOL * max(1.0, (cfg.hidden_size / 1024.0) ** 0.5)
@@ -75,6 +82,51 @@ def test_talker_teacher_forced_vs_golden(engines, preset):
         assert nmse(lg, g["step_logits"][i]) <= NMSE_TOL
         assert np.abs(lg - g["step_logits"][i]).max() <= abs_tol
         assert nmse(hd, g["step_hidden"][i]) <= NMSE_TOL
+    T.set_numerics(0, 4)
+
+
+def test_forward_prefill_all_rows_and_forward_text_codec(engines, pkg, ref_mod):
+    """forward_prefill's [n_tokens x H] output, forward_text and forward_codec (src/tts_transformer.cpp:1829-1950,
+    2030-2040) against the compiled reference live."""
+    T, cfg, path = engines("tiny")
+    g = load_gold("tiny")
+    R = ref_mod.Reference(path)
+    R.init_kv(64)
+    T.set_numerics(0, 4)
+    T.clear_kv_cache()
+    hid_all, _ = T.forward_prefill(g["prefill"])
+    n, H = g["prefill"].shape
+    # the harness returns the last row; rows 0..n-2 are checked through prefixes (causal: row t of a longer prefill
+    # equals the last row of the prefill cut after t + 1 rows)
+    for t in (0, 3, n - 1):
+        R.init_kv(64)
+        h_t, _ = R.forward_prefill(g["prefill"][:t + 1])
+        assert nmse(hid_all[t], h_t) <= NMSE_TOL, t
+    # forward_codec: codec_embd row -> forward_step at n_past = n
+    R.init_kv(64)
+    R.forward_prefill(g["prefill"])
+    import restate
+    model = restate.Model.from_gguf(path, pkg.gguf_io.parse_config)
+    tok = 123
+    emb = model.t["talker.codec_embd.weight"][tok].astype(np.float32)
+    lr, _ = R.forward_step(emb, n)
+    lt = T.forward_codec(tok, n)
+    assert lt is not None, T.get_error()
+    assert nmse(lt, lr) <= NMSE_TOL
+    # forward_text: text projection rows (+ speaker) -> prefill
+    toks = g["tokens"][:6]
+    spk = g["speaker"]
+    S = restate.Restatement(model, n_ctx=64)
+    rows = (S.project_text_tokens(list(int(x) for x in toks)) + spk[None, :]).astype(np.float32)
+    R.init_kv(64)
+    h_ref, _ = R.forward_prefill(rows)
+    T.clear_kv_cache()
+    h_eng = T.forward_text(toks, spk, 0)
+    assert h_eng is not None, T.get_error()
+    assert h_eng.shape == (6, H) and nmse(h_eng[-1], h_ref) <= NMSE_TOL
+    assert T.forward_text(toks[:0], spk, 0) is None and "n_tokens must be > 0" in T.get_error()
+    assert T.forward_step(emb, -1) is None and T.forward_step(emb, 10 ** 6) is None
+    R.close()
 
 
 @pytest.mark.parametrize("preset", ["tiny", "tiny-mtp", "0.6b", "1.7b"])
@@ -109,7 +161,27 @@ def test_generate_greedy_vs_golden(engines, preset, persistent):
     m = min(len(out), len(ref))
     bad = (out[:m] != ref[:m]).any(axis=1)
     first_bad = int(np.argmax(bad)) if bad.any() else m
-    assert first_bad >= EXACT_FRAMES[preset], f"greedy ids diverge at frame {first_bad}"
+    print(f"{preset} persistent={persistent}: free-running greedy ids equal the reference's for {first_bad} of {m} frames")
+    assert first_bad >= min(EXACT_FRAMES[preset], m), f"greedy ids diverge at frame {first_bad}"
+    if first_bad < m:
+        # the first differing id must be a near-tie of the reference (top-2 margin within twice the logit tolerance)
+        import ref as ref_live
+        if ref_live.available():
+            import restate
+            R = ref_live.Reference(engines(preset)[2])
+            tr = R.generate_trace(g["tokens"], g["speaker"], max_len=first_bad + 1, temperature=0.0)
+            book = int(np.argmax(out[first_bad] != ref[first_bad]))
+            if book == 0:
+                lg = restate.cb0_postprocess(tr["raw"][first_bad], set(int(c) for c in ref[:first_bad, 0]), first_bad,
+                                             len(g["tokens"]), 1.05, 2150, 3072)
+                lg = lg[np.isfinite(lg)]
+            else:
+                _, cpl = R.predict_codes_logits(tr["hidden"][first_bad], int(ref[first_bad, 0]))
+                lg = cpl[book - 1]
+            R.close()
+            top2 = np.sort(lg)[-2:]
+            abs_tol = ABS_TOL * max(1.0, (cfg.hidden_size / 1024.0) ** 0.5)
+            assert top2[1] - top2[0] <= 2 * abs_tol, f"frame {first_bad} code {book}: margin {top2[1] - top2[0]:.3e} is not a near-tie"
 
 
 def test_persistent_equals_stagewise(engines):
@@ -186,30 +258,37 @@ def test_fast_numerics_close_to_reference_numerics(engines):
     for mode in (0, 1):
         T.set_numerics(mode, 4)
         T.clear_kv_cache()
-        T.forward_prefill(g["prefill"])
+        T.forward_prefill(g["prefill"], all_rows=False)
         outs.append(T.forward_step(g["step_embd"][0], n_past)[0])
     T.set_numerics(0, 4)
-    assert nmse(outs[1], outs[0]) <= 1e-4
+    assert nmse(outs[1], outs[0]) <= 2e-5
 
 
-def test_live_reference_long_context(engines, pkg, ref_mod):
+@pytest.mark.parametrize("mode", [0, 1], ids=["reference", "fast"])
+@pytest.mark.parametrize("n", [520, 1100])
+def test_live_reference_long_context(engines, pkg, ref_mod, mode, n):
     """>= 512 keys: the reference's split-KV flash attention depends on its thread count
-    (ops.cpp:8740-8772); the engine reproduces the 4-thread reduction order."""
-    T, cfg, path = engines("tiny")
+    (ops.cpp:8740-8772); REFERENCE numerics reproduce the 4-thread reduction order, FAST numerics (what bench.py
+    runs) merge FP32 split-KV partials across CTAs (9 key ranges at 1100 keys)."""
+    T, cfg, path = engines("tiny", max_ctx=1280)
     R = ref_mod.Reference(path)
-    R.init_kv(1024)
+    R.init_kv(1280)
     r = np.random.default_rng(2)
-    n = 520
     emb = (0.05 * r.standard_normal((n + 4, cfg.hidden_size))).astype(np.float32)
-    T.set_numerics(0, 4)
+    T.set_numerics(mode, 4)
     T.clear_kv_cache()
-    for c0 in range(0, n, 52):                      # fill the cache through prefill chunks
-        R.forward_prefill(emb[c0:c0 + 52], n_past=c0)
-        T.forward_prefill(emb[c0:c0 + 52], n_past=c0)
+    step = 52 if n == 520 else 55
+    for c0 in range(0, n, step):                    # fill the cache through prefill chunks
+        R.forward_prefill(emb[c0:c0 + step], n_past=c0)
+        assert T.forward_prefill(emb[c0:c0 + step], n_past=c0, all_rows=False) is not None, T.get_error()
+    worst = 0.0
     for i in range(3):
         lr, hr = R.forward_step(emb[n + i], n + i)
         lg, hg = T.forward_step(emb[n + i], n + i)
+        worst = max(worst, nmse(lg, lr), nmse(hg, hr))
         assert nmse(lg, lr) <= 10 * NMSE_TOL and nmse(hg, hr) <= 10 * NMSE_TOL
+    print(f"long context {n} keys, numerics {mode}: worst NMSE {worst:.2e}")
+    T.set_numerics(0, 4)
     R.close()
 
 

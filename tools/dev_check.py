@@ -44,6 +44,7 @@ def check(preset, n_frames, text="Hello, world!", speaker=True, n_text=None):
     hid_r, log_r = R.forward_prefill(pre_r)
     T.clear_kv_cache()
     hid_g, log_g = T.forward_prefill(pre_r)
+    hid_g = hid_g[-1]
     print(f"[{preset}] forward_prefill nmse logits {nmse(log_g, log_r):.3e} hidden {nmse(hid_g, hid_r):.3e} "
           f"argmax {log_r.argmax()} {log_g.argmax()}")
     # --- forward_step (teacher-forced on reference inputs), both numerics
