@@ -41,10 +41,20 @@ def load_frames(preset):
     return np.load(p)
 
 
+_TRACES = {}
+
+
 def live_trace(ref_available, path, toks, spk, n, temperature=0.0, seed=None):
-    """The reference's per-frame intermediates, live (None when oracle/_ref did not travel)."""
+    """The reference's per-frame intermediates, live (None when oracle/_ref did not travel); cached per input."""
     if not ref_available:
         return None
+    key = (path, tuple(int(t) for t in toks), None if spk is None else spk.tobytes(), n, temperature, seed)
+    if key not in _TRACES:
+        _TRACES[key] = _live_trace(path, toks, spk, n, temperature, seed)
+    return _TRACES[key]
+
+
+def _live_trace(path, toks, spk, n, temperature, seed):
     import ref
     R = ref.Reference(path)
     if seed is not None:
