@@ -35,7 +35,7 @@ FRAMES = 512            # frames per utterance (configs[1])
 N_TEXT = 200            # synthetic text ids: EOS ramp would start at frame 4*208 > 512
 PRESET, SEED = "0.6b", 1234
 TEMP, TOP_K, REP_PEN = 0.9, 50, 1.05
-REF_FRAMES = 24         # bounded CPU sample per step of the reference arm
+REF_FRAMES = (8, 136)   # reference arm: two generate() lengths per step; frame loop = their difference (128 frames)
 B_FRAMES = 64           # frames per stream of the batched legs (configs[2] / configs[3])
 B_TEXT = (32, 256)      # ragged text lengths of the batched legs
 B_TOTAL = 512           # configs[3]: 512 concurrent streams sharded by utterance over the GPUs
@@ -45,6 +45,9 @@ METRIC, UNIT = "codec_frames_per_s", "frames/s"
 #   talker 887,095,296 + code-pred layers 15 x 157,286,400 + lm_heads 62,914,560
 WEIGHT_BYTES_PER_FRAME = 887_095_296 + 15 * 157_286_400 + 62_914_560
 KV_BYTES_PER_TOKEN = 114_688      # 28 layers x 2 x 8 x 128 x 2 B, read per cached token per frame
+FLOP_PER_FRAME_STREAM = 2 * (443_547_648 + 16 * 78_643_200 + 31_457_280)     # 3.467 GFLOP
+ATTN_FLOP_PER_KEY = 229_376       # 2 x 2 x 16 heads x 128 x 28 layers per cached key
+LOCKSTEP_GROUP = 256              # streams one launch of qtts_run_batched advances (qtts_engine.h: Engine::bgroup)
 
 
 def gguf_path() -> str:
@@ -108,6 +111,17 @@ def measured_peak_hbm():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def measured_peak_tensor():
+    """sustained dense BF16 TFLOP/s: the batched kernel is timed inside a long step"""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+        except Exception:
+            pass
+    return 1400.0, "fallback (B200_PROFILING.md ~1.4 PFLOP/s sustained)"
+
+
 # ---------------------------------------------------------------------------------------------------
 # reference arm / cpu_baseline: the UNMODIFIED reference on the host cores (oracle/_ref)
 # ---------------------------------------------------------------------------------------------------
@@ -118,26 +132,35 @@ def host_cores() -> int:
         return os.cpu_count() or 1
 
 
-def time_reference(path: str, toks, spk, n_frames: int, steps: int, warmup: int, threads: int):
-    """Returns (frames_per_s over whole generate() calls, ms list, frames list)."""
+def time_reference(path: str, toks, spk, steps: int, warmup: int, threads: int, lengths=REF_FRAMES):
+    """The UNMODIFIED reference's generate() (oracle/_ref, ggml CPU backend) timed at two lengths per step.
+    The reference exposes no timer inside generate() (src/tts_transformer.cpp:2342-2574), so the frame loop is the
+    difference: frames(long) - frames(short) over ms(long) - ms(short); the short call's time is prefill
+    (text projection + 10-token pass) plus its few frames.  Returns a dict."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import ref
     if not ref.available():
         raise RuntimeError("oracle/_ref/libqtts_ref.so is missing (make -f oracle/Makefile.ref)")
     R = ref.Reference(path, threads=threads)
-    ms, frames = [], []
+    rows = []
     for i in range(warmup + steps):
-        # greedy: the reference seeds its sampler from std::random_device (src/tts_transformer.h:298),
-        # so a sampled run would stop at a random frame; per-frame arithmetic is identical
-        codes, wall_ms = R.generate(toks, spk, max_len=n_frames, temperature=0.0, top_k=TOP_K, rep_pen=REF_PEN)
+        # greedy: the reference has no EOS-off switch and seeds its sampler from std::random_device
+        # (src/tts_transformer.h:298), so a sampled run would stop at a random frame; the per-frame
+        # arithmetic (Talker step + 16 code-predictor positions) is the same
+        c0, ms0 = R.generate(toks, spk, max_len=lengths[0], temperature=0.0, top_k=TOP_K, rep_pen=REP_PEN)
+        c1, ms1 = R.generate(toks, spk, max_len=lengths[1], temperature=0.0, top_k=TOP_K, rep_pen=REP_PEN)
         if i >= warmup:
-            ms.append(wall_ms)
-            frames.append(len(codes))
+            rows.append((len(c0), ms0, len(c1), ms1))
     R.close()
-    return sum(frames) / (sum(ms) / 1e3), ms, frames
-
-
-REF_PEN = REP_PEN
+    f0 = sum(r[0] for r in rows); m0 = sum(r[1] for r in rows); f1 = sum(r[2] for r in rows); m1 = sum(r[3] for r in rows)
+    loop_frames, loop_ms = f1 - f0, m1 - m0
+    if loop_frames <= 0 or loop_ms <= 0:
+        raise RuntimeError(f"reference stopped early (frames {f0}/{f1}): cannot separate the frame loop")
+    ms_per_frame = loop_ms / loop_frames
+    prefill_ms = (m0 - f0 * ms_per_frame) / len(rows)
+    return {"loop_fps": loop_frames / (loop_ms / 1e3), "ms_per_frame": ms_per_frame, "prefill_ms": prefill_ms,
+            "call_fps": f1 / (m1 / 1e3), "long_call_ms": m1 / len(rows), "frames_long": f1 // len(rows),
+            "frames_short": f0 // len(rows), "threads": threads, "steps": len(rows)}
 
 
 def run_reference(args, pkg):
@@ -149,15 +172,28 @@ def run_reference(args, pkg):
     toks = pkg.synth.synth_tokens(cfg, n_text=N_TEXT, seed=0)
     spk = pkg.synth.synth_speaker(cfg)
     cores = host_cores()
-    fps, ms, frames = time_reference(path, toks, spk, REF_FRAMES, args.steps, args.warmup, cores)
-    sample = (f"{args.steps} x generate() of {REF_FRAMES} frames (prefill of {len(toks)} text tokens included), greedy, "
-              f"same GGUF/text/speaker as the GPU arm, ggml CPU backend, {cores} threads")
-    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True, "scaling": "weak",
+    r = time_reference(path, toks, spk, args.steps, args.warmup, cores)
+    # the reference as shipped ignores -j and runs ggml's default of 4 threads (src/main.cpp:203-214,
+    # ggml/include/ggml.h:232): BASELINE.md section 3 promises that row too
+    r4 = time_reference(path, toks, spk, 1, 0, 4) if cores != 4 else r
+    sample = (f"{r['steps']} x [generate({r['frames_short']} frames) + generate({r['frames_long']} frames)], greedy, same GGUF / text "
+              f"({len(toks)} tokens) / speaker as the GPU arm, unmodified reference on the ggml CPU backend, {cores} threads; "
+              f"value = frame loop only ({r['frames_long'] - r['frames_short']} frames by difference, {r['ms_per_frame']:.1f} ms/frame), "
+              f"prefill {r['prefill_ms']:.0f} ms per call reported separately; e2e = whole generate({r['frames_long']}) calls incl. prefill")
+    conf = workload_config(1)
+    conf["workload"] = (f"BASELINE configs[1] workload on the reference's CPU path, BOUNDED sample: Qwen3-TTS-12Hz-0.6B random-init, batch 1, "
+                        f"{r['frames_long']} frames per generate() (not {FRAMES}), GREEDY (temperature 0, not {TEMP}: the reference cannot "
+                        f"suppress EOS and would stop at a random frame when sampling)")
+    conf.update({"frames_per_step": r["frames_long"], "temperature": 0.0, "numerics": "ggml-cpu (F16 weights, F32 accumulate)",
+                 "eos": "not suppressed (greedy run did not reach EOS)", "l2": "n/a (CPU)", "parallelism": f"{cores} host threads"})
+    line = {"impl": "reference", "metric": METRIC, "value": r["loop_fps"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["long_call_ms"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16 weights / f32 accumulate (ggml-cpu)", "data": "synthetic",
-            "config": workload_config(1),
-            "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
-            "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "config": conf, "ms_per_frame": r["ms_per_frame"], "prefill_ms_per_call": r["prefill_ms"],
+            "cpu_baseline": {"value": r["loop_fps"], "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample,
+                             "default_4_threads": {"value": r4["loop_fps"], "ms_per_frame": r4["ms_per_frame"],
+                                                   "prefill_ms_per_call": r4["prefill_ms"], "cores": 4}},
+            "e2e": {"value": r["call_fps"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
@@ -272,36 +308,55 @@ def run_ours(args, pkg):
                              "algorithmic_bytes_per_frame": bytes_per_frame},
                 "clocks": clocks.summary()}
         line["gpu_launches"] = launches + sum(b["launches"] for b in batched)
+        tpeak, tpeak_src = measured_peak_tensor()
         line["batched"] = []
         for b in batched:
             S = b["streams_per_gpu"]
             fps = b["frames"] / (b["dev_ms"] / 1e3)
             step_ms = b["dev_ms"] / (b["frames"] / (S * world))
-            # one frame-step of a group of <= 128 streams streams the weights once; KV per stream
-            groups = (S + 127) // 128
-            bytes_step = groups * WEIGHT_BYTES_PER_FRAME + S * KV_BYTES_PER_TOKEN * (b["n_kv_mean"] + 1)
-            ach = bytes_step / (step_ms / 1e3) / 1e9
-            line["batched"].append({
-                "workload": ("BASELINE configs[2]: 64 concurrent utterances on one GPU" if S == 64 and world == 1 else
-                             f"BASELINE configs[3]: {B_TOTAL} concurrent streams sharded by utterance over {world} GPU(s)"
-                             if S * world == B_TOTAL else
-                             f"one full lock-step group per GPU: {S} streams x {world} GPU(s), sharded by utterance") +
-                            f", ragged texts {B_TEXT[0]}-{B_TEXT[1]} tokens, cached speaker embeddings, temperature {TEMP} top-k {TOP_K}, "
-                            f"{B_FRAMES} frames per stream, batched tcgen05 kernel (groups of <= 256 streams in lock step)",
-                "streams_per_gpu": S, "streams_total": S * world, "value": fps, "unit": UNIT,
-                "ms_per_frame_step": step_ms, "rtf_per_stream": (step_ms / 1e3) * 12.5,
-                "e2e": {"value": b["frames"] / (b["wall_ms"] / 1e3), "unit": UNIT,
-                        "includes": "stream_prepare per stream (token/speaker H2D, embedding assembly) + one batched prefill_pending + step_frames with codes D2H",
-                        "stream_begin_ms_total": b["begin_ms"]},
-                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                             "kernel": "qtts_run_batched", "algorithmic_bytes_per_frame_step": bytes_step}})
+            # One launch of qtts_run_batched advances one lock-step group of <= 256 streams and streams the weights once
+            # for it; S streams on a GPU are ceil(S / 256) groups launched back to back (qtts_step_frames), so the
+            # kernel's algorithmic bytes count the weights once PER GROUP.  The job-level minimum (weights once per
+            # frame-step whatever S is) is reported next to it: their ratio is the excess the grouping costs.
+            groups = (S + LOCKSTEP_GROUP - 1) // LOCKSTEP_GROUP
+            kv_bytes = S * KV_BYTES_PER_TOKEN * (b["n_kv_mean"] + 1)
+            bytes_launched = groups * WEIGHT_BYTES_PER_FRAME + kv_bytes
+            bytes_min = WEIGHT_BYTES_PER_FRAME + kv_bytes
+            ach = bytes_min / (step_ms / 1e3) / 1e9
+            flops = S * (FLOP_PER_FRAME_STREAM + ATTN_FLOP_PER_KEY * b["n_kv_mean"])
+            tf = flops / (step_ms / 1e3) / 1e12
+            ridge = tpeak * 1e12 / (peak * 1e9)        # streams per GPU above which the weight GEMMs are FLOP-bound
+            wl = ("configs[2]: 64 concurrent utterances on 1 GPU" if S == 64 and world == 1 else
+                  f"configs[3]: {B_TOTAL} streams sharded over {world} GPU(s)" if S * world == B_TOTAL else
+                  f"full lock-step group: {S} streams x {world} GPU(s)")
+            entry = {"workload": wl, "streams_per_gpu": S, "streams_total": S * world, "value": round(fps, 1), "unit": UNIT,
+                     "ms_per_frame_step": round(step_ms, 3), "e2e": round(b["frames"] / (b["wall_ms"] / 1e3), 1),
+                     "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                                  "groups": groups, "bytes_min": int(bytes_min), "bytes_launched": int(bytes_launched),
+                                  "excess": round(bytes_launched / bytes_min, 3)}}
+            if S >= ridge:
+                entry["roofline_tensor"] = {"bound": "tensor", "achieved": round(tf, 2), "peak": tpeak, "unit": "TFLOP/s",
+                                            "frac": round(tf / tpeak, 4), "ridge_streams": round(ridge, 1)}
+            else:
+                entry["tensor_tflops"] = round(tf, 2)
+            line["batched"].append(entry)
+            # every leg also goes out as its own short line BEFORE the headline line, so a truncated tail keeps it
+            print(json.dumps({"batched_leg": entry, "n_gpus": world, "frames_per_stream": B_FRAMES, "text_tokens": list(B_TEXT),
+                              "temperature": TEMP, "top_k": TOP_K, "kernel": "qtts_run_batched",
+                              "e2e_includes": "stream_prepare per stream (H2D, embedding assembly) + batched prefill + step_frames with codes D2H",
+                              "peak_source": peak_src, "tensor_peak_source": tpeak_src}), flush=True)
         if world == 1 and not args.no_cpu_baseline:
             try:
                 cores = host_cores()
-                fps, ms, fr = time_reference(path, toks, spk, 48, 1, 0, cores)
-                line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": cores, "kind": "reference",
-                                        "sample": f"1 x generate() of {fr[0]} frames incl. prefill, greedy, same GGUF/text, "
-                                                  f"unmodified reference on ggml CPU backend ({ms[0] / 1e3:.1f} s)"}
+                r = time_reference(path, toks, spk, 1, 0, cores, lengths=(8, 72))
+                r4 = time_reference(path, toks, spk, 1, 0, 4, lengths=(4, 36)) if cores != 4 else r
+                line["cpu_baseline"] = {"value": r["loop_fps"], "unit": UNIT, "cores": cores, "kind": "reference",
+                                        "sample": f"frame loop of the unmodified reference (ggml CPU backend, {cores} threads) by difference of "
+                                                  f"generate({r['frames_short']}) and generate({r['frames_long']}), greedy, same GGUF / text / speaker: "
+                                                  f"{r['ms_per_frame']:.1f} ms/frame; prefill {r['prefill_ms']:.0f} ms per call on top",
+                                        "prefill_ms_per_call": r["prefill_ms"],
+                                        "default_4_threads": {"value": r4["loop_fps"], "ms_per_frame": r4["ms_per_frame"], "cores": 4,
+                                                              "note": "the reference ignores -j: ggml default (ggml/include/ggml.h:232)"}}
             except Exception as ex:   # the checker is missing: say so instead of inventing a number
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
         print(json.dumps(line), flush=True)

@@ -10,7 +10,7 @@
 
 #include "qtts_transformer.hpp"
 
-using qtts_b200::CodePredictor;
+using qtts_b200::TRTCodePredictor;
 using qtts_b200::TTSTransformer;
 
 static void print_ints(const char * key, const std::vector<int32_t> & v, bool comma = true) {
@@ -95,7 +95,7 @@ int main(int argc, char ** argv) {
 
     // 2. the same first frame by hand: build_prefill -> forward_prefill -> greedy cb0 -> code predictor loop
     std::vector<float> prefill, trailing, pad, hidden, logits;
-    if (!tr.init_kv_cache(4096) || !tr.build_prefill(tokens.data(), (int32_t) tokens.size(), nullptr, 2050, prefill, trailing, pad)) {
+    if (!tr.init_kv_cache(256) || !tr.build_prefill(tokens.data(), (int32_t) tokens.size(), nullptr, 2050, prefill, trailing, pad)) {
         fprintf(stderr, "build_prefill failed: %s\n", tr.get_error().c_str());
         return 1;
     }
@@ -107,25 +107,64 @@ int main(int argc, char ** argv) {
     // greedy over the unsuppressed range (generate(): src/tts_transformer.cpp:2432-2440 keeps [0, vocab-1024) + EOS)
     int cb0 = 0;
     for (int i = 1; i < cfg.codec_vocab_size - 1024; ++i) if (logits[i] > logits[cb0]) cb0 = i;
-    CodePredictor cp(tr);
-    std::vector<int32_t> greedy15(cfg.n_codebooks - 1), via_class;
-    if (!cp.run_greedy_loop(hidden.data(), cfg.hidden_size, cb0, cfg.cp_hidden_size != cfg.hidden_size, greedy15.data(),
+    if ((int) hidden.size() != n_prefill * cfg.hidden_size) { fprintf(stderr, "forward_prefill: output is not [n_tokens x H]\n"); return 1; }
+    const float * last_hidden = hidden.data() + (size_t) (n_prefill - 1) * cfg.hidden_size;
+    TRTCodePredictor cp(tr);
+    const bool needs_proj = cfg.code_pred_hidden_size != cfg.hidden_size;
+    std::vector<int32_t> greedy15(cfg.n_codebooks - 1), via_class, stepwise;
+    if (!cp.run_greedy_loop(last_hidden, cfg.hidden_size, cb0, needs_proj, greedy15.data(),
                             (int32_t) greedy15.size())) {
         fprintf(stderr, "run_greedy_loop failed: %s\n", cp.get_error().c_str());
         return 1;
     }
-    if (!tr.predict_codes_autoregressive(hidden.data(), cb0, via_class, 0.0f, 0)) {
+    if (!tr.predict_codes_autoregressive(last_hidden, cb0, via_class, 0.0f, 0)) {
         fprintf(stderr, "predict_codes_autoregressive failed: %s\n", tr.get_error().c_str());
         return 1;
     }
+    // the same 15 codes position by position through step / step_with_token, the way the reference's first TRT
+    // integration drove the engine (src/trt_code_predictor.h:53-66): pos 0 = hidden (no head), pos 1 = codec_embd[cb0]
+    // -> head 0, pos s + 1 = code_pred_embd[s - 1][code] -> head s
+    {
+        std::vector<float> lg(cfg.code_pred_vocab_size), hid(cfg.code_pred_hidden_size);
+        cp.reset_kv_cache();
+        if (!cp.step(last_hidden, cfg.hidden_size, 0, -1, needs_proj, hid.data(), (int32_t) hid.size())) {
+            fprintf(stderr, "step failed: %s\n", cp.get_error().c_str());
+            return 1;
+        }
+        int tok = cb0;
+        for (int s = 0; s < cfg.n_codebooks - 1; ++s) {
+            if (!cp.step_with_token(tok, s, s + 1, s, lg.data(), (int32_t) lg.size())) {
+                fprintf(stderr, "step_with_token failed: %s\n", cp.get_error().c_str());
+                return 1;
+            }
+            int best = 0;
+            for (int i = 1; i < cfg.code_pred_vocab_size; ++i) if (lg[i] > lg[best]) best = i;
+            stepwise.push_back(best);
+            tok = greedy15[s];          // teacher-forced on the loop's codes: every position is comparable
+        }
+    }
     // argument checking mirrors the reference's (wrong width is an error, not UB)
     int32_t dummy[15];
-    const bool bad_ok = cp.run_greedy_loop(hidden.data(), cfg.hidden_size + 1, cb0, false, dummy, 15);
+    const bool bad_ok = cp.run_greedy_loop(last_hidden, cfg.hidden_size + 1, cb0, false, dummy, 15);
+    // the upload_* calls validate the shapes the reference's load_model block would pass (src/tts_transformer.cpp:186-230)
+    std::vector<std::vector<float>> heads(15, std::vector<float>((size_t) cfg.code_pred_vocab_size * cfg.code_pred_hidden_size));
+    const bool up_ok = cp.upload_lm_heads(heads, cfg.code_pred_vocab_size, cfg.code_pred_hidden_size) &&
+                       !cp.upload_lm_heads(heads, cfg.code_pred_vocab_size + 1, cfg.code_pred_hidden_size);
+    // a second generate() must not replay the first one's uniforms (the seed advances), and a request beyond the
+    // engine's context cap must fail without losing the loaded model
+    std::vector<int32_t> codes2, codes3;
+    tr.generate(tokens.data(), (int32_t) tokens.size(), nullptr, max_len, codes2, 2050, 1.05f, temperature, top_k);
+    const bool too_long_fails = !tr.generate(tokens.data(), (int32_t) tokens.size(), nullptr, 100000, codes3);
+    const bool still_loaded = tr.generate(tokens.data(), (int32_t) tokens.size(), nullptr, 4, codes3, 2050, 1.05f, 0.0f, 0) && codes3.size() == 4u * cfg.n_codebooks;
 
     printf("{\n");
     printf("\"n_codebooks\": %d,\n\"n_frames\": %d,\n\"cb_calls\": %d,\n\"cb_frames\": %d,\n\"n_prefill\": %d,\n\"cb0\": %d,\n",
            cfg.n_codebooks, (int) (codes.size() / cfg.n_codebooks), cb_calls, cb_frames, n_prefill, cb0);
     printf("\"bad_width_rejected\": %s,\n", bad_ok ? "false" : "true");
+    printf("\"upload_validation\": %s,\n\"too_long_fails\": %s,\n\"still_loaded\": %s,\n", up_ok ? "true" : "false",
+           too_long_fails ? "true" : "false", still_loaded ? "true" : "false");
+    print_ints("codes_second_call", codes2);
+    print_ints("stepwise15", stepwise);
     print_ints("codes", codes);
     print_ints("greedy15", greedy15);
     print_ints("predict15", via_class, false);

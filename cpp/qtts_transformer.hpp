@@ -10,6 +10,8 @@
 #include <algorithm>
 #include <cstdint>
 #include <functional>
+#include <memory>
+#include <random>
 #include <string>
 #include <vector>
 
@@ -18,8 +20,58 @@
 
 namespace qtts_b200 {
 
-// reference: tts_transformer_config (src/tts_transformer.h:21-69); the C ABI struct carries the same fields
-using tts_transformer_config = qtts_config;
+// tts_transformer_config (src/tts_transformer.h:21-69): same field names and defaults, so that callers reading
+// get_config().n_attention_heads / code_pred_hidden_size / tts_bos_token_id ... compile unchanged.  The C ABI's
+// qtts_config carries the same values under shorter names (to_abi / from_abi below).
+struct tts_transformer_config {
+    int32_t text_vocab_size = 151936;
+    int32_t text_embd_dim = 2048;
+    int32_t hidden_size = 1024;
+    int32_t n_layers = 28;
+    int32_t n_attention_heads = 16;
+    int32_t n_key_value_heads = 8;
+    int32_t intermediate_size = 3072;
+    int32_t head_dim = 128;
+    float rms_norm_eps = 1e-6f;
+    float rope_theta = 1000000.0f;
+    int32_t mrope_section[3] = {24, 20, 20};      // parsed by the reference, never read (src/tts_transformer.h:37)
+    int32_t codec_vocab_size = 3072;
+    int32_t n_codebooks = 16;
+    int32_t code_pred_layers = 5;
+    int32_t code_pred_vocab_size = 2048;
+    int32_t code_pred_hidden_size = 0;
+    int32_t code_pred_intermediate_size = 0;
+    int32_t code_pred_n_attention_heads = 0;
+    int32_t code_pred_n_kv_heads = 0;
+    int32_t code_pred_head_dim = 0;
+    int32_t codec_pad_id = 2148;
+    int32_t codec_bos_id = 2149;
+    int32_t codec_eos_id = 2150;
+    int32_t tts_bos_token_id = 151672;
+    int32_t tts_eos_token_id = 151673;
+    int32_t tts_pad_token_id = 151671;
+    int32_t codec_think_id = 2154;
+    int32_t codec_nothink_id = 2155;
+    int32_t codec_think_bos_id = 2156;
+    int32_t codec_think_eos_id = 2157;
+    int32_t english_language_id = 2050;
+};
+
+inline tts_transformer_config from_abi(const qtts_config & c) {
+    tts_transformer_config r;
+    r.text_vocab_size = c.text_vocab_size; r.text_embd_dim = c.text_embd_dim; r.hidden_size = c.hidden_size;
+    r.n_layers = c.n_layers; r.n_attention_heads = c.n_heads; r.n_key_value_heads = c.n_kv_heads;
+    r.intermediate_size = c.intermediate_size; r.head_dim = c.head_dim; r.rms_norm_eps = c.rms_norm_eps;
+    r.rope_theta = c.rope_theta; r.codec_vocab_size = c.codec_vocab_size; r.n_codebooks = c.n_codebooks;
+    r.code_pred_layers = c.cp_layers; r.code_pred_vocab_size = c.cp_vocab_size; r.code_pred_hidden_size = c.cp_hidden_size;
+    r.code_pred_intermediate_size = c.cp_intermediate_size; r.code_pred_n_attention_heads = c.cp_n_heads;
+    r.code_pred_n_kv_heads = c.cp_n_kv_heads; r.code_pred_head_dim = c.cp_head_dim;
+    r.codec_pad_id = c.codec_pad_id; r.codec_bos_id = c.codec_bos_id; r.codec_eos_id = c.codec_eos_id;
+    r.tts_bos_token_id = c.tts_bos_id; r.tts_eos_token_id = c.tts_eos_id; r.tts_pad_token_id = c.tts_pad_id;
+    r.codec_think_id = c.codec_think_id; r.codec_nothink_id = c.codec_nothink_id;
+    r.codec_think_bos_id = c.codec_think_bos_id; r.codec_think_eos_id = c.codec_think_eos_id;
+    return r;
+}
 
 namespace detail {
 struct KeyU32 { int32_t qtts_config::* field; std::vector<const char *> keys; int64_t def; int32_t qtts_config::* fallback; };
@@ -75,7 +127,7 @@ public:
     // frame_callback_t, src/tts_transformer.h:222-223
     using frame_callback_t = std::function<bool(const int32_t *, int32_t, int32_t)>;
 
-    TTSTransformer() = default;
+    TTSTransformer() : seed_(std::random_device{}()) {}      // like rng_{std::random_device{}()}, src/tts_transformer.h:298
     ~TTSTransformer() { unload_model(); }
     TTSTransformer(const TTSTransformer &) = delete;
     TTSTransformer & operator=(const TTSTransformer &) = delete;
@@ -83,33 +135,37 @@ public:
     // engine-creation knobs without a counterpart in the reference (it owns one stream on one device)
     void set_device(int device) { device_ = device; }
     void set_max_streams(int n) { max_streams_ = n; }
+    // Sampling is seeded from std::random_device like the reference's rng_; set_seed makes a run reproducible.
+    // Every generate() call advances the seed, so repeated calls do not replay one uniform sequence.
     void set_seed(uint64_t seed) { seed_ = seed; }
 
-    // load_model (src/tts_transformer.cpp:155-286): parse config, create tensors, copy the data
+    // load_model (src/tts_transformer.cpp:51-286): parse config, create tensors, copy the data
     bool load_model(const std::string & model_path) {
         unload_model();
         GgufFile g;
         if (!g.open(model_path, error_msg_)) return false;
-        cfg_ = qtts_config{};
-        detail::parse_config(g, cfg_);
+        abi_cfg_ = qtts_config{};
+        detail::parse_config(g, abi_cfg_);
+        cfg_ = from_abi(abi_cfg_);
         model_path_ = model_path;
-        // the engine allocates its KV cache at creation; init_kv_cache may re-create it with another n_ctx
-        return create_engine(n_ctx_);
+        return create_engine(g);
     }
 
     // unload_model (src/tts_transformer.cpp:2576-2640)
     void unload_model() {
         if (eng_) qtts_destroy(eng_);
         eng_ = nullptr;
+        last_hidden_.clear();
     }
 
-    // init_kv_cache (src/tts_transformer.cpp:794-870): the reference frees and re-allocates
+    // init_kv_cache (src/tts_transformer.cpp:794-842): the reference frees and re-allocates the cache tensors; here
+    // qtts_resize_kv re-sizes the per-stream slabs and leaves the weights where they are
     bool init_kv_cache(int32_t n_ctx) {
         if (!eng_) { error_msg_ = "Model not loaded"; return false; }
         if (n_ctx <= 0) { error_msg_ = "init_kv_cache: n_ctx must be positive"; return false; }
         if (n_ctx != n_ctx_) {
-            unload_model();
-            if (!create_engine(n_ctx)) return false;
+            if (!check(qtts_resize_kv(eng_, std::max(n_ctx, 32), max_text_))) return false;     // on failure the old cache stays
+            n_ctx_ = std::max(n_ctx, 32);
         }
         return check(qtts_clear_kv_cache(eng_, 0));
     }
@@ -120,18 +176,42 @@ public:
         if (n_ctx > 16) { error_msg_ = "code predictor context is at most 16"; return false; }
         return true;
     }
-    void clear_code_pred_kv_cache() {}
+    void clear_code_pred_kv_cache() {}      // positions above the current one are never read
 
-    // forward_prefill (src/tts_transformer.cpp:1829-1920): output = normalised hidden of the last token
+    // forward_text (src/tts_transformer.cpp:1922-1950): output = hidden states [n_tokens, hidden_size]
+    bool forward_text(const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd, int32_t n_past,
+                      std::vector<float> & output) {
+        if (!eng_) { error_msg_ = "Model not loaded"; return false; }
+        if (!text_tokens) { error_msg_ = "text_tokens is null"; return false; }
+        if (n_tokens <= 0) { error_msg_ = "n_tokens must be > 0"; return false; }
+        output.resize((size_t) n_tokens * cfg_.hidden_size);
+        if (!check(qtts_forward_text(eng_, 0, text_tokens, n_tokens, speaker_embd, n_past, output.data()))) return false;
+        last_hidden_.assign(output.end() - cfg_.hidden_size, output.end());
+        return true;
+    }
+
+    // forward_prefill (src/tts_transformer.cpp:1829-1920): output = normalised hidden of EVERY token
+    // [n_tokens, hidden_size] (:1893), logits_out = logits of the last token
     bool forward_prefill(const float * prefill_embd, int32_t n_tokens, int32_t n_past,
                          std::vector<float> & output, std::vector<float> * logits_out = nullptr) {
         if (!eng_) { error_msg_ = "Model not loaded"; return false; }
-        output.resize(cfg_.hidden_size);
+        if (!prefill_embd) { error_msg_ = "prefill_embd is null"; return false; }
+        if (n_tokens <= 0) { error_msg_ = "n_tokens must be > 0"; return false; }
+        output.resize((size_t) n_tokens * cfg_.hidden_size);
         std::vector<float> logits(cfg_.codec_vocab_size);
         if (!check(qtts_forward_prefill(eng_, 0, prefill_embd, n_tokens, n_past, output.data(), logits.data()))) return false;
-        last_hidden_ = output;
+        last_hidden_.assign(output.end() - cfg_.hidden_size, output.end());
         if (logits_out) *logits_out = std::move(logits);
         return true;
+    }
+
+    // forward_codec (src/tts_transformer.cpp:2030-2040): output = codec logits
+    bool forward_codec(int32_t codec_token, int32_t n_past, std::vector<float> & output) {
+        if (!eng_) { error_msg_ = "Model not loaded"; return false; }
+        output.resize(cfg_.codec_vocab_size);
+        if (!check(qtts_forward_codec(eng_, 0, codec_token, n_past, output.data()))) return false;
+        last_hidden_.resize(cfg_.hidden_size);
+        return check(qtts_get_hidden_states(eng_, 0, last_hidden_.data()));
     }
 
     // forward_step (src/tts_transformer.cpp:1952-2028): output = codec logits
@@ -145,7 +225,7 @@ public:
         return true;
     }
 
-    // get_hidden_states (src/tts_transformer.cpp:2030-2040)
+    // get_hidden_states (src/tts_transformer.cpp:2042-2048)
     bool get_hidden_states(std::vector<float> & hidden) const {
         if (last_hidden_.empty()) return false;
         hidden = last_hidden_;
@@ -158,6 +238,7 @@ public:
                        int32_t language_id, std::vector<float> & prefill_embd,
                        std::vector<float> & trailing_text_hidden, std::vector<float> & tts_pad_embed) {
         if (!eng_) { error_msg_ = "Model not loaded"; return false; }
+        if (!fit(n_tokens, 0)) return false;
         int32_t pl = 0, tl = 0;
         const int H = cfg_.hidden_size;
         // first call sizes the outputs, second fills them
@@ -175,7 +256,7 @@ public:
                                       std::vector<int32_t> & output, float temperature = 0.9f,
                                       int32_t top_k = 50) {
         if (!eng_) { error_msg_ = "Model not loaded"; return false; }
-        output.resize(cfg_.n_codebooks - 1);
+        output.resize(15);                  // always 15, whatever n_codebooks says (:2192)
         return check(qtts_predict_codes(eng_, 0, hidden, codebook_0_token, temperature, top_k,
                                         nullptr, nullptr, output.data(), nullptr));
     }
@@ -186,25 +267,28 @@ public:
                   float repetition_penalty = 1.05f, float temperature = 0.9f, int32_t top_k = 50,
                   frame_callback_t on_frames = nullptr, int32_t callback_interval = 40) {
         if (!eng_) { error_msg_ = "Model not loaded"; return false; }
-        if (max_len + 64 + n_tokens > n_ctx_) {
-            // the reference sizes the cache from the request (:2378-2386); do the same
-            unload_model();
-            if (!create_engine(max_len + n_tokens + 64)) return false;
-        }
+        if (!text_tokens) { error_msg_ = "text_tokens is null"; return false; }
+        if (n_tokens < 4) { error_msg_ = "Need at least 4 text tokens for generation"; return false; }
+        if (max_len <= 0) { output.clear(); return true; }                   // :2364-2367
+        if (!fit(n_tokens, max_len)) return false;
         output.assign((size_t) max_len * cfg_.n_codebooks, 0);
         int32_t n_frames = 0;
         const int rc = qtts_generate(eng_, 0, text_tokens, n_tokens, speaker_embd, max_len, language_id,
                                      repetition_penalty, temperature, top_k, seed_, output.data(), &n_frames,
                                      on_frames ? &TTSTransformer::trampoline : nullptr, callback_interval,
                                      on_frames ? (void *) &on_frames : nullptr);
+        seed_ = seed_ * 6364136223846793005ull + 1442695040888963407ull;       // the next call draws a fresh sequence
         if (!check(rc)) { output.clear(); return false; }
         output.resize((size_t) n_frames * cfg_.n_codebooks);
+        last_hidden_.resize(cfg_.hidden_size);
+        qtts_get_hidden_states(eng_, 0, last_hidden_.data());
         return true;
     }
 
     const tts_transformer_config & get_config() const { return cfg_; }
     const std::string & get_error() const { return error_msg_; }
     qtts_engine * engine() const { return eng_; }
+    const qtts_config & abi_config() const { return abi_cfg_; }
 
 private:
     static int trampoline(const int32_t * codes, int32_t n_frames, int32_t n_codebooks, void * user) {
@@ -215,20 +299,31 @@ private:
         error_msg_ = eng_ ? qtts_last_error(eng_) : qtts_create_error();
         return false;
     }
-    bool create_engine(int32_t n_ctx) {
-        GgufFile g;
-        if (!g.open(model_path_, error_msg_)) return false;
-        if (qtts_create(&cfg_, device_, max_streams_, n_ctx, &eng_) == 0) {
+    // The reference re-sizes its KV cache from the request: required = prefill_len + max_len + 8, re-allocated when
+    // the cache is too small or more than max(2 * required, 512) (src/tts_transformer.cpp:2383-2388); prefill_len is
+    // at most 11.  Same policy, through qtts_resize_kv (weights untouched); a request beyond the engine's cap fails
+    // BEFORE anything is freed, the loaded engine stays usable.
+    bool fit(int32_t n_tokens, int32_t max_len) {
+        const int32_t required = 11 + max_len + 8;
+        int32_t n_ctx = n_ctx_, max_text = max_text_;
+        if (n_ctx < required || n_ctx > std::max<int32_t>(required * 2, 512)) n_ctx = std::max(required, 32);
+        if (n_tokens > max_text) max_text = std::max(n_tokens, 2 * max_text);
+        if (n_ctx == n_ctx_ && max_text == max_text_) return true;
+        if (!check(qtts_resize_kv(eng_, n_ctx, max_text))) return false;
+        n_ctx_ = n_ctx; max_text_ = max_text;
+        return true;
+    }
+    bool create_engine(GgufFile & g) {
+        if (qtts_create(&abi_cfg_, device_, max_streams_, n_ctx_, &eng_) == 0) {
             error_msg_ = qtts_create_error();
             eng_ = nullptr;
             return false;
         }
-        n_ctx_ = n_ctx;
         std::vector<uint8_t> buf;
         for (const auto & t : g.tensors()) {
             // vocoder / speaker-encoder tensors live in other GGUF files; unknown names are skipped by the engine
             if (!g.read_tensor(t, buf, error_msg_)) { unload_model(); return false; }
-            const int dtype = t.ggml_type == 0 ? QTTS_F32 : QTTS_F16;
+            const int dtype = t.ggml_type == 0 ? QTTS_F32 : t.ggml_type == 1 ? QTTS_F16 : -1;
             if (qtts_upload_tensor(eng_, t.name.c_str(), dtype, t.dims.data(), (int) t.dims.size(), buf.data()) == 0) {
                 error_msg_ = qtts_last_error(eng_);
                 unload_model();
@@ -244,22 +339,87 @@ private:
     }
 
     qtts_engine * eng_ = nullptr;
-    qtts_config cfg_{};
+    qtts_config abi_cfg_{};
+    tts_transformer_config cfg_{};
     std::string model_path_, error_msg_;
     std::vector<float> last_hidden_;
     int device_ = 0, max_streams_ = 1;
-    int32_t n_ctx_ = 4096;
-    uint64_t seed_ = 0;
+    int32_t n_ctx_ = 512, max_text_ = 512;
+    uint64_t seed_;
 };
 
-// Loop entry points of qwen3_tts::TRTCodePredictor (src/trt_code_predictor.h:61-79) over the same
-// engine: the reference keeps a second, TensorRT-built code predictor next to the transformer
-// (tts_transformer.h:304-311); here both views share one set of weights.
-class CodePredictor {
+// Drop-in for qwen3_tts::TRTCodePredictor (src/trt_code_predictor.h:25-87): the whole method set.  The reference
+// keeps this second, TensorRT-built copy of the code predictor next to the transformer (src/tts_transformer.h:304-311)
+// and feeds it from load_model (src/tts_transformer.cpp:155-230: load_engine, upload_lm_heads, upload_mtp_proj,
+// upload_codec_embeddings, warmup_cublas).  Here the code predictor lives in the same engine as the Talker:
+//   * attach(transformer): share the transformer's engine (the INTEGRATION.md section 2 hook);
+//   * load_engine(path): stand-alone - `path` is the model GGUF (there is no serialized .trt engine to load);
+//   * upload_*: the engine already holds these tensors from the GGUF, so the calls VALIDATE the shapes the
+//     reference would upload (vocab x hidden heads, cp_hidden x talker_hidden projection, 15 embedding tables of
+//     talker width) and keep nothing.
+class TRTCodePredictor {
 public:
-    explicit CodePredictor(TTSTransformer & owner) : tr_(owner) {}
+    TRTCodePredictor() = default;
+    explicit TRTCodePredictor(TTSTransformer & owner) : tr_(&owner) {}
+    ~TRTCodePredictor() { unload(); }
 
-    bool is_ready() const { return tr_.engine() != nullptr; }
+    void attach(TTSTransformer & owner) { unload(); tr_ = &owner; }
+
+    bool load_engine(const std::string & engine_path) {
+        unload();
+        own_.reset(new TTSTransformer());
+        if (!own_->load_model(engine_path)) { error_msg_ = "Failed to load code predictor: " + own_->get_error(); own_.reset(); return false; }
+        tr_ = own_.get();
+        return true;
+    }
+
+    bool upload_lm_heads(const std::vector<std::vector<float>> & weights, int32_t vocab_size, int32_t hidden_size) {
+        if (!ready()) return false;
+        const auto & c = tr_->get_config();
+        if ((int) weights.size() != 15 || vocab_size != c.code_pred_vocab_size || hidden_size != c.code_pred_hidden_size)
+            return fail("upload_lm_heads: shape does not match the loaded model");
+        for (const auto & w : weights) if (w.size() != (size_t) vocab_size * hidden_size) return fail("upload_lm_heads: bad weight size");
+        return true;
+    }
+    bool upload_mtp_proj(const std::vector<float> & weight, const std::vector<float> & bias, int32_t cp_hidden, int32_t talker_hidden) {
+        if (!ready()) return false;
+        const auto & c = tr_->get_config();
+        if (cp_hidden != c.code_pred_hidden_size || talker_hidden != c.hidden_size || weight.size() != (size_t) cp_hidden * talker_hidden ||
+            (!bias.empty() && bias.size() != (size_t) cp_hidden))
+            return fail("upload_mtp_proj: shape does not match the loaded model");
+        if (c.code_pred_hidden_size == c.hidden_size) return fail("upload_mtp_proj: the loaded model has no mtp_proj");
+        return true;
+    }
+    bool upload_codec_embeddings(const std::vector<std::vector<float>> & weights, int32_t embd_dim) {
+        if (!ready()) return false;
+        const auto & c = tr_->get_config();
+        if (weights.empty() || weights.size() > 15 || embd_dim != c.hidden_size) return fail("upload_codec_embeddings: shape does not match the loaded model");
+        for (size_t i = 0; i < weights.size(); ++i) {
+            const size_t vocab = i == 0 ? c.codec_vocab_size : c.code_pred_vocab_size;
+            if (weights[i].size() != vocab * (size_t) embd_dim) return fail("upload_codec_embeddings: bad table size");
+        }
+        return true;
+    }
+
+    void reset_kv_cache() {}                // positions above the current one are never read
+    void warmup_cublas() {}                 // nothing to warm: no cuBLAS, no JIT
+
+    // one position with a host input vector (src/trt_code_predictor.cpp:384-424)
+    bool step(const float * input, int32_t input_size, int32_t position_id, int32_t lm_head_idx, bool needs_proj,
+              float * output, int32_t output_size) {
+        if (!ready()) return false;
+        if (qtts_cp_step(tr_->engine(), 0, input, input_size, 0, 0, position_id, lm_head_idx, needs_proj ? 1 : 0, output, output_size) == 0)
+            return fail(qtts_last_error(tr_->engine()));
+        return true;
+    }
+    // one position from a device-resident embedding row (src/trt_code_predictor.cpp:426-482)
+    bool step_with_token(int32_t token_id, int32_t embedding_idx, int32_t position_id, int32_t lm_head_idx,
+                         float * output, int32_t output_size) {
+        if (!ready()) return false;
+        if (qtts_cp_step(tr_->engine(), 0, nullptr, 0, token_id, embedding_idx, position_id, lm_head_idx, 1, output, output_size) == 0)
+            return fail(qtts_last_error(tr_->engine()));
+        return true;
+    }
 
     // run_greedy_loop (src/trt_code_predictor.cpp:484-600).  needs_proj: the 1.7B Talker->code
     // predictor projection (mtp_proj) is part of the engine's program whenever the model has one,
@@ -268,34 +428,40 @@ public:
                          int32_t * output_tokens, int32_t n_outputs) {
         return run(hidden, hidden_size, cb0_token, needs_proj, 0.0f, 0, nullptr, output_tokens, n_outputs);
     }
-
-    // run_sampling_loop (src/trt_code_predictor.cpp:602-726): rand_vals = one uniform in [0,1) per code
+    // run_sampling_loop (src/trt_code_predictor.cpp:602-726): rand_vals = one uniform in [0,1) per code.
+    // Sampling rule: the GGML path's (mask `< k-th largest`, ties kept, softmax with a double sum, CDF scan against
+    // the uniform) - NOT k_sample_topk_f32's -1e30 mask and `rand * sum` scan (src/trt_cuda_kernels.cu:124,172);
+    // both select from the same candidate set, the id can differ when the uniform falls within float rounding of a step.
     bool run_sampling_loop(const float * hidden, int32_t hidden_size, int32_t cb0_token, bool needs_proj,
                            float temperature, int32_t top_k, const float * rand_vals,
                            int32_t * output_tokens, int32_t n_outputs) {
         return run(hidden, hidden_size, cb0_token, needs_proj, temperature, top_k, rand_vals, output_tokens, n_outputs);
     }
 
-    const std::string & get_error() const { return err_.empty() ? tr_.get_error() : err_; }
+    bool is_loaded() const { return tr_ && tr_->engine() != nullptr; }
+    bool is_ready() const { return is_loaded(); }
+    const std::string & get_error() const { return error_msg_; }
+    void unload() { own_.reset(); tr_ = nullptr; }
 
 private:
+    bool fail(const std::string & m) { error_msg_ = m; return false; }
+    bool ready() { if (is_loaded()) return true; return fail("TRT code predictor not loaded"); }
     bool run(const float * hidden, int32_t hidden_size, int32_t cb0, bool needs_proj, float temperature, int32_t top_k,
              const float * rand_vals, int32_t * out, int32_t n_outputs) {
-        err_.clear();
-        if (!is_ready()) { err_ = "Model not loaded"; return false; }
-        const auto & c = tr_.get_config();
-        if (hidden_size != c.hidden_size) { err_ = "hidden_size does not match the model"; return false; }
-        if (needs_proj != (c.cp_hidden_size != c.hidden_size)) { err_ = "needs_proj does not match the model"; return false; }
-        if (n_outputs != c.n_codebooks - 1) { err_ = "n_outputs must be n_codebooks - 1"; return false; }
-        if (qtts_predict_codes(tr_.engine(), 0, hidden, cb0, temperature, top_k, rand_vals, nullptr, out, nullptr) == 0) {
-            err_ = qtts_last_error(tr_.engine());
-            return false;
-        }
+        if (!ready()) return false;
+        const auto & c = tr_->get_config();
+        if (hidden_size != c.hidden_size) return fail("hidden_size does not match the model");
+        if (needs_proj != (c.code_pred_hidden_size != c.hidden_size)) return fail("needs_proj does not match the model");
+        if (n_outputs != c.n_codebooks - 1) return fail("n_outputs must be n_codebooks - 1");
+        if (qtts_predict_codes(tr_->engine(), 0, hidden, cb0, temperature, top_k, rand_vals, nullptr, out, nullptr) == 0)
+            return fail(qtts_last_error(tr_->engine()));
         return true;
     }
-    TTSTransformer & tr_;
-    std::string err_;
+    TTSTransformer * tr_ = nullptr;
+    std::unique_ptr<TTSTransformer> own_;
+    std::string error_msg_;
 };
+using CodePredictor = TRTCodePredictor;     // round-1 name
 
 // Concurrent utterances on one GPU (the reference serves one utterance at a time):
 // begin() fills a slot, step() advances every live slot in lock step with the batched kernel.

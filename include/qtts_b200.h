@@ -135,6 +135,16 @@ int qtts_predict_codes(qtts_engine * e, int slot, const float * hidden, int32_t 
                        float temperature, int32_t top_k, const float * uniforms15,
                        const int32_t * forced15, int32_t * out15, float * logits_out);
 
+/* TRTCodePredictor::step / step_with_token (src/trt_code_predictor.h:53-66, .cpp:384-482): ONE code-predictor
+ * position at position_id in [0, 16) over the slot's 16-entry code-predictor cache (reset_kv_cache, :50, has nothing
+ * to clear: positions above the current one are never read).  input != NULL: F32 vector of input_size floats
+ * (hidden_size when needs_proj and the model has mtp_proj, else cp_hidden_size); input == NULL: row token_id of
+ * embedding table embedding_idx (0 = talker codec_embd, 1..14 = code_pred.codec_embd[0..13]).
+ * lm_head_idx >= 0: output = logits [cp_vocab]; < 0: output = normalised hidden [cp_hidden]. */
+int qtts_cp_step(qtts_engine * e, int slot, const float * input, int32_t input_size, int32_t token_id,
+                 int32_t embedding_idx, int32_t position_id, int32_t lm_head_idx, int needs_proj,
+                 float * output, int32_t output_size);
+
 /* frame callback: frame_callback_t (src/tts_transformer.h:164-170): codes for n_frames frames,
  * row-major [n_frames][n_codebooks]; return 0 to stop generation. */
 typedef int (*qtts_frame_cb)(const int32_t * codes, int32_t n_frames, int32_t n_codebooks,

@@ -347,6 +347,48 @@ int qtts_predict_codes(qtts_engine * h, int slot, const float * hidden, int32_t 
     return 1;
 }
 
+// TRTCodePredictor::step / step_with_token (src/trt_code_predictor.cpp:384-482): ONE code-predictor position.
+// input != NULL: an F32 vector of input_size floats (hidden_size when needs_proj and the model has mtp_proj, else
+// cp_hidden_size); input == NULL: row token_id of embedding table embedding_idx (0 = talker codec_embd,
+// 1..14 = code_pred.codec_embd[0..13], :46 of the header), always projected when the model has mtp_proj.
+// lm_head_idx in [0, 15): output = logits [cp_vocab]; < 0: output = normalised hidden [cp_hidden] (:342-382).
+int qtts_cp_step(qtts_engine * h, int slot, const float * input, int32_t input_size, int32_t token_id, int32_t embedding_idx,
+                 int32_t position_id, int32_t lm_head_idx, int needs_proj, float * output, int32_t output_size) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    const qtts_config & c = e->cfg;
+    if (position_id < 0 || position_id >= 16) { e->err = "cp_step: position_id must be in [0, 16)"; return 0; }
+    if (lm_head_idx >= c.n_codebooks - 1) { e->err = "cp_step: lm_head_idx out of range"; return 0; }
+    const int want_out = lm_head_idx >= 0 ? c.cp_vocab_size : c.cp_hidden_size;
+    if (!output || output_size < want_out) { e->err = "cp_step: output buffer too small"; return 0; }
+    const __half * table = nullptr;
+    bool proj;
+    if (input) {
+        proj = needs_proj != 0 && e->mtp != nullptr;
+        const int want_in = proj ? c.hidden_size : c.cp_hidden_size;
+        if (input_size != want_in) { e->err = "cp_step: input_size does not match the model"; return 0; }
+        cudaMemcpyAsync(s->cp_hidden_in, input, (size_t) want_in * sizeof(float), cudaMemcpyHostToDevice, e->stream);
+    } else {
+        if (embedding_idx < 0 || embedding_idx >= c.n_codebooks - 1) { e->err = "Invalid embedding index: " + std::to_string(embedding_idx); return 0; }
+        const int vocab = embedding_idx == 0 ? c.codec_vocab_size : c.cp_vocab_size;
+        if (token_id < 0 || token_id >= vocab) { e->err = "Token ID out of range: " + std::to_string(token_id); return 0; }
+        table = embedding_idx == 0 ? e->codec_embd : e->cp_embd[embedding_idx - 1];
+        proj = e->mtp != nullptr;
+        if (!proj && c.cp_hidden_size != c.hidden_size) { e->err = "cp_step: embedding rows need mtp_proj"; return 0; }
+        cudaMemcpyAsync(&s->tokens[0], &token_id, sizeof(int32_t), cudaMemcpyHostToDevice, e->stream);
+    }
+    cudaStreamSynchronize(e->stream);
+    std::vector<Op> P;
+    emit_cp_step(e, *s, P, s->cp_hidden_in, table, s->tokens, position_id, lm_head_idx, proj, s->misc);
+    if (!run_program(e, *s, P, 1, false)) return 0;
+    cudaError_t r = cudaStreamSynchronize(e->stream);
+    if (r != cudaSuccess) { e->err = std::string("cp_step: ") + cudaGetErrorString(r); return 0; }
+    cudaMemcpy(output, lm_head_idx >= 0 ? s->cp_logits : s->misc, (size_t) want_out * sizeof(float), cudaMemcpyDeviceToHost);
+    return 1;
+}
+
 // embeddings (A12) + per-stream state; the Talker prefill (A3) is left to the caller
 static bool stream_prepare(Engine * e, Slot & s, const int32_t * tokens, int32_t n, const float * speaker, int32_t max_len,
                            int32_t language_id, float rep_pen, float temperature, int32_t top_k, uint64_t seed) {

@@ -188,6 +188,8 @@ void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float 
                          float * dump, const int32_t * forced, const float * uniforms,
                          bool override_sampling, float temperature, int top_k);
 void emit_frame(Engine * e, Slot & s, std::vector<Op> & P);
+void emit_cp_step(Engine * e, Slot & s, std::vector<Op> & P, const float * in_vec, const __half * table,
+                  const int32_t * tok_ptr, int pos, int head, bool proj, float * hid_out);
 bool emit_build_prefill(Engine * e, Slot & s, std::vector<Op> & P, const int32_t * tokens, int n_tokens,
                         bool has_speaker, int language_id);
 bool run_program(Engine * e, Slot & s, const std::vector<Op> & P, int n_frames, bool check_done);

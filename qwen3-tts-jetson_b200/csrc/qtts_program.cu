@@ -163,6 +163,38 @@ void emit_code_predictor(Engine * e, Slot & s, std::vector<Op> & P, const float 
     }
 }
 
+// One single-token code-predictor position (TRTCodePredictor::step / step_with_token,
+// src/trt_code_predictor.cpp:384-482 -> run_trt_and_lm_head :303-382): input = an F32 vector already on the device
+// (in_vec) or row tok_ptr[0] of an F16 embedding table, projected by mtp_proj when the model has one and `proj` is
+// set; 5 layers at `pos` attending to the slot's code-predictor cache [0, pos]; output norm; lm_head[head] -> cp_logits
+// (head < 0: lm_head 0 runs only for its prologue, the normalised hidden lands in hid_out).
+void emit_cp_step(Engine * e, Slot & s, std::vector<Op> & P, const float * in_vec, const __half * table,
+                  const int32_t * tok_ptr, int pos, int head, bool proj, float * hid_out) {
+    const qtts_config & c = e->cfg;
+    const Dims D{c.cp_hidden_size, c.cp_n_heads, c.cp_n_kv_heads, c.cp_intermediate_size};
+    LayerBuf B{s.cp_x, s.cp_qkv, s.cp_attn, s.cp_act, s.cp_kc, s.cp_vc, (size_t) 16 * c.cp_n_kv_heads * kHeadDim,
+               s.attn_part, s.attn_cnt, s.cp_x_ll, s.cp_act_ll, s.cp_qkv_ll, s.cp_attn_ll};
+    Op first = blank();
+    if (table) { first.in_kind = IN_EMBED_ROW; first.table = table; first.tok_ptr = tok_ptr; first.tok_slot = -1; }
+    else { first.in_kind = IN_VEC; first.in = in_vec; }
+    if (e->mtp && proj) {
+        Op m = gemv(e->mtp, c.cp_hidden_size, c.hidden_size, in_vec, nullptr, c.rms_norm_eps, e->mtp_b ? EPI_BIAS : EPI_STORE, s.cp_x);
+        m.in_kind = first.in_kind; m.table = first.table; m.tok_ptr = first.tok_ptr; m.tok_slot = -1; m.bias = e->mtp_b;
+        m.out_stride = c.cp_hidden_size;
+        P.push_back(m);
+        first = blank(); first.in_kind = IN_VEC; first.in = s.cp_x;
+    } else {
+        first.x_out = s.cp_x;
+    }
+    for (int l = 0; l < c.cp_layers; ++l)
+        emit_layer(e, P, e->cp[l], D, B, l, l == 0 ? &first : nullptr, false, pos, ATTN_SOFTMAX_P16, 1);
+    Op hd = gemv(e->lm_head[head >= 0 ? head : 0], c.cp_vocab_size, c.cp_hidden_size, s.cp_x, e->cp_output_norm,
+                 c.rms_norm_eps, EPI_STORE, s.cp_logits);
+    hd.hid_out = hid_out;
+    if (e->ll) { hd.in_ll = s.cp_x_ll; hd.in_dist = 1; }
+    P.push_back(hd);
+}
+
 void emit_frame(Engine * e, Slot & s, std::vector<Op> & P) {
     const qtts_config & c = e->cfg;
     Op s0 = blank();

@@ -45,7 +45,7 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_step_frames",
            "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
            "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle",
-           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states"]
+           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step"]
 
 _lib = None
 
@@ -84,6 +84,7 @@ def load_library(path: str | None = None):
     lib.qtts_set_debug.argtypes = [vp, C.c_int]
     lib.qtts_resize_kv.argtypes = [vp, i32, i32]
     lib.qtts_get_hidden_states.argtypes = [vp, C.c_int, vp]
+    lib.qtts_cp_step.argtypes = [vp, C.c_int, vp, i32, i32, i32, i32, i32, C.c_int, vp, i32]
     lib.qtts_predict_codes.argtypes = [vp, C.c_int, vp, i32, C.c_float, i32, vp, vp, vp, vp]
     lib.qtts_generate.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64,
                                   vp, i32p, FRAME_CB, i32, vp]
@@ -294,6 +295,17 @@ class TTSTransformer:
         if not self._lib.qtts_forward_codec(self._h, slot, int(codec_token), n_past, _ptr(logits)):
             return None
         return logits
+
+    # TRTCodePredictor::step / step_with_token (src/trt_code_predictor.h:53-66): one code-predictor position
+    def cp_step(self, position_id: int, lm_head_idx: int, input_vec=None, token_id: int = 0, embedding_idx: int = 0,
+                needs_proj: bool = True, slot: int = 0):
+        n = self.config["cp_vocab_size"] if lm_head_idx >= 0 else self.config["cp_hidden_size"]
+        out = np.zeros(n, np.float32)
+        v = None if input_vec is None else np.ascontiguousarray(input_vec, dtype=np.float32)
+        if not self._lib.qtts_cp_step(self._h, slot, _ptr(v), 0 if v is None else v.shape[0], int(token_id), int(embedding_idx),
+                                      position_id, lm_head_idx, 1 if needs_proj else 0, _ptr(out), n):
+            return None
+        return out
 
     # -- parity hooks ------------------------------------------------------------------------------------
     def stream_force(self, slot: int, forced_codes=None, uniforms=None) -> bool:

@@ -69,6 +69,18 @@ def test_adapter_matches_ctypes_path(pkg, exe, make_gguf, tmp_path, preset, temp
     assert got["cb_frames"] == len(want) and got["cb_calls"] == -(-len(want) // 4)
     assert got["bad_width_rejected"] is True
     assert got["greedy15"] == got["predict15"]
+    # TRTCodePredictor::step / step_with_token position by position (teacher-forced on the loop's codes): the same ids
+    # except where the single-token attention of positions 0/1 (F16 cache) meets a near-tie of the merged F32 pass
+    same = sum(int(a == b) for a, b in zip(got["stepwise15"], got["greedy15"]))
+    assert len(got["stepwise15"]) == 15 and same >= 13, (got["stepwise15"], got["greedy15"])
+    assert got["upload_validation"] is True
+    # a request beyond the context cap fails without unloading the model (round-1 advisor finding)
+    assert got["too_long_fails"] is True and got["still_loaded"] is True
+    second = np.array(got["codes_second_call"], np.int32).reshape(-1, nb)
+    if temperature > 0.0:
+        assert not np.array_equal(second, codes), "a second generate() replayed the first call's uniforms"
+    else:
+        assert np.array_equal(second, codes)
     if temperature == 0.0:
         # first frame by hand (prefill -> greedy cb0 -> code predictor loop) == first frame of generate()
         assert got["cb0"] == int(want[0, 0])

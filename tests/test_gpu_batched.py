@@ -183,6 +183,10 @@ def test_batched_sampling_reproducible_and_ragged(engines, pkg):
     toks = [pkg.synth.synth_tokens(cfg, t) for t in texts]
     spk = [None] * 5
     T.set_batched(True)
+    # FAST numerics = exact top-k.  (REFERENCE numerics reproduce the reference's std::nth_element threshold, which on
+    # these random-init logits often keeps a handful of candidates + EOS: utterances then end within a few frames,
+    # as the seeded reference's do - tests/test_gpu_frames.py covers that mode against the reference.)
+    T.set_numerics(1, 4)
     a = run_streams(T, toks, spk, 120, temperature=0.9, seeds=[1, 2, 3, 1, 5], chunk=16)
     b = run_streams(T, toks, spk, 120, temperature=0.9, seeds=[1, 2, 3, 1, 5], chunk=7)
     for i in range(5):
@@ -190,6 +194,7 @@ def test_batched_sampling_reproducible_and_ragged(engines, pkg):
         assert 0 < len(a[i]) <= 120
     assert np.array_equal(a[0], a[3])            # same text, same seed, different slot
     assert not np.array_equal(a[0][:8], a[4][:8])
+    T.set_numerics(0, 4)
 
 
 @pytest.mark.gpu

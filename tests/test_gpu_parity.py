@@ -314,3 +314,31 @@ def test_concurrent_streams_match_single(engines, pkg):
     T.set_batched(True)
     for i in range(3):
         assert np.array_equal(np.concatenate(got[i]), alone[i])
+
+
+def test_resize_kv_keeps_weights_and_results(pkg, make_gguf):
+    """init_kv_cache / qtts_resize_kv (src/tts_transformer.cpp:794-842, :2383-2388): the per-stream KV slabs are
+    re-sized without touching the weights; results are unchanged; over-long requests fail and leave the engine usable."""
+    path, cfg = make_gguf("tiny", 1234)
+    g = load_gold("tiny")
+    T = pkg.TTSTransformer(device=0, max_streams=2, max_ctx=64)
+    assert T.load_model(path), T.get_error()
+    w0 = T.weight_stats()
+    a = T.generate(g["tokens"], g["speaker"], max_len=20, temperature=0.0)
+    assert T.generate(g["tokens"], g["speaker"], max_len=200, temperature=0.0) is None      # 64 slots are too few
+    assert T.init_kv_cache(512, max_text=300), T.get_error()
+    w1 = T.weight_stats()
+    assert w1["weight_bytes"] == w0["weight_bytes"] and w1["kv_bytes"] == 8 * w0["kv_bytes"]
+    b = T.generate(g["tokens"], g["speaker"], max_len=20, temperature=0.0)
+    assert np.array_equal(a, b)
+    long_text = pkg.synth.synth_tokens(cfg, n_text=250, seed=1)
+    c = T.generate(long_text, None, max_len=200, temperature=0.0)
+    assert c is not None and 0 < len(c) <= 200, T.get_error()
+    # the batched kernel works on the rebuilt lock-step groups
+    for i in range(2):
+        assert T.stream_prepare(i, g["tokens"], g["speaker"], max_len=6, temperature=0.0), T.get_error()
+    codes, produced, active = T.step_frames(6)
+    assert (produced == 6).all() and np.array_equal(codes[0], codes[1])
+    assert not T.init_kv_cache(100000) and "limit" in T.get_error()
+    assert T.generate(g["tokens"], g["speaker"], max_len=20, temperature=0.0) is not None
+    T.unload_model()
