@@ -8,9 +8,12 @@ Every matrix value is drawn N(0, std), rounded to a BF16-representable number an
 zero below 2^-14, so the SAME real number is stored in the F16 file the reference reads and in
 the BF16 copy the B200 engine streams.
 
-There is no tokenizer vocabulary in these files (the tokenizer is outside the hot path);
-`synth_tokens()` builds the `encode_for_tts` frame (`src/text_tokenizer.cpp:293-330`) around
-byte-valued text ids instead.
+The tokenizer is outside the hot path, but the reference's pipeline (`Qwen3TTS::load_models`,
+`src/qwen3_tts.cpp:107-160`) loads it from the same GGUF, so the file carries a synthetic byte-level
+vocabulary (`tokenizer.ggml.tokens`, no merges): id b < 256 is the GPT-2 byte-to-unicode character of
+byte b, so the reference's `TextTokenizer::encode` (`src/text_tokenizer.cpp:234-291`) maps ASCII text to
+one id per byte — exactly what `synth_tokens()` builds without a tokenizer — and `assistant`, `Ċ`,
+`<|im_start|>`, `<|im_end|>` sit at the ids `encode_for_tts` (`:293-330`) expects.
 """
 from __future__ import annotations
 
@@ -76,6 +79,34 @@ PRESETS = {
                             tts_bos_id=4001, tts_eos_id=4002, tts_pad_id=4000,
                             im_start_id=4010, im_end_id=4011, assistant_id=4012, newline_id=10),
 }
+
+
+def byte_to_unicode() -> list:
+    """GPT-2's byte -> printable unicode character table (the reference's BYTE_TO_UNICODE, src/text_tokenizer.cpp:12-46)."""
+    bs = list(range(33, 127)) + list(range(161, 173)) + list(range(174, 256))
+    cs = bs[:]
+    n = 0
+    for b in range(256):
+        if b not in bs:
+            bs.append(b)
+            cs.append(256 + n)
+            n += 1
+    m = dict(zip(bs, cs))
+    return [chr(m[b]) for b in range(256)]
+
+
+def synth_vocab(cfg: "SynthConfig") -> list:
+    """text_vocab_size token strings: byte characters at ids 0..255, the chat-frame specials at their ids, unique
+    fillers elsewhere (no merges: BPE leaves every word as single characters)."""
+    b2u = byte_to_unicode()
+    toks = [f"<|filler_{i}|>" for i in range(cfg.text_vocab_size)]
+    for b in range(256):
+        toks[b] = b2u[b]
+    toks[cfg.assistant_id] = "assistant"
+    toks[cfg.newline_id] = b2u[10]              # "Ċ": the newline token is looked up by content (:157-160)
+    toks[cfg.im_start_id] = "<|im_start|>"
+    toks[cfg.im_end_id] = "<|im_end|>"
+    return toks
 
 
 def bf16_round(x: np.ndarray) -> np.ndarray:
@@ -173,6 +204,10 @@ def write_gguf(path: str, preset: str | SynthConfig = "0.6b", seed: int = 1234,
     w.add_uint32(f"{arch}.tts_bos_token_id", cfg.tts_bos_id)
     w.add_uint32(f"{arch}.tts_eos_token_id", cfg.tts_eos_id)
     w.add_uint32(f"{arch}.tts_pad_token_id", cfg.tts_pad_id)
+    # synthetic byte-level vocabulary for the reference's TextTokenizer (src/text_tokenizer.cpp:80-165)
+    w.add_array("tokenizer.ggml.tokens", synth_vocab(cfg))
+    w.add_uint32("tokenizer.ggml.bos_token_id", cfg.im_start_id)
+    w.add_uint32("tokenizer.ggml.eos_token_id", cfg.im_end_id)
 
     rng = np.random.Generator(np.random.PCG64(seed))
     for name, kind, shape in tensor_specs(cfg):
