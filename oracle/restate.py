@@ -448,6 +448,8 @@ def sample_topk(logits, temperature, top_k, u, eos_id=-1) -> int:
         lg[eos_id] = eos_logit
     e = np.exp((lg - lg.max()).astype(F32), dtype=F32)
     probs = (e.astype(np.float64) / e.astype(np.float64).sum()).astype(F32)
+    if u <= 0.0:
+        return 0      # the scan starts with cumsum = probs[0] >= 0: a draw of exactly 0 selects index 0 (:2490-2494)
     cum = F32(0.0)
     for i in np.nonzero(probs)[0]:
         cum = F32(cum + probs[i])
