@@ -88,6 +88,9 @@ def check_forced_run(T, pkg, cfg, slot, toks, spk, ref_codes, ref_raw, ref_cp, m
     import restate
     nm_tol, abs_tol = TOL[mode]
     abs_tol *= max(1.0, (cfg.hidden_size / 1024.0) ** 0.5)
+    # code-predictor logits: 4e-3 in the batch-1 kernel; 6e-3 in the batched kernel, whose tensor-core accumulation
+    # order (K split over issuers / M tiles) moved single outliers of 2048 logits to 4.4e-3 at NMSE 2e-6 (measured)
+    cp_abs = (6e-3 if batched else 4e-3) * max(1.0, (cfg.hidden_size / 1024.0) ** 0.5)
     T.set_batched(batched)
     ok = (T.stream_prepare if prepare else T.stream_begin)(slot, toks, spk, max_len=n_frames, temperature=0.0)
     assert ok, T.get_error()
@@ -114,7 +117,6 @@ def check_forced_run(T, pkg, cfg, slot, toks, spk, ref_codes, ref_raw, ref_cp, m
             if top2[1] - top2[0] > 2 * d:
                 assert own[0] == ref_codes[f, 0], f"{label} frame {f}: codebook 0 {own[0]} != {ref_codes[f, 0]}"
         if f in ref_cp:
-            cp_abs = 4e-3 * max(1.0, (cfg.hidden_size / 1024.0) ** 0.5)      # the code predictor's input is Talker-wide
             for s in range(15):
                 e = nmse(cp[s], ref_cp[f][s])
                 d = float(np.abs(cp[s] - ref_cp[f][s]).max())
