@@ -111,9 +111,9 @@ static bool rebuild_frame_programs(Engine * e) {
     for (auto & s : e->slots) {
         s.frame_host.clear();
         emit_frame(e, s, s.frame_host);
-        QTTS_CUDA(cudaMemcpy(s.frame_prog, s.frame_host.data(), s.frame_host.size() * sizeof(Op), cudaMemcpyHostToDevice));
+        if (!e->h2d(s.frame_prog, s.frame_host.data(), s.frame_host.size() * sizeof(Op))) return false;
         const std::vector<WSched> S = build_sched(e, s.frame_host);
-        QTTS_CUDA(cudaMemcpy(s.frame_sched, S.data(), S.size() * sizeof(WSched), cudaMemcpyHostToDevice));
+        if (!e->h2d(s.frame_sched, S.data(), S.size() * sizeof(WSched))) return false;
     }
     return true;
 }
@@ -717,6 +717,7 @@ int qtts_batched_profile(qtts_engine * h, int on, uint64_t * out64) {
     cudaStreamSynchronize(e->stream);
     if (out64) cudaMemcpy(out64, e->prof + 2048, 64 * sizeof(uint64_t), cudaMemcpyDeviceToHost);
     cudaMemset(e->prof + 2048, 0, 64 * sizeof(uint64_t));
+    cudaStreamSynchronize(0);
     e->prof_on = on ? 1 : 0;
     return 1;
 }
@@ -856,7 +857,7 @@ int qtts_profile(qtts_engine * h, int on, uint64_t * out64) {
     cudaSetDevice(e->device);
     cudaStreamSynchronize(e->stream);
     if (out64) cudaMemcpy(out64, e->prof, (64 + 4 * 256) * sizeof(uint64_t), cudaMemcpyDeviceToHost);
-    if (on != e->prof_on || on) cudaMemset(e->prof, 0, (64 + 4 * 256) * sizeof(uint64_t));
+    if (on != e->prof_on || on) { cudaMemset(e->prof, 0, (64 + 4 * 256) * sizeof(uint64_t)); cudaStreamSynchronize(0); }
     e->prof_on = on > 0 ? on : 0;      // on = 1 + index of the CTA that records
     return 1;
 }

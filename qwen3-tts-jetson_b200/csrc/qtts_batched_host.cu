@@ -333,8 +333,8 @@ bool batched_build_groups(Engine * e) {
         G.ops = e->dalloc<BOp>(E.P.size(), false);
         G.sched = e->dalloc<BSched>(E.S.size(), false);
         if (!G.ops || !G.sched) return e->fail("out of device memory for the batched program");
-        QTTS_CUDA(cudaMemcpy(G.ops, E.P.data(), E.P.size() * sizeof(BOp), cudaMemcpyHostToDevice));
-        QTTS_CUDA(cudaMemcpy(G.sched, E.S.data(), E.S.size() * sizeof(BSched), cudaMemcpyHostToDevice));
+        if (!e->h2d(G.ops, E.P.data(), E.P.size() * sizeof(BOp))) return false;
+        if (!e->h2d(G.sched, E.S.data(), E.S.size() * sizeof(BSched))) return false;
         G.host_ops = E.P;
         // batched prefill program: one Talker step over private residual rows / outputs
         G.pf_x = e->dalloc<float>(B * H); G.pf_ssq_e = e->dalloc<float>(B);
@@ -349,8 +349,8 @@ bool batched_build_groups(Engine * e) {
         G.pf_ops = e->dalloc<BOp>(F.P.size(), false);
         G.pf_sched = e->dalloc<BSched>(F.S.size(), false);
         if (!G.pf_ops || !G.pf_sched) return e->fail("out of device memory for the batched prefill program");
-        QTTS_CUDA(cudaMemcpy(G.pf_ops, F.P.data(), F.P.size() * sizeof(BOp), cudaMemcpyHostToDevice));
-        QTTS_CUDA(cudaMemcpy(G.pf_sched, F.S.data(), F.S.size() * sizeof(BSched), cudaMemcpyHostToDevice));
+        if (!e->h2d(G.pf_ops, F.P.data(), F.P.size() * sizeof(BOp))) return false;
+        if (!e->h2d(G.pf_sched, F.S.data(), F.S.size() * sizeof(BSched))) return false;
         e->groups.push_back(G);
     }
     e->batched_ready = true;

@@ -163,9 +163,24 @@ struct Engine {
     template <typename T> T * dalloc(size_t n, bool zero = true) {
         void * p = nullptr;
         if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-        if (zero) cudaMemset(p, 0, n * sizeof(T));
+        if (zero) {
+            // cudaMemset runs on the legacy stream and is asynchronous to the host; the engine's stream is
+            // non-blocking, so without this wait a later copy / kernel on it could be overtaken by the memset
+            cudaMemset(p, 0, n * sizeof(T));
+            cudaStreamSynchronize(0);
+        }
         (stream_phase ? stream_allocs : allocs).push_back(p);
         return (T *) p;
+    }
+    // host -> device on the engine's stream, complete on return (a synchronous cudaMemcpy from pageable memory may
+    // return before the DMA has landed, and is not ordered with the non-blocking stream the kernels run on)
+    bool h2d(void * dst, const void * src, size_t bytes) {
+        if (cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream) != cudaSuccess ||
+            cudaStreamSynchronize(stream) != cudaSuccess) {
+            err = std::string("host to device copy failed: ") + cudaGetErrorString(cudaGetLastError());
+            return false;
+        }
+        return true;
     }
 };
 

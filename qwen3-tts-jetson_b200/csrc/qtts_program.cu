@@ -320,7 +320,7 @@ bool fold_text_table(Engine * e) {
     if (!e->text_tab || !ids) { e->text_tab = nullptr; return e->fail("out of device memory for the folded text table"); }
     std::vector<int32_t> iota(V);
     for (int i = 0; i < V; ++i) iota[i] = i;
-    QTTS_CUDA(cudaMemcpy(ids, iota.data(), (size_t) V * sizeof(int32_t), cudaMemcpyHostToDevice));
+    if (!e->h2d(ids, iota.data(), (size_t) V * sizeof(int32_t))) return false;
     Slot & s = e->slots[0];
     const int chunk = 2048;
     std::vector<Op> P;

@@ -78,7 +78,7 @@ bool engine_upload(Engine * e, const char * name_c, int dtype, const int64_t * d
     t.dtype = want;
     const size_t bytes = t.n_elem * (want == QTTS_F32 ? 4 : 2);
     if (cudaMalloc(&t.raw, bytes) != cudaSuccess) { cudaGetLastError(); return e->fail("cudaMalloc failed for " + name); }
-    QTTS_CUDA(cudaMemcpy(t.raw, src, bytes, cudaMemcpyHostToDevice));
+    if (!e->h2d(t.raw, src, bytes)) return false;
     auto it = e->tensors.find(name);
     if (it != e->tensors.end()) { cudaFree(it->second.raw); }
     e->tensors[name] = t;
@@ -222,18 +222,18 @@ static bool alloc_slot(Engine * e, Slot & s, int index) {
     es.n_books = c.n_codebooks;
     es.trailing = s.trailing;
     es.pad = s.pad;
-    QTTS_CUDA(cudaMemcpy(s.es, &es, sizeof(es), cudaMemcpyHostToDevice));
+    if (!e->h2d(s.es, &es, sizeof(es))) return false;
     s.frame_host.clear();
     emit_frame(e, s, s.frame_host);
     s.frame_prog_n = (int) s.frame_host.size();
     s.frame_prog = e->dalloc<Op>(s.frame_host.size(), false);
     if (!s.frame_prog) return e->fail("out of device memory for frame program");
-    QTTS_CUDA(cudaMemcpy(s.frame_prog, s.frame_host.data(), s.frame_host.size() * sizeof(Op), cudaMemcpyHostToDevice));
+    if (!e->h2d(s.frame_prog, s.frame_host.data(), s.frame_host.size() * sizeof(Op))) return false;
     const std::vector<WSched> S = build_sched(e, s.frame_host);
     s.frame_sched_n = (int) S.size();
     s.frame_sched = e->dalloc<WSched>(S.size(), false);
     if (!s.frame_sched) return e->fail("out of device memory for frame schedule");
-    QTTS_CUDA(cudaMemcpy(s.frame_sched, S.data(), S.size() * sizeof(WSched), cudaMemcpyHostToDevice));
+    if (!e->h2d(s.frame_sched, S.data(), S.size() * sizeof(WSched))) return false;
     return true;
 }
 
@@ -321,7 +321,7 @@ bool engine_build_streams(Engine * e) {
         }
         e->rope = e->dalloc<float>(tab.size(), false);
         if (!e->rope) return e->fail("out of device memory for rope table");
-        QTTS_CUDA(cudaMemcpy(e->rope, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice));
+        if (!e->h2d(e->rope, tab.data(), tab.size() * sizeof(float))) return false;
     }
     {   // per-stream buffers shared with the batched kernel: contiguous over the slots
         BatchBufs & bb = e->bb;
