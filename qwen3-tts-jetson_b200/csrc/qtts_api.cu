@@ -754,9 +754,9 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
     }
     e->bar = e->dalloc<GridBarrier>(1);
     const size_t nW = (size_t) rows * K, nX = (size_t) rows_act * K;
-    std::vector<__nv_bfloat16> wb(nW);
-    for (size_t i = 0; i < nW; ++i) wb[i] = __float2bfloat16_rn(W[i]);
-    __nv_bfloat16 * dW = e->dalloc<__nv_bfloat16>(nW, false);
+    std::vector<wt_t> wb(nW);       // W rounded to BF16 (the synthetic fixtures' precision), held as its exact F16 image
+    for (size_t i = 0; i < nW; ++i) wb[i] = __float2half_rn(__bfloat162float(__float2bfloat16_rn(W[i])));
+    wt_t * dW = e->dalloc<wt_t>(nW, false);
     cudaMemcpy(dW, wb.data(), nW * 2, cudaMemcpyHostToDevice);
     TiledW T;
     if (!tile_matrix(e, dW, rows, K, T, in_f16 != 0 && epi == EPI_ADD)) return cleanup(0);

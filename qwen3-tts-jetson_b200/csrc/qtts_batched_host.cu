@@ -9,14 +9,14 @@ namespace qtts {
 
 extern "C" __global__ void qtts_run_batched(const __grid_constant__ BRun run_param);
 
-// src: BF16 [rows][K] row-major (the batch-1 kernel's fused layouts).  dst: for tile t (n_tile
+// src: F16 [rows][K] row-major (the batch-1 kernel's fused layouts).  dst: for tile t (n_tile
 // rows) and piece p (kpp K-elements, the last one shorter), the piece is one contiguous block in
 // the K-major no-swizzle canonical layout: (row r, 8-element chunk c) at
 //   (r / 8) * (kp * 16) + c * 128 + (r % 8) * 16,  kp = K-extent of the piece.
 // With ksplit > 1 a row block is stored as ksplit virtual tiles, one per K-range of Kh = K / ksplit
 // columns (virtual tile index = row block * ksplit + K-half); kpp / pieces refer to the virtual tile.
-__global__ void k_tile_weights(const __nv_bfloat16 * __restrict__ src, unsigned char * __restrict__ dst,
-                               int rows, int K, int n_tile, int kpp, int to_f16, int ksplit) {
+__global__ void k_tile_weights(const wt_t * __restrict__ src, unsigned char * __restrict__ dst,
+                               int rows, int K, int n_tile, int kpp, int to_bf16, int ksplit) {
     const size_t n_units = (size_t) rows * (K / 8);
     const int Kh = K / ksplit;
     for (size_t u = (size_t) blockIdx.x * blockDim.x + threadIdx.x; u < n_units; u += (size_t) gridDim.x * blockDim.x) {
@@ -28,12 +28,12 @@ __global__ void k_tile_weights(const __nv_bfloat16 * __restrict__ src, unsigned 
         const size_t off = (size_t) (t * ksplit + h) * n_tile * Kh * 2 + (size_t) p * n_tile * kpp * 2 +
                            (size_t) (rr / 8) * (kp * 16) + (size_t) (kin / 8) * 128 + (size_t) (rr % 8) * 16;
         uint4 v = *reinterpret_cast<const uint4 *>(src + (size_t) r * K + kfull);
-        if (to_f16) {
-            const __nv_bfloat16 * b = reinterpret_cast<const __nv_bfloat16 *>(&v);
-            __half h[8];
+        if (to_bf16) {      // bring-up only (qtts_debug_bgemm with a BF16 B operand)
+            const __half * h = reinterpret_cast<const __half *>(&v);
+            __nv_bfloat16 b[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) h[i] = __float2half_rn(__bfloat162float(b[i]));
-            v = *reinterpret_cast<const uint4 *>(h);
+            for (int i = 0; i < 8; ++i) b[i] = __float2bfloat16_rn(__half2float(h[i]));
+            v = *reinterpret_cast<const uint4 *>(b);
         }
         *reinterpret_cast<uint4 *>(dst + off) = v;
     }
@@ -51,7 +51,7 @@ static int pick_n_tile(int rows, int grid) {
     return best;
 }
 
-bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T, bool allow_split) {
+bool tile_matrix(Engine * e, const wt_t * src, int rows, int K, TiledW & T, bool allow_split) {
     if (rows % 16 || K % kKc) return e->fail("batched path: projection shape must be a multiple of 16 x 128");
     T.rows = rows;
     T.n_tile = pick_n_tile(rows, e->n_sms);
@@ -73,7 +73,7 @@ bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW 
     T.n_pieces = (Kh + kpp - 1) / kpp;
     T.p = e->dalloc<unsigned char>((size_t) rows * K * 2, false);
     if (!T.p) return e->fail("out of device memory for tiled weights");
-    k_tile_weights<<<1184, 256, 0, e->stream>>>(src, T.p, rows, K, T.n_tile, kpp, e->bfmt == 0 ? 1 : 0, T.ksplit);
+    k_tile_weights<<<1184, 256, 0, e->stream>>>(src, T.p, rows, K, T.n_tile, kpp, e->bfmt == 0 ? 0 : 1, T.ksplit);
     QTTS_CUDA(cudaGetLastError());
     e->weight_bytes_batched += (int64_t) rows * K * 2;
     return true;

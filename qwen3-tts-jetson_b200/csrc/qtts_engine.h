@@ -14,7 +14,6 @@ namespace qtts {
 
 struct DevTensor {
     void * raw = nullptr;          // as uploaded: F16 (2-D) or F32 (1-D)
-    __nv_bfloat16 * bf = nullptr;  // BF16 copy (projection matrices only)
     int dtype = 0;
     int64_t ne[4] = {1, 1, 1, 1};  // ggml order (ne[0] innermost)
     int n_dims = 0;
@@ -22,7 +21,7 @@ struct DevTensor {
 };
 
 struct LayerW {
-    __nv_bfloat16 * wqkv = nullptr, * wo = nullptr, * wgu = nullptr, * wdown = nullptr;
+    wt_t * wqkv = nullptr, * wo = nullptr, * wgu = nullptr, * wdown = nullptr;
     float * attn_norm = nullptr, * ffn_norm = nullptr, * q_norm = nullptr, * k_norm = nullptr;
 };
 
@@ -141,8 +140,8 @@ struct Engine {
     float * rope = nullptr;
     // fused weights
     std::vector<LayerW> talker, cp;
-    __nv_bfloat16 * codec_head = nullptr, * fc1 = nullptr, * fc2 = nullptr, * mtp = nullptr;
-    std::vector<__nv_bfloat16 *> lm_head;
+    wt_t * codec_head = nullptr, * fc1 = nullptr, * fc2 = nullptr, * mtp = nullptr;
+    std::vector<wt_t *> lm_head;
     float * output_norm = nullptr, * cp_output_norm = nullptr, * fc1_b = nullptr, * fc2_b = nullptr, * mtp_b = nullptr;
     const __half * codec_embd = nullptr, * text_embd = nullptr;
     float * text_tab = nullptr;    // folded text table [text_vocab][H] (fold_text_table), nullptr: per-token projection
@@ -214,7 +213,7 @@ std::vector<WSched> build_sched(Engine * e, const std::vector<Op> & P);
 bool fold_text_table(Engine * e);
 
 // qtts_batched_host.cu
-bool tile_matrix(Engine * e, const __nv_bfloat16 * src, int rows, int K, TiledW & T, bool allow_split = false);
+bool tile_matrix(Engine * e, const wt_t * src, int rows, int K, TiledW & T, bool allow_split = false);
 bool batched_init(Engine * e);              // tiles the weights (once)
 bool batched_build_groups(Engine * e);      // lock-step groups over the current slots
 uint32_t batched_idesc(const Engine * e);

@@ -26,6 +26,9 @@
 #ifndef QTTS_OPT_ATTN
 #define QTTS_OPT_ATTN 1
 #endif
+#ifndef QTTS_OPT_ATTN_WARP
+#define QTTS_OPT_ATTN_WARP 1      // warp-per-head attention for <= 16 keys (0: the CTA-wide path, for A/B runs)
+#endif
 #include <math_constants.h>
 
 namespace qtts {
@@ -34,8 +37,20 @@ namespace qtts {
 // small helpers
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ float f16r(float v) { return __half2float(__float2half_rn(v)); }
-__device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+// d = a * b + c with a, b F16 (low / high half of a 32-bit register: ptxas folds the selection into the .H1 operand
+// modifier) and c, d F32, one rounding: the sm_100 mixed-precision FMA (SASS FHFMA).  Same real arithmetic as
+// fmaf((float) a, (float) b, c) - both conversions are exact - at one instruction per multiply-add.
+__device__ __forceinline__ float fhfma(uint16_t a, uint16_t b, float c) {
+    float d;
+    asm("fma.rn.f32.f16 %0, %1, %2, %3;" : "=f"(d) : "h"(a), "h"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ float fhfma2(uint32_t w, uint32_t x, float c) {      // c + w.lo * x.lo, then + w.hi * x.hi
+    uint16_t w0, w1, x0, x1;
+    asm("mov.b32 {%0, %1}, %2;" : "=h"(w0), "=h"(w1) : "r"(w));
+    asm("mov.b32 {%0, %1}, %2;" : "=h"(x0), "=h"(x1) : "r"(x));
+    return fhfma(w1, x1, fhfma(w0, x0, c));
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -163,7 +178,7 @@ struct Prefetch {
     int32_t q, p1;          // next row pair / end of this CTA's slice of the entry
     int32_t K, ppc, slot;
     uint32_t seq;
-    const __nv_bfloat16 * W;
+    const wt_t * W;
     uint64_t policy;
     int4 ent[4][2];         // schedule entries idx .. idx+2 (slot = entry index & 3)
 };
@@ -194,7 +209,7 @@ __device__ __noinline__ void prefetch_issue(const WSched * __restrict__ sched, i
             asm volatile("cp.async.wait_group 1;" ::: "memory");      // entry k landed (k+1 may be in flight)
             const int4 e0 = pf.ent[k & 3][0], e1 = pf.ent[k & 3][1];
             sched_fetch(pf, sched, n_sched, k + 2);
-            pf.W = reinterpret_cast<const __nv_bfloat16 *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
+            pf.W = reinterpret_cast<const wt_t *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
             pf.K = e0.z;
             const unsigned pairs = (unsigned) e0.w;
             pf.ppc = e1.x;
@@ -288,19 +303,12 @@ __device__ __forceinline__ float gemv_input_elem(const Op & op, const LocalState
     }
 }
 
-// 8 weights (bf16, one uint4) x 8 activations (f16, one uint4), f32 accumulate
+// 8 weights (F16, one uint4) x 8 activations (F16, one uint4), F32 accumulate in element order: 8 FHFMA, no unpacking
 __device__ __forceinline__ float dot8h(const uint4 w, const uint4 x) {
-    const __half2 * xh = reinterpret_cast<const __half2 *>(&x);
-    const float2 x0 = __half22float2(xh[0]), x1 = __half22float2(xh[1]);
-    const float2 x2 = __half22float2(xh[2]), x3 = __half22float2(xh[3]);
-    float s = bf_lo(w.x) * x0.x;
-    s = fmaf(bf_hi(w.x), x0.y, s);
-    s = fmaf(bf_lo(w.y), x1.x, s);
-    s = fmaf(bf_hi(w.y), x1.y, s);
-    s = fmaf(bf_lo(w.z), x2.x, s);
-    s = fmaf(bf_hi(w.z), x2.y, s);
-    s = fmaf(bf_lo(w.w), x3.x, s);
-    s = fmaf(bf_hi(w.w), x3.y, s);
+    float s = fhfma2(w.x, x.x, 0.f);
+    s = fhfma2(w.y, x.y, s);
+    s = fhfma2(w.z, x.z, s);
+    s = fhfma2(w.w, x.w, s);
     return s;
 }
 
@@ -985,6 +993,178 @@ __device__ __noinline__ void attn_reference(const Op & op, const LocalState * ls
     }
 }
 
+// ---- ATTN_SOFTMAX_P16 with at most 16 keys (the code predictor's single-token passes, 70 stages per frame, and
+// the first prefill tokens): ONE WARP per query head, no CTA barrier at all.  The CTA-wide path above spends ~12
+// __syncthreads and three block reductions on 16 keys (measured 4.85 us per stage); here lane l holds dims
+// l + 32 j (j < 4) of q / k / v - the NEOX pair (i, i + 64) sits in one lane - and for the key loop half-warp `hw`
+// takes the keys of its parity, lane l16 of it 8 consecutive dims (one 16-byte load per cached key).
+// Same arithmetic and rounding points as attn_reference / the reference's step graph (src/tts_transformer.cpp:
+// 1666-1827): F16 Q, F16 cache, F32 scores, softmax with a double sum, P rounded to F16, P.V partial sums per key
+// class j mod 4 combined as (p0 + p1) + (p2 + p3).
+struct AttnWarpSmem {
+    __half kc[16][kHeadDim], vc[16][kHeadDim];     // the KV group's cache rows [0, pos] (cp.async) + the current token's
+    float q[kHeadDim];
+    float wq[kHeadDim], wk[kHeadDim];
+    float2 cs[64];
+    float sc[16];
+};
+
+__device__ __noinline__ void attn_p16_warp(const Op & op, int pos, float * scratch, const unsigned long long * qkv_ll,
+                                           uint32_t tag_in, unsigned long long * out_ll_base, uint32_t tag) {
+    const int h = blockIdx.x;
+    if (h >= op.n_heads || threadIdx.x >= 32) return;
+    const int lane = threadIdx.x, hw = lane >> 4, l16 = lane & 15;
+    const int rep = op.n_heads / op.n_kv_heads, g = h / rep;
+    const int kvw = op.n_kv_heads * kHeadDim, n_kv = pos + 1;
+    AttnWarpSmem * sm = reinterpret_cast<AttnWarpSmem *>(scratch);
+    // Everything that does not depend on this token is requested BEFORE the projections are polled and waits in
+    // shared memory, not in registers (the kernel is capped at 128 registers per thread, and the IEEE sqrt /
+    // divisions below are calls that would spill whatever is live across them): the cached key / value rows of the
+    // earlier positions by cp.async (16 bytes per lane and row), the norm weights and the RoPE factors.
+    {
+        const __half * kbase = op.kcache + g * kHeadDim + 8 * l16;
+        const __half * vbase = op.vcache + g * kHeadDim + 8 * l16;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int jk = 2 * i + hw;
+            if (jk < pos) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_u32(&sm->kc[jk][8 * l16])), "l"(kbase + (size_t) jk * kvw) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_u32(&sm->vc[jk][8 * l16])), "l"(vbase + (size_t) jk * kvw) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        sm->wq[lane + 32 * j] = op.q_norm_w ? __ldg(op.q_norm_w + lane + 32 * j) : 1.f;
+        sm->wk[lane + 32 * j] = op.k_norm_w ? __ldg(op.k_norm_w + lane + 32 * j) : 1.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+        sm->cs[lane + 32 * j] = __ldg(reinterpret_cast<const float2 *>(op.rope) + (size_t) pos * 64 + lane + 32 * j);
+    float q[4], k[4], v[4];
+    {
+        const size_t oq = (size_t) h * kHeadDim, ok = (size_t) (op.n_heads + g) * kHeadDim,
+                     ov = (size_t) (op.n_heads + op.n_kv_heads + g) * kHeadDim;
+        if (qkv_ll) {
+            unsigned long long w[12];
+            uint32_t spins = 0;
+            bool good;
+            do {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    w[j] = ll_load(qkv_ll + oq + lane + 32 * j);
+                    w[4 + j] = ll_load(qkv_ll + ok + lane + 32 * j);
+                    w[8 + j] = ll_load(qkv_ll + ov + lane + 32 * j);
+                }
+                good = true;
+#pragma unroll
+                for (int j = 0; j < 12; ++j) good = good && ((uint32_t) (w[j] >> 32) == tag_in);
+                if (!good) ll_spin_guard(spins);
+            } while (!good);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                q[j] = __uint_as_float((uint32_t) w[j]); k[j] = __uint_as_float((uint32_t) w[4 + j]); v[j] = __uint_as_float((uint32_t) w[8 + j]);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                q[j] = __ldcg(op.qkv + oq + lane + 32 * j); k[j] = __ldcg(op.qkv + ok + lane + 32 * j); v[j] = __ldcg(op.qkv + ov + lane + 32 * j);
+            }
+        }
+    }
+    // per-head RMSNorm (double sum of float squares, ops.cpp:3738-3747) + NEOX RoPE
+    auto norm_rope = [&](float * x, const float * w, bool do_norm) {
+        if (do_norm) {
+            double ss = 0.0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ss += (double) (x[j] * x[j]);
+            ss = warp_sum_d(ss);
+            const float mean = (float) (ss * (1.0 / (double) kHeadDim));      // exact: a power of two
+            const float scale = 1.0f / sqrtf(mean + op.eps);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = (x[j] * scale) * w[lane + 32 * j];
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const float2 cs = sm->cs[lane + 32 * j];
+            const float x0 = x[j], x1 = x[j + 2];
+            x[j] = x0 * cs.x - x1 * cs.y;
+            x[j + 2] = x0 * cs.y + x1 * cs.x;
+        }
+    };
+    norm_rope(k, sm->wk, op.k_norm_w != nullptr);
+    norm_rope(q, sm->wq, op.q_norm_w != nullptr);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const __half kh = __float2half_rn(k[j]), vh = __float2half_rn(v[j]);
+        sm->kc[pos][lane + 32 * j] = kh; sm->vc[pos][lane + 32 * j] = vh;
+        sm->q[lane + 32 * j] = f16r(q[j]);
+        if (h % rep == 0) {     // one head of the group appends to the cache; nobody reads row `pos` from it in this stage
+            op.kcache[(size_t) pos * kvw + g * kHeadDim + lane + 32 * j] = kh;
+            op.vcache[(size_t) pos * kvw + g * kHeadDim + lane + 32 * j] = vh;
+        }
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncwarp();
+    float qa[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) qa[i] = sm->q[8 * l16 + i];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int jk = 2 * i + hw;
+        const uint4 kr = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(&sm->kc[jk][8 * l16]) : make_uint4(0u, 0u, 0u, 0u);
+        const __half2 * hk = reinterpret_cast<const __half2 *>(&kr);
+        float sdot = 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float2 f = __half22float2(hk[u]);
+            sdot = fmaf(f.x, qa[2 * u], sdot);
+            sdot = fmaf(f.y, qa[2 * u + 1], sdot);
+        }
+#pragma unroll
+        for (int o2 = 8; o2 > 0; o2 >>= 1) sdot += __shfl_xor_sync(0xffffffffu, sdot, o2);
+        if (l16 == 0 && jk < n_kv) sm->sc[jk] = sdot * op.kq_scale;
+    }
+    __syncwarp();
+    float mx = -CUDART_INF_F;
+    for (int jk = 0; jk < n_kv; ++jk) mx = fmaxf(mx, sm->sc[jk]);
+    double sum = 0.0;
+    for (int jk = 0; jk < n_kv; ++jk) sum += (double) expf(sm->sc[jk] - mx);
+    const float inv = (float) (1.0 / sum);
+    float accA[8], accB[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { accA[u] = 0.f; accB[u] = 0.f; }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int jk = 2 * i + hw;
+        if (jk < n_kv) {
+            const float pk = f16r(expf(sm->sc[jk] - mx) * inv);        // soft_max scales by 1/sum; the P.V mul_mat rounds P to F16
+            const uint4 vr = *reinterpret_cast<const uint4 *>(&sm->vc[jk][8 * l16]);
+            const __half2 * hv = reinterpret_cast<const __half2 *>(&vr);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float2 f = __half22float2(hv[u]);
+                if (i & 1) { accB[2 * u] = fmaf(f.x, pk, accB[2 * u]); accB[2 * u + 1] = fmaf(f.y, pk, accB[2 * u + 1]); }
+                else       { accA[2 * u] = fmaf(f.x, pk, accA[2 * u]); accA[2 * u + 1] = fmaf(f.y, pk, accA[2 * u + 1]); }
+            }
+        }
+    }
+    float * out = op.out + (size_t) h * kHeadDim + 8 * l16;
+    unsigned long long * out_ll = out_ll_base ? out_ll_base + (size_t) h * kHeadDim + 8 * l16 : nullptr;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        // half-warp 0 holds key classes 0 (A) and 2 (B), half-warp 1 classes 1 and 3: (p0 + p1) + (p2 + p3)
+        const float a = accA[u] + __shfl_xor_sync(0xffffffffu, accA[u], 16);
+        const float b = accB[u] + __shfl_xor_sync(0xffffffffu, accB[u], 16);
+        if (hw == 0) {
+            const float o = a + b;
+            out[u] = o;
+            if (out_ll) ll_store(out_ll + u, o, tag);
+        }
+    }
+}
+
 __device__ __noinline__ void stage_attn(const Op & op, const LocalState * ls, float * scratch, uint32_t tag, bool ll) {
     AttnSmem * sm = reinterpret_cast<AttnSmem *>(scratch);
     float * sc = scratch + (sizeof(AttnSmem) + 15) / 16 * 4;
@@ -993,6 +1173,10 @@ __device__ __noinline__ void stage_attn(const Op & op, const LocalState * ls, fl
     unsigned long long * out_ll = ll ? op.out_ll : nullptr;
     const uint32_t tag_in = tag - (uint32_t) op.in_dist;
     if (op.mode == ATTN_F32) { attn_f32_pair(op, sm, sc, qkv_ll, tag_in, out_ll, tag); return; }
+    if (op.mode == ATTN_SOFTMAX_P16 && QTTS_OPT_ATTN_WARP) {
+        const int p16_pos = (op.use_n_past ? ls->n_past : 0) + op.pos_off;
+        if (p16_pos < 16) { attn_p16_warp(op, p16_pos, scratch, qkv_ll, tag_in, out_ll, tag); return; }
+    }
     if (op.mode != ATTN_FAST) { attn_reference(op, ls, sm, sc, qkv_ll, tag_in, out_ll, tag); return; }
     const int pos = (op.use_n_past ? ls->n_past : 0) + op.pos_off;
     const int rep = op.n_heads / op.n_kv_heads;
@@ -1054,9 +1238,16 @@ __device__ __noinline__ float block_kth_largest(const float * l, int n, int k, S
     for (int shift = 24; shift >= 0; shift -= 8) {
         for (int i = threadIdx.x; i < 256; i += kThreads) sm->hist[i] = 0;
         __syncthreads();
-        for (int i = threadIdx.x; i < n; i += kThreads) {
-            const unsigned int key = ord_key(l[i]);
-            if ((key & mask) == prefix) atomicAdd(&sm->hist[(key >> shift) & 255u], 1u);
+        // warp-aggregated histogram: logits of similar magnitude share their top key bits, so a plain atomicAdd per
+        // element serialises 32 lanes on one shared-memory word (measured: the first pass cost ~2 us of the 10 us
+        // sampling stage); lanes with the same bin elect one leader that adds the group's population count
+        for (int i0 = 0; i0 < n; i0 += kThreads) {
+            const int i = i0 + (int) threadIdx.x;
+            const unsigned int key = (i < n) ? ord_key(l[i]) : 0u;
+            const bool act = (i < n) && ((key & mask) == prefix);
+            const unsigned int bin = act ? ((key >> shift) & 255u) : (256u + (threadIdx.x & 31u));
+            const unsigned int grp = __match_any_sync(0xffffffffu, bin);
+            if (act && (__ffs(grp) - 1) == (int) (threadIdx.x & 31u)) atomicAdd(&sm->hist[bin], (unsigned int) __popc(grp));
         }
         __syncthreads();
         if (threadIdx.x < 32) {
@@ -1173,21 +1364,25 @@ __device__ __noinline__ int block_sample(int n, float temperature, int top_k, fl
     int base = 0;
     for (int w = 0; w < warp; ++w) base += sm->wcount[w];
     int pos = base + incl - cnt;
-    for (int i = b0; i < b1; ++i) if (p[i] != 0.0f) { sm->idx[pos++] = (unsigned short) i; }
+    // candidates in index order: id in idx[], probability in l[] (the logits are not needed any more), so the scan
+    // below reads two dense arrays instead of chasing p[idx[t]]
+    for (int i = b0; i < b1; ++i) if (p[i] != 0.0f) { sm->idx[pos] = (unsigned short) i; l[pos] = p[i]; ++pos; }
     if (threadIdx.x == kThreads - 1) sm->count = base + incl;
     __syncthreads();
     if (threadIdx.x == 0) {
-        // src/tts_transformer.cpp:2487-2494: the scan starts at index 0 with cumsum = probs[0], so a draw of
-        // exactly 0 selects index 0 even when its probability is 0 (zeros are skipped below)
+        // src/tts_transformer.cpp:2487-2494: sequential float running sum, first index with cumsum >= u; the scan
+        // starts at index 0 with cumsum = probs[0], so a draw of exactly 0 selects index 0 even when its probability
+        // is 0 (zeros do not move the sum and are skipped).  No early exit: the adds form one dependent chain of
+        // ~4 cycles each while the loads run ahead; `hit` keeps the first match.
         float cum = 0.f;
-        int tok = (u <= 0.0f) ? 0 : n - 1;
+        int hit = -1;
         const int m = (u <= 0.0f) ? 0 : sm->count;
+#pragma unroll 4
         for (int t = 0; t < m; ++t) {
-            const int i = sm->idx[t];
-            cum += p[i];
-            if (cum >= u) { tok = i; break; }
+            cum += l[t];
+            if (hit < 0 && cum >= u) hit = t;
         }
-        sm->token = tok;
+        sm->token = (u <= 0.0f) ? 0 : (hit >= 0 ? (int) sm->idx[hit] : n - 1);
     }
     __syncthreads();
     return sm->token;

@@ -11,6 +11,12 @@
 
 namespace qtts {
 
+// Projection weights are kept in the GGUF's own type, F16 (scripts/convert_tts_to_gguf.py:289-297), exactly the
+// values the reference's ggml_mul_mat multiplies; the activations are rounded to F16 like ggml does
+// (ggml/src/ggml-cpu/ggml-cpu.c:1241-1243), and sm_100's mixed-precision FMA (fma.rn.f32.f16 -> SASS FHFMA: F16 x F16
+// + F32 with one rounding) accumulates in FP32 without a conversion instruction per operand.
+using wt_t = __half;
+
 constexpr int kThreads   = 512;   // threads per CTA (16 warps)
 constexpr int kWarps     = kThreads / 32;
 constexpr int kHeadDim   = 128;   // every Qwen3-TTS config uses 128 (src/tts_transformer.h:33,47)
@@ -91,7 +97,7 @@ struct Op {
     int32_t type;
     int32_t flags;           // F_* below
     // ---- OP_GEMV ----
-    const __nv_bfloat16 * W; // [rows][K] row-major
+    const wt_t * W;          // [rows][K] row-major, F16
     int32_t rows, K;
     int32_t in_kind, epi;
     int32_t n_tok;           // 1, or 2 for the merged code-predictor positions 0/1 (also OP_ATTN)
@@ -155,7 +161,7 @@ enum OpFlags : int32_t {
 // Host-built list of the program's GEMV stages in execution order (one frame); the prefetcher
 // walks it cyclically, so that issuing a chunk costs a handful of integer instructions.
 struct WSched {
-    const __nv_bfloat16 * W;
+    const wt_t * W;
     int32_t K, pairs, ppc, pad;     // ppc = row pairs per ring chunk
     int32_t pad2[2];                // 32-byte entries: read as two 16-byte loads
 };

@@ -24,7 +24,7 @@ static Op blank() {
     return o;
 }
 
-static Op gemv(const __nv_bfloat16 * W, int rows, int K, const float * in, const float * norm_w, float eps,
+static Op gemv(const wt_t * W, int rows, int K, const float * in, const float * norm_w, float eps,
                int epi, float * out) {
     Op o = blank();
     o.type = OP_GEMV; o.W = W; o.rows = rows; o.K = K; o.in_kind = IN_VEC; o.in = in;
