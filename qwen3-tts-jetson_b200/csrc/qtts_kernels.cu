@@ -1238,16 +1238,9 @@ __device__ __noinline__ float block_kth_largest(const float * l, int n, int k, S
     for (int shift = 24; shift >= 0; shift -= 8) {
         for (int i = threadIdx.x; i < 256; i += kThreads) sm->hist[i] = 0;
         __syncthreads();
-        // warp-aggregated histogram: logits of similar magnitude share their top key bits, so a plain atomicAdd per
-        // element serialises 32 lanes on one shared-memory word (measured: the first pass cost ~2 us of the 10 us
-        // sampling stage); lanes with the same bin elect one leader that adds the group's population count
-        for (int i0 = 0; i0 < n; i0 += kThreads) {
-            const int i = i0 + (int) threadIdx.x;
-            const unsigned int key = (i < n) ? ord_key(l[i]) : 0u;
-            const bool act = (i < n) && ((key & mask) == prefix);
-            const unsigned int bin = act ? ((key >> shift) & 255u) : (256u + (threadIdx.x & 31u));
-            const unsigned int grp = __match_any_sync(0xffffffffu, bin);
-            if (act && (__ffs(grp) - 1) == (int) (threadIdx.x & 31u)) atomicAdd(&sm->hist[bin], (unsigned int) __popc(grp));
+        for (int i = threadIdx.x; i < n; i += kThreads) {
+            const unsigned int key = ord_key(l[i]);
+            if ((key & mask) == prefix) atomicAdd(&sm->hist[(key >> shift) & 255u], 1u);
         }
         __syncthreads();
         if (threadIdx.x < 32) {

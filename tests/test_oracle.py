@@ -117,8 +117,10 @@ def test_sample_topk_known_answers():
     assert restate.sample_topk(lg, 1.0, 2, 0.51) == 2
     assert restate.sample_topk(lg, 1.0, 2, 1.0) in (2, 5)     # cum reaches 1.0 at index 2
     # EOS (index 4) survives top-k for codebook 0 even though it is below the threshold
-    hits = {restate.sample_topk(lg, 1.0, 2, u, eos_id=4) for u in np.linspace(0, 0.99999, 4001)}
+    hits = {restate.sample_topk(lg, 1.0, 2, u, eos_id=4) for u in np.linspace(1e-6, 0.99999, 4001)}
     assert hits == {1, 2, 4}
+    # a draw of exactly 0 selects index 0 even at probability 0: the scan starts with cumsum = probs[0] >= 0 (:2490-2494)
+    assert restate.sample_topk(lg, 1.0, 2, 0.0, eos_id=4) == 0
     # argmax: first maximum wins
     assert restate.argmax_first(lg) == 1
 
