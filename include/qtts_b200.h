@@ -230,6 +230,11 @@ int qtts_stream_logits(qtts_engine * e, int slot, float * cb0_out, float * cp_ou
  * receives the 64 + 4*256 counters accumulated so far (after the first 64: per-CTA [cta][gemv stage, gemv barrier, attn stage, attn barrier]); they are then cleared.  on = 0: off; on = 1 + c:
  * CTA c records.  [6] = cycles thread 0 waited for ring chunks. */
 int qtts_profile(qtts_engine * e, int on, uint64_t * out64);
+/* stage timeline of the batch-1 frame kernel: thread 0 of CTA `cta` stores SM-clock stamps (low 32 bits) for the
+ * first 8192 stages of every launch, 8 words per stage: [type | op index << 8, start, own input poll done, input
+ * staged, rows done, stage end (after the grid barrier if any), frame, 0].  Store-only, so the timeline is not
+ * distorted by read-modify-write round trips.  out (may be NULL) receives the previous recording, which is cleared. */
+int qtts_trace(qtts_engine * e, int on, int cta, uint32_t * out, int32_t max_stages);
 /* instrumentation: microseconds per grid-wide barrier of `variant` (see csrc/qtts_microbench.cu) */
 double qtts_debug_barrier_us(int device, int variant, int iters);
 /* batched kernel stage timers (CTA 0, SM clock cycles): out64[(2*type + 8*f16_input)*4 + {0 count,

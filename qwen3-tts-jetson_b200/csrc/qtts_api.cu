@@ -862,6 +862,26 @@ int qtts_profile(qtts_engine * h, int on, uint64_t * out64) {
     return 1;
 }
 
+int qtts_trace(qtts_engine * h, int on, int cta, uint32_t * out, int32_t max_stages) {
+    Engine * e = &h->e;
+    if (!e->finalized) { e->err = "engine not finalized"; return 0; }
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    const int cap = 8192;
+    if (!e->trace) {
+        e->stream_phase = false;
+        e->trace = e->dalloc<uint32_t>((size_t) cap * 8);
+        e->stream_phase = true;
+        if (!e->trace) { e->err = "out of device memory for the trace"; return 0; }
+    }
+    if (out && max_stages > 0)
+        cudaMemcpy(out, e->trace, (size_t) std::min(max_stages, cap) * 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+    cudaMemset(e->trace, 0, (size_t) cap * 8 * sizeof(uint32_t));
+    cudaStreamSynchronize(0);
+    e->trace_on = on ? 1 : 0; e->trace_cta = cta; e->trace_cap = cap;
+    return 1;
+}
+
 int64_t qtts_launch_count(const qtts_engine * h) { return h->e.launches; }
 double qtts_last_loop_ms(const qtts_engine * h) { return h->e.last_loop_ms; }
 void * qtts_stream_handle(const qtts_engine * h) { return (void *) h->e.stream; }

@@ -137,6 +137,7 @@ struct Engine {
     unsigned long long * d_inexact = nullptr;
     GridBarrier * bar = nullptr;
     unsigned long long * prof = nullptr; int prof_on = 0;   // [8][8] stage cycle counters (instrumentation)
+    uint32_t * trace = nullptr; int trace_on = 0, trace_cta = 0, trace_cap = 0;   // stage timeline of one CTA (qtts_trace)
     float * rope = nullptr;
     // fused weights
     std::vector<LayerW> talker, cp;

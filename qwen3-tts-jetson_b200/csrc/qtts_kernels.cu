@@ -120,6 +120,9 @@ struct RunCfg {
     const WSched * sched;   // [n_sched]
     uint32_t tag_base;      // stage tags of this launch are tag_base + 1 + (frame * n_ops + op index)
     unsigned long long * prof;   // optional [8 op types][8] cycle counters filled by CTA 0 (nullptr: off)
+    uint32_t * trace;            // optional stage timeline of CTA prof_cta, thread 0: 8 words per stage, store-only (no
+    int32_t trace_cap;           //   read-modify-write on the critical path): [type | op << 8, start, own poll done,
+                                 //   input staged, rows done, stage end (after the barrier if any), frame, spare]
 };
 
 // ------------------------------------------------------------------------------------------
@@ -406,7 +409,7 @@ __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, cons
 // round trip) and the RMSNorm runs out of registers.
 template <int NPER, bool LL>
 __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * ls, const __half * row, const float * trow,
-                                             int t, __half * xh, double * red, uint32_t tag_in, uint32_t tag_x) {
+                                             int t, __half * xh, double * red, uint32_t tag_in, uint32_t tag_x, uint32_t * tr) {
     const int K = op.K;
     float xv[NPER], nw[NPER];
     if (LL) {
@@ -451,6 +454,7 @@ __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * l
             }
         }
     }
+    if (tr) tr[2] = (uint32_t) clock64();
     if (op.x_out && blockIdx.x == 0) {
 #pragma unroll
         for (int j = 0; j < NPER; ++j) {
@@ -489,7 +493,7 @@ __device__ __forceinline__ void gemv_prepare(const Op & op, const LocalState * l
 __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, LocalState * ls, float * xs, double * red,
                                const Ring & ring, uint32_t cons_seq,
                                const WSched * sched, int n_sched, int n_frames, Prefetch & pf, unsigned long long * prof,
-                               uint32_t tag, bool ll, bool pf_pending) {
+                               uint32_t tag, bool ll, bool pf_pending, uint32_t * tr) {
     const int K = op.K;
     const bool ll_in = ll && op.in_ll != nullptr && op.in_kind == IN_VEC;
     const uint32_t tag_in = tag - (uint32_t) op.in_dist;
@@ -512,18 +516,19 @@ __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, 
     const int nper = (K + kThreads - 1) / kThreads;
     for (int t = 0; t < op.n_tok; ++t) {
         if (ll_in) {
-            if (nper <= 2)      gemv_prepare<2, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
-            else if (nper <= 4) gemv_prepare<4, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
-            else if (nper <= 6) gemv_prepare<6, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
-            else                gemv_prepare<kMaxPerThread, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            if (nper <= 2)      gemv_prepare<2, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
+            else if (nper <= 4) gemv_prepare<4, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
+            else if (nper <= 6) gemv_prepare<6, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
+            else                gemv_prepare<kMaxPerThread, true>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
         } else {
-            if (nper <= 2)      gemv_prepare<2, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
-            else if (nper <= 4) gemv_prepare<4, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
-            else if (nper <= 6) gemv_prepare<6, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
-            else                gemv_prepare<kMaxPerThread, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u);
+            if (nper <= 2)      gemv_prepare<2, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
+            else if (nper <= 4) gemv_prepare<4, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
+            else if (nper <= 6) gemv_prepare<6, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
+            else                gemv_prepare<kMaxPerThread, false>(op, ls, row, trow, t, xh, red, tag_in, ll ? tag : 0u, tr);
         }
     }
     __syncthreads();
+    if (tr) tr[3] = (uint32_t) clock64();
     if (pf_pending && threadIdx.x == kPfThread) prefetch_issue(sched, n_sched, n_frames, pf, cons_seq, ring);
     if (prof_on) { const long long t = clock64(); prof[OP_GEMV * 8 + 4] += (unsigned long long) (t - tA); tA = t; }
 
@@ -550,6 +555,7 @@ __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, 
         }
     }
     if (prof_on) { const long long t = clock64(); prof[OP_GEMV * 8 + 5] += (unsigned long long) (t - tA); }
+    if (tr) tr[4] = (uint32_t) clock64();
     return (uint32_t) nch;
 }
 
@@ -1602,12 +1608,19 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
             const bool pf_in_stage = pf_pending && op.type == OP_GEMV;
             pf_pending = false;
             bool all_to_all = true;
+            uint32_t * tr = nullptr;
+            if (cfg.trace && blockIdx.x == cfg.prof_cta && threadIdx.x == 0 && f * n_ops + i < cfg.trace_cap) {
+                tr = cfg.trace + (size_t) (f * n_ops + i) * 8;
+                tr[0] = (uint32_t) op.type | ((uint32_t) i << 8);
+                tr[6] = (uint32_t) f;
+                tr[1] = (uint32_t) clock64();
+            }
             const bool prof_on = cfg.prof && blockIdx.x == cfg.prof_cta && threadIdx.x == 0;
             const long long t0 = prof_on ? clock64() : 0;
             const long long t0p = (cfg.prof && threadIdx.x == 0) ? clock64() : 0;
             switch (op.type) {
                 case OP_GEMV:       cons_seq += stage_gemv(op, st, &ls, xs, red, ring, cons_seq, cfg.sched, cfg.n_sched, n_frames, pf, prof_on ? cfg.prof : nullptr,
-                                                           cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll, pf_in_stage); break;
+                                                           cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll, pf_in_stage, tr); break;
                 case OP_ATTN:       stage_attn(op, &ls, scratch, cfg.tag_base + 1u + (uint32_t) (f * n_ops + i), ll); break;
                 case OP_COPY:       stage_copy(op); break;
                 case OP_SAMPLE_CB0: stage_sample_cb0(op, st, &ls, scratch, xs); all_to_all = false; break;
@@ -1615,7 +1628,7 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
                 case OP_FRAME_END:  stage_frame_end(op, st, &ls); all_to_all = false; break;
             }
             const long long t1 = prof_on ? clock64() : 0;
-            const long long t1p = (cfg.prof && threadIdx.x == 0) ? clock64() : 0;
+            const long long t1p = ((cfg.prof || tr) && threadIdx.x == 0) ? clock64() : 0;
             if (!all_to_all) {
                 if (cfg.check_done && op.type != OP_SAMPLE_CP && ls.done) stop = true;
             } else if (ll && (op.flags & F_LL_OUT)) {
@@ -1625,6 +1638,7 @@ qtts_run_program(const Op * __restrict__ ops, int n_ops, StreamState * st, GridB
             } else {
                 __syncthreads();
             }
+            if (tr) { if (op.type != OP_GEMV) tr[4] = (uint32_t) t1p; tr[5] = (uint32_t) clock64(); }
             if (cfg.prof && threadIdx.x == 0 && op.type <= OP_ATTN) {   // per-CTA view: prof[64 + cta*4 + ...]
                 const long long t2 = clock64();
                 cfg.prof[64 + blockIdx.x * 4 + op.type * 2 + 0] += (unsigned long long) (t1p - t0p);

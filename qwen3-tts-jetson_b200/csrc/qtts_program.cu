@@ -410,8 +410,8 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
             }
             e->ll_seq = 0;
         }
-        RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 1, check_done ? 1 : 0, e->prof_on - 1, n_sched, d_sched,
-                   e->ll_seq, e->prof_on ? e->prof : nullptr};
+        RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 1, check_done ? 1 : 0, e->trace_on ? e->trace_cta : e->prof_on - 1, n_sched, d_sched,
+                   e->ll_seq, e->prof_on ? e->prof : nullptr, e->trace_on ? e->trace : nullptr, e->trace_cap};
         e->ll_seq += (uint32_t) n_tags;
         StreamState * st = s.st;
         GridBarrier * bar = e->bar;
@@ -431,7 +431,7 @@ bool run_device_program(Engine * e, Slot & s, const Op * d_ops, const std::vecto
         int si = 0;     // schedule entry of the i-th op when it is a GEMV
         for (int i = 0; i < n_ops; ++i) {
             const bool is_gemv = (*host_ops)[i].type == OP_GEMV;
-            RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 0, 0, 0, is_gemv ? 1 : 0, d_sched + si, 0u, nullptr};
+            RunCfg cfg{e->slot_bytes, e->n_slots, e->xs_elems, 0, 0, 0, is_gemv ? 1 : 0, d_sched + si, 0u, nullptr, nullptr, 0};
             if (is_gemv) ++si;
             qtts_run_program<<<e->n_sms, kThreads, e->smem_bytes, e->stream>>>(d_ops + i, 1, s.st, e->bar, 1, cfg);
             e->launches += 1;

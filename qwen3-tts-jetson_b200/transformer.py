@@ -45,7 +45,7 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_step_frames",
            "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
            "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle",
-           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step"]
+           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step", "qtts_trace"]
 
 _lib = None
 
@@ -84,6 +84,7 @@ def load_library(path: str | None = None):
     lib.qtts_set_debug.argtypes = [vp, C.c_int]
     lib.qtts_resize_kv.argtypes = [vp, i32, i32]
     lib.qtts_get_hidden_states.argtypes = [vp, C.c_int, vp]
+    lib.qtts_trace.argtypes = [vp, C.c_int, C.c_int, vp, i32]
     lib.qtts_cp_step.argtypes = [vp, C.c_int, vp, i32, i32, i32, i32, i32, C.c_int, vp, i32]
     lib.qtts_predict_codes.argtypes = [vp, C.c_int, vp, i32, C.c_float, i32, vp, vp, vp, vp]
     lib.qtts_generate.argtypes = [vp, C.c_int, vp, i32, vp, i32, i32, C.c_float, C.c_float, i32, C.c_uint64,
@@ -223,6 +224,12 @@ class TTSTransformer:
         d = {n: out[i * 8:(i + 1) * 8].tolist() for i, n in enumerate(names)}
         d["per_cta"] = out[64:].reshape(256, 4)
         return d
+
+    def trace(self, on: bool, cta: int = 0, max_stages: int = 8192):
+        """Read-and-clear the stage timeline (qtts_trace): uint32 [stages, 8]; then switch recording."""
+        out = np.zeros((max_stages, 8), np.uint32)
+        self._lib.qtts_trace(self._h, 1 if on else 0, cta, _ptr(out), max_stages)
+        return out
 
     def launch_count(self) -> int:
         return int(self._lib.qtts_launch_count(self._h))
