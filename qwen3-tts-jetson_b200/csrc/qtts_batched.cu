@@ -101,7 +101,9 @@ struct BShared {
     uint32_t tag;            // this stage's tag (split-K hand-off)
     uint32_t rows_target;    // rows signalled by all BF_ROWS_SIGNAL stages of this launch so far (uniform over the grid)
     int32_t all_done;
+    uint32_t * tr;           // this stage's 16-word trace slot (nullptr: not traced)
 };
+#define BTR(k) do { if (S->tr) S->tr[k] = (uint32_t) clock64(); } while (0)
 constexpr size_t kBSharedBytes = (sizeof(BShared) + 127) & ~(size_t) 127;
 
 // [BShared][A buffers 2 x kABufBytes][weight ring]: an M = 128 MMA reads 128 rows although a piece
@@ -174,11 +176,13 @@ __device__ __forceinline__ void bgrid_barrier(BShared * S, unsigned int & epoch)
         __threadfence();
         atomicAdd(cnt, 1u);
 #endif
+        BTR(9);
         unsigned int v;
         do {
             asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
         } while ((int) (v - target) < 0);
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
+        BTR(10);
     } else if (threadIdx.x == kPfThread) {
         bpf_poll(S);
     }
@@ -355,7 +359,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
 #pragma unroll
                 for (int i = 0; i < 4; ++i) side[i] = __ldg(reinterpret_cast<const float4 *>(op.bias + n0 + 4 * i));
             }
-            if (!waited) { mbar_wait(&S->dbar, d_use & 1u); tc_fence_after(); waited = true; }
+            if (!waited) { mbar_wait(&S->dbar, d_use & 1u); tc_fence_after(); waited = true; if (threadIdx.x == 32) BTR(6); }
             __syncwarp();
             float acc[16];
             if (!(dbg & 2)) {
@@ -586,6 +590,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     } while ((int) (v - target) < 0);
                 }
                 asm volatile("fence.proxy.async.global;" ::: "memory");
+                if (t == t_first) BTR(2);
                 const unsigned char * in = reinterpret_cast<const unsigned char *>(op.in);
                 for (int s = 0; s < steps; ++s) {
                     const int kc = s / m_tiles, mt = s - kc * m_tiles;
@@ -602,6 +607,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     }
                     S->n_fill[bi] = nf + 1;
                 }
+                if (t == t_first) BTR(3);
             } else if (lane == 0 && warp < kIssuers) {
                 // Chunk-alternating issue: issuer w takes the K-chunks kc = w, w + n_alt, ... and issues all
                 // 8 K-steps of each into its OWN accumulators (summed by the epilogue).  A tcgen05.mma costs
@@ -624,6 +630,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     const uint32_t seq = cons_seq + (uint32_t) piece;
                     const int slot = (int) (seq % (uint32_t) kBSlots);
                     mbar_wait(S->full + slot, (seq / (uint32_t) kBSlots) & 1u);     // every issuer: keeps the slot phases aligned
+                    if (warp == 0 && piece == 0 && t == t_first) BTR(11);
                     const uint32_t w0 = ring0 + (uint32_t) slot * kBSlotBytes;
                     bool mine = false;
                     for (int c = 0; c < chunks; ++c, ++kc) {
@@ -635,6 +642,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                             const uint32_t fill = S->fill_base[bi] + (uint32_t) (s >> nab_shift);
                             const long long ca = pr ? clock64() : 0;
                             mbar_wait(S->tfull + bi, fill & 1u);
+                            if (warp == 0 && s == 0 && t == t_first) BTR(4);
                             const long long cb2 = pr ? clock64() : 0;
                             tc_fence_after();
                             if (!skip_mma) {
@@ -656,6 +664,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->empty + slot)) : "memory");
                 }
                 umma_commit(&S->dbar);
+                if (warp == 0 && t == t_first) BTR(5);
                 if (pr) {
                     unsigned long long * P = S->run.prof;
                     P[40] += 1; P[41] += (unsigned long long) c_first; P[42] += (unsigned long long) c_wait;
@@ -669,6 +678,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
             const bool pr1 = S->run.prof != nullptr && tid == 32 && t == 0;      // a thread without issue duties
             const long long e0 = pr1 ? clock64() : 0;
             bgemm_epilogue(S, t, m_tiles, d_use, acc_mode, mt0);
+            if (tid == 32 && t == t_first) BTR(7);
             const long long e1 = pr1 ? clock64() : 0;
             d_use++;
             tc_fence_before();
@@ -1466,9 +1476,20 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                 reinterpret_cast<uint32_t *>(&S->op)[threadIdx.x] = next_word;
                 have_next = true;
             }
-            if (threadIdx.x == kThreads - 1) S->tag = run_param.tag_base + 1u + (uint32_t) (f * n_ops + i);
+            if (threadIdx.x == kThreads - 1) {
+                S->tag = run_param.tag_base + 1u + (uint32_t) (f * n_ops + i);
+                uint32_t * tr = nullptr;
+                if (run_param.trace && (int) blockIdx.x == run_param.trace_cta && f * n_ops + i < run_param.trace_cap)
+                    tr = run_param.trace + (size_t) (f * n_ops + i) * 16;
+                S->tr = tr;
+            }
             __syncthreads();
             const int type = S->op.type, in_kind = S->op.in_kind;
+            if (threadIdx.x == 0 && S->tr) {
+                S->tr[0] = (uint32_t) type | ((uint32_t) (in_kind & 1) << 4) | ((uint32_t) (S->op.flags & 0xff) << 8) | ((uint32_t) i << 16);
+                S->tr[12] = (uint32_t) S->op.K; S->tr[13] = (uint32_t) S->op.rows; S->tr[14] = (uint32_t) f;
+                S->tr[1] = (uint32_t) clock64();
+            }
             const long long t0 = prof ? clock64() : 0;
             switch (type) {
                 case BOP_GEMM:
@@ -1484,6 +1505,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                 case BOP_NORM:    bstage_norm(S); break;
             }
             const long long t1 = prof ? clock64() : 0;
+            if (threadIdx.x == 0) BTR(8);
             if (threadIdx.x < (int) (sizeof(BOp) / 4)) {     // next stage's descriptor lands during the barrier
                 const int ni = (i + 1 < n_ops) ? i + 1 : 0;
                 next_word = __ldg(reinterpret_cast<const uint32_t *>(run_param.ops + ni) + threadIdx.x);

@@ -378,6 +378,7 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
     }
     run.prof = e->prof_on ? e->prof + 2048 : nullptr;
     { const char * d = getenv("QTTS_BDBG"); run.dbg = d ? atoi(d) : 0; }
+    run.trace = e->trace_on ? e->trace : nullptr; run.trace_cta = e->trace_cta; run.trace_cap = e->trace_cap / 2;
     void * args[] = {(void *) &run};
     QTTS_CUDA(cudaLaunchCooperativeKernel((const void *) qtts_run_batched, dim3(e->n_sms), dim3(kThreads), args,
                                           kBSmemBytes, e->stream));

@@ -118,6 +118,8 @@ struct BRun {
     uint32_t tag_base;           // stage tag = tag_base + 1 + frame * n_ops + op index (never repeated)
     unsigned long long * prof;   // optional stage timers
     int32_t dbg;                 // bring-up switches (env QTTS_BDBG): 1 skip MMA issue, 2 skip TMEM loads
+    uint32_t * trace;            // optional stage timeline of CTA trace_cta: 16 words per stage, store-only stamps written
+    int32_t trace_cta, trace_cap;//   by the threads that own each step (see tools/trace_batched.py for the slots)
 };
 
 }  // namespace qtts
