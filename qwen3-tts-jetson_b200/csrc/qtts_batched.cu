@@ -162,10 +162,12 @@ __device__ __forceinline__ void bpf_ensure(BShared * S, uint32_t seq_needed) {
     while ((int32_t) (S->pf.seq - seq_needed) <= 0) if (!bpf_issue(S, true)) break;
 }
 
-__device__ __forceinline__ void bgrid_barrier(BShared * S, unsigned int & epoch) {
-    asm volatile("fence.proxy.async.global;" ::: "memory");   // F16 activations are re-read by bulk copies (async proxy)
+__device__ __forceinline__ void bgrid_barrier(BShared * S, unsigned int & epoch, bool async_out) {
+    // F16 activations are re-read by bulk copies (async proxy): writer-side proxy fence, only behind such stages
+    if (async_out) asm volatile("fence.proxy.async.global;" ::: "memory");
     __syncthreads();
     if (threadIdx.x == 0) {
+        BTR(15);
         const unsigned int target = epoch + gridDim.x;
         epoch = target;
         unsigned int * cnt = &S->run.bar->count;
@@ -989,6 +991,150 @@ __device__ __noinline__ void bstage_attn_cp(BShared * S) {
     }
 }
 
+// Single-token code-predictor attention, one warp per (stream, QUERY HEAD): twice the items of the per-group form
+// above (1024 at 64 streams: every warp of the grid still gets at most one), half the dependent chain per warp,
+// and the softmax over the <= 16 keys is evaluated by the lanes in parallel (lane j owns key j; the double sum runs
+// through the same xor tree as the batch-1 kernel's block_sum_d over one warp).  Both head-warps of a KV group
+// compute the group's new key themselves; the first one appends it to the cache, and neither reads row `pos` back
+// from global memory (the current key / value travel through the warp's own shared-memory scratch).
+__device__ __noinline__ void bstage_attn_cp_head(BShared * S) {
+    const BOp & op = S->op;
+    const int lane = threadIdx.x & 31, hw = lane >> 4, l16 = lane & 15;
+    const int wib = threadIdx.x >> 5;
+    const int gw = blockIdx.x * kWarps + wib, nw = gridDim.x * kWarps;
+    const int B = op.n_streams, nh = op.n_heads, nkv = op.n_kv_heads, rep = nh / nkv;
+    const int kvw = nkv * kHeadDim;
+    const int pos = op.pos, n_kv = pos + 1;          // <= 16
+    // per-warp scratch in the (idle) A-buffer area: q (F16-rounded, as floats), current key / value (F16), scores
+    unsigned char * wsm = babuf_base(S) + (size_t) wib * 1280;
+    float * qs = reinterpret_cast<float *>(wsm);                       // [128]
+    __half * ks = reinterpret_cast<__half *>(wsm + 512);               // [128]
+    __half * vs = reinterpret_cast<__half *>(wsm + 768);               // [128]
+    float * scw = reinterpret_cast<float *>(wsm + 1024);               // [16] scores, then probabilities
+    float wq[4], wk[4], rc[2], rs[2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        wq[j] = op.q_norm_w ? __ldg(op.q_norm_w + lane + 32 * j) : 1.f;
+        wk[j] = op.k_norm_w ? __ldg(op.k_norm_w + lane + 32 * j) : 1.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const float2 cs = __ldg(reinterpret_cast<const float2 *>(op.rope) + (size_t) pos * 64 + lane + 32 * j);
+        rc[j] = cs.x; rs[j] = cs.y;
+    }
+    const int cb = canon_chunk_bytes(op.rows_act);
+    for (int item = gw; item < B * nh; item += nw) {
+        const int b = item / nh, h = item - b * nh, g = h / rep;
+        __half * kc = op.kc + (size_t) b * op.kv_stream_stride + g * kHeadDim;
+        __half * vc = op.vc + (size_t) b * op.kv_stream_stride + g * kHeadDim;
+        const float * base = op.qkv + (size_t) b * op.qkvw;
+        // cached rows of the earlier positions: requested first, they do not depend on this token
+        uint4 kv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int jk = 2 * i + hw;
+            kv[i] = (jk < pos) ? __ldcg(reinterpret_cast<const uint4 *>(kc + (size_t) jk * kvw + 8 * l16)) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        float k[4], v[4], q[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            k[j] = __ldcg(base + (size_t) (nh + g) * kHeadDim + lane + 32 * j);
+            v[j] = __ldcg(base + (size_t) (nh + nkv + g) * kHeadDim + lane + 32 * j);
+            q[j] = __ldcg(base + (size_t) h * kHeadDim + lane + 32 * j);
+        }
+        warp_norm_rope_pre(k, wk, rc, rs, op.eps, op.k_norm_w != nullptr);
+        warp_norm_rope_pre(q, wq, rc, rs, op.eps, op.q_norm_w != nullptr);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const __half kh = __float2half_rn(k[j]), vh = __float2half_rn(v[j]);
+            ks[lane + 32 * j] = kh; vs[lane + 32 * j] = vh;
+            qs[lane + 32 * j] = f16r(q[j]);
+            if (h == g * rep) {
+                kc[(size_t) pos * kvw + lane + 32 * j] = kh;
+                vc[(size_t) pos * kvw + lane + 32 * j] = vh;
+            }
+        }
+        __syncwarp();
+        float qa[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) qa[i] = qs[8 * l16 + i];
+        {
+            const uint4 kcur = *reinterpret_cast<const uint4 *>(ks + 8 * l16);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) if (2 * i + hw == pos) kv[i] = kcur;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const __half2 * hk = reinterpret_cast<const __half2 *>(&kv[i]);
+            float sdot = 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float2 f = __half22float2(hk[u]);
+                sdot = fmaf(f.x, qa[2 * u], sdot);
+                sdot = fmaf(f.y, qa[2 * u + 1], sdot);
+            }
+#pragma unroll
+            for (int o2 = 8; o2 > 0; o2 >>= 1) sdot += __shfl_xor_sync(0xffffffffu, sdot, o2);
+            if (l16 == 0 && 2 * i + hw < n_kv) scw[2 * i + hw] = sdot * op.kq_scale;
+        }
+        // the value rows are requested before the softmax needs the scores
+        {
+            const uint4 vcur = *reinterpret_cast<const uint4 *>(vs + 8 * l16);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int jk = 2 * i + hw;
+                kv[i] = (jk < pos) ? __ldcg(reinterpret_cast<const uint4 *>(vc + (size_t) jk * kvw + 8 * l16))
+                                   : (jk == pos ? vcur : make_uint4(0u, 0u, 0u, 0u));
+            }
+        }
+        __syncwarp();
+        // softmax: lane j owns key j (ggml soft_max: exp(x - max), double sum, scale by (float) (1 / sum); the P.V
+        // mul_mat then rounds P to F16)
+        const float sj = (lane < n_kv) ? scw[lane] : -CUDART_INF_F;
+        const float mx = warp_max(sj);
+        const float ej = (lane < n_kv) ? expf(sj - mx) : 0.f;
+        const double sum = warp_sum_d((double) ej);
+        const float inv = (float) (1.0 / sum);
+        __syncwarp();
+        if (lane < n_kv) scw[lane] = f16r(ej * inv);
+        __syncwarp();
+        float accA[8], accB[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { accA[u] = 0.f; accB[u] = 0.f; }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int jk = 2 * i + hw;
+            if (jk < n_kv) {
+                const float pk = scw[jk];
+                const __half2 * hv = reinterpret_cast<const __half2 *>(&kv[i]);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float2 f = __half22float2(hv[u]);
+                    if (i & 1) { accB[2 * u] = fmaf(f.x, pk, accB[2 * u]); accB[2 * u + 1] = fmaf(f.y, pk, accB[2 * u + 1]); }
+                    else       { accA[2 * u] = fmaf(f.x, pk, accA[2 * u]); accA[2 * u + 1] = fmaf(f.y, pk, accA[2 * u + 1]); }
+                }
+            }
+        }
+        __half2 oh[4];
+#pragma unroll
+        for (int u = 0; u < 8; u += 2) {
+            // half-warp 0 holds key classes 0 (A) and 2 (B), half-warp 1 classes 1 and 3: (p0 + p1) + (p2 + p3)
+            const float a0 = accA[u] + __shfl_xor_sync(0xffffffffu, accA[u], 16);
+            const float b0 = accB[u] + __shfl_xor_sync(0xffffffffu, accB[u], 16);
+            const float a1 = accA[u + 1] + __shfl_xor_sync(0xffffffffu, accA[u + 1], 16);
+            const float b1 = accB[u + 1] + __shfl_xor_sync(0xffffffffu, accB[u + 1], 16);
+            oh[u >> 1] = __floats2half2_rn(a0 + b0, a1 + b1);
+        }
+        if (hw == 0) {
+            uint4 pk4;
+            pk4.x = *reinterpret_cast<const uint32_t *>(&oh[0]); pk4.y = *reinterpret_cast<const uint32_t *>(&oh[1]);
+            pk4.z = *reinterpret_cast<const uint32_t *>(&oh[2]); pk4.w = *reinterpret_cast<const uint32_t *>(&oh[3]);
+            *reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(op.attn16) + canon_off(b, h * kHeadDim + 8 * l16, cb)) = pk4;
+        }
+        __syncwarp();
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // BOP_ATTN_TK — Talker decode attention, one CTA pass per (stream, KV group): QK-norm + NEOX RoPE
 // + F16 KV append, FP32 softmax and P.V over the F16 cache (ATTN_FAST numerics of qtts_kernels.cu).
@@ -1496,7 +1642,11 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                     if (in_kind == BIN_F32) bstage_gemm<BIN_F32>(S);
                     else                    bstage_gemm_tma(S);
                     break;
-                case BOP_ATTN_CP: if (S->op.pair_f32) bstage_attn_cp<true>(S); else bstage_attn_cp<false>(S); break;
+                case BOP_ATTN_CP:
+                    if (S->op.pair_f32) bstage_attn_cp<true>(S);
+                    else if (S->run.dbg & 64) bstage_attn_cp<false>(S);        // A/B switch: the per-group form
+                    else bstage_attn_cp_head(S);
+                    break;
                 case BOP_ATTN_TK:
                     if (S->op.pair_f32 == 2 && S->op.n_heads == 2 * S->op.n_kv_heads) bstage_attn_tk_warp(S);
                     else bstage_attn_tk(S);
@@ -1514,7 +1664,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                 if (threadIdx.x == kPfThread) bpf_poll(S);      // no barrier: the consumer waits for the row counter
                 __syncthreads();
             } else {
-                bgrid_barrier(S, epoch);
+                bgrid_barrier(S, epoch, (S->op.flags & BF_ASYNC_OUT) != 0 || (S->run.dbg & 32) != 0);
             }
             if (prof) {
                 const long long t2 = clock64();

@@ -116,12 +116,13 @@ struct BEmit {
                 n.part32 = part32 + (reinterpret_cast<const float *>(in) - pending_x);
                 pending_x = nullptr;
             }
+            n.flags |= BF_ASYNC_OUT;            // xn16 is fetched by bulk copies (matters when the stage ends with a grid barrier)
             if (rows_signal) { n.flags |= BF_ROWS_SIGNAL; flags |= BF_ROWS_WAIT; }
             P.push_back(n);
             in_kind = BIN_F16; in = xn16; norm_w = nullptr; ssq_in = nullptr; n_parts_in = 0; hid_out = nullptr;
         }
         BOp o = bblank(B);
-        o.type = BOP_GEMM; o.rows_act = rows_act; o.flags = flags | (ssq_out ? BF_SSQ_OUT : 0);
+        o.type = BOP_GEMM; o.rows_act = rows_act; o.flags = flags | (ssq_out ? BF_SSQ_OUT : 0) | (out16 ? BF_ASYNC_OUT : 0);
         o.Wt = T.p; o.rows = T.rows; o.K = T.K; o.n_tile = T.n_tile; o.n_tiles = T.n_tiles; o.cta_off = cta_off;
         o.kpp = T.kpp; o.n_pieces = T.n_pieces;
         o.ksplit = T.ksplit; o.part_ll = (T.ksplit > 1) ? part_ll : nullptr;
@@ -155,6 +156,7 @@ static void emit_blayer(BEmit & E, const TiledLayer & L, const LayerW & W, const
     attn.qkv = qkv; attn.qkvw = qkvw; attn.q_norm_w = W.q_norm; attn.k_norm_w = W.k_norm;
     attn.n_heads = D.nh; attn.n_kv_heads = D.nkv; attn.n_tok = n_tok; attn.rows_act = rows_act;
     attn.attn16 = attn16; attn.attn_w = aw;
+    attn.flags |= BF_ASYNC_OUT;         // the O projection fetches attn16 by bulk copies
     E.P.push_back(attn);
     E.gemm(L.o, rows_act, BIN_F16, attn16, aw, B * aw, nullptr, nullptr, 0, EPI_ADD,
            x, nullptr, x, nullptr, D.H, B * D.H, ssq_p);

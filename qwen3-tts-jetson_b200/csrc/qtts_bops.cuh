@@ -41,6 +41,9 @@ enum BFlags : int32_t {
     BF_SSQ_OUT   = 2,      // GEMM epilogue writes per-row sum-of-squares partials of its output
     BF_ROWS_SIGNAL = 4,    // BOP_NORM: every finished row bumps the group's row counter; NO grid barrier after the stage
     BF_ROWS_WAIT   = 8,    // GEMM fed by such a stage: the A-operand producer waits for the row counter instead
+    BF_ASYNC_OUT   = 16,   // the stage's output (F16 canonical chunks) is fetched by BULK COPIES (async proxy) in the next
+                           // stage: the grid barrier behind it needs fence.proxy.async.global on the writer side; stages
+                           // whose output is read with ordinary loads skip that fence
 };
 
 struct BOp {

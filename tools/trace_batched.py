@@ -53,9 +53,9 @@ for key, ks in groups.items():
     if key[0] == "gemm" and key[4]:
         line += (f" | in-ready {np.nanmean(d(2, 1)[ks]):5.2f} copies {np.nanmean(d(3, 1)[ks]):5.2f} w {np.nanmean(d(11, 1)[ks]):5.2f} A0 {np.nanmean(d(4, 1)[ks]):5.2f}"
                  f" mma {np.nanmean(d(5, 1)[ks]):5.2f} acc {np.nanmean(d(6, 1)[ks]):5.2f} stored {np.nanmean(d(7, 1)[ks]):5.2f}")
-    bar = d(10, 8)[ks]; arr = d(9, 8)[ks]
+    bar = d(10, 8)[ks]; arr = d(9, 8)[ks]; syn = d(15, 8)[ks]
     if np.isfinite(bar).any():
-        line += f" | barrier arrive {np.nanmean(arr):5.2f} release {np.nanmean(bar):5.2f}"
+        line += f" | barrier: cta-sync {np.nanmean(syn):5.2f} arrive {np.nanmean(arr):5.2f} release {np.nanmean(bar):5.2f}"
     print(line)
     tot += np.nansum(d(8, 1)[ks] + nxt[ks]) / frames
 print(f"sum {tot / 1e3:.3f} ms per frame-step")
