@@ -545,13 +545,15 @@ int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int
     Engine * e = &h->e;
     if (!e->finalized) { e->err = "engine not finalized"; return 0; }
     cudaSetDevice(e->device);
-    if (!prefill_pending(e)) return 0;        // streams prepared since the last call join here
+    // the timed region starts before the batched prefill of streams prepared since the last call (they join here):
+    // qtts_last_loop_ms of such a call includes it
+    cudaEventRecord(e->ev0, e->stream);
+    if (!prefill_pending(e)) return 0;
     const int nb = e->cfg.n_codebooks;
     const size_t ns = e->slots.size();
     std::vector<StreamState> hs0(ns), hs1(ns);
     if (cudaMemcpyAsync(hs0.data(), e->bb.st, ns * sizeof(StreamState), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
         cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = "step_frames: state read failed"; return 0; }
-    cudaEventRecord(e->ev0, e->stream);
     if (e->batched && e->batched_ready) {
         for (auto & G : e->groups) if (!run_batched_group(e, G, n_frames)) return 0;
     } else {

@@ -5,7 +5,7 @@ synthesises ONE request at a time and answers `OK\\t<seconds>\\t<ms>\\t<file>` o
 on stdout.  The hot path alone has no tokenizer and no vocoder, so the requests here carry token ids
 and the product is the codec-frame stream the vocoder consumes:
 
-    request :  <id> TAB <comma-separated text token ids> TAB <output file> [TAB <max frames>]
+    request :  <id> TAB <comma-separated text token ids> TAB <output file> [TAB <max frames> [TAB <seed>]]
     answer  :  OK TAB <id> TAB <frames> TAB <ms> TAB <output file>        (or ERR TAB <id> TAB <message>)
     `quit` / `exit` end the loop after the requests in flight have finished.
 
@@ -19,6 +19,7 @@ frames as little-endian int32 [n_frames][n_codebooks].
 """
 from __future__ import annotations
 
+import os
 import sys
 import time
 from collections import deque
@@ -39,8 +40,14 @@ class BatchingServer:
     get_error, config['n_codebooks'])."""
 
     def __init__(self, engine, max_len: int = 4096, frames_per_call: int = 40, chunk_frames: int = 40,
-                 on_chunk=None, **sampling):
+                 on_chunk=None, base_seed: int | None = None, **sampling):
+        """base_seed: None (default) seeds the per-request sampler seeds from os.urandom, the way the reference seeds
+        its mt19937 from std::random_device (src/tts_transformer.h:298); an integer makes a server run reproducible.
+        Either way every request gets its OWN seed (the device uniform is philox(seed, frame, codebook): one shared
+        seed would make all concurrent requests draw the same uniform sequence)."""
         self.engine, self.max_len = engine, max_len
+        self._seed_base = int.from_bytes(os.urandom(8), "little") if base_seed is None else int(base_seed)
+        self._n_submitted = 0
         self.frames_per_call, self.chunk_frames = frames_per_call, chunk_frames
         self.on_chunk, self.sampling = on_chunk, sampling
         self.queue: deque = deque()
@@ -49,8 +56,16 @@ class BatchingServer:
         self.nb = engine.config["n_codebooks"]
 
     # -- requests ---------------------------------------------------------------------------------
-    def submit(self, req_id: str, tokens, out: str | None = None, speaker=None, max_len: int | None = None, seed: int = 0):
-        self.queue.append((req_id, np.asarray(tokens, np.int32), out, speaker, max_len or self.max_len, seed))
+    def submit(self, req_id: str, tokens, out: str | None = None, speaker=None, max_len: int | None = None,
+               seed: int | None = None):
+        """seed: None = the server's next per-request seed; an explicit value reproduces a request exactly."""
+        if seed is None:
+            z = (self._seed_base + 0x9E3779B97F4A7C15 * (self._n_submitted + 1)) & 0xFFFFFFFFFFFFFFFF      # splitmix64
+            z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+            z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+            seed = (z ^ (z >> 31)) & 0x7FFFFFFFFFFFFFFF
+        self._n_submitted += 1
+        self.queue.append((req_id, np.asarray(tokens, np.int32), out, speaker, max_len or self.max_len, int(seed)))
 
     def idle(self) -> bool:
         return not self.queue and not self.live
@@ -116,7 +131,7 @@ class BatchingServer:
     # -- the line protocol ------------------------------------------------------------------------
     @staticmethod
     def parse(line: str):
-        """-> ("quit",) | ("req", id, tokens, out, max_len) | ("err", id, message)"""
+        """-> ("quit",) | ("req", id, tokens, out, max_len, seed) | ("err", id, message)"""
         line = line.rstrip("\r\n")
         if not line:
             return None
@@ -128,9 +143,10 @@ class BatchingServer:
         try:
             tokens = [int(t) for t in f[1].replace(" ", "").split(",") if t]
             max_len = int(f[3]) if len(f) > 3 and f[3] else None
+            seed = int(f[4]) if len(f) > 4 and f[4] else None
         except ValueError:
-            return ("err", f[0], "token ids and max frames must be integers")
-        return ("req", f[0], tokens, f[2] if len(f) > 2 and f[2] else None, max_len)
+            return ("err", f[0], "token ids, max frames and seed must be integers")
+        return ("req", f[0], tokens, f[2] if len(f) > 2 and f[2] else None, max_len, seed)
 
     def serve(self, lines, out=sys.stdout, err=sys.stderr):
         """`lines`: an iterable of request lines (sys.stdin, or a list in tests).  Requests that are
@@ -160,8 +176,8 @@ class BatchingServer:
             if p[0] == "err":
                 print(f"ERR\t{p[1]}\t{p[2]}", file=out, flush=True)
                 continue
-            _, req_id, tokens, path, max_len = p
-            self.submit(req_id, tokens, path, max_len=max_len)
+            _, req_id, tokens, path, max_len, seed = p
+            self.submit(req_id, tokens, path, max_len=max_len, seed=seed)
             # keep reading while slots are free; once they are all taken, make room
             while self.queue and not self.free:
                 answer(self.pump())
@@ -181,12 +197,14 @@ def main(argv=None):
     ap.add_argument("--top-k", type=int, default=50)
     ap.add_argument("--repetition-penalty", type=float, default=1.05)
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--seed", type=int, default=None, help="base of the per-request sampler seeds (default: os.urandom)")
     a = ap.parse_args(argv)
-    T = transformer.TTSTransformer(device=a.device, max_streams=a.streams, max_ctx=a.max_tokens + 512)
+    # KV slots per stream: prefill (<= 11) + frames + 8 (src/tts_transformer.cpp:2383); the engine's cap is 4608
+    T = transformer.TTSTransformer(device=a.device, max_streams=a.streams, max_ctx=min(a.max_tokens + 32, 4608))
     if not T.load_model(a.model):
         print("ERR\t-\t" + T.get_error(), flush=True)
         return 1
-    srv = BatchingServer(T, max_len=a.max_tokens, temperature=a.temperature, top_k=a.top_k,
+    srv = BatchingServer(T, max_len=a.max_tokens, base_seed=a.seed, temperature=a.temperature, top_k=a.top_k,
                          repetition_penalty=a.repetition_penalty)
     return srv.serve(sys.stdin)
 

@@ -27,8 +27,9 @@ def shard(items: Sequence, rank: int, world: int):
     return items[lo:hi]
 
 
-def slot_groups(n_streams: int, group: int = 128) -> list[tuple[int, int]]:
-    """Slots of one GPU advance in lock-step groups of <= `group` streams (one batched launch each)."""
+def slot_groups(n_streams: int, group: int = 256) -> list[tuple[int, int]]:
+    """Slots of one GPU advance in lock-step groups of <= `group` streams (one batched launch each; the engine's
+    group is 256 = Engine::bgroup, csrc/qtts_engine.h)."""
     return [(lo, min(lo + group, n_streams)) for lo in range(0, n_streams, group)]
 
 
@@ -83,7 +84,9 @@ def serve_sharded(engine, utterances: Sequence[dict], rank: int, world: int, cou
     `engine` needs the TTSTransformer stream interface: max_streams, stream_begin, step_frames,
     get_error, last_loop_ms, config['n_codebooks'].
     Returns {'codes': {utterance index: int32 [frames, n_codebooks]} (this rank's shard only),
-             'frames_per_utterance': full list over all ranks, 'frames', 'device_ms', 'value'}."""
+             'frames_per_utterance': full list over all ranks, 'frames', 'device_ms', 'value'}.
+    device_ms (and therefore value) INCLUDES the batched Talker prefill of every wave: it runs inside the wave's
+    first step_frames call, whose timed region (qtts_last_loop_ms) starts before it."""
     import numpy as np
     lo, hi = shard_bounds(len(utterances), rank, world)
     nb = engine.config["n_codebooks"]

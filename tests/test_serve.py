@@ -15,9 +15,35 @@ def test_parse_lines():
     P = qtts_pkg.load().serve.BatchingServer.parse
     assert P("\n") is None
     assert P("quit\n") == ("quit",) and P("exit") == ("quit",)
-    assert P("a\t1,2, 3\tout.bin\t7\n") == ("req", "a", [1, 2, 3], "out.bin", 7)
-    assert P("b\t4,5") == ("req", "b", [4, 5], None, None)
+    assert P("a\t1,2, 3\tout.bin\t7\n") == ("req", "a", [1, 2, 3], "out.bin", 7, None)
+    assert P("a\t1,2, 3\tout.bin\t7\t99\n") == ("req", "a", [1, 2, 3], "out.bin", 7, 99)
+    assert P("b\t4,5") == ("req", "b", [4, 5], None, None, None)
     assert P("only-id")[0] == "err" and P("c\t1,x")[0] == "err"
+
+
+def test_every_request_gets_its_own_seed():
+    """Round-1 advisor finding: all sampled requests ran on seed 0 (same uniform sequence for every concurrent
+    request).  Now: distinct per-request seeds, reproducible with base_seed, overridable per request."""
+    serve = qtts_pkg.load().serve
+    seen = []
+
+    class Rec(FakeEngine):
+        def stream_begin(self, slot, tokens, speaker, max_len, seed, **kw):
+            seen.append(seed)
+            return super().stream_begin(slot, tokens, speaker, max_len, seed, **kw)
+
+    def run(base):
+        seen.clear()
+        srv = serve.BatchingServer(Rec(2, 1.0), max_len=6, base_seed=base)
+        for i in range(5):
+            srv.submit(f"r{i}", [1, 2, 3, 4, 5], seed=1234 if i == 4 else None)
+        srv.drain()
+        return list(seen)
+
+    a, b, c = run(7), run(7), run(8)
+    assert a == b and a[:4] != c[:4]
+    assert len(set(a[:4])) == 4 and a[4] == 1234
+    assert run(None)[:4] != run(None)[:4]       # default: seeded from os.urandom, like std::random_device
 
 
 def test_continuous_batching_and_chunks(tmp_path):
