@@ -30,7 +30,7 @@ def test_every_request_gets_its_own_seed():
     class Rec(FakeEngine):
         def stream_begin(self, slot, tokens, speaker, max_len, seed, **kw):
             seen.append(seed)
-            return super().stream_begin(slot, tokens, speaker, max_len, seed, **kw)
+            return super().stream_begin(slot, tokens, speaker, max_len, seed % 1000, **kw)     # (the test double hashes small seeds)
 
     def run(base):
         seen.clear()
