@@ -30,7 +30,7 @@ def test_every_request_gets_its_own_seed():
     class Rec(FakeEngine):
         def stream_begin(self, slot, tokens, speaker, max_len, seed, **kw):
             seen.append(seed)
-            return super().stream_begin(slot, tokens, speaker, max_len, seed % 1000, **kw)     # (the test double hashes small seeds)
+            return super().stream_begin(slot, tokens, speaker, max_len, seed, **kw)
 
     def run(base):
         seen.clear()
@@ -54,7 +54,8 @@ def test_continuous_batching_and_chunks(tmp_path):
                                on_chunk=lambda rid, c: chunks.setdefault(rid, []).append(c.copy()))
     r = np.random.default_rng(3)
     reqs = {f"r{i}": r.integers(0, 4000, size=5 + i).astype(np.int32) for i in range(5)}
-    lines = [f"{rid}\t{','.join(map(str, t))}\t{tmp_path / (rid + '.i32')}\n" for rid, t in reqs.items()]
+    # explicit seed 0 (5th field): the expected frames below are the test double's seed-0 frames
+    lines = [f"{rid}\t{','.join(map(str, t))}\t{tmp_path / (rid + '.i32')}\t\t0\n" for rid, t in reqs.items()]
     lines.insert(2, "bad line without tab\n")
     lines.append("quit\n")
     lines.append("late\t1,2,3,4\n")                      # after quit: never served

@@ -27,7 +27,7 @@ class FakeEngine:
 
     @staticmethod
     def frame(tokens, seed, f):
-        return (np.arange(NB, dtype=np.int64) * 31 + int(np.sum(tokens)) * 7 + seed * 13 + f * 101) % 2048
+        return (np.arange(NB, dtype=np.int64) * 31 + int(np.sum(tokens)) * 7 + (int(seed) % 1000) * 13 + f * 101) % 2048
 
     def stream_begin(self, slot, tokens, speaker, max_len, seed, **kw):
         if slot >= self.max_streams:
