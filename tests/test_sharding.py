@@ -84,7 +84,7 @@ def test_shard_bounds_cover_and_balance():
             assert max(sizes) - min(sizes) <= 1
     with pytest.raises(ValueError):
         sh.shard_bounds(4, 2, 2)
-    assert sh.slot_groups(300) == [(0, 128), (128, 256), (256, 300)]
+    assert sh.slot_groups(300) == [(0, 256), (256, 300)] and sh.slot_groups(300, 128) == [(0, 128), (128, 256), (256, 300)]
     assert sh.slot_groups(64) == [(0, 64)]
 
 
