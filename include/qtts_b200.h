@@ -210,6 +210,15 @@ int qtts_set_debug(qtts_engine * e, int flags);
  * dropped.  n_ctx is capped at 4608 KV slots per stream (the attention scratch; the reference has no cap). */
 int qtts_resize_kv(qtts_engine * e, int32_t n_ctx, int32_t max_text);
 
+/* Vocoder hand-off: frames [first_frame, first_frame + n_frames) of `slot`, read from the
+ * stream's device-resident code ring, in the input layout of the reference's streamed vocoder: int64
+ * [1][n_codebooks][fixed_frames], frames beyond n_frames zero (TRTVocoderDecoder::decode, src/trt_vocoder.cpp:98-170,
+ * called with the 40-frame chunks of generate()'s callback, src/tts_transformer.cpp:2517-2523, 2563-2570).
+ * out_is_device = 1: `out` is a DEVICE pointer (e.g. the TensorRT input binding: the chunk never visits the host);
+ * 0: host memory.  n_frames <= fixed_frames; the frames must have been generated. */
+int qtts_codes_chunk(qtts_engine * e, int slot, int32_t first_frame, int32_t n_frames, int32_t fixed_frames,
+                     int64_t * out, int out_is_device);
+
 /* 1 (default): qtts_step_frames advances all active streams in lock step with the batched tcgen05
  * kernel (groups of <= 256 slots, env QTTS_BGROUP lowers it); 0: the batch-1 kernel, one stream after another. */
 int qtts_set_batched(qtts_engine * e, int on);

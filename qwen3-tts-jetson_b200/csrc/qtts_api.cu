@@ -83,6 +83,7 @@ void qtts_destroy(qtts_engine * h) {
     cudaStreamSynchronize(e->stream);
     for (void * p : e->allocs) cudaFree(p);
     for (void * p : e->stream_allocs) cudaFree(p);
+    if (e->step_host) cudaFreeHost(e->step_host);
     for (auto & kv : e->tensors) if (kv.second.raw) cudaFree(kv.second.raw);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
@@ -537,23 +538,68 @@ int qtts_prefill_pending(qtts_engine * h) {
     return 1;
 }
 
-// Batched mode (default): all active streams of a group of <= 128 slots advance in lock step inside
-// ONE launch of the tcgen05 frame kernel (qtts_batched.cu), weights streamed once per frame for the
-// whole group.  Sequential mode (qtts_set_batched(e, 0)): the batch-1 kernel, one stream after
-// another (kept as the A/B reference of the parity tests).
+// frames emitted so far by every stream, before the launch (device to device: no host round trip)
+__global__ void k_snapshot_frames(const StreamState * __restrict__ st, int n, int32_t * __restrict__ frame0) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) frame0[i] = st[i].frame;
+}
+
+// After the launch: the frames every stream produced, out of its device-resident code ring into ONE buffer laid out
+// like the caller's [slot][n_frames][n_codebooks] (unproduced rows zero), plus {produced, done} per slot.  One
+// gather + one copy to the host replaces one cudaMemcpyAsync per slot (512 of them at BASELINE configs[3]).
+__global__ void k_gather_codes(const StreamState * __restrict__ st, const int32_t * __restrict__ frame0,
+                               const int32_t * __restrict__ ring, size_t ring_stride, int nb, int n_frames,
+                               int32_t * __restrict__ out, int32_t * __restrict__ meta) {
+    const int i = blockIdx.x;
+    const int f0 = frame0[i], newf = min(max(st[i].frame - f0, 0), n_frames);
+    if (threadIdx.x == 0) { meta[2 * i] = newf; meta[2 * i + 1] = st[i].done; }
+    const int32_t * src = ring + (size_t) i * ring_stride + (size_t) f0 * nb;
+    int32_t * dst = out + (size_t) i * n_frames * nb;
+    for (int k = threadIdx.x; k < n_frames * nb; k += blockDim.x) dst[k] = (k < newf * nb) ? src[k] : 0;
+}
+
+// int32 [frames][n_codebooks] ring rows -> the TRT vocoder's input layout, int64 [1][n_codebooks][fixed_frames] with
+// the frames beyond n zero (src/trt_vocoder.cpp:110-121)
+__global__ void k_codes_chunk(const int32_t * __restrict__ ring_rows, int nb, int n, int fixed, long long * __restrict__ out) {
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nb * fixed; k += gridDim.x * blockDim.x) {
+        const int c = k / fixed, f = k - c * fixed;
+        out[k] = (f < n) ? (long long) ring_rows[(size_t) f * nb + c] : 0ll;
+    }
+}
+
+static bool ensure_step_buffers(Engine * e, int n_frames) {
+    const size_t ns = e->slots.size();
+    const size_t need = ns * (size_t) n_frames * e->cfg.n_codebooks + 2 * ns;      // int32 words: codes + meta
+    if (need <= e->step_words && e->step_dev) return true;
+    if (e->step_host) { cudaFreeHost(e->step_host); e->step_host = nullptr; }
+    // (an older, smaller device buffer stays in stream_allocs until the next resize / destroy)
+    e->step_dev = e->dalloc<int32_t>(need + ns, false);
+    if (!e->step_dev || cudaMallocHost((void **) &e->step_host, need * sizeof(int32_t)) != cudaSuccess) {
+        cudaGetLastError();
+        e->step_dev = nullptr; e->step_host = nullptr; e->step_words = 0;
+        return e->fail("out of memory for the step_frames staging buffers");
+    }
+    e->step_words = need;
+    return true;
+}
+
+// Batched mode (default): all active streams of a lock-step group (<= 256 slots) advance inside ONE launch of the
+// tcgen05 frame kernel (qtts_batched.cu), weights streamed once per frame for the whole group.  Sequential mode
+// (qtts_set_batched(e, 0)): the batch-1 kernel, one stream after another (kept as the A/B reference of the parity tests).
 int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int32_t * produced, int32_t * active) {
     Engine * e = &h->e;
     if (!e->finalized) { e->err = "engine not finalized"; return 0; }
+    if (n_frames <= 0 || n_frames > e->max_ctx) { e->err = "step_frames: n_frames out of range"; return 0; }
     cudaSetDevice(e->device);
+    if (!ensure_step_buffers(e, n_frames)) return 0;
     // the timed region starts before the batched prefill of streams prepared since the last call (they join here):
     // qtts_last_loop_ms of such a call includes it
     cudaEventRecord(e->ev0, e->stream);
     if (!prefill_pending(e)) return 0;
     const int nb = e->cfg.n_codebooks;
     const size_t ns = e->slots.size();
-    std::vector<StreamState> hs0(ns), hs1(ns);
-    if (cudaMemcpyAsync(hs0.data(), e->bb.st, ns * sizeof(StreamState), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
-        cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = "step_frames: state read failed"; return 0; }
+    int32_t * d_codes = e->step_dev, * d_meta = d_codes + ns * (size_t) n_frames * nb, * d_frame0 = d_meta + 2 * ns;
+    k_snapshot_frames<<<(unsigned) ((ns + 255) / 256), 256, 0, e->stream>>>(e->bb.st, (int) ns, d_frame0);
     if (e->batched && e->batched_ready) {
         for (auto & G : e->groups) if (!run_batched_group(e, G, n_frames)) return 0;
     } else {
@@ -564,27 +610,66 @@ int qtts_step_frames(qtts_engine * h, int32_t n_frames, int32_t * codes_out, int
         }
     }
     cudaEventRecord(e->ev1, e->stream);
-    if (cudaMemcpyAsync(hs1.data(), e->bb.st, ns * sizeof(StreamState), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
+    k_gather_codes<<<(unsigned) ns, 128, 0, e->stream>>>(e->bb.st, d_frame0, e->bb.codes, e->bb.codes_stride, nb, n_frames, d_codes, d_meta);
+    e->launches += 2;
+    const size_t words = ns * (size_t) n_frames * nb + 2 * ns;
+    if (cudaMemcpyAsync(e->step_host, d_codes, words * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
         cudaStreamSynchronize(e->stream) != cudaSuccess) {
         e->err = std::string("step_frames: ") + cudaGetErrorString(cudaGetLastError());
         return 0;
     }
+    const int32_t * meta = e->step_host + ns * (size_t) n_frames * nb;
+    memcpy(codes_out, e->step_host, ns * (size_t) n_frames * nb * sizeof(int32_t));
     for (size_t i = 0; i < ns; ++i) {
         Slot & s = e->slots[i];
-        produced[i] = 0;
-        if (!s.active) { active[i] = 0; continue; }
-        const int newf = hs1[i].frame - hs0[i].frame;
-        produced[i] = newf;
-        if (newf > 0)
-            cudaMemcpyAsync(codes_out + ((size_t) i * n_frames) * nb, s.codes + (size_t) hs0[i].frame * nb,
-                            (size_t) newf * nb * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream);
-        if (hs1[i].done) s.active = false;
+        if (!s.active) {
+            produced[i] = 0; active[i] = 0;
+            memset(codes_out + i * (size_t) n_frames * nb, 0, (size_t) n_frames * nb * sizeof(int32_t));
+            continue;
+        }
+        produced[i] = meta[2 * i];
+        if (meta[2 * i + 1]) s.active = false;
         active[i] = s.active ? 1 : 0;
     }
-    if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("step_frames: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e->ev0, e->ev1);
     e->last_loop_ms = ms;
+    return 1;
+}
+
+// N4 (vocoder hand-off): frames [first_frame, first_frame + n_frames) of `slot` straight out of the device-resident
+// code ring in the layout the reference's streamed vocoder consumes - int64 [1][n_codebooks][fixed_frames], frames
+// beyond n_frames zero (TRTVocoderDecoder::decode, src/trt_vocoder.cpp:98-170, fed by the 40-frame callback of
+// generate(), src/tts_transformer.cpp:2517-2523, src/qwen3_tts.cpp:437-451).  out_is_device = 1: `out` is a device
+// pointer (a TensorRT binding: the chunk never visits the host); 0: host memory.
+int qtts_codes_chunk(qtts_engine * h, int slot, int32_t first_frame, int32_t n_frames, int32_t fixed_frames,
+                     int64_t * out, int out_is_device) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    cudaSetDevice(e->device);
+    const int nb = e->cfg.n_codebooks;
+    if (!out || fixed_frames <= 0 || n_frames < 0 || n_frames > fixed_frames || first_frame < 0 || first_frame + n_frames > e->max_ctx) {
+        e->err = "codes_chunk: bad frame range"; return 0;
+    }
+    int32_t have = 0;
+    cudaMemcpyAsync(&have, &s->st->frame, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream);
+    cudaStreamSynchronize(e->stream);
+    if (first_frame + n_frames > have) { e->err = "codes_chunk: frames not generated yet"; return 0; }
+    const size_t words = (size_t) nb * fixed_frames;
+    long long * dst = (long long *) out;
+    if (!out_is_device) {
+        if (words > e->chunk_words) {
+            e->chunk_dev = e->dalloc<long long>(words, false);
+            if (!e->chunk_dev) { e->chunk_words = 0; e->err = "out of device memory for the code chunk"; return 0; }
+            e->chunk_words = words;
+        }
+        dst = e->chunk_dev;
+    }
+    k_codes_chunk<<<(unsigned) ((words + 255) / 256), 256, 0, e->stream>>>(s->codes + (size_t) first_frame * nb, nb, n_frames, fixed_frames, dst);
+    e->launches += 1;
+    if (!out_is_device) cudaMemcpyAsync(out, dst, words * sizeof(long long), cudaMemcpyDeviceToHost, e->stream);
+    if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("codes_chunk: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
     return 1;
 }
 

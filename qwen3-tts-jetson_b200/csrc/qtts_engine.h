@@ -137,6 +137,9 @@ struct Engine {
     unsigned long long * d_inexact = nullptr;
     GridBarrier * bar = nullptr;
     unsigned long long * prof = nullptr; int prof_on = 0;   // [8][8] stage cycle counters (instrumentation)
+    // qtts_step_frames staging: device gather buffer + pinned host mirror (codes [slot][n_frames][n_books] + meta)
+    int32_t * step_dev = nullptr, * step_host = nullptr; size_t step_words = 0;
+    long long * chunk_dev = nullptr; size_t chunk_words = 0;       // qtts_codes_chunk staging (host destination)
     uint32_t * trace = nullptr; int trace_on = 0, trace_cta = 0, trace_cap = 0;   // stage timeline of one CTA (qtts_trace)
     float * rope = nullptr;
     // fused weights

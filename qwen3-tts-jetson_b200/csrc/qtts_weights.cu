@@ -362,6 +362,7 @@ bool engine_resize(Engine * e, int n_ctx, int max_text) {
     QTTS_CUDA(cudaStreamSynchronize(e->stream));
     for (void * p : e->stream_allocs) cudaFree(p);
     e->stream_allocs.clear();
+    e->step_dev = nullptr; e->step_words = 0; e->chunk_dev = nullptr; e->chunk_words = 0;
     e->slots.clear();
     e->groups.clear();
     e->batched_ready = false;

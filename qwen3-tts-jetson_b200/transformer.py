@@ -45,7 +45,7 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_step_frames",
            "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
            "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle",
-           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step", "qtts_trace"]
+           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step", "qtts_trace", "qtts_codes_chunk"]
 
 _lib = None
 
@@ -84,6 +84,7 @@ def load_library(path: str | None = None):
     lib.qtts_set_debug.argtypes = [vp, C.c_int]
     lib.qtts_resize_kv.argtypes = [vp, i32, i32]
     lib.qtts_get_hidden_states.argtypes = [vp, C.c_int, vp]
+    lib.qtts_codes_chunk.argtypes = [vp, C.c_int, i32, i32, i32, vp, C.c_int]
     lib.qtts_trace.argtypes = [vp, C.c_int, C.c_int, vp, i32]
     lib.qtts_cp_step.argtypes = [vp, C.c_int, vp, i32, i32, i32, i32, i32, C.c_int, vp, i32]
     lib.qtts_predict_codes.argtypes = [vp, C.c_int, vp, i32, C.c_float, i32, vp, vp, vp, vp]
@@ -302,6 +303,17 @@ class TTSTransformer:
         if not self._lib.qtts_forward_codec(self._h, slot, int(codec_token), n_past, _ptr(logits)):
             return None
         return logits
+
+    def codes_chunk(self, slot: int, first_frame: int, n_frames: int, fixed_frames: int = 40, device_ptr: int | None = None):
+        """Vocoder hand-off: int64 [1, n_codebooks, fixed_frames] chunk of the stream's device-resident code ring,
+        zero-padded (src/trt_vocoder.cpp:98-170).  device_ptr: write to that device address instead (returns True)."""
+        nb = self.config["n_codebooks"]
+        if device_ptr is not None:
+            return bool(self._lib.qtts_codes_chunk(self._h, slot, first_frame, n_frames, fixed_frames, C.c_void_p(device_ptr), 1))
+        out = np.zeros((1, nb, fixed_frames), np.int64)
+        if not self._lib.qtts_codes_chunk(self._h, slot, first_frame, n_frames, fixed_frames, _ptr(out), 0):
+            return None
+        return out
 
     # TRTCodePredictor::step / step_with_token (src/trt_code_predictor.h:53-66): one code-predictor position
     def cp_step(self, position_id: int, lm_head_idx: int, input_vec=None, token_id: int = 0, embedding_idx: int = 0,

@@ -342,3 +342,40 @@ def test_resize_kv_keeps_weights_and_results(pkg, make_gguf):
     assert not T.init_kv_cache(100000) and "limit" in T.get_error()
     assert T.generate(g["tokens"], g["speaker"], max_len=20, temperature=0.0) is not None
     T.unload_model()
+
+
+def test_vocoder_handoff_chunks_equal_generated_frames(pkg, make_gguf):
+    """N4: qtts_codes_chunk hands the stream's device-resident code ring to a vocoder in the reference's TRT vocoder
+    layout - int64 [1, 16, 40], frames beyond the utterance zero (src/trt_vocoder.cpp:98-170) - for the 40-frame
+    chunks generate()'s callback delivers (src/tts_transformer.cpp:2517-2523, 2563-2570); host and device destinations."""
+    import torch
+    path, cfg = make_gguf("tiny", 1234)
+    g = load_gold("tiny")
+    T = pkg.TTSTransformer(device=0, max_streams=2, max_ctx=160)
+    assert T.load_model(path), T.get_error()
+    T.set_ignore_eos(True)
+    for i in range(2):
+        assert T.stream_prepare(i, g["tokens"], g["speaker"], max_len=95, temperature=0.9, seed=3 + i), T.get_error()
+    got = [[] for _ in range(2)]
+    while True:
+        codes, produced, active = T.step_frames(40)
+        for i in range(2):
+            got[i].append(codes[i, :produced[i]])
+        if not active.any():
+            break
+    for i in range(2):
+        frames = np.concatenate(got[i])
+        assert len(frames) == 95
+        for first in (0, 40, 80):
+            n = min(40, 95 - first)
+            chunk = T.codes_chunk(i, first, n, 40)
+            assert chunk is not None, T.get_error()
+            want = np.zeros((1, 16, 40), np.int64)
+            want[0, :, :n] = frames[first:first + n].T
+            assert chunk.dtype == np.int64 and np.array_equal(chunk, want)
+        dev = torch.full((1, 16, 40), -1, dtype=torch.int64, device="cuda:0")
+        assert T.codes_chunk(i, 80, 15, 40, device_ptr=dev.data_ptr())
+        torch.cuda.synchronize()
+        assert np.array_equal(dev.cpu().numpy()[0, :, :15], frames[80:95].T) and (dev[0, :, 15:] == 0).all()
+    assert T.codes_chunk(0, 90, 10, 40) is None and "not generated" in T.get_error()
+    T.unload_model()
