@@ -86,8 +86,8 @@ struct BPrefetch {           // used by the prefetcher thread only
 
 struct BShared {
     uint64_t full[kBSlots], empty[kBSlots], abar[2], dbar;
-    uint64_t tfull[8], tempty[8];     // A pieces brought by bulk copies (F16-input stages)
-    uint32_t n_fill[8], fill_base[8];  // fills issued per A buffer (producer's counter) / its value at the start of the stage
+    uint64_t tfull[4], tempty[4];     // A pieces brought by bulk copies (F16-input stages)
+    uint32_t n_fill[4], fill_base[4];  // fills issued per A buffer (producer's counter) / its value at the start of the stage
     BRun run;                // copy of the kernel parameter
     BOp op;                  // the stage being executed
     Op item_op;              // Talker attention: per-item view for the batch-1 helpers
@@ -106,10 +106,10 @@ struct BShared {
 #define BTR(k) do { if (S->tr) S->tr[k] = (uint32_t) clock64(); } while (0)
 constexpr size_t kBSharedBytes = (sizeof(BShared) + 127) & ~(size_t) 127;
 
-// [BShared][A area kAAreaBytes][weight ring]: an M = 128 MMA reads 128 rows although a piece
+// [BShared][A buffers 2 x kABufBytes][weight ring]: an M = 128 MMA reads 128 rows although a piece
 // may hold fewer; the over-read then falls into the ring (valid shared memory), never past the end
 __device__ __forceinline__ unsigned char * babuf_base(BShared * S) { return reinterpret_cast<unsigned char *>(S) + kBSharedBytes; }
-__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return babuf_base(S) + (size_t) kAAreaBytes; }
+__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return babuf_base(S) + 2 * (size_t) kABufBytes; }
 // byte offset of element (row r, column col) of an F16 activation matrix stored in global memory
 // as UMMA-canonical chunks of 128 columns (chunk_bytes = ceil(rows / 8) * 2048): LBO 128, SBO 2048
 __device__ __forceinline__ size_t canon_off(int r, int col, int chunk_bytes) {
@@ -562,16 +562,13 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
         const int nkc = op.K / kKc;
         const int steps = nkc * m_tiles;
         const int Rg = (op.rows_act + 7) >> 3, cb = Rg << 11;
-        // buffers in use: <= 64 rows -> 6 chunk buffers of 16 KB (with 4, the second half of a projection's 8 K-chunks
-        // waited for copy latency + MMA + commit latency of the first half: measured 2.5 us of a 5.7 us stage);
-        // more rows -> two 128-row buffers.  bstep = barrier index step.
-        const int nab = (Rg <= 8) ? ((S->run.dbg & 128) ? 4 : 6) : 2, bstep = (nab == 2) ? 2 : 1;
+        const int nab = (Rg <= 8) ? 4 : 2, bstep = 4 / nab;          // buffers in use, barrier index step
         const int lane = tid & 31, warp = tid >> 5;
-        const int abstride = (nab == 2) ? kABufBytes : 16384;
+        const int abstride = (nab == 4) ? kABufBytes / 2 : kABufBytes;
         // accumulators: issuer w (< nab) writes (w, mt) for the steps that land in its buffer; with two
         // buffers and two m-tiles step kc * 2 + mt lands in buffer mt, i.e. m-tile mt has ONE accumulator, issuer mt's
         // (generally: with m_tiles a multiple of the buffer count, m-tile mt always lands in buffer mt % nab)
-        const int acc_mode = (m_tiles >= nab && m_tiles % nab == 0) ? -nab : min(min(nab, kIssuers), steps);
+        const int acc_mode = (m_tiles >= nab && m_tiles % nab == 0) ? -nab : min(nab, steps);
         const uint32_t tmem_base = S->tmem_base;
         const uint32_t idesc = (op.rows_act <= 64 ? (S->run.idesc_base & ~(0x1Fu << 24)) | (4u << 24) : S->run.idesc_base) | ((uint32_t) (op.n_tile >> 3) << 17);
         uint32_t d_use = S->d_use, cons_seq = S->cons_seq;
@@ -626,6 +623,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                 const uint32_t ring0 = smem_u32(bring_base(S));
                 const uint32_t abuf0 = smem_u32(abuf);
                 const bool skip_mma = (S->run.dbg & 1) != 0;
+                const int nab_shift = (nab == 4) ? 2 : 1;
                 uint32_t started = 0;       // accumulators (w, mt) this issuer has written
                 int kc = 0;
                 for (int piece = 0; piece < op.n_pieces; ++piece) {
@@ -640,10 +638,10 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     for (int c = 0; c < chunks; ++c, ++kc) {
                         for (int mt = 0; mt < m_tiles; ++mt) {
                             const int s = kc * m_tiles + mt;
-                            const int buf = s % nab, bi = buf * bstep;
-                            if ((buf & (kIssuers - 1)) != w) continue;     // issuer w owns A buffers w, w + 4: their fills are consumed in order by one thread
+                            const int buf = s & (nab - 1), bi = buf * bstep;
+                            if (buf != w) continue;             // issuer w owns A buffer w: its fills are consumed in order by one thread
                             mine = true;
-                            const uint32_t fill = S->fill_base[bi] + (uint32_t) (s / nab);
+                            const uint32_t fill = S->fill_base[bi] + (uint32_t) (s >> nab_shift);
                             const long long ca = pr ? clock64() : 0;
                             mbar_wait(S->tfull + bi, fill & 1u);
                             if (warp == 0 && s == 0 && t == t_first) BTR(4);
@@ -688,7 +686,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
             tc_fence_before();
             __syncthreads();
             if (pr1) { S->run.prof[45] += (unsigned long long) (e1 - e0); S->run.prof[46] += (unsigned long long) (clock64() - e1); }
-            if (tid < 8) S->fill_base[tid] = S->n_fill[tid];      // all fills of this tile were issued and consumed
+            if (tid < 4) S->fill_base[tid] = S->n_fill[tid];      // all fills of this tile were issued and consumed
             if (t + G < op.n_tiles) __syncthreads();
             cons_seq += (uint32_t) op.n_pieces;
         }
@@ -1564,11 +1562,10 @@ __device__ __noinline__ void bstage_sample(BShared * S) {
 // ------------------------------------------------------------------------------------------
 // the batched program runner
 // ------------------------------------------------------------------------------------------
-constexpr size_t kBSmemBytes = kBSharedBytes + (size_t) kBSlots * kBSlotBytes + (size_t) kAAreaBytes;
-static_assert(2 * (size_t) kABufBytes <= (size_t) kAAreaBytes, "two 128-row activation buffers fit the staging area");
+constexpr size_t kBSmemBytes = kBSharedBytes + (size_t) kBSlots * kBSlotBytes + 2 * (size_t) kABufBytes;
 static_assert(kBSmemBytes <= 232448, "batched kernel exceeds the 227 KB of shared memory per CTA");
-static_assert(sizeof(AttnSmem) + 64 + 2 * kMaxScores * sizeof(float) <= (size_t) kAAreaBytes, "attention scratch overlays the A buffers");
-static_assert(sizeof(SampleSmem) + 64 + kMaxVocab * sizeof(float) <= (size_t) kAAreaBytes, "sampling scratch overlays the A buffers");
+static_assert(sizeof(AttnSmem) + 64 + 2 * kMaxScores * sizeof(float) <= 2 * (size_t) kABufBytes, "attention scratch overlays the A buffers");
+static_assert(sizeof(SampleSmem) + 64 + kMaxVocab * sizeof(float) <= 2 * (size_t) kABufBytes, "sampling scratch overlays the A buffers");
 
 extern "C" __global__ void __launch_bounds__(kThreads, 1)
 qtts_run_batched(const __grid_constant__ BRun run_param) {
@@ -1580,7 +1577,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
     if (threadIdx.x == 0) {
         for (int i = 0; i < kBSlots; ++i) { mbar_init(S->full + i, 1); mbar_init(S->empty + i, kIssuers); }
         mbar_init(S->abar, kIssuers); mbar_init(S->abar + 1, kIssuers); mbar_init(&S->dbar, kIssuers);
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < 4; ++i) {
             mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, 1); S->n_fill[i] = 0; S->fill_base[i] = 0;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

@@ -19,9 +19,7 @@ constexpr int kKc         = 128;                 // K-elements per activation ch
 constexpr int kALbo       = 144;
 constexpr int kASbo       = (kKc / 8) * kALbo;   // 2304
 constexpr int kABufBytes  = 16 * kASbo;          // 128 rows -> 36864 B
-constexpr int kAAreaBytes = 6 * 16384;           // activation staging area: 2 x kABufBytes (128-row buffers) or, for groups of
-                                                 // <= 64 rows, 6 x 16 KB chunk buffers (6 of a projection's 8 K-chunks in flight)
-constexpr int kBSlots     = 5;                   // weight ring slots
+constexpr int kBSlots     = 6;                   // weight ring slots
 constexpr int kBSlotBytes = 24576;
 constexpr int kBMaxRows   = 512;                 // activation rows per GEMM (streams x tokens)
 constexpr int kBMaxGroup  = 256;                 // streams advanced in lock step by one launch
