@@ -46,8 +46,28 @@ static int dump_config(const char * path) {
     return 0;
 }
 
+// --tensors <model.gguf>: walk the tensor table the way the library's loader does (type check per tensor, no GPU)
+static int check_tensors(const char * path) {
+    qtts_b200::GgufFile g;
+    std::string err;
+    if (!g.open(path, err) || !g.map(err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+    size_t n = 0;
+    for (const auto & t : g.tensors()) {
+        if (t.ggml_type != 0 && t.ggml_type != 1) {
+            fprintf(stderr, "tensor %s: unsupported GGUF type %s (only F32/F16; quantised GGUF files are rejected)\n",
+                    t.name.c_str(), qtts_b200::GgufFile::type_name(t.ggml_type));
+            return 1;
+        }
+        if (!g.data(t)) { fprintf(stderr, "tensor %s lies outside the file\n", t.name.c_str()); return 1; }
+        ++n;
+    }
+    printf("{\"n_tensors\": %zu}\n", n);
+    return 0;
+}
+
 int main(int argc, char ** argv) {
     if (argc == 3 && std::string(argv[1]) == "--config") return dump_config(argv[2]);
+    if (argc == 3 && std::string(argv[1]) == "--tensors") return check_tensors(argv[2]);
     if (argc < 7) {
         fprintf(stderr, "usage: %s model.gguf tokens.i32 max_len temperature top_k seed\n", argv[0]);
         return 2;

@@ -9,6 +9,10 @@
 #include <map>
 #include <string>
 #include <vector>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 namespace qtts_b200 {
 
@@ -22,11 +26,18 @@ struct GgufTensor {
 
 class GgufFile {
 public:
-    ~GgufFile() { if (f_) fclose(f_); }
+    ~GgufFile() {
+        if (map_) munmap(map_, map_size_);
+        if (f_) fclose(f_);
+    }
+    GgufFile() = default;
+    GgufFile(const GgufFile &) = delete;
+    GgufFile & operator=(const GgufFile &) = delete;
 
     bool open(const std::string & path, std::string & err) {
         f_ = fopen(path.c_str(), "rb");
         if (!f_) { err = "Failed to open GGUF file: " + path; return false; }
+        path_ = path;
         uint32_t magic = 0, version = 0;
         uint64_t n_tensors = 0, n_kv = 0;
         if (!rd(magic) || magic != 0x46554747u) { err = "not a GGUF file: " + path; return false; }
@@ -65,8 +76,37 @@ public:
     double num(const std::string & key) const { return kv_.at(key); }
     const std::vector<GgufTensor> & tensors() const { return tensors_; }
 
+    // ggml type id -> name, for the messages that reject quantised files (ggml/include/ggml.h: enum ggml_type)
+    static const char * type_name(int t) {
+        switch (t) {
+            case 0: return "F32"; case 1: return "F16"; case 2: return "Q4_0"; case 3: return "Q4_1"; case 6: return "Q5_0";
+            case 7: return "Q5_1"; case 8: return "Q8_0"; case 9: return "Q8_1"; case 10: return "Q2_K"; case 11: return "Q3_K";
+            case 12: return "Q4_K"; case 13: return "Q5_K"; case 14: return "Q6_K"; case 15: return "Q8_K"; case 30: return "BF16";
+            default: return "unknown";
+        }
+    }
+
+    // Read-only mapping of the whole file: tensor data is then addressed in place (data(t)), so a loader can copy
+    // file pages straight into its pinned staging buffers without an intermediate std::vector per tensor.
+    bool map(std::string & err) {
+        if (map_) return true;
+        const int fd = ::open(path_.c_str(), O_RDONLY);
+        struct stat st;
+        if (fd < 0 || fstat(fd, &st) != 0) { if (fd >= 0) ::close(fd); err = "Failed to open GGUF file: " + path_; return false; }
+        void * p = mmap(nullptr, (size_t) st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+        ::close(fd);
+        if (p == MAP_FAILED) { err = "mmap failed for " + path_; return false; }
+        map_ = p; map_size_ = (size_t) st.st_size;
+        madvise(map_, map_size_, MADV_SEQUENTIAL);
+        return true;
+    }
+    const uint8_t * data(const GgufTensor & t) const {
+        if (!map_ || data_start_ + t.offset + t.n_bytes > map_size_) return nullptr;
+        return static_cast<const uint8_t *>(map_) + data_start_ + t.offset;
+    }
+
     bool read_tensor(const GgufTensor & t, std::vector<uint8_t> & out, std::string & err) {
-        if (t.n_bytes == 0) { err = "tensor " + t.name + ": unsupported GGUF type (only F32/F16; quantised types are rejected)"; return false; }
+        if (t.n_bytes == 0) { err = "tensor " + t.name + ": unsupported GGUF type " + type_name(t.ggml_type) + " (only F32/F16; quantised GGUF files are rejected)"; return false; }
         out.resize(t.n_bytes);
         if (fseek(f_, (long) (data_start_ + t.offset), SEEK_SET) != 0 || fread(out.data(), 1, t.n_bytes, f_) != t.n_bytes) {
             err = "failed to read tensor " + t.name;
@@ -111,6 +151,9 @@ private:
     }
 
     FILE * f_ = nullptr;
+    std::string path_;
+    void * map_ = nullptr;
+    size_t map_size_ = 0;
     std::map<std::string, double> kv_;
     std::vector<GgufTensor> tensors_;
     uint64_t data_start_ = 0;

@@ -319,16 +319,12 @@ private:
             eng_ = nullptr;
             return false;
         }
-        std::vector<uint8_t> buf;
-        for (const auto & t : g.tensors()) {
-            // vocoder / speaker-encoder tensors live in other GGUF files; unknown names are skipped by the engine
-            if (!g.read_tensor(t, buf, error_msg_)) { unload_model(); return false; }
-            const int dtype = t.ggml_type == 0 ? QTTS_F32 : t.ggml_type == 1 ? QTTS_F16 : -1;
-            if (qtts_upload_tensor(eng_, t.name.c_str(), dtype, t.dims.data(), (int) t.dims.size(), buf.data()) == 0) {
-                error_msg_ = qtts_last_error(eng_);
-                unload_model();
-                return false;
-            }
+        // tensors: the library's own loader (mapped file -> pinned staging ring -> HBM; quantised types rejected by name)
+        (void) g;
+        if (qtts_load_gguf(eng_, model_path_.c_str()) == 0) {
+            error_msg_ = qtts_last_error(eng_);
+            unload_model();
+            return false;
         }
         if (qtts_finalize(eng_) == 0) {
             error_msg_ = qtts_last_error(eng_);

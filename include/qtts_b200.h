@@ -68,10 +68,17 @@ const char * qtts_create_error(void);
 /* Upload one GGUF tensor by its GGUF name (names: scripts/convert_tts_to_gguf.py:42-109,
  * consumed by create_tensors src/tts_transformer.cpp:444-731).  dims are in GGUF/ggml order
  * (dims[0] = innermost = input features).  Replaces load_tensor_data
- * (src/tts_transformer.cpp:733-792).  Projection matrices are converted to BF16 on the device;
- * the count of values not exactly representable in BF16 is accumulated (qtts_weight_stats). */
+ * (src/tts_transformer.cpp:733-792).  Projection matrices stay F16, the file's own values (2-D F32 tensors are
+ * rounded to F16, as ggml's F16 mat-mul path would); the count of values a BF16 copy could not represent is
+ * accumulated for information (qtts_weight_stats; the synthetic fixtures are BF16-exact). */
 int qtts_upload_tensor(qtts_engine * e, const char * name, int dtype,
                        const int64_t * dims, int n_dims, const void * host_data);
+/* The whole tensor set straight from a GGUF file (replaces load_tensor_data, src/tts_transformer.cpp:733-792): the
+ * file is mapped and its F16 / F32 tensors go page cache -> pinned staging ring -> HBM without a per-tensor host
+ * copy; quantised tensor types (Q8_0, Q4_0, Q4_K ... which scripts/convert_tts_to_gguf.py can emit) are rejected with
+ * the tensor's name and type.  Call qtts_finalize afterwards.  qtts_load_stats: wall ms and bytes of that stage. */
+int qtts_load_gguf(qtts_engine * e, const char * gguf_path);
+int qtts_load_stats(const qtts_engine * e, double * load_ms, int64_t * bytes);
 /* Build the fused device layouts (QKV concatenation, gate/up row interleave), check that every
  * tensor of the path is present.  Must be called once after the uploads. */
 int qtts_finalize(qtts_engine * e);

@@ -98,6 +98,17 @@ int qtts_upload_tensor(qtts_engine * h, const char * name, int dtype, const int6
     return engine_upload(&h->e, name, dtype, dims, n_dims, host) ? 1 : 0;
 }
 
+int qtts_load_gguf(qtts_engine * h, const char * path) {
+    cudaSetDevice(h->e.device);
+    return engine_load_gguf(&h->e, path) ? 1 : 0;
+}
+
+int qtts_load_stats(const qtts_engine * h, double * load_ms, int64_t * bytes) {
+    if (load_ms) *load_ms = h->e.load_ms;
+    if (bytes) *bytes = h->e.load_bytes;
+    return 1;
+}
+
 int qtts_finalize(qtts_engine * h) {
     cudaSetDevice(h->e.device);
     return engine_finalize(&h->e) ? 1 : 0;

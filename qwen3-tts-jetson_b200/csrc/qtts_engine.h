@@ -133,6 +133,7 @@ struct Engine {
     int ignore_eos = 0;
     int64_t n_weights = 0, n_inexact = 0, weight_bytes = 0, kv_bytes = 0;
     int64_t launches = 0;
+    double load_ms = 0.0; int64_t load_bytes = 0;       // qtts_load_gguf: wall time and bytes of the file -> HBM stage
     double last_loop_ms = 0.0;
     unsigned long long * d_inexact = nullptr;
     GridBarrier * bar = nullptr;
@@ -189,6 +190,7 @@ struct Engine {
 
 // qtts_weights.cu
 bool engine_upload(Engine * e, const char * name, int dtype, const int64_t * dims, int n_dims, const void * host);
+bool engine_load_gguf(Engine * e, const char * path);
 bool engine_finalize(Engine * e);
 bool engine_build_streams(Engine * e);      // per-stream buffers, frame programs, lock-step groups (after the weights)
 bool engine_resize(Engine * e, int n_ctx, int max_text);

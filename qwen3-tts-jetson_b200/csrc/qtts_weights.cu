@@ -8,6 +8,8 @@
 // weights and embedding tables stay F16, bit copies of the file (round 1 converted the projections to
 // BF16, which loses mantissa bits on any checkpoint that is not BF16-exact).
 #include "qtts_engine.h"
+#include "../../cpp/qtts_gguf.hpp"
+#include <chrono>
 #include <cmath>
 #include <cstring>
 
@@ -86,6 +88,72 @@ bool engine_upload(Engine * e, const char * name_c, int dtype, const int64_t * d
     if (it != e->tensors.end()) { cudaFree(it->second.raw); }
     e->tensors[name] = t;
     return true;
+}
+
+// GGUF -> device without a per-tensor host copy (replaces load_tensor_data,
+// src/tts_transformer.cpp:733-792, which freads every tensor into a std::vector before ggml_backend_tensor_set):
+// the file is mapped, tensors already in their device storage type (2-D F16, 1-D F32: what the converter writes,
+// scripts/convert_tts_to_gguf.py:289-297) are copied page cache -> pinned staging buffer -> HBM in 16 MB pieces
+// through two buffers, so the memcpy out of the page cache overlaps the DMA of the previous piece.  Other F32/F16
+// combinations take the converting path of engine_upload; every quantised type is rejected by name.
+bool engine_load_gguf(Engine * e, const char * path) {
+    if (e->finalized) return e->fail("load after finalize");
+    const auto t0 = std::chrono::steady_clock::now();
+    qtts_b200::GgufFile g;
+    std::string err;
+    if (!g.open(path, err) || !g.map(err)) return e->fail(err);
+    constexpr size_t kPiece = 16u << 20;
+    uint8_t * pin[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2];
+    bool busy[2] = {false, false};
+    for (int i = 0; i < 2; ++i) {
+        if (cudaMallocHost((void **) &pin[i], kPiece) != cudaSuccess) { cudaGetLastError(); if (i) cudaFreeHost(pin[0]); return e->fail("out of pinned host memory for the loader"); }
+        cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
+    }
+    auto done = [&](bool ok) {
+        cudaStreamSynchronize(e->stream);
+        for (int i = 0; i < 2; ++i) { cudaFreeHost(pin[i]); cudaEventDestroy(ev[i]); }
+        e->load_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        return ok;
+    };
+    int cur = 0;
+    for (const auto & t : g.tensors()) {
+        if (!wanted(t.name)) continue;
+        if (t.ggml_type != 0 && t.ggml_type != 1) {
+            e->err = "tensor " + t.name + ": unsupported GGUF type " + qtts_b200::GgufFile::type_name(t.ggml_type) +
+                     " (only F32/F16; quantised GGUF files are rejected)";
+            return done(false);
+        }
+        const uint8_t * src = g.data(t);
+        if (!src) { e->err = "tensor " + t.name + " lies outside the file"; return done(false); }
+        const int n_dims = (int) t.dims.size();
+        const int dtype = t.ggml_type == 0 ? QTTS_F32 : QTTS_F16;
+        const int want = (n_dims == 1) ? QTTS_F32 : QTTS_F16;
+        if (n_dims < 1 || n_dims > 2 || dtype != want) {        // rank / conversion handling lives in engine_upload
+            if (!engine_upload(e, t.name.c_str(), dtype, t.dims.data(), n_dims, src)) return done(false);
+            continue;
+        }
+        DevTensor d;
+        d.n_dims = n_dims; d.n_elem = 1; d.dtype = want;
+        for (int i = 0; i < n_dims; ++i) { d.ne[i] = t.dims[i]; d.n_elem *= (size_t) t.dims[i]; }
+        if (cudaMalloc(&d.raw, t.n_bytes) != cudaSuccess) { cudaGetLastError(); e->err = "cudaMalloc failed for " + t.name; return done(false); }
+        for (size_t off = 0; off < t.n_bytes; off += kPiece) {
+            const size_t n = std::min(kPiece, t.n_bytes - off);
+            if (busy[cur]) cudaEventSynchronize(ev[cur]);
+            memcpy(pin[cur], src + off, n);                                       // page cache -> pinned
+            if (cudaMemcpyAsync((uint8_t *) d.raw + off, pin[cur], n, cudaMemcpyHostToDevice, e->stream) != cudaSuccess) {
+                e->err = "host to device copy failed for " + t.name; cudaFree(d.raw); return done(false);
+            }
+            cudaEventRecord(ev[cur], e->stream);
+            busy[cur] = true;
+            cur ^= 1;
+        }
+        auto it = e->tensors.find(t.name);
+        if (it != e->tensors.end()) cudaFree(it->second.raw);
+        e->tensors[t.name] = d;
+        e->load_bytes += (int64_t) t.n_bytes;
+    }
+    return done(true);
 }
 
 static DevTensor * need(Engine * e, const std::string & name, int64_t ne0, int64_t ne1) {

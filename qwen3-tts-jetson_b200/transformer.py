@@ -45,7 +45,7 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_step_frames",
            "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
            "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle",
-           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step", "qtts_trace", "qtts_codes_chunk"]
+           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step", "qtts_trace", "qtts_codes_chunk", "qtts_load_gguf", "qtts_load_stats"]
 
 _lib = None
 
@@ -69,6 +69,8 @@ def load_library(path: str | None = None):
     lib.qtts_create_error.restype = C.c_char_p
     lib.qtts_upload_tensor.argtypes = [vp, C.c_char_p, C.c_int, C.POINTER(C.c_int64), C.c_int, vp]
     lib.qtts_finalize.argtypes = [vp]
+    lib.qtts_load_gguf.argtypes = [vp, C.c_char_p]
+    lib.qtts_load_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     lib.qtts_weight_stats.argtypes = [vp, C.POINTER(C.c_int64)]
     lib.qtts_set_numerics.argtypes = [vp, C.c_int, C.c_int]
     lib.qtts_set_persistent.argtypes = [vp, C.c_int]
@@ -139,16 +141,32 @@ class TTSTransformer:
 
     # -- load_model (src/tts_transformer.cpp:51-153) ----------------------------------------------
     def load_model(self, model_path: str) -> bool:
+        """parse_config from the GGUF metadata here (host logic), tensors by the library's own loader
+        (qtts_load_gguf: mapped file -> pinned staging ring -> HBM, quantised types rejected by name)."""
         self.unload_model()
         try:
-            cfg, tensors = gguf_io.read_gguf(model_path)
-        except Exception as ex:  # unreadable file / unsupported tensor type
+            cfg, _ = gguf_io.read_gguf(model_path)
+        except Exception as ex:  # unreadable file
             self._err = f"Failed to open GGUF file: {ex}"
             return False
-        return self.load_tensors(cfg, tensors())
+        if not self._create(cfg):
+            return False
+        if not self._lib.qtts_load_gguf(self._h, model_path.encode()):
+            self._err = self._lib.qtts_last_error(self._h).decode()
+            self.unload_model()
+            return False
+        if not self._lib.qtts_finalize(self._h):
+            self._err = self._lib.qtts_last_error(self._h).decode()
+            self.unload_model()
+            return False
+        return True
 
-    def load_tensors(self, cfg: dict, tensors) -> bool:
-        """cfg: gguf_io.parse_config dict; tensors: iterable of (name, dtype_code, ggml_dims, array)."""
+    def load_stats(self) -> dict:
+        ms, nbytes = C.c_double(), C.c_int64()
+        self._lib.qtts_load_stats(self._h, C.byref(ms), C.byref(nbytes))
+        return {"load_ms": ms.value, "bytes": nbytes.value, "gb_per_s": nbytes.value / 1e6 / ms.value if ms.value else 0.0}
+
+    def _create(self, cfg: dict) -> bool:
         self.config = dict(cfg)
         c = QttsConfig()
         for n in _CFG_INT_FIELDS + _CFG_TAIL_FIELDS:
@@ -159,7 +177,12 @@ class TTSTransformer:
             self._err = self._lib.qtts_create_error().decode()
             return False
         self._h = h
-        if not self._lib.qtts_set_batched_weight_format(self._h, int(self.batched_weight_format)):
+        return bool(self._lib.qtts_set_batched_weight_format(self._h, int(self.batched_weight_format)))
+
+    def load_tensors(self, cfg: dict, tensors) -> bool:
+        """Tensor-by-tensor upload (qtts_upload_tensor) for callers that hold the tensors in memory.
+        cfg: gguf_io.parse_config dict; tensors: iterable of (name, dtype_code, ggml_dims, array)."""
+        if not self._create(cfg):
             return False
         for name, code, dims, arr in tensors:
             d = (C.c_int64 * len(dims))(*dims)

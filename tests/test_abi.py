@@ -89,3 +89,23 @@ def test_synth_tokens_frame(pkg):
     # encode_for_tts frame: src/text_tokenizer.cpp:293-330 (tests/test_tokenizer.cpp:14 head/tail)
     assert t[:3].tolist() == [151644, 77091, 198] and t[-5:].tolist() == [151645, 198, 151644, 77091, 198]
     assert len(t) == 21
+
+
+def test_quantised_gguf_is_rejected_by_name(pkg, tmp_path):
+    """N2: scripts/convert_tts_to_gguf.py can emit Q8_0 / Q4_0 / Q4_K; the loaders reject such a tensor with its name
+    and type instead of reading garbage (Python metadata reader, C++ GGUF reader used by the library's loader)."""
+    import gguf
+    import subprocess
+    path = str(tmp_path / "q8.gguf")
+    w = gguf.GGUFWriter(path, "qwen3-tts")
+    w.add_block_count(1)
+    w.add_tensor("talker.output_norm.weight", np.ones(64, np.float32))
+    q = np.zeros((8, 34 * 2), np.uint8)                    # 8 rows x 64 values of Q8_0: 2 blocks of 34 bytes per row
+    w.add_tensor("talker.codec_head.weight", q, raw_dtype=gguf.GGMLQuantizationType.Q8_0)
+    w.write_header_to_file(); w.write_kv_data_to_file(); w.write_tensors_to_file(); w.close()
+    cfg, tensors = pkg.gguf_io.read_gguf(path)
+    with pytest.raises(ValueError, match="talker.codec_head.weight.*Q8_0"):
+        list(tensors())
+    exe = pkg.build.build_adapter_check()
+    r = subprocess.run([exe, "--tensors", path], capture_output=True, text=True)
+    assert r.returncode == 1 and "talker.codec_head.weight" in r.stderr and "Q8_0" in r.stderr and "rejected" in r.stderr
