@@ -26,8 +26,12 @@
 #ifndef QTTS_OPT_ATTN
 #define QTTS_OPT_ATTN 1
 #endif
+#ifndef QTTS_OPT_FHFMA
+#define QTTS_OPT_FHFMA 1          // GEMV dot on the mixed-precision FMA (0: convert + FFMA, for A/B runs)
+#endif
 #ifndef QTTS_OPT_ATTN_WARP
-#define QTTS_OPT_ATTN_WARP 1      // warp-per-head attention for <= 16 keys (0: the CTA-wide path, for A/B runs)
+#define QTTS_OPT_ATTN_WARP 0      // 1: warp-per-head attention for <= 16 keys.  Measured SLOWER than the CTA-wide path
+                                  // (3.005 vs 2.820 ms/frame, profiles/r02_ab.md), so it stays off
 #endif
 #include <math_constants.h>
 
@@ -46,6 +50,10 @@ __device__ __forceinline__ float fhfma(uint16_t a, uint16_t b, float c) {
     return d;
 }
 __device__ __forceinline__ float fhfma2(uint32_t w, uint32_t x, float c) {      // c + w.lo * x.lo, then + w.hi * x.hi
+#if !QTTS_OPT_FHFMA
+    const float2 wf = __half22float2(*reinterpret_cast<const __half2 *>(&w)), xf = __half22float2(*reinterpret_cast<const __half2 *>(&x));
+    return fmaf(wf.y, xf.y, fmaf(wf.x, xf.x, c));
+#endif
     uint16_t w0, w1, x0, x1;
     asm("mov.b32 {%0, %1}, %2;" : "=h"(w0), "=h"(w1) : "r"(w));
     asm("mov.b32 {%0, %1}, %2;" : "=h"(x0), "=h"(x1) : "r"(x));

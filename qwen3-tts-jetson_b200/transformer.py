@@ -55,7 +55,7 @@ def load_library(path: str | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    path = path or _build.LIB
+    path = path or os.environ.get("QTTS_LIB_PATH") or _build.LIB      # QTTS_LIB_PATH: A/B builds of the same sources (tools/ab_build.py)
     if not os.path.exists(path):
         raise RuntimeError(f"{path} is missing: run __graft_entry__.build() (nvcc, sm_100a). "
                            "There is no CPU fallback for this path.")
