@@ -207,7 +207,8 @@ def workload_config(world: int) -> dict:
                         f"{FRAMES} frames per utterance",
             "streams_per_gpu": 1, "frames_per_step": FRAMES, "text_tokens": N_TEXT + 8,
             "eos": "suppressed by the benchmark switch qtts_set_ignore_eos so every utterance runs all frames",
-            "numerics": "fast (F16-rounded activations/KV like the reference, FP32 P.V accumulation)",
+            "numerics": "fast: F16 weights as stored in the GGUF, F16-rounded activations / KV like ggml-cpu, F32 accumulate "
+                        "(parity vs the reference per frame: profiles/r02_summary.md section 1)",
             "l2": "inputs larger than L2 (3.3 GB of weights streamed per frame vs 126 MB L2)",
             "parallelism": f"{world} x independent utterance streams, no collective"}
 
@@ -293,7 +294,7 @@ def run_ours(args, pkg):
         achieved = bytes_per_frame * per_gpu_frames_per_s / 1e9
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": loop_ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
                 "config": workload_config(world),
                 "ms_per_frame": loop_ms / (frames / world), "rtf_per_stream": (loop_ms / 1e3) / ((frames / world) / 12.5),
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(toks.nbytes + spk.nbytes),
