@@ -6,4 +6,4 @@ name is not a Python identifier; import it through `qtts_pkg.load()` at the repo
 """
 from .transformer import (TTSTransformer, load_library, debug_bgemm, EXPORTS, NUMERICS_FAST,  # noqa: F401
                           NUMERICS_REFERENCE, F32, F16, BF16, EPI_STORE, EPI_ADD, EPI_SWIGLU, EPI_BIAS)
-from . import build, gguf_io, serve, sharding, synth  # noqa: F401
+from . import build, gguf_io, serve, sharding, synth, synth_vocoder  # noqa: F401

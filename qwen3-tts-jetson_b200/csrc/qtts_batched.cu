@@ -1200,7 +1200,12 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
     const int lane = threadIdx.x & 31, hw = lane >> 4, l16 = lane & 15;
     const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
     const int B = op.n_streams, nkv = op.n_kv_heads, kvw = nkv * kHeadDim;
-    float * qs = reinterpret_cast<float *>(babuf_base(S)) + (threadIdx.x >> 5) * (REP * kHeadDim);
+    // per-warp shared memory (4608 B of the activation-buffer region, free during an attention stage), used in turn
+    // as: Q redistribution (1 KB) -> staging of the block's V rows (4 KB, written by cp.async) -> split-KV hand-over
+    constexpr int kWarpRegion = 2 * kABufBytes / kWarps;
+    static_assert(kWarpRegion >= 4096 && kWarpRegion >= 20 * 32 * 4, "attention warp region");
+    unsigned char * wreg = babuf_base(S) + (threadIdx.x >> 5) * kWarpRegion;
+    float * qs = reinterpret_cast<float *>(wreg);
     const int cb = canon_chunk_bytes(op.rows_act);
     float wq[4], wk[4];
 #pragma unroll
@@ -1218,7 +1223,7 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
     if (S->run.dbg & 16) spl = 1;      // A/B switch (QTTS_BDBG=16): one warp per item
     const int part = gw % spl, ngrp = nw / spl;
     const bool tail = part == spl - 1;
-    float * pbuf = reinterpret_cast<float *>(babuf_base(S) + kWarps * REP * kHeadDim * sizeof(float));   // [warp][20][32]
+    const uint32_t vst = smem_u32(wreg) + (uint32_t) (threadIdx.x & 31) * 16u;       // this lane's slot of V row i: + i * 512
     for (int item = gw / spl; item < B * nkv; item += ngrp) {
         const int b = item / nkv, g = item - b * nkv;
         const int pos = __ldcg(&run.st[b].n_past), n_kv = pos + 1;
@@ -1266,24 +1271,47 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
         const __half * kb = kc + 8 * l16, * vb = vc + 8 * l16;
         const int per = ((n_kv + 15) / 16) / spl;                   // 16-key blocks of every warp but the last
         const int jb0 = part * per * 16, jb1 = tail ? n_kv : (part + 1) * per * 16;
+        // Software pipeline over 16-key blocks: K of block j+1 is requested as soon as block j's scores are done and V
+        // of block j+1 as soon as block j's P.V is done, so a warp always has 4 - 8 KB of KV in flight instead of one
+        // operand at a time (profiles/r01p: 14.5 % of the samples waited on the V rows with nothing else pending).
+        // Q stays packed F16 and the dot product runs on the mixed-precision FMA: same products, same order, same
+        // single rounding as fmaf on the converted values (both conversions are exact), without the conversions.
+        uint32_t qh[REP][4];
+        __syncwarp();       // every lane has read its Q values: the region becomes the V staging buffer
+#pragma unroll
+        for (int r = 0; r < REP; ++r)
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const __half2 h = __floats2half2_rn(qa[r][2 * u], qa[r][2 * u + 1]);      // exact: qa holds F16 values
+                qh[r][u] = *reinterpret_cast<const uint32_t *>(&h);
+            }
+        uint4 kA[8];
+        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+        if (jb0 < jb1) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int jk = jb0 + 2 * i + hw;
+                kA[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : z4;
+            }
+        }
         for (int jb = jb0; jb < jb1; jb += 16) {
-            uint4 kv[8];
+            const bool more = jb + 16 < jb1;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int jk = jb + 2 * i + hw;
-                kv[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : make_uint4(0u, 0u, 0u, 0u);
+                const bool ok = jk < n_kv;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
+                             :: "r"(vst + (uint32_t) i * 512u), "l"(vb + (size_t) (ok ? jk : 0) * kvw), "r"(ok ? 16 : 0) : "memory");
             }
+            asm volatile("cp.async.commit_group;" ::: "memory");
             float sc[REP][8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const __half2 * hk = reinterpret_cast<const __half2 *>(&kv[i]);
                 float d0 = 0.f, d1 = 0.f;
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const float2 f = __half22float2(hk[u]);
-                    d0 = fmaf(f.x, qa[0][2 * u], d0); d0 = fmaf(f.y, qa[0][2 * u + 1], d0);
-                    d1 = fmaf(f.x, qa[1][2 * u], d1); d1 = fmaf(f.y, qa[1][2 * u + 1], d1);
-                }
+                d0 = fhfma2(kA[i].x, qh[0][0], d0); d1 = fhfma2(kA[i].x, qh[1][0], d1);
+                d0 = fhfma2(kA[i].y, qh[0][1], d0); d1 = fhfma2(kA[i].y, qh[1][1], d1);
+                d0 = fhfma2(kA[i].z, qh[0][2], d0); d1 = fhfma2(kA[i].z, qh[1][2], d1);
+                d0 = fhfma2(kA[i].w, qh[0][3], d0); d1 = fhfma2(kA[i].w, qh[1][3], d1);
 #pragma unroll
                 for (int o2 = 8; o2 > 0; o2 >>= 1) {
                     d0 += __shfl_xor_sync(0xffffffffu, d0, o2);
@@ -1293,11 +1321,12 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
                 sc[0][i] = ok ? d0 * op.kq_scale : -CUDART_INF_F;
                 sc[1][i] = ok ? d1 * op.kq_scale : -CUDART_INF_F;
             }
-            // the value rows are requested before the softmax update needs the scores
+            if (more) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int jk = jb + 2 * i + hw;
-                kv[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(vb + (size_t) jk * kvw) : make_uint4(0u, 0u, 0u, 0u);
+                for (int i = 0; i < 8; ++i) {
+                    const int jk = jb + 16 + 2 * i + hw;
+                    kA[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : z4;
+                }
             }
 #pragma unroll
             for (int r = 0; r < REP; ++r) {
@@ -1316,9 +1345,12 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
 #pragma unroll
                 for (int u = 0; u < 8; ++u) acc[r][u] *= scale;
             }
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const __half2 * hv = reinterpret_cast<const __half2 *>(&kv[i]);
+                uint4 vv;
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(vv.x), "=r"(vv.y), "=r"(vv.z), "=r"(vv.w) : "r"(vst + (uint32_t) i * 512u) : "memory");
+                const __half2 * hv = reinterpret_cast<const __half2 *>(&vv);
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const float2 f = __half22float2(hv[u]);
@@ -1329,7 +1361,7 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
         }
         if (spl > 1) {
             if (!tail) {
-                float * pw = pbuf + wib * (20 * 32) + lane;
+                float * pw = reinterpret_cast<float *>(wreg) + lane;
 #pragma unroll
                 for (int r = 0; r < REP; ++r) {
                     pw[(r * 10 + 0) * 32] = m[r]; pw[(r * 10 + 1) * 32] = l[r];
@@ -1340,7 +1372,7 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
             asm volatile("bar.sync %0, %1;" :: "r"(1 + wib / spl), "r"(32 * spl) : "memory");
             if (tail) {
                 for (int p = 0; p < spl - 1; ++p) {
-                    const float * pw = pbuf + (wib - (spl - 1) + p) * (20 * 32) + lane;
+                    const float * pw = reinterpret_cast<const float *>(wreg - (size_t) (spl - 1 - p) * kWarpRegion) + lane;
 #pragma unroll
                     for (int r = 0; r < REP; ++r) {
                         const float mp = pw[(r * 10 + 0) * 32], lp = pw[(r * 10 + 1) * 32];
