@@ -1271,9 +1271,9 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
         const __half * kb = kc + 8 * l16, * vb = vc + 8 * l16;
         const int per = ((n_kv + 15) / 16) / spl;                   // 16-key blocks of every warp but the last
         const int jb0 = part * per * 16, jb1 = tail ? n_kv : (part + 1) * per * 16;
-        // Software pipeline over 16-key blocks: K of block j+1 is requested as soon as block j's scores are done and V
-        // of block j+1 as soon as block j's P.V is done, so a warp always has 4 - 8 KB of KV in flight instead of one
-        // operand at a time (profiles/r01p: 14.5 % of the samples waited on the V rows with nothing else pending).
+        // Per 16-key block: K rows to registers, V rows by cp.async into the warp's shared-memory staging buffer at the same
+        // time (they land while the scores are computed; profiles/r01p: 14.5 % of the samples waited on the V rows with
+        // nothing else pending), and both operands of the blocks further ahead prefetched into L2.
         // Q stays packed F16 and the dot product runs on the mixed-precision FMA: same products, same order, same
         // single rounding as fmaf on the converted values (both conversions are exact), without the conversions.
         uint32_t qh[REP][4];
@@ -1287,15 +1287,28 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
             }
         uint4 kA[8];
         const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-        if (jb0 < jb1) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int jk = jb0 + 2 * i + hw;
-                kA[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : z4;
+        // L2 prefetch `pfd` blocks ahead: lane l asks for line (l & 1) of key (l >> 1)'s K and V segments (256 B each).
+        // It costs no registers, so the bytes in flight per warp are no longer bounded by the register file; the
+        // demand loads below then hit L2 instead of waiting on DRAM twice per block.
+        const int pfd = (S->run.dbg & 128) ? 0 : (((S->run.dbg >> 8) & 7) ? ((S->run.dbg >> 8) & 7) : 3);
+        const size_t pf_off = (size_t) (lane >> 1) * kvw + (size_t) (lane & 1) * 64;      // in halves
+        for (int d = 0; d < pfd; ++d) {
+            const int jk = jb0 + d * 16 + (lane >> 1);
+            if (jk < jb1) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(kc + (size_t) (jb0 + d * 16) * kvw + pf_off));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(vc + (size_t) (jb0 + d * 16) * kvw + pf_off));
             }
         }
         for (int jb = jb0; jb < jb1; jb += 16) {
-            const bool more = jb + 16 < jb1;
+            if (pfd > 0 && jb + pfd * 16 + (lane >> 1) < jb1) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(kc + (size_t) (jb + pfd * 16) * kvw + pf_off));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(vc + (size_t) (jb + pfd * 16) * kvw + pf_off));
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int jk = jb + 2 * i + hw;
+                kA[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : z4;
+            }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int jk = jb + 2 * i + hw;
@@ -1320,13 +1333,6 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
                 const bool ok = jb + 2 * i + hw < n_kv;
                 sc[0][i] = ok ? d0 * op.kq_scale : -CUDART_INF_F;
                 sc[1][i] = ok ? d1 * op.kq_scale : -CUDART_INF_F;
-            }
-            if (more) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int jk = jb + 16 + 2 * i + hw;
-                    kA[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : z4;
-                }
             }
 #pragma unroll
             for (int r = 0; r < REP; ++r) {
