@@ -1287,10 +1287,10 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
             }
         uint4 kA[8];
         const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-        // L2 prefetch `pfd` blocks ahead: lane l asks for line (l & 1) of key (l >> 1)'s K and V segments (256 B each).
-        // It costs no registers, so the bytes in flight per warp are no longer bounded by the register file; the
-        // demand loads below then hit L2 instead of waiting on DRAM twice per block.
-        const int pfd = (S->run.dbg & 128) ? 0 : (((S->run.dbg >> 8) & 7) ? ((S->run.dbg >> 8) & 7) : 3);
+        // Optional L2 prefetch `pfd` blocks ahead (A/B switch, off): lane l asks for line (l & 1) of key (l >> 1)'s K and V
+        // segments (256 B each).  1.7B, 128 streams, 2054 keys: 14.60 ms per frame-step without, 14.46 at depth 2, 15.65 at
+        // depth 3, 16.84 at depth 5 (profiles/r02q_1p7b_attention_ab.log) - the 4096 attention warps already keep HBM busy.
+        const int pfd = (S->run.dbg >> 8) & 7;      // QTTS_BDBG = depth << 8; measured: 0 / 2 equal, 3 and 5 slower -> off by default
         const size_t pf_off = (size_t) (lane >> 1) * kvw + (size_t) (lane & 1) * 64;      // in halves
         for (int d = 0; d < pfd; ++d) {
             const int jk = jb0 + d * 16 + (lane >> 1);
