@@ -226,6 +226,21 @@ int qtts_resize_kv(qtts_engine * e, int32_t n_ctx, int32_t max_text);
 int qtts_codes_chunk(qtts_engine * e, int slot, int32_t first_frame, int32_t n_frames, int32_t fixed_frames,
                      int64_t * out, int out_is_device);
 
+/* No counterpart in the reference.  Allocation-free form of
+ * qtts_codes_chunk with a HOST destination, for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it): qtts_codes_chunk stages the chunk in a device buffer it allocates on
+ * first use and regrows on demand, this entry point stages it in a file-scope `static __device__` array of
+ * QTTS_NOALLOC_CHUNK_WORDS int64 words (64 KB; every GPU that loads the library holds it until the process exits) and
+ * calls no cudaMalloc / cudaFree / allocating library routine.  Same arguments, result and layout as qtts_codes_chunk
+ * with out_is_device = 0 (int64 [1][n_codebooks][fixed_frames], frames beyond n_frames zero).
+ * Limit: n_codebooks * fixed_frames <= QTTS_NOALLOC_CHUNK_WORDS (16 codebooks x 512 frames); larger requests fail
+ * with a message naming the limit.  All calls on one GPU share the array (it keeps the last call's contents; every
+ * word that is read back is rewritten first, so nothing needs clearing): calls that OVERLAP on a GPU - two engines or
+ * two host threads - race on it; the call is synchronous, so serialise callers per GPU. */
+#define QTTS_NOALLOC_CHUNK_WORDS 8192
+int qtts_codes_chunk_noalloc(qtts_engine * e, int slot, int32_t first_frame, int32_t n_frames, int32_t fixed_frames,
+                             int64_t * out_host);
+
 /* 1 (default): qtts_step_frames advances all active streams in lock step with the batched tcgen05
  * kernel (groups of <= 256 slots, env QTTS_BGROUP lowers it); 0: the batch-1 kernel, one stream after another. */
 int qtts_set_batched(qtts_engine * e, int on);

@@ -3,6 +3,7 @@
 #include <cstring>
 #include <cstdio>
 #include <algorithm>
+#include <mutex>
 
 using namespace qtts;
 
@@ -681,6 +682,71 @@ int qtts_codes_chunk(qtts_engine * h, int slot, int32_t first_frame, int32_t n_f
     e->launches += 1;
     if (!out_is_device) cudaMemcpyAsync(out, dst, words * sizeof(long long), cudaMemcpyDeviceToHost, e->stream);
     if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("codes_chunk: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
+    return 1;
+}
+
+// ------------------------------------------------------------------------------------------
+// qtts_codes_chunk_noalloc: the host-destination form of qtts_codes_chunk for callers that must not allocate (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// qtts_codes_chunk stages the chunk in a device buffer it cudaMalloc's
+// on first use and regrows on demand; here the staging buffer is the file-scope array below: QTTS_NOALLOC_CHUNK_WORDS
+// int64 words (64 KB) that every GPU which loads the library holds until the process exits.
+//   * In host code `g_chunk_scratch` is a host-side stand-in, NOT a device address; the kernel gets the address
+//     cudaGetSymbolAddress returns, looked up once per device with that device current (chunk_scratch_for).
+//   * Every call on a GPU - whatever engine or thread it comes from - shares the array, and the array keeps the last
+//     call's contents.  Nothing needs clearing: k_codes_chunk writes all n_codebooks x fixed_frames words the copy then
+//     reads (frames beyond n_frames as zeros).  Calls that overlap on one GPU race on it; the call itself is
+//     synchronous (it returns after its copy has landed), so one thread per GPU, or a lock around the call, is safe.
+//   * No cudaMalloc / cudaFree / allocating library call on any path; sizes beyond the array are rejected.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) long long g_chunk_scratch[QTTS_NOALLOC_CHUNK_WORDS];
+
+constexpr int kScratchMaxDevices = 64;
+static long long * g_chunk_scratch_ptr[kScratchMaxDevices];      // device address of g_chunk_scratch on device d (or null)
+static std::mutex g_chunk_scratch_mu;
+
+// device must be current
+static long long * chunk_scratch_for(Engine * e) {
+    if (e->device < 0 || e->device >= kScratchMaxDevices) { e->err = "codes_chunk_noalloc: device index out of range"; return nullptr; }
+    std::lock_guard<std::mutex> lk(g_chunk_scratch_mu);
+    if (!g_chunk_scratch_ptr[e->device]) {
+        long long * p = nullptr;
+        const cudaError_t rc = cudaGetSymbolAddress((void **) &p, g_chunk_scratch);
+        if (rc != cudaSuccess || !p) {
+            e->err = std::string("codes_chunk_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(rc);
+            cudaGetLastError();
+            return nullptr;
+        }
+        g_chunk_scratch_ptr[e->device] = p;
+    }
+    return g_chunk_scratch_ptr[e->device];
+}
+
+int qtts_codes_chunk_noalloc(qtts_engine * h, int slot, int32_t first_frame, int32_t n_frames, int32_t fixed_frames, int64_t * out_host) {
+    Engine * e = &h->e;
+    Slot * s = get_slot(e, slot);
+    if (!s) return 0;
+    if (cudaSetDevice(e->device) != cudaSuccess) { e->err = "codes_chunk_noalloc: cudaSetDevice failed"; cudaGetLastError(); return 0; }
+    const int nb = e->cfg.n_codebooks;
+    if (!out_host || fixed_frames <= 0 || n_frames < 0 || n_frames > fixed_frames || first_frame < 0 || first_frame + n_frames > e->max_ctx) {
+        e->err = "codes_chunk_noalloc: bad frame range"; return 0;
+    }
+    const size_t words = (size_t) nb * (size_t) fixed_frames;
+    if (words > (size_t) QTTS_NOALLOC_CHUNK_WORDS) {
+        e->err = "codes_chunk_noalloc: n_codebooks * fixed_frames = " + std::to_string(words) + " int64 words exceeds the static scratch of " +
+                 std::to_string((int) QTTS_NOALLOC_CHUNK_WORDS) + " (QTTS_NOALLOC_CHUNK_WORDS); use qtts_codes_chunk or smaller chunks";
+        return 0;
+    }
+    long long * scratch = chunk_scratch_for(e);
+    if (!scratch) return 0;
+    int32_t have = 0;
+    cudaMemcpyAsync(&have, &s->st->frame, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream);
+    if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("codes_chunk_noalloc: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
+    if (first_frame + n_frames > have) { e->err = "codes_chunk_noalloc: frames not generated yet"; return 0; }
+    k_codes_chunk<<<(unsigned) ((words + 255) / 256), 256, 0, e->stream>>>(s->codes + (size_t) first_frame * nb, nb, n_frames, fixed_frames, scratch);
+    e->launches += 1;
+    cudaMemcpyAsync(out_host, scratch, words * sizeof(long long), cudaMemcpyDeviceToHost, e->stream);
+    if (cudaStreamSynchronize(e->stream) != cudaSuccess) { e->err = std::string("codes_chunk_noalloc: ") + cudaGetErrorString(cudaGetLastError()); return 0; }
     return 1;
 }
 

@@ -45,7 +45,7 @@ EXPORTS = ["qtts_create", "qtts_destroy", "qtts_last_error", "qtts_create_error"
            "qtts_step_frames",
            "qtts_set_batched", "qtts_set_batched_weight_format", "qtts_stream_logits", "qtts_batched_profile",
            "qtts_debug_bgemm", "qtts_profile", "qtts_debug_barrier_us", "qtts_launch_count", "qtts_last_loop_ms", "qtts_stream_handle",
-           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step", "qtts_trace", "qtts_codes_chunk", "qtts_load_gguf", "qtts_load_stats"]
+           "qtts_forward_text", "qtts_forward_codec", "qtts_stream_force", "qtts_sample_cb0", "qtts_set_debug", "qtts_resize_kv", "qtts_get_hidden_states", "qtts_cp_step", "qtts_trace", "qtts_codes_chunk", "qtts_load_gguf", "qtts_load_stats", "qtts_codes_chunk_noalloc"]
 
 _lib = None
 
@@ -87,6 +87,7 @@ def load_library(path: str | None = None):
     lib.qtts_resize_kv.argtypes = [vp, i32, i32]
     lib.qtts_get_hidden_states.argtypes = [vp, C.c_int, vp]
     lib.qtts_codes_chunk.argtypes = [vp, C.c_int, i32, i32, i32, vp, C.c_int]
+    lib.qtts_codes_chunk_noalloc.argtypes = [vp, C.c_int, i32, i32, i32, vp]
     lib.qtts_trace.argtypes = [vp, C.c_int, C.c_int, vp, i32]
     lib.qtts_cp_step.argtypes = [vp, C.c_int, vp, i32, i32, i32, i32, i32, C.c_int, vp, i32]
     lib.qtts_predict_codes.argtypes = [vp, C.c_int, vp, i32, C.c_float, i32, vp, vp, vp, vp]
@@ -335,6 +336,17 @@ class TTSTransformer:
             return bool(self._lib.qtts_codes_chunk(self._h, slot, first_frame, n_frames, fixed_frames, C.c_void_p(device_ptr), 1))
         out = np.zeros((1, nb, fixed_frames), np.int64)
         if not self._lib.qtts_codes_chunk(self._h, slot, first_frame, n_frames, fixed_frames, _ptr(out), 0):
+            return None
+        return out
+
+    def codes_chunk_noalloc(self, slot: int, first_frame: int, n_frames: int, fixed_frames: int = 40, out=None):
+        """qtts_codes_chunk_noalloc: the same chunk through the library's static device scratch (no device allocation;
+        n_codebooks * fixed_frames <= NOALLOC_CHUNK_WORDS).  `out`: caller's int64 [1, n_codebooks, fixed_frames] array."""
+        nb = self.config["n_codebooks"]
+        if out is None:
+            out = np.zeros((1, nb, fixed_frames), np.int64)
+        assert out.dtype == np.int64 and out.flags.c_contiguous and out.size >= nb * max(fixed_frames, 0)
+        if not self._lib.qtts_codes_chunk_noalloc(self._h, slot, first_frame, n_frames, fixed_frames, _ptr(out)):
             return None
         return out
 
