@@ -199,7 +199,7 @@ def run_reference(args, pkg):
     return 0
 
 
-NCU_DRAM_BYTES_PER_LAUNCH = 129936908000 + 29512448
+NCU_DRAM_BYTES_PER_LAUNCH = 129986763000 + 33807360      # dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02s_frame_ncu.md
 
 
 def workload_config(world: int) -> dict:
@@ -302,8 +302,8 @@ def run_ours(args, pkg):
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              # dram__bytes_read.sum + dram__bytes_write.sum of one 40-frame launch, from the
-                             # ncu --set full capture summarised in profiles/r01h_frame_ncu.md
-                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r01h_frame_ncu.md",
+                             # ncu --set full capture summarised in profiles/r02s_frame_ncu.md
+                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r02s_frame_ncu.md",
                              "frames_per_launch": 40, "algorithmic_bytes_per_launch": bytes_per_frame * 40,
                              "kernel": "qtts_run_program", "peak_source": peak_src,
                              "algorithmic_bytes_per_frame": bytes_per_frame},
