@@ -29,6 +29,11 @@
 #ifndef QTTS_OPT_FHFMA
 #define QTTS_OPT_FHFMA 1          // GEMV dot on the mixed-precision FMA (0: convert + FFMA, for A/B runs)
 #endif
+#ifndef QTTS_OPT_SPLITK
+#define QTTS_OPT_SPLITK 0         // 1: narrow projections (<= 8 row pairs per CTA): 2 or 4 warps share a row pair, each a K slice.
+                                  // Measured SLOWER (2.834 -> 2.995 ms/frame, profiles/r02t_ab_splitk.log): the extra CTA barrier and the
+                                  // shared-memory hand-over cost more than the shorter walk over weights that already sit in shared memory
+#endif
 #ifndef QTTS_OPT_ATTN_WARP
 #define QTTS_OPT_ATTN_WARP 0      // 1: warp-per-head attention for <= 16 keys.  Measured SLOWER than the CTA-wide path
                                   // (3.005 vs 2.820 ms/frame, profiles/r02_ab.md), so it stays off
@@ -326,6 +331,79 @@ __device__ __forceinline__ float dot8h(const uint4 w, const uint4 x) {
 // rows are handled as pairs (2p, 2p+1) — EPI_SWIGLU needs exactly that pairing; the pair's
 // weights are read from the shared-memory ring (chunk = cons_seq + q / pairs_per_chunk), the
 // F16-rounded activations from xh.  Residual / bias values are requested before the dot products.
+// Narrow projections (O, down, lm_head: <= 8 row pairs per CTA) left 8 - 13 of the 16 warps without rows while 3 - 4 warps
+// walked the whole K (14 % of the kernel's stall samples sat at the next stage-top barrier, profiles/r02s_frame_ncu.md).
+// Here S = 2 or 4 adjacent warps share a row pair: warp w takes pair w / S and the K slice w % S, the partial sums meet
+// in shared memory (`part`, kWarps x 2 floats) and slice 0's warp adds them in fixed order and runs the epilogue.
+// One-token stages only.  All threads of the CTA must call (one CTA barrier inside).
+__device__ __forceinline__ void gemv_rows_split(const Op & op, const __half * xh, const Ring & ring, uint32_t cons_seq, int p0,
+                                                int q_begin, int q_end, int S, float * part, uint32_t tag, bool ll) {
+    const int K = op.K, kv = K >> 3;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ppc = ring.slot_bytes / (4 * K);
+    const uint4 * x4 = reinterpret_cast<const uint4 *>(xh);
+    const int qi = warp / S, ks = warp - qi * S;
+    const int q = q_begin + qi, p = p0 + q;
+    const bool active = q < q_end;
+    float side = 0.f;
+    const unsigned long long * side_p = nullptr;
+    unsigned long long side_w = 0;
+    if (active && ks == 0 && lane < 2) {
+        const int r = 2 * p + lane;
+        if (op.epi == EPI_ADD) {
+            if (ll && op.res_ll) { side_p = op.res_ll + r; side_w = ll_load(side_p); }
+            else side = __ldcg(op.res + r);
+        }
+        else if (op.epi == EPI_BIAS || op.epi == EPI_BIAS_SILU) side = __ldg(op.bias + r);
+    }
+    if (active) {
+        const int j = q / ppc;
+        const uint32_t seq = cons_seq + (uint32_t) j;
+        const int slot = (int) (seq % (uint32_t) ring.n_slots);
+        mbar_wait(ring.full + slot, (seq / (uint32_t) ring.n_slots) & 1u);
+        const uint4 * w0 = reinterpret_cast<const uint4 *>(ring.base + (size_t) slot * ring.slot_bytes +
+                                                            (size_t) (q - j * ppc) * 4 * K);
+        const uint4 * w1 = w0 + kv;
+        const int per = (kv + S - 1) / S, lo = ks * per, hi = min(kv, lo + per);
+        float a0 = 0.f, a1 = 0.f;
+        // a K slice is <= 3 uint4 per lane and the weights are already in shared memory: no load batching needed
+#pragma unroll 1
+        for (int i = lo + lane; i < hi; i += 32) {
+            const uint4 xv = x4[i];
+            a0 += dot8h(w0[i], xv);
+            a1 += dot8h(w1[i], xv);
+        }
+        a0 = warp_sum(a0); a1 = warp_sum(a1);
+        if (lane == 0) { part[2 * warp] = a0; part[2 * warp + 1] = a1; }
+    }
+    __syncthreads();
+    if (active && ks == 0) {
+        if (op.epi == EPI_SWIGLU) {
+            if (lane == 0) {
+                float g = 0.f, u = 0.f;
+                for (int i = 0; i < S; ++i) { g += part[2 * (warp + i)]; u += part[2 * (warp + i) + 1]; }
+                const float v = silu_f(g) * u;
+                op.out[p] = v;
+                if (ll && op.out_ll) ll_store(op.out_ll + p, v, tag);
+            }
+        } else if (lane < 2) {
+            const int r = 2 * p + lane;
+            float acc = 0.f;
+            for (int i = 0; i < S; ++i) acc += part[2 * (warp + i) + lane];
+            if (side_p) {
+                const uint32_t want = tag - (uint32_t) op.res_dist;
+                uint32_t spins = 0;
+                while ((uint32_t) (side_w >> 32) != want) { ll_spin_guard(spins); side_w = ll_load(side_p); }
+                side = __uint_as_float((uint32_t) side_w);
+            }
+            acc += side;
+            if (op.epi == EPI_BIAS_SILU) acc = silu_f(acc);
+            op.out[r] = acc;
+            if (ll && op.out_ll) ll_store(op.out_ll + r, acc, tag);
+        }
+    }
+}
+
 template <int NT>
 __device__ __forceinline__ void gemv_rows(const Op & op, const __half * xh, const Ring ring, uint32_t cons_seq, int p0,
                           int q_begin, int q_end, unsigned long long * prof_wait, uint32_t tag, bool ll) {
@@ -549,8 +627,15 @@ __device__ __forceinline__ uint32_t stage_gemv(const Op & op, StreamState * st, 
     for (int c0 = 0; c0 < nch; c0 += ring.n_slots) {
         const int c1 = min(c0 + ring.n_slots, nch);
         const int qb = c0 * ppc, qe = min(c1 * ppc, p1 - p0);
-        if (op.n_tok == 2) gemv_rows<2>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr, tag, ll);
-        else               gemv_rows<1>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr, tag, ll);
+        int split = 1;
+#if QTTS_OPT_SPLITK
+        if (op.n_tok == 1 && nch <= ring.n_slots && (K & 255) == 0) {
+            if (4 * (qe - qb) <= kWarps) split = 4; else if (2 * (qe - qb) <= kWarps) split = 2;
+        }
+#endif
+        if (split > 1)          gemv_rows_split(op, xh, ring, cons_seq, p0, qb, qe, split, reinterpret_cast<float *>(red), tag, ll);
+        else if (op.n_tok == 2) gemv_rows<2>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr, tag, ll);
+        else                    gemv_rows<1>(op, xh, ring, cons_seq, p0, qb, qe, prof_on ? prof + OP_GEMV * 8 + 6 : nullptr, tag, ll);
         if (c1 < nch) {
             __syncthreads();
             if (threadIdx.x == kPfThread) prefetch_issue(sched, n_sched, n_frames, pf, cons_seq + (uint32_t) c1, ring);
