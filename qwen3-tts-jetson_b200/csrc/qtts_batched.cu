@@ -109,7 +109,13 @@ constexpr size_t kBSharedBytes = (sizeof(BShared) + 127) & ~(size_t) 127;
 // [BShared][A buffers 2 x kABufBytes][weight ring]: an M = 128 MMA reads 128 rows although a piece
 // may hold fewer; the over-read then falls into the ring (valid shared memory), never past the end
 __device__ __forceinline__ unsigned char * babuf_base(BShared * S) { return reinterpret_cast<unsigned char *>(S) + kBSharedBytes; }
-__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return babuf_base(S) + 2 * (size_t) kABufBytes; }
+// Shared memory behind BShared: [activation buffers: a_bufs x kABufBytes][weight ring: bring_slots x kBSlotBytes].  Small groups
+// (<= 64 rows) are bound by how far the weights run ahead: 2 buffers (used as 4 halves) + 6 ring slots.  Large groups move
+// 8x more activation bytes than weight bytes per CTA and stage and were bound by the turnaround of two buffers
+// (copy -> MMA -> commit -> next copy, ~0.9 us, profiles/r02_summary.md section 11): 4 buffers + 3 ring slots.
+__device__ __forceinline__ int bring_slots(const BShared * S) { return S->run.a_bufs == 4 ? kBSlots - 3 : kBSlots; }
+__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return babuf_base(S) + (size_t) (S->run.a_bufs == 4 ? 4 : 2) * kABufBytes; }
+static_assert(3 * kBSlotBytes == 2 * kABufBytes, "two more activation buffers replace exactly three ring slots");
 // byte offset of element (row r, column col) of an F16 activation matrix stored in global memory
 // as UMMA-canonical chunks of 128 columns (chunk_bytes = ceil(rows / 8) * 2048): LBO 128, SBO 2048
 __device__ __forceinline__ size_t canon_off(int r, int col, int chunk_bytes) {
@@ -121,6 +127,33 @@ __device__ __forceinline__ int first_tile(int cta_off) {
     const int G = (int) gridDim.x;
     int f = ((int) blockIdx.x - cta_off) % G;
     return f < 0 ? f + G : f;
+}
+
+__device__ __forceinline__ int first_tile_of(int block, int cta_off) {
+    const int G = (int) gridDim.x;
+    int f = (block - cta_off) % G;
+    return f < 0 ? f + G : f;
+}
+// split-M work items: virtual tile t -> (weight tile, M half).  Without clusters adjacent items are the two halves of one
+// weight tile; in cluster mode the two CTAs of a pair (adjacent items) must read the SAME activation rows to share them
+// by multicast, so adjacent items are two weight tiles of the same half: t = 4a + 2h + b -> (tile 2a + b, half h).
+__device__ __forceinline__ bool msplit_paired(int cluster, int msplit, int n_tiles) { return cluster && msplit == 2 && (n_tiles & 3) == 0; }
+__device__ __forceinline__ int tile_weight(int t, int msplit, bool paired) { return paired ? (((t >> 2) << 1) | (t & 1)) : t / msplit; }
+__device__ __forceinline__ int tile_half(int t, int msplit, bool paired) { return paired ? ((t >> 1) & 1) : t % msplit; }
+
+// cluster mode: bulk copy multicast to the CTAs of `mask` (same shared-memory offsets, each CTA's own mbarrier counts the bytes)
+__device__ __forceinline__ void bulk_g2s_mc(void * dst, const void * src, uint32_t bytes, uint64_t * bar, uint16_t mask, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint [%0], [%1], %2, [%3], %4, %5;"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "h"(mask), "l"(policy) : "memory");
+}
+// tcgen05.commit that arrives on the mbarrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void umma_commit_mc(uint64_t * bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 // advance to the next piece of this CTA; false when the launch needs no more weights
@@ -143,14 +176,15 @@ __device__ __forceinline__ bool bpf_advance(BShared * S) {
 __device__ __forceinline__ bool bpf_issue(BShared * S, bool blocking) {
     if (!bpf_advance(S)) return false;
     BPrefetch & pf = S->pf;
-    const int slot = (int) (pf.seq % (uint32_t) kBSlots);
-    const uint32_t par = ((pf.seq / (uint32_t) kBSlots) & 1u) ^ 1u;
+    const uint32_t nsl = (uint32_t) bring_slots(S);
+    const int slot = (int) (pf.seq % nsl);
+    const uint32_t par = ((pf.seq / nsl) & 1u) ^ 1u;
     if (blocking) mbar_wait(S->empty + slot, par);
     else if (!mbar_test(S->empty + slot, par)) return false;
     const int off = pf.p * pf.piece_bytes;
     const uint32_t bytes = (uint32_t) min(pf.piece_bytes, pf.tile_bytes - off);
     mbar_expect_tx(S->full + slot, bytes);
-    bulk_g2s(bring_base(S) + (size_t) slot * kBSlotBytes, pf.W + (size_t) (pf.t / pf.msplit) * pf.tile_bytes + off, bytes,
+    bulk_g2s(bring_base(S) + (size_t) slot * kBSlotBytes, pf.W + (size_t) tile_weight(pf.t, pf.msplit, msplit_paired(S->run.cluster, pf.msplit, pf.n_tiles)) * pf.tile_bytes + off, bytes,
              S->full + slot, pf.policy);
     pf.p++; pf.seq++;
     return true;
@@ -310,8 +344,9 @@ __device__ __forceinline__ void bgemm_issue(BShared * S, int w, int n_iss, int k
     const BOp & op = S->op;
     tc_fence_after();
     const uint32_t seq = cons_seq + (uint32_t) piece;
-    const int slot = (int) (seq % (uint32_t) kBSlots);
-    if (mt == 0 && koff == 0) mbar_wait(S->full + slot, (seq / (uint32_t) kBSlots) & 1u);
+    const uint32_t nsl = (uint32_t) bring_slots(S);
+    const int slot = (int) (seq % nsl);
+    if (mt == 0 && koff == 0) mbar_wait(S->full + slot, (seq / nsl) & 1u);
     if (w < n_iss && !(S->run.dbg & 1)) {
         const uint32_t w0 = smem_u32(bring_base(S) + (size_t) slot * kBSlotBytes) + (uint32_t) (koff >> 3) * 128u;
         const uint32_t d = S->tmem_base + (uint32_t) ((w * m_tiles + mt) * op.n_tile);
@@ -340,7 +375,8 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
     // split-K: virtual tile -> (row block t, K-half); half 1 only publishes its partial accumulator
     const int ks = op.ksplit > 1 ? op.ksplit : 1;
     const int ms = op.msplit > 1 ? op.msplit : 1;       // split-M: m_tiles / mt below are local, rows start at M tile mt0
-    const int t = t_virtual / (ks * ms), half = (ks > 1) ? t_virtual - t * ks : 0;
+    const int t = (ms > 1) ? tile_weight(t_virtual, ms, msplit_paired(S->run.cluster, ms, op.n_tiles)) : t_virtual / ks;
+    const int half = (ks > 1) ? t_virtual - t * ks : 0;      // (split-M and split-K are never combined)
     const int rows_pad = (op.rows_act + 31) & ~31;
     const uint32_t tag = S->tag;
     bool waited = false;
@@ -365,9 +401,18 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
             __syncwarp();
             float acc[16];
             if (!(dbg & 2)) {
-                const int wa = (n_acc < 0) ? (mt & (-n_acc - 1)) : 0;
+                // issuers whose accumulators hold m-tile mt: n_acc > 0: 0 .. n_acc-1; n_acc = -nab: step s = kc * m_tiles + mt lands in
+                // buffer (= issuer) s % nab, i.e. issuer mt % nab alone when m_tiles is a multiple of nab, issuers mt, mt + m_tiles,
+                // ... < nab when nab is a multiple of m_tiles.  Fixed order: results do not depend on timing.
+                int wa = 0, wstep = 1, wn = n_iss;
+                if (n_acc < 0) {
+                    const int nab = -n_acc;
+                    if (m_tiles >= nab) { wa = mt & (nab - 1); wn = 1; }
+                    else { wa = mt; wstep = m_tiles; wn = nab / m_tiles; }
+                }
                 tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) ((wa * m_tiles + mt) * op.n_tile + cg * 16), acc);
-                for (int w = 1; w < n_iss; ++w) {
+                for (int j = 1; j < wn; ++j) {
+                    const int w = wa + j * wstep;
                     float more[16];
                     tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) ((w * m_tiles + mt) * op.n_tile + cg * 16), more);
 #pragma unroll
@@ -562,21 +607,34 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
         const int nkc = op.K / kKc;
         const int steps = nkc * m_tiles;
         const int Rg = (op.rows_act + 7) >> 3, cb = Rg << 11;
-        const int nab = (Rg <= 8) ? 4 : 2, bstep = 4 / nab;          // buffers in use, barrier index step
+        // buffers in use: 4 halves of the two buffers for <= 64 rows; 4 full buffers when the launch has them (a_bufs = 4) and
+        // the accumulators of 4 issuers fit in TMEM; else the two full buffers
+        const bool four_full = Rg > 8 && S->run.a_bufs == 4 && m_tiles <= 2 && 4 * m_tiles * op.n_tile <= 512;
+        const int nab = (Rg <= 8 || four_full) ? 4 : 2, bstep = 4 / nab;          // buffers in use, barrier index step
         const int lane = tid & 31, warp = tid >> 5;
-        const int abstride = (nab == 4) ? kABufBytes / 2 : kABufBytes;
+        const int abstride = (Rg <= 8) ? kABufBytes / 2 : kABufBytes;
         // accumulators: issuer w (< nab) writes (w, mt) for the steps that land in its buffer; with two
         // buffers and two m-tiles step kc * 2 + mt lands in buffer mt, i.e. m-tile mt has ONE accumulator, issuer mt's
         // (generally: with m_tiles a multiple of the buffer count, m-tile mt always lands in buffer mt % nab)
-        const int acc_mode = (m_tiles >= nab && m_tiles % nab == 0) ? -nab : min(nab, steps);
+        // (with 4 buffers and 2 m-tiles: m-tile mt has two accumulators, issuers mt and mt + 2 - the epilogue's -nab rule)
+        const int acc_mode = ((m_tiles >= nab && m_tiles % nab == 0) || (m_tiles > 1 && nab % m_tiles == 0)) ? -nab : min(nab, steps);
         const uint32_t tmem_base = S->tmem_base;
         const uint32_t idesc = (op.rows_act <= 64 ? (S->run.idesc_base & ~(0x1Fu << 24)) | (4u << 24) : S->run.idesc_base) | ((uint32_t) (op.n_tile >> 3) << 17);
         uint32_t d_use = S->d_use, cons_seq = S->cons_seq;
         unsigned char * abuf = babuf_base(S);
+        const bool paired = msplit_paired(S->run.cluster, msplit, op.n_tiles);
+        // cluster mode: the other CTA of the pair, and whether it walks the same (K range, M tiles) as this one in a
+        // given round - then the two share every activation piece (each copies half of it, multicast to both)
+        const int t_peer_first = S->run.cluster ? first_tile_of((int) (blockIdx.x ^ 1u), op.cta_off) : op.n_tiles;
+        const uint32_t crank = blockIdx.x & 1u;
         for (int t = t_first; t < op.n_tiles; t += G) {
             // split-K: virtual tile t reads the activation chunks of its K-half
             const int kc_base = (op.ksplit > 1) ? (t % op.ksplit) * nkc : 0;
-            const int mt0 = (t % msplit) * m_tiles;                 // split-M: first M tile of this work item
+            const int mt0 = tile_half(t, msplit, paired) * m_tiles;   // split-M: first M tile of this work item
+            const int t_peer = t_peer_first + (t - t_first);
+            const bool shared_a = S->run.cluster && !(S->run.dbg & 4) && t_peer < op.n_tiles &&
+                                  ((op.ksplit > 1) ? (t_peer % op.ksplit) * nkc : 0) == kc_base &&
+                                  tile_half(t_peer, msplit, paired) * m_tiles == mt0;
             if (tid == kAProd) {
                 uint64_t pol;
                 asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
@@ -605,7 +663,14 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     } else {
                         const int kcs = kc_base + ((S->run.dbg & 8) ? (kc + (int) blockIdx.x) % nkc : kc);   // (dbg 8: bring-up, staggered chunk order)
                         mbar_expect_tx(S->tfull + bi, bytes);
-                        bulk_g2s(abuf + (size_t) buf * abstride, in + (size_t) kcs * cb + (size_t) (mt0 + mt) * 32768, bytes, S->tfull + bi, pol);
+                        if (shared_a) {
+                            // this CTA brings its half of the piece for both CTAs; the other half arrives from the peer
+                            const uint32_t hb = bytes >> 1, ho = crank * hb;
+                            bulk_g2s_mc(abuf + (size_t) buf * abstride + ho, in + (size_t) kcs * cb + (size_t) (mt0 + mt) * 32768 + ho, hb,
+                                        S->tfull + bi, (uint16_t) 3, pol);
+                        } else {
+                            bulk_g2s(abuf + (size_t) buf * abstride, in + (size_t) kcs * cb + (size_t) (mt0 + mt) * 32768, bytes, S->tfull + bi, pol);
+                        }
                     }
                     S->n_fill[bi] = nf + 1;
                 }
@@ -621,6 +686,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                 const long long c0 = pr ? clock64() : 0;
                 const int w = warp;
                 const uint32_t ring0 = smem_u32(bring_base(S));
+                const uint32_t nsl = (uint32_t) bring_slots(S);
                 const uint32_t abuf0 = smem_u32(abuf);
                 const bool skip_mma = (S->run.dbg & 1) != 0;
                 const int nab_shift = (nab == 4) ? 2 : 1;
@@ -630,8 +696,8 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                     const int kp = min(op.kpp, op.K - piece * op.kpp);
                     const int chunks = kp / kKc;
                     const uint32_t seq = cons_seq + (uint32_t) piece;
-                    const int slot = (int) (seq % (uint32_t) kBSlots);
-                    mbar_wait(S->full + slot, (seq / (uint32_t) kBSlots) & 1u);     // every issuer: keeps the slot phases aligned
+                    const int slot = (int) (seq % nsl);
+                    mbar_wait(S->full + slot, (seq / nsl) & 1u);     // every issuer: keeps the slot phases aligned
                     if (warp == 0 && piece == 0 && t == t_first) BTR(11);
                     const uint32_t w0 = ring0 + (uint32_t) slot * kBSlotBytes;
                     bool mine = false;
@@ -657,7 +723,13 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                                 for (int i = 0; i < kKc / 16; ++i)
                                     umma_f16_ss(d, ad0 + (uint64_t) (i * 16), bd0 + (uint64_t) (i * 16), idesc, (!fresh || i > 0) ? 1u : 0u);
                             }
-                            umma_commit(S->tempty + bi);
+                            // buffer recycling: in cluster mode tempty counts two arrivals per fill - both CTAs of the pair must
+                            // have consumed the buffer before either half of the next piece is multicast into it
+                            if (shared_a) umma_commit_mc(S->tempty + bi, (uint16_t) 3);
+                            else {
+                                umma_commit(S->tempty + bi);
+                                if (S->run.cluster) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->tempty + bi)) : "memory");
+                            }
                             if (pr) { const long long cc = clock64(); c_wait += cb2 - ca; c_issue += cc - cb2; if (s == 0) c_first = cb2 - c0; }
                         }
                     }
@@ -1616,7 +1688,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
         for (int i = 0; i < kBSlots; ++i) { mbar_init(S->full + i, 1); mbar_init(S->empty + i, kIssuers); }
         mbar_init(S->abar, kIssuers); mbar_init(S->abar + 1, kIssuers); mbar_init(&S->dbar, kIssuers);
         for (int i = 0; i < 4; ++i) {
-            mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, 1); S->n_fill[i] = 0; S->fill_base[i] = 0;
+            mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, run_param.cluster ? 2 : 1); S->n_fill[i] = 0; S->fill_base[i] = 0;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -1632,6 +1704,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
     }
     tc_fence_before();
     __syncthreads();
+    if (run_param.cluster) cluster_sync_all();      // the peer's mbarriers exist before anything is multicast to them
     tc_fence_after();
     if (threadIdx.x == kPfThread) bpf_poll(S);
     unsigned int epoch = 0;
@@ -1717,10 +1790,11 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
     __syncthreads();
     if (threadIdx.x == kPfThread) {
         for (uint32_t s = S->cons_seq; s != S->pf.seq; ++s)
-            mbar_wait(S->full + (s % (uint32_t) kBSlots), (s / (uint32_t) kBSlots) & 1u);
+            mbar_wait(S->full + (s % (uint32_t) bring_slots(S)), (s / (uint32_t) bring_slots(S)) & 1u);
     }
     tc_fence_before();
     __syncthreads();
+    if (run_param.cluster) cluster_sync_all();      // no CTA exits while its peer can still signal its mbarriers
     if (threadIdx.x < 32) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(S->tmem_base), "r"(512));
     }

@@ -382,8 +382,32 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
     { const char * d = getenv("QTTS_BDBG"); run.dbg = d ? atoi(d) : 0; }
     run.trace = e->trace_on ? e->trace : nullptr; run.trace_cta = e->trace_cta; run.trace_cap = e->trace_cap / 2;
     void * args[] = {(void *) &run};
-    QTTS_CUDA(cudaLaunchCooperativeKernel((const void *) qtts_run_batched, dim3(e->n_sms), dim3(kThreads), args,
-                                          kBSmemBytes, e->stream));
+    // Thread-block clusters of 2 (148 = 2 x 74 packs): the CTAs of a pair share the activation operand of the GEMM stages
+    // by multicast.  Still a cooperative launch (the grid barrier needs every CTA resident).  e->bcluster: -1 = not probed,
+    // 0 = off (default; odd SM count, or the driver cannot co-schedule n_sms / 2 clusters), 1 = on (QTTS_BCLUSTER=1).
+    cudaLaunchConfig_t lc;
+    memset(&lc, 0, sizeof(lc));
+    lc.gridDim = dim3(e->n_sms); lc.blockDim = dim3(kThreads); lc.dynamicSmemBytes = kBSmemBytes; lc.stream = e->stream;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
+    at[1].id = cudaLaunchAttributeClusterDimension; at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+    lc.attrs = at;
+    if (e->bcluster < 0) {
+        const char * env = getenv("QTTS_BCLUSTER");
+        e->bcluster = 0;
+        if (env && atoi(env) != 0 && e->n_sms % 2 == 0) {        // opt-in: measured neutral at 256 streams, -1 % at <= 128 (profiles/r02_summary.md)
+            int n_clusters = 0;
+            lc.numAttrs = 2;
+            if (cudaOccupancyMaxActiveClusters(&n_clusters, (const void *) qtts_run_batched, &lc) == cudaSuccess && 2 * n_clusters >= e->n_sms)
+                e->bcluster = 1;
+            cudaGetLastError();
+        }
+    }
+    run.cluster = e->bcluster;
+    // activation buffers vs weight-ring slots (bring_slots): groups of more than 64 rows take 4 buffers + 3 slots
+    { const char * ab = getenv("QTTS_BABUFS"); run.a_bufs = ab ? (atoi(ab) == 4 ? 4 : 2) : (run.n_streams > 64 ? 4 : 2); }
+    lc.numAttrs = e->bcluster ? 2 : 1;
+    QTTS_CUDA(cudaLaunchKernelExC(&lc, (const void *) qtts_run_batched, args));
     e->launches += 1;
     return true;
 }

@@ -123,6 +123,8 @@ struct BRun {
     int32_t dbg;                 // bring-up switches (env QTTS_BDBG): 1 skip MMA issue, 2 skip TMEM loads
     uint32_t * trace;            // optional stage timeline of CTA trace_cta: 16 words per stage, store-only stamps written
     int32_t trace_cta, trace_cap;//   by the threads that own each step (see tools/trace_batched.py for the slots)
+    int32_t cluster;             // 1: launched as thread-block clusters of 2 (CTA pairs share the A operand by multicast)
+    int32_t a_bufs;              // full-size activation buffers: 2 (weight ring of kBSlots slots) or 4 (ring of kBSlots - 3): see bring_slots
 };
 
 }  // namespace qtts

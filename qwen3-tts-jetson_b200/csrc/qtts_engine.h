@@ -130,6 +130,7 @@ struct Engine {
     uint32_t ll_seq = 0;           // stage tags handed out so far (monotonic across launches)
     uint32_t bll_seq = 0;          // same for the batched kernel's split-K hand-off
     int bgroup = 256;              // streams per lock-step group of the batched kernel (env QTTS_BGROUP, <= kBMaxGroup)
+    int bcluster = -1;             // batched kernel launched as clusters of 2 CTAs (A operand multicast): -1 not probed yet, 0 off, 1 on (env QTTS_BCLUSTER=0 disables)
     int ignore_eos = 0;
     int64_t n_weights = 0, n_inexact = 0, weight_bytes = 0, kv_bytes = 0;
     int64_t launches = 0;
