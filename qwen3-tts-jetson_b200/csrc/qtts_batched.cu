@@ -841,6 +841,67 @@ __device__ __noinline__ void bstage_norm(BShared * S) {
     }
 }
 
+// BOP_NORM at warp granularity: one WARP per row instead of one CTA per row, rows dealt over CTAs first (row r -> CTA
+// r % grid, warp r / grid), so every row of a stage has its own warp somewhere and no CTA barrier or block reduction is on
+// the path: 256 rows were two passes of ~2 us per CTA, now one warp-latency.  Same arithmetic and rounding point; the
+// double-precision sum runs lane-strided + xor tree instead of warp-partials in warp order (both fixed orders).
+__device__ __noinline__ void bstage_norm_warp(BShared * S) {
+    const BOp & op = S->op;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, K = op.K, np = op.n_parts_in;
+    const int cb = canon_chunk_bytes(op.rows_act);
+    const bool signal = (op.flags & BF_ROWS_SIGNAL) != 0;
+    const int G = (int) gridDim.x;
+    if (signal && tid == 0) S->rows_target += (uint32_t) op.rows_act;       // every CTA keeps the same running target
+    for (int r = (int) blockIdx.x + G * warp; r < op.rows_act; r += G * kWarps) {
+        const float * x = reinterpret_cast<const float *>(op.in) + row_off(r, op.n_streams, op.in_row_stride, op.in_tok_stride);
+        double ss = 0.0;
+        if (op.part32) {
+            // the producing projection was split over K: x = x + (second half's partial), in this fixed order; the row is
+            // written back (it is the residual of the next projection) and squared here
+            const float * pr = op.part32 + (x - reinterpret_cast<const float *>(op.in));
+            float * xw = const_cast<float *>(x);
+            for (int kk = lane * 8; kk < K; kk += 256) {
+                float4 a = __ldcg(reinterpret_cast<const float4 *>(x + kk)), b = __ldcg(reinterpret_cast<const float4 *>(x + kk + 4));
+                const float4 pa = __ldcg(reinterpret_cast<const float4 *>(pr + kk)), pb = __ldcg(reinterpret_cast<const float4 *>(pr + kk + 4));
+                a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w; b.x += pb.x; b.y += pb.y; b.z += pb.z; b.w += pb.w;
+                *reinterpret_cast<float4 *>(xw + kk) = a; *reinterpret_cast<float4 *>(xw + kk + 4) = b;
+                ss += (double) (a.x * a.x); ss += (double) (a.y * a.y); ss += (double) (a.z * a.z); ss += (double) (a.w * a.w);
+                ss += (double) (b.x * b.x); ss += (double) (b.y * b.y); ss += (double) (b.z * b.z); ss += (double) (b.w * b.w);
+            }
+        } else {
+            for (int i = lane; i < np; i += 32) ss += (double) __ldcg(op.ssq_in + (size_t) r * np + i);
+        }
+        ss = warp_sum_d(ss);
+        const float mean = (float) (ss / (double) K);
+        const float sc = 1.0f / sqrtf(mean + op.eps);
+        for (int kk = lane * 8; kk < K; kk += 256) {
+            // (after the split-K combine above these are this lane's own writes)
+            const float4 xa = __ldcg(reinterpret_cast<const float4 *>(x + kk)), xb = __ldcg(reinterpret_cast<const float4 *>(x + kk + 4));
+            const float4 wa = __ldg(reinterpret_cast<const float4 *>(op.norm_w + kk)), wb = __ldg(reinterpret_cast<const float4 *>(op.norm_w + kk + 4));
+            const float v0 = (xa.x * sc) * wa.x, v1 = (xa.y * sc) * wa.y, v2 = (xa.z * sc) * wa.z, v3 = (xa.w * sc) * wa.w;
+            const float v4 = (xb.x * sc) * wb.x, v5 = (xb.y * sc) * wb.y, v6 = (xb.z * sc) * wb.z, v7 = (xb.w * sc) * wb.w;
+            if (op.hid_out) {
+                *reinterpret_cast<float4 *>(op.hid_out + (size_t) r * K + kk) = make_float4(v0, v1, v2, v3);
+                *reinterpret_cast<float4 *>(op.hid_out + (size_t) r * K + kk + 4) = make_float4(v4, v5, v6, v7);
+            }
+            const __half2 h0 = __floats2half2_rn(v0, v1), h1 = __floats2half2_rn(v2, v3);
+            const __half2 h2 = __floats2half2_rn(v4, v5), h3 = __floats2half2_rn(v6, v7);
+            uint4 pk;
+            pk.x = *reinterpret_cast<const uint32_t *>(&h0); pk.y = *reinterpret_cast<const uint32_t *>(&h1);
+            pk.z = *reinterpret_cast<const uint32_t *>(&h2); pk.w = *reinterpret_cast<const uint32_t *>(&h3);
+            *reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(op.out16) + canon_off(r, kk, cb)) = pk;
+        }
+        if (signal) {
+            asm volatile("fence.proxy.async.global;" ::: "memory");    // the row is read by bulk copies (async proxy)
+            __syncwarp();
+            if (lane == 0) {
+                __threadfence();
+                atomicAdd(&S->run.bar->pad[15], 1u);
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // BOP_ATTN_CP — one warp per (stream, KV group); lane holds dims lane + 32 j (j < 4), so the NEOX
 // pairs (i, i + 64) sit in one lane.  pair_f32: positions 0 and 1 in one pass with the all-F32
@@ -1763,7 +1824,13 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                     else bstage_attn_tk(S);
                     break;
                 case BOP_SAMPLE:  bstage_sample(S); break;
-                case BOP_NORM:    bstage_norm(S); break;
+                case BOP_NORM:
+                    // more rows than CTAs: one warp per row (one pass instead of two, 9.24 -> 9.13 ms per frame-step at 256
+                    // streams); otherwise a CTA per row is the lower latency (a single warp was 6 % slower at 64 / 128 streams,
+                    // profiles/r02z_normwarp_ab.log).  QTTS_BDBG=2048 forces the CTA form, 4096 the warp form.
+                    if (((int) S->op.rows_act > (int) gridDim.x && !(S->run.dbg & 2048)) || (S->run.dbg & 4096)) bstage_norm_warp(S);
+                    else bstage_norm(S);
+                    break;
             }
             const long long t1 = prof ? clock64() : 0;
             if (threadIdx.x == 0) BTR(8);
