@@ -11,6 +11,7 @@ namespace qtts {
 extern "C" __global__ void qtts_run_program(const Op * ops, int n_ops, StreamState * st, GridBarrier * bar,
                                             int n_frames, RunCfg cfg);
 extern "C" __global__ void qtts_run_batched(const __grid_constant__ BRun run_param);
+extern "C" __global__ void qtts_run_batched_ext(const __grid_constant__ BRun run_param);
 }
 
 struct qtts_engine { Engine e; };
@@ -913,7 +914,8 @@ int qtts_debug_bgemm(int device, int weight_fmt, int n_streams, int n_tok, int r
         if (!rc) g_create_err = e->err;
         return rc;
     };
-    if (cudaFuncSetAttribute(qtts_run_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess) {
+    if (cudaFuncSetAttribute(qtts_run_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess ||
+        cudaFuncSetAttribute(qtts_run_batched_ext, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess) {
         e->err = "bgemm: cudaFuncSetAttribute failed"; return cleanup(0);
     }
     e->bar = e->dalloc<GridBarrier>(1);

@@ -82,6 +82,10 @@ struct BPrefetch {           // used by the prefetcher thread only
     uint32_t seq;
     int32_t exhausted;
     uint64_t policy;
+    // ring position kept incrementally (no division by the run-time slot count on the issue path)
+    int32_t slot, nsl, paired;
+    uint32_t par;            // parity to wait for on empty[slot]
+    uint32_t ring;           // shared-memory address of the ring
 };
 
 struct BShared {
@@ -113,8 +117,14 @@ __device__ __forceinline__ unsigned char * babuf_base(BShared * S) { return rein
 // (<= 64 rows) are bound by how far the weights run ahead: 2 buffers (used as 4 halves) + 6 ring slots.  Large groups move
 // 8x more activation bytes than weight bytes per CTA and stage and were bound by the turnaround of two buffers
 // (copy -> MMA -> commit -> next copy, ~0.9 us, profiles/r02_summary.md section 11): 4 buffers + 3 ring slots.
-__device__ __forceinline__ int bring_slots(const BShared * S) { return S->run.a_bufs == 4 ? kBSlots - 3 : kBSlots; }
-__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return babuf_base(S) + (size_t) (S->run.a_bufs == 4 ? 4 : 2) * kABufBytes; }
+#ifndef QTTS_BRING_RUNTIME
+#define QTTS_BRING_RUNTIME 1
+#endif
+#ifndef QTTS_BCLUSTER_CODE
+#define QTTS_BCLUSTER_CODE 1
+#endif
+__device__ __forceinline__ int bring_slots(const BShared * S) { return (QTTS_BRING_RUNTIME && S->run.a_bufs == 4) ? kBSlots - 3 : kBSlots; }
+__device__ __forceinline__ unsigned char * bring_base(BShared * S) { return babuf_base(S) + (size_t) ((QTTS_BRING_RUNTIME && S->run.a_bufs == 4) ? 4 : 2) * kABufBytes; }
 static_assert(3 * kBSlotBytes == 2 * kABufBytes, "two more activation buffers replace exactly three ring slots");
 // byte offset of element (row r, column col) of an F16 activation matrix stored in global memory
 // as UMMA-canonical chunks of 128 columns (chunk_bytes = ceil(rows / 8) * 2048): LBO 128, SBO 2048
@@ -168,6 +178,7 @@ __device__ __forceinline__ bool bpf_advance(BShared * S) {
         pf.W = reinterpret_cast<const unsigned char *>(((unsigned long long) (unsigned) e0.y << 32) | (unsigned) e0.x);
         pf.tile_bytes = e0.z; pf.piece_bytes = e0.w; pf.n_pieces = e1.x; pf.n_tiles = e1.y; pf.msplit = e1.w > 1 ? e1.w : 1;
         pf.t = first_tile(e1.z); pf.p = 0;
+        pf.paired = msplit_paired(S->run.cluster, pf.msplit, pf.n_tiles) ? 1 : 0;
     }
     return true;
 }
@@ -176,16 +187,18 @@ __device__ __forceinline__ bool bpf_advance(BShared * S) {
 __device__ __forceinline__ bool bpf_issue(BShared * S, bool blocking) {
     if (!bpf_advance(S)) return false;
     BPrefetch & pf = S->pf;
-    const uint32_t nsl = (uint32_t) bring_slots(S);
-    const int slot = (int) (pf.seq % nsl);
-    const uint32_t par = ((pf.seq / nsl) & 1u) ^ 1u;
+    const int slot = pf.slot;
+    const uint32_t par = pf.par;
     if (blocking) mbar_wait(S->empty + slot, par);
     else if (!mbar_test(S->empty + slot, par)) return false;
     const int off = pf.p * pf.piece_bytes;
     const uint32_t bytes = (uint32_t) min(pf.piece_bytes, pf.tile_bytes - off);
     mbar_expect_tx(S->full + slot, bytes);
-    bulk_g2s(bring_base(S) + (size_t) slot * kBSlotBytes, pf.W + (size_t) tile_weight(pf.t, pf.msplit, msplit_paired(S->run.cluster, pf.msplit, pf.n_tiles)) * pf.tile_bytes + off, bytes,
-             S->full + slot, pf.policy);
+    const int wt = pf.paired ? tile_weight(pf.t, 2, true) : pf.t / pf.msplit;
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(pf.ring + (uint32_t) slot * (uint32_t) kBSlotBytes), "l"(pf.W + (size_t) wt * pf.tile_bytes + off), "r"(bytes),
+                    "r"(smem_u32(S->full + slot)), "l"(pf.policy) : "memory");
+    if (slot + 1 == pf.nsl) { pf.slot = 0; pf.par = par ^ 1u; } else pf.slot = slot + 1;
     pf.p++; pf.seq++;
     return true;
 }
@@ -363,6 +376,7 @@ __device__ __forceinline__ void bgemm_issue(BShared * S, int w, int n_iss, int k
 }
 
 // epilogue of tile t: warp w reads TMEM lanes 32*(w%4).. (its sub-partition), 16 columns per pass
+template <bool EXT>
 __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_tiles, uint32_t d_use, int n_acc = 0, int mt0 = 0) {
     const BOp & op = S->op;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -375,7 +389,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
     // split-K: virtual tile -> (row block t, K-half); half 1 only publishes its partial accumulator
     const int ks = op.ksplit > 1 ? op.ksplit : 1;
     const int ms = op.msplit > 1 ? op.msplit : 1;       // split-M: m_tiles / mt below are local, rows start at M tile mt0
-    const int t = (ms > 1) ? tile_weight(t_virtual, ms, msplit_paired(S->run.cluster, ms, op.n_tiles)) : t_virtual / ks;
+    const int t = (EXT && ms > 1) ? tile_weight(t_virtual, ms, msplit_paired(S->run.cluster, ms, op.n_tiles)) : t_virtual / (ks * ms);
     const int half = (ks > 1) ? t_virtual - t * ks : 0;      // (split-M and split-K are never combined)
     const int rows_pad = (op.rows_act + 31) & ~31;
     const uint32_t tag = S->tag;
@@ -407,7 +421,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
                 int wa = 0, wstep = 1, wn = n_iss;
                 if (n_acc < 0) {
                     const int nab = -n_acc;
-                    if (m_tiles >= nab) { wa = mt & (nab - 1); wn = 1; }
+                    if (!EXT || m_tiles >= nab) { wa = mt & (nab - 1); wn = 1; }
                     else { wa = mt; wstep = m_tiles; wn = nab / m_tiles; }
                 }
                 tmem_ld16(tmem_base + ((uint32_t) (q * 32) << 16) + (uint32_t) ((wa * m_tiles + mt) * op.n_tile + cg * 16), acc);
@@ -462,7 +476,7 @@ __device__ __noinline__ void bgemm_epilogue(BShared * S, int t_virtual, int m_ti
     }
 }
 
-template <int IN_KIND>
+template <int IN_KIND, bool EXT>
 __device__ __noinline__ void bstage_gemm(BShared * S) {
     const BOp & op = S->op;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -573,7 +587,7 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
                     issue_unit(j + 1);
                 }
             }
-            bgemm_epilogue(S, t, m_tiles, d_use);
+            bgemm_epilogue<EXT>(S, t, m_tiles, d_use);
             d_use++;
             tc_fence_before();
             __syncthreads();
@@ -596,6 +610,11 @@ __device__ __noinline__ void bstage_gemm(BShared * S) {
 // ------------------------------------------------------------------------------------------
 constexpr int kAProd = 4 * 32;      // lane 0 of warp 4 (warps 0..3 hold the MMA issuers)
 
+// EXT = false: the configuration of groups of <= 64 rows without clusters (two activation buffers, kBSlots ring slots) with
+// every choice a compile-time constant - the issue path of this stage is latency-critical to the point where a run-time
+// slot count and two shared-memory flag reads per chunk cost 7 % of a 64-stream frame-step (profiles/r02_summary.md
+// section 14).  EXT = true: four buffers / 3 slots and / or cluster multicast, chosen per launch.
+template <bool EXT>
 __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
     const BOp & op = S->op;
     const int tid = threadIdx.x;
@@ -609,7 +628,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
         const int Rg = (op.rows_act + 7) >> 3, cb = Rg << 11;
         // buffers in use: 4 halves of the two buffers for <= 64 rows; 4 full buffers when the launch has them (a_bufs = 4) and
         // the accumulators of 4 issuers fit in TMEM; else the two full buffers
-        const bool four_full = Rg > 8 && S->run.a_bufs == 4 && m_tiles <= 2 && 4 * m_tiles * op.n_tile <= 512;
+        const bool four_full = EXT && QTTS_BRING_RUNTIME && Rg > 8 && S->run.a_bufs == 4 && m_tiles <= 2 && 4 * m_tiles * op.n_tile <= 512;
         const int nab = (Rg <= 8 || four_full) ? 4 : 2, bstep = 4 / nab;          // buffers in use, barrier index step
         const int lane = tid & 31, warp = tid >> 5;
         const int abstride = (Rg <= 8) ? kABufBytes / 2 : kABufBytes;
@@ -617,22 +636,22 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
         // buffers and two m-tiles step kc * 2 + mt lands in buffer mt, i.e. m-tile mt has ONE accumulator, issuer mt's
         // (generally: with m_tiles a multiple of the buffer count, m-tile mt always lands in buffer mt % nab)
         // (with 4 buffers and 2 m-tiles: m-tile mt has two accumulators, issuers mt and mt + 2 - the epilogue's -nab rule)
-        const int acc_mode = ((m_tiles >= nab && m_tiles % nab == 0) || (m_tiles > 1 && nab % m_tiles == 0)) ? -nab : min(nab, steps);
+        const int acc_mode = ((m_tiles >= nab && m_tiles % nab == 0) || (EXT && m_tiles > 1 && nab % m_tiles == 0)) ? -nab : min(nab, steps);
         const uint32_t tmem_base = S->tmem_base;
         const uint32_t idesc = (op.rows_act <= 64 ? (S->run.idesc_base & ~(0x1Fu << 24)) | (4u << 24) : S->run.idesc_base) | ((uint32_t) (op.n_tile >> 3) << 17);
         uint32_t d_use = S->d_use, cons_seq = S->cons_seq;
         unsigned char * abuf = babuf_base(S);
-        const bool paired = msplit_paired(S->run.cluster, msplit, op.n_tiles);
+        const bool paired = EXT && msplit_paired(S->run.cluster, msplit, op.n_tiles);
         // cluster mode: the other CTA of the pair, and whether it walks the same (K range, M tiles) as this one in a
         // given round - then the two share every activation piece (each copies half of it, multicast to both)
-        const int t_peer_first = S->run.cluster ? first_tile_of((int) (blockIdx.x ^ 1u), op.cta_off) : op.n_tiles;
+        const int t_peer_first = (EXT && S->run.cluster) ? first_tile_of((int) (blockIdx.x ^ 1u), op.cta_off) : op.n_tiles;
         const uint32_t crank = blockIdx.x & 1u;
         for (int t = t_first; t < op.n_tiles; t += G) {
             // split-K: virtual tile t reads the activation chunks of its K-half
             const int kc_base = (op.ksplit > 1) ? (t % op.ksplit) * nkc : 0;
             const int mt0 = tile_half(t, msplit, paired) * m_tiles;   // split-M: first M tile of this work item
             const int t_peer = t_peer_first + (t - t_first);
-            const bool shared_a = S->run.cluster && !(S->run.dbg & 4) && t_peer < op.n_tiles &&
+            const bool shared_a = EXT && QTTS_BCLUSTER_CODE && S->run.cluster && !(S->run.dbg & 4) && t_peer < op.n_tiles &&
                                   ((op.ksplit > 1) ? (t_peer % op.ksplit) * nkc : 0) == kc_base &&
                                   tile_half(t_peer, msplit, paired) * m_tiles == mt0;
             if (tid == kAProd) {
@@ -685,8 +704,8 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                 long long c_wait = 0, c_issue = 0, c_first = 0;
                 const long long c0 = pr ? clock64() : 0;
                 const int w = warp;
-                const uint32_t ring0 = smem_u32(bring_base(S));
-                const uint32_t nsl = (uint32_t) bring_slots(S);
+                const uint32_t ring0 = EXT ? smem_u32(bring_base(S)) : smem_u32(babuf_base(S)) + 2u * (uint32_t) kABufBytes;
+                const uint32_t nsl = EXT ? (uint32_t) bring_slots(S) : (uint32_t) kBSlots;
                 const uint32_t abuf0 = smem_u32(abuf);
                 const bool skip_mma = (S->run.dbg & 1) != 0;
                 const int nab_shift = (nab == 4) ? 2 : 1;
@@ -728,7 +747,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                             if (shared_a) umma_commit_mc(S->tempty + bi, (uint16_t) 3);
                             else {
                                 umma_commit(S->tempty + bi);
-                                if (S->run.cluster) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->tempty + bi)) : "memory");
+                                if (EXT && QTTS_BCLUSTER_CODE && S->run.cluster) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->tempty + bi)) : "memory");
                             }
                             if (pr) { const long long cc = clock64(); c_wait += cb2 - ca; c_issue += cc - cb2; if (s == 0) c_first = cb2 - c0; }
                         }
@@ -751,7 +770,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
             __syncwarp();
             const bool pr1 = S->run.prof != nullptr && tid == 32 && t == 0;      // a thread without issue duties
             const long long e0 = pr1 ? clock64() : 0;
-            bgemm_epilogue(S, t, m_tiles, d_use, acc_mode, mt0);
+            bgemm_epilogue<EXT>(S, t, m_tiles, d_use, acc_mode, mt0);
             if (tid == 32 && t == t_first) BTR(7);
             const long long e1 = pr1 ? clock64() : 0;
             d_use++;
@@ -1738,8 +1757,12 @@ static_assert(kBSmemBytes <= 232448, "batched kernel exceeds the 227 KB of share
 static_assert(sizeof(AttnSmem) + 64 + 2 * kMaxScores * sizeof(float) <= 2 * (size_t) kABufBytes, "attention scratch overlays the A buffers");
 static_assert(sizeof(SampleSmem) + 64 + kMaxVocab * sizeof(float) <= 2 * (size_t) kABufBytes, "sampling scratch overlays the A buffers");
 
-extern "C" __global__ void __launch_bounds__(kThreads, 1)
-qtts_run_batched(const __grid_constant__ BRun run_param) {
+// Two kernels from one body.  qtts_run_batched (EXT = false) is the configuration of groups of <= 64 streams: two
+// activation buffers, kBSlots ring slots, no clusters, every such choice a compile-time constant.  qtts_run_batched_ext
+// (EXT = true) takes them from the launch (BRun::a_bufs, BRun::cluster).  One kernel with run-time switches cost the
+// small groups 3 - 7 % (profiles/r02_summary.md section 14): the GEMM stage's issue path is that latency-critical.
+template <bool EXT>
+__device__ __forceinline__ void run_batched_body(const BRun & run_param) {
     extern __shared__ __align__(128) unsigned char bsm[];
     BShared * S = reinterpret_cast<BShared *>(bsm);
 
@@ -1749,7 +1772,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
         for (int i = 0; i < kBSlots; ++i) { mbar_init(S->full + i, 1); mbar_init(S->empty + i, kIssuers); }
         mbar_init(S->abar, kIssuers); mbar_init(S->abar + 1, kIssuers); mbar_init(&S->dbar, kIssuers);
         for (int i = 0; i < 4; ++i) {
-            mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, run_param.cluster ? 2 : 1); S->n_fill[i] = 0; S->fill_base[i] = 0;
+            mbar_init(S->tfull + i, 1); mbar_init(S->tempty + i, (EXT && run_param.cluster) ? 2 : 1); S->n_fill[i] = 0; S->fill_base[i] = 0;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -1758,6 +1781,9 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
         pf.idx = -1; pf.frame = 0; pf.t = 0; pf.p = 0; pf.n_tiles = 0; pf.n_pieces = 0; pf.tile_bytes = 0; pf.piece_bytes = 0; pf.msplit = 1;
         pf.W = nullptr; pf.seq = 0; pf.exhausted = (run_param.n_sched <= 0) ? 1 : 0;
         pf.policy = policy_evict_first();
+        pf.slot = 0; pf.par = 1u; pf.paired = 0;
+        pf.nsl = (EXT && QTTS_BRING_RUNTIME && run_param.a_bufs == 4) ? kBSlots - 3 : kBSlots;
+        pf.ring = smem_u32(babuf_base(S)) + (uint32_t) ((EXT && QTTS_BRING_RUNTIME && run_param.a_bufs == 4) ? 4 : 2) * (uint32_t) kABufBytes;
     }
     if (threadIdx.x < 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&S->tmem_base)), "r"(512));
@@ -1765,7 +1791,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
     }
     tc_fence_before();
     __syncthreads();
-    if (run_param.cluster) cluster_sync_all();      // the peer's mbarriers exist before anything is multicast to them
+    if (EXT && run_param.cluster) cluster_sync_all();      // the peer's mbarriers exist before anything is multicast to them
     tc_fence_after();
     if (threadIdx.x == kPfThread) bpf_poll(S);
     unsigned int epoch = 0;
@@ -1811,8 +1837,8 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
             const long long t0 = prof ? clock64() : 0;
             switch (type) {
                 case BOP_GEMM:
-                    if (in_kind == BIN_F32) bstage_gemm<BIN_F32>(S);
-                    else                    bstage_gemm_tma(S);
+                    if (in_kind == BIN_F32) bstage_gemm<BIN_F32, EXT>(S);
+                    else                    bstage_gemm_tma<EXT>(S);
                     break;
                 case BOP_ATTN_CP:
                     if (S->op.pair_f32) bstage_attn_cp<true>(S);
@@ -1828,7 +1854,7 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
                     // more rows than CTAs: one warp per row (one pass instead of two, 9.24 -> 9.13 ms per frame-step at 256
                     // streams); otherwise a CTA per row is the lower latency (a single warp was 6 % slower at 64 / 128 streams,
                     // profiles/r02z_normwarp_ab.log).  QTTS_BDBG=2048 forces the CTA form, 4096 the warp form.
-                    if (((int) S->op.rows_act > (int) gridDim.x && !(S->run.dbg & 2048)) || (S->run.dbg & 4096)) bstage_norm_warp(S);
+                    if (EXT && (((int) S->op.rows_act > (int) gridDim.x && !(S->run.dbg & 2048)) || (S->run.dbg & 4096))) bstage_norm_warp(S);
                     else bstage_norm(S);
                     break;
             }
@@ -1857,14 +1883,20 @@ qtts_run_batched(const __grid_constant__ BRun run_param) {
     __syncthreads();
     if (threadIdx.x == kPfThread) {
         for (uint32_t s = S->cons_seq; s != S->pf.seq; ++s)
-            mbar_wait(S->full + (s % (uint32_t) bring_slots(S)), (s / (uint32_t) bring_slots(S)) & 1u);
+            mbar_wait(S->full + (s % (uint32_t) S->pf.nsl), (s / (uint32_t) S->pf.nsl) & 1u);
     }
     tc_fence_before();
     __syncthreads();
-    if (run_param.cluster) cluster_sync_all();      // no CTA exits while its peer can still signal its mbarriers
+    if (EXT && run_param.cluster) cluster_sync_all();      // no CTA exits while its peer can still signal its mbarriers
     if (threadIdx.x < 32) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(S->tmem_base), "r"(512));
     }
 }
+
+extern "C" __global__ void __launch_bounds__(kThreads, 1)
+qtts_run_batched(const __grid_constant__ BRun run_param) { run_batched_body<false>(run_param); }
+
+extern "C" __global__ void __launch_bounds__(kThreads, 1)
+qtts_run_batched_ext(const __grid_constant__ BRun run_param) { run_batched_body<true>(run_param); }
 
 }  // namespace qtts

@@ -8,6 +8,7 @@
 namespace qtts {
 
 extern "C" __global__ void qtts_run_batched(const __grid_constant__ BRun run_param);
+extern "C" __global__ void qtts_run_batched_ext(const __grid_constant__ BRun run_param);
 
 // src: F16 [rows][K] row-major (the batch-1 kernel's fused layouts).  dst: for tile t (n_tile
 // rows) and piece p (kpp K-elements, the last one shorter), the piece is one contiguous block in
@@ -259,11 +260,13 @@ uint32_t batched_idesc(const Engine * e) {
 
 bool batched_init(Engine * e) {
     const qtts_config & c = e->cfg;
-    if (cudaFuncSetAttribute(qtts_run_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess)
+    if (cudaFuncSetAttribute(qtts_run_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess ||
+        cudaFuncSetAttribute(qtts_run_batched_ext, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kBSmemBytes) != cudaSuccess)
         return e->fail(std::string("batched kernel: cudaFuncSetAttribute: ") + cudaGetErrorString(cudaGetLastError()));
-    int occ = 0;
+    int occ = 0, occ_ext = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, qtts_run_batched, kThreads, kBSmemBytes);
-    if (occ < 1) return e->fail("batched kernel does not fit one CTA per SM");
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, qtts_run_batched_ext, kThreads, kBSmemBytes);
+    if (occ < 1 || occ_ext < 1) return e->fail("batched kernel does not fit one CTA per SM");
     const int rep = c.n_heads / c.n_kv_heads;
     if (rep > kMaxRep || e->max_ctx * rep > 2 * kMaxScores) return e->fail("batched path: context too long for the attention scratch");
     if (const char * v = getenv("QTTS_BGROUP")) e->bgroup = std::max(8, std::min(atoi(v), kBMaxGroup));
@@ -398,7 +401,7 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
         if (env && atoi(env) != 0 && e->n_sms % 2 == 0) {        // opt-in: measured neutral at 256 streams, -1 % at <= 128 (profiles/r02_summary.md)
             int n_clusters = 0;
             lc.numAttrs = 2;
-            if (cudaOccupancyMaxActiveClusters(&n_clusters, (const void *) qtts_run_batched, &lc) == cudaSuccess && 2 * n_clusters >= e->n_sms)
+            if (cudaOccupancyMaxActiveClusters(&n_clusters, (const void *) qtts_run_batched_ext, &lc) == cudaSuccess && 2 * n_clusters >= e->n_sms)
                 e->bcluster = 1;
             cudaGetLastError();
         }
@@ -407,7 +410,10 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
     // activation buffers vs weight-ring slots (bring_slots): groups of more than 64 rows take 4 buffers + 3 slots
     { const char * ab = getenv("QTTS_BABUFS"); run.a_bufs = ab ? (atoi(ab) == 4 ? 4 : 2) : (run.n_streams > 64 ? 4 : 2); }
     lc.numAttrs = e->bcluster ? 2 : 1;
-    QTTS_CUDA(cudaLaunchKernelExC(&lc, (const void *) qtts_run_batched, args));
+    // qtts_run_batched: <= 64 streams, compile-time configuration; qtts_run_batched_ext: four activation buffers and / or clusters
+    const bool ext = run.a_bufs == 4 || run.cluster;
+    if (!ext) { run.a_bufs = 2; run.cluster = 0; }
+    QTTS_CUDA(cudaLaunchKernelExC(&lc, ext ? (const void *) qtts_run_batched_ext : (const void *) qtts_run_batched, args));
     e->launches += 1;
     return true;
 }
