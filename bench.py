@@ -343,7 +343,8 @@ def run_ours(args, pkg):
             line["batched"].append(entry)
             # every leg also goes out as its own short line BEFORE the headline line, so a truncated tail keeps it
             print(json.dumps({"batched_leg": entry, "n_gpus": world, "frames_per_stream": B_FRAMES, "text_tokens": list(B_TEXT),
-                              "temperature": TEMP, "top_k": TOP_K, "kernel": "qtts_run_batched",
+                              "temperature": TEMP, "top_k": TOP_K,
+                              "kernel": "qtts_run_batched" if S <= 64 else "qtts_run_batched_ext (same body: 4 activation buffers, 3-slot weight ring)",
                               "e2e_includes": "stream_prepare per stream (H2D, embedding assembly) + batched prefill + step_frames with codes D2H",
                               "peak_source": peak_src, "tensor_peak_source": tpeak_src}), flush=True)
         if world == 1 and not args.no_cpu_baseline:
