@@ -671,16 +671,18 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                 asm volatile("fence.proxy.async.global;" ::: "memory");
                 if (t == t_first) BTR(2);
                 const unsigned char * in = reinterpret_cast<const unsigned char *>(op.in);
-                for (int s = 0; s < steps; ++s) {
-                    const int kc = s / m_tiles, mt = s - kc * m_tiles;
-                    const int buf = s % nab, bi = buf * bstep;
+                const int pdbg = S->run.dbg;                 // (read once: this loop decides how early the first pieces are in flight)
+                int kc = 0, mt = 0;
+                for (int s = 0; s < steps; ++s, ++mt) {
+                    if (mt == m_tiles) { mt = 0; ++kc; }
+                    const int buf = s & (nab - 1), bi = buf * bstep;
                     const uint32_t nf = S->n_fill[bi];
                     mbar_wait(S->tempty + bi, (nf & 1u) ^ 1u);
                     const uint32_t bytes = (uint32_t) min(16, Rg - 16 * (mt0 + mt)) << 11;
-                    if (S->run.dbg & 4) {      // bring-up: pipeline overhead without the copy
+                    if (pdbg & 4) {      // bring-up: pipeline overhead without the copy
                         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(S->tfull + bi)) : "memory");
                     } else {
-                        const int kcs = kc_base + ((S->run.dbg & 8) ? (kc + (int) blockIdx.x) % nkc : kc);   // (dbg 8: bring-up, staggered chunk order)
+                        const int kcs = kc_base + ((pdbg & 8) ? (kc + (int) blockIdx.x) % nkc : kc);   // (dbg 8: bring-up, staggered chunk order)
                         mbar_expect_tx(S->tfull + bi, bytes);
                         if (shared_a) {
                             // this CTA brings its half of the piece for both CTAs; the other half arrives from the peer
@@ -710,6 +712,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                 const bool skip_mma = (S->run.dbg & 1) != 0;
                 const int nab_shift = (nab == 4) ? 2 : 1;
                 uint32_t started = 0;       // accumulators (w, mt) this issuer has written
+                const uint32_t my_fill_base = S->fill_base[(w & (nab - 1)) * bstep];      // issuer w only ever waits on buffer w
                 int kc = 0;
                 for (int piece = 0; piece < op.n_pieces; ++piece) {
                     const int kp = min(op.kpp, op.K - piece * op.kpp);
@@ -726,7 +729,7 @@ __device__ __noinline__ void bstage_gemm_tma(BShared * S) {
                             const int buf = s & (nab - 1), bi = buf * bstep;
                             if (buf != w) continue;             // issuer w owns A buffer w: its fills are consumed in order by one thread
                             mine = true;
-                            const uint32_t fill = S->fill_base[bi] + (uint32_t) (s >> nab_shift);
+                            const uint32_t fill = my_fill_base + (uint32_t) (s >> nab_shift);
                             const long long ca = pr ? clock64() : 0;
                             mbar_wait(S->tfull + bi, fill & 1u);
                             if (warp == 0 && s == 0 && t == t_first) BTR(4);
