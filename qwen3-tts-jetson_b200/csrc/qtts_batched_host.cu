@@ -267,6 +267,23 @@ bool batched_init(Engine * e) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, qtts_run_batched, kThreads, kBSmemBytes);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, qtts_run_batched_ext, kThreads, kBSmemBytes);
     if (occ < 1 || occ_ext < 1) return e->fail("batched kernel does not fit one CTA per SM");
+    {   // clusters of 2 for the _ext kernel (opt-in, QTTS_BCLUSTER=1): can the driver co-schedule n_sms / 2 of them?
+        const char * env = getenv("QTTS_BCLUSTER");
+        e->bcluster = 0;
+        if (env && atoi(env) != 0 && e->n_sms % 2 == 0) {        // measured neutral at 256 streams, -1 % at <= 128 (profiles/r02_summary.md section 12)
+            cudaLaunchConfig_t lc;
+            memset(&lc, 0, sizeof(lc));
+            lc.gridDim = dim3(e->n_sms); lc.blockDim = dim3(kThreads); lc.dynamicSmemBytes = kBSmemBytes; lc.stream = e->stream;
+            cudaLaunchAttribute at[2];
+            at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
+            at[1].id = cudaLaunchAttributeClusterDimension; at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+            lc.attrs = at; lc.numAttrs = 2;
+            int n_clusters = 0;
+            if (cudaOccupancyMaxActiveClusters(&n_clusters, (const void *) qtts_run_batched_ext, &lc) == cudaSuccess && 2 * n_clusters >= e->n_sms)
+                e->bcluster = 1;
+            cudaGetLastError();
+        }
+    }
     const int rep = c.n_heads / c.n_kv_heads;
     if (rep > kMaxRep || e->max_ctx * rep > 2 * kMaxScores) return e->fail("batched path: context too long for the attention scratch");
     if (const char * v = getenv("QTTS_BGROUP")) e->bgroup = std::max(8, std::min(atoi(v), kBMaxGroup));
@@ -386,8 +403,8 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
     run.trace = e->trace_on ? e->trace : nullptr; run.trace_cta = e->trace_cta; run.trace_cap = e->trace_cap / 2;
     void * args[] = {(void *) &run};
     // Thread-block clusters of 2 (148 = 2 x 74 packs): the CTAs of a pair share the activation operand of the GEMM stages
-    // by multicast.  Still a cooperative launch (the grid barrier needs every CTA resident).  e->bcluster: -1 = not probed,
-    // 0 = off (default; odd SM count, or the driver cannot co-schedule n_sms / 2 clusters), 1 = on (QTTS_BCLUSTER=1).
+    // by multicast.  Still a cooperative launch (the grid barrier needs every CTA resident).  e->bcluster (set by batched_init):
+    // 0 = off (default; odd SM count, or the driver cannot co-schedule n_sms / 2 clusters), 1 = on (QTTS_BCLUSTER=1 at load).
     cudaLaunchConfig_t lc;
     memset(&lc, 0, sizeof(lc));
     lc.gridDim = dim3(e->n_sms); lc.blockDim = dim3(kThreads); lc.dynamicSmemBytes = kBSmemBytes; lc.stream = e->stream;
@@ -395,24 +412,13 @@ bool launch_batched(Engine * e, const BOp * d_ops, int n_ops, const BSched * d_s
     at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
     at[1].id = cudaLaunchAttributeClusterDimension; at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
     lc.attrs = at;
-    if (e->bcluster < 0) {
-        const char * env = getenv("QTTS_BCLUSTER");
-        e->bcluster = 0;
-        if (env && atoi(env) != 0 && e->n_sms % 2 == 0) {        // opt-in: measured neutral at 256 streams, -1 % at <= 128 (profiles/r02_summary.md)
-            int n_clusters = 0;
-            lc.numAttrs = 2;
-            if (cudaOccupancyMaxActiveClusters(&n_clusters, (const void *) qtts_run_batched_ext, &lc) == cudaSuccess && 2 * n_clusters >= e->n_sms)
-                e->bcluster = 1;
-            cudaGetLastError();
-        }
-    }
-    run.cluster = e->bcluster;
+    run.cluster = e->bcluster > 0 ? 1 : 0;      // probed at load time (batched_init)
     // activation buffers vs weight-ring slots (bring_slots): groups of more than 64 rows take 4 buffers + 3 slots
     { const char * ab = getenv("QTTS_BABUFS"); run.a_bufs = ab ? (atoi(ab) == 4 ? 4 : 2) : (run.n_streams > 64 ? 4 : 2); }
-    lc.numAttrs = e->bcluster ? 2 : 1;
     // qtts_run_batched: <= 64 streams, compile-time configuration; qtts_run_batched_ext: four activation buffers and / or clusters
     const bool ext = run.a_bufs == 4 || run.cluster;
     if (!ext) { run.a_bufs = 2; run.cluster = 0; }
+    lc.numAttrs = run.cluster ? 2 : 1;
     QTTS_CUDA(cudaLaunchKernelExC(&lc, ext ? (const void *) qtts_run_batched_ext : (const void *) qtts_run_batched, args));
     e->launches += 1;
     return true;

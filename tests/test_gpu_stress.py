@@ -89,3 +89,40 @@ def test_batched_kernel_500_steps_vs_barrier_path(pkg, make_gguf, streams):
     for rep, out in enumerate(runs):
         bad = np.nonzero((out != ref).any(axis=(1, 2)))[0]
         assert bad.size == 0, f"repetition {rep}: {bad.size} streams differ from the barrier path (first: stream {bad[0]})"
+
+
+def test_batched_cluster_multicast_equals_plain_launch(pkg, make_gguf):
+    """The opt-in cluster mode of qtts_run_batched_ext (QTTS_BCLUSTER=1: CTA pairs, every activation piece copied half by
+    each CTA and multicast to both, buffers recycled by multicast tcgen05.commit) only changes how operands travel: codes
+    must be bit-equal to the plain launch, for a group with two M tiles (140 streams, split-M re-dealt for the pairs) and
+    for a group of <= 64 rows."""
+    path, cfg = make_gguf("0.6b", 1234)
+    n = 60
+    for streams in (140, 48):
+        r = np.random.default_rng(7)
+        toks = [pkg.synth.synth_tokens(cfg, n_text=int(r.integers(20, 120)), seed=i) for i in range(streams)]
+        spks = [pkg.synth.synth_speaker(cfg, seed=i) for i in range(streams)]
+
+        def run(T):
+            for i in range(streams):
+                assert T.stream_prepare(i, toks[i], spks[i], max_len=n, temperature=0.9, top_k=50, seed=300 + i), T.get_error()
+            got = [[] for _ in range(streams)]
+            while True:
+                out = T.step_frames(30)
+                assert out is not None, T.get_error()
+                codes, produced, active = out
+                for i in range(streams):
+                    got[i].append(codes[i, :produced[i]])
+                if not active.any():
+                    break
+            return np.stack([np.concatenate(g) for g in got])
+
+        T = make_engine(pkg, path, {"QTTS_BCLUSTER": "0"}, max_streams=streams, max_ctx=n + 160)
+        plain = run(T)
+        T.unload_model()
+        T = make_engine(pkg, path, {"QTTS_BCLUSTER": "1"}, max_streams=streams, max_ctx=n + 160)
+        clustered = [run(T) for _ in range(2)]
+        T.unload_model()
+        assert plain.shape == (streams, n, 16)
+        for out in clustered:
+            assert np.array_equal(out, plain), f"{streams} streams: cluster launch differs from the plain launch"
