@@ -1348,6 +1348,11 @@ __device__ void battn_tk_item(const Op & iop, const float * qkv, unsigned char *
 // keys of its parity, lane l16 of it 8 consecutive dims (one 16-byte load per key and operand).
 // ATTN_FAST numerics: F16 Q / K / V, FP32 scores, softmax and P.V.  All (stream, group) items of the
 // stage run concurrently (2048 warps at 256 streams) instead of 14 CTA-wide items in sequence per SM.
+// KSM = true (the _ext kernel with four activation buffers: 9 KB of shared memory per warp): the K rows of a block are staged
+// by cp.async like the V rows and the loop is software-pipelined - K of block j+1 is requested as soon as block j's scores
+// are done, V of block j+1 as soon as its P.V is done - so every warp always has 4 - 8 KB of KV in flight and no K load
+// sits on the dependency chain.  KSM = false: K through registers (4.5 KB per warp in the two-buffer layout).
+template <bool KSM>
 __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
     constexpr int REP = 2;
     const BOp & op = S->op;
@@ -1357,8 +1362,8 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
     const int B = op.n_streams, nkv = op.n_kv_heads, kvw = nkv * kHeadDim;
     // per-warp shared memory (4608 B of the activation-buffer region, free during an attention stage), used in turn
     // as: Q redistribution (1 KB) -> staging of the block's V rows (4 KB, written by cp.async) -> split-KV hand-over
-    constexpr int kWarpRegion = 2 * kABufBytes / kWarps;
-    static_assert(kWarpRegion >= 4096 && kWarpRegion >= 20 * 32 * 4, "attention warp region");
+    constexpr int kWarpRegion = (KSM ? 4 : 2) * kABufBytes / kWarps;
+    static_assert(kWarpRegion >= (KSM ? 8192 : 4096) && kWarpRegion >= 20 * 32 * 4, "attention warp region");
     unsigned char * wreg = babuf_base(S) + (threadIdx.x >> 5) * kWarpRegion;
     float * qs = reinterpret_cast<float *>(wreg);
     const int cb = canon_chunk_bytes(op.rows_act);
@@ -1442,6 +1447,18 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
             }
         uint4 kA[8];
         const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+        const uint32_t kst = vst + 4096u;        // KSM: this lane's slot of K row i: + i * 512
+        auto stage_rows = [&](const __half * base, uint32_t dst, int jb_) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int jk = jb_ + 2 * i + hw;
+                const bool ok = jk < n_kv;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
+                             :: "r"(dst + (uint32_t) i * 512u), "l"(base + (size_t) (ok ? jk : 0) * kvw), "r"(ok ? 16 : 0) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        if (KSM && jb0 < jb1) { stage_rows(kb, kst, jb0); stage_rows(vb, vst, jb0); }
         // Optional L2 prefetch `pfd` blocks ahead (A/B switch, off): lane l asks for line (l & 1) of key (l >> 1)'s K and V
         // segments (256 B each).  1.7B, 128 streams, 2054 keys: 14.60 ms per frame-step without, 14.46 at depth 2, 15.65 at
         // depth 3, 16.84 at depth 5 (profiles/r02q_1p7b_attention_ab.log) - the 4096 attention warps already keep HBM busy.
@@ -1459,22 +1476,22 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(kc + (size_t) (jb + pfd * 16) * kvw + pf_off));
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(vc + (size_t) (jb + pfd * 16) * kvw + pf_off));
             }
+            const bool more = jb + 16 < jb1;
+            if (KSM) {
+                // pending groups here: K(jb), V(jb), in this order: K(jb) has landed once at most one is pending
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int jk = jb + 2 * i + hw;
-                kA[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : z4;
+                for (int i = 0; i < 8; ++i) {
+                    const int jk = jb + 2 * i + hw;
+                    kA[i] = (jk < n_kv) ? *reinterpret_cast<const uint4 *>(kb + (size_t) jk * kvw) : z4;
+                }
+                stage_rows(vb, vst, jb);
             }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int jk = jb + 2 * i + hw;
-                const bool ok = jk < n_kv;
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
-                             :: "r"(vst + (uint32_t) i * 512u), "l"(vb + (size_t) (ok ? jk : 0) * kvw), "r"(ok ? 16 : 0) : "memory");
-            }
-            asm volatile("cp.async.commit_group;" ::: "memory");
             float sc[REP][8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
+                if (KSM) asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(kA[i].x), "=r"(kA[i].y), "=r"(kA[i].z), "=r"(kA[i].w) : "r"(kst + (uint32_t) i * 512u) : "memory");
                 float d0 = 0.f, d1 = 0.f;
                 d0 = fhfma2(kA[i].x, qh[0][0], d0); d1 = fhfma2(kA[i].x, qh[1][0], d1);
                 d0 = fhfma2(kA[i].y, qh[0][1], d0); d1 = fhfma2(kA[i].y, qh[1][1], d1);
@@ -1506,7 +1523,12 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
 #pragma unroll
                 for (int u = 0; u < 8; ++u) acc[r][u] *= scale;
             }
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            if (KSM && more) {
+                stage_rows(kb, kst, jb + 16);                          // the K staging buffer is free: its rows are in the scores
+                asm volatile("cp.async.wait_group 1;" ::: "memory");   // pending: V(jb), K(jb + 16) -> V(jb) has landed
+            } else {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+            }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 uint4 vv;
@@ -1519,6 +1541,7 @@ __device__ __noinline__ void bstage_attn_tk_warp(BShared * S) {
                     acc[1][2 * u] = fmaf(f.x, sc[1][i], acc[1][2 * u]); acc[1][2 * u + 1] = fmaf(f.y, sc[1][i], acc[1][2 * u + 1]);
                 }
             }
+            if (KSM && more) stage_rows(vb, vst, jb + 16);         // the V staging buffer is free
         }
         if (spl > 1) {
             if (!tail) {
@@ -1849,7 +1872,10 @@ __device__ __forceinline__ void run_batched_body(const BRun & run_param) {
                     else bstage_attn_cp_head(S);
                     break;
                 case BOP_ATTN_TK:
-                    if (S->op.pair_f32 == 2 && S->op.n_heads == 2 * S->op.n_kv_heads) bstage_attn_tk_warp(S);
+                    if (S->op.pair_f32 == 2 && S->op.n_heads == 2 * S->op.n_kv_heads) {
+                        if (EXT && S->run.a_bufs == 4 && !(S->run.dbg & 8192)) bstage_attn_tk_warp<true>(S);      // QTTS_BDBG=8192: K through registers (A/B)
+                        else bstage_attn_tk_warp<false>(S);
+                    }
                     else bstage_attn_tk(S);
                     break;
                 case BOP_SAMPLE:  bstage_sample(S); break;

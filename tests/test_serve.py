@@ -118,8 +118,10 @@ def test_server_hands_out_what_generate_returns(make_gguf, tmp_path):
     # and on the batched kernel: every request answered, frame counts within range
     T.set_batched(True)
     out = io.StringIO()
-    pkg.serve.BatchingServer(T, max_len=9, temperature=0.9, top_k=50).serve(
+    # (fixed base seed: with the default os.urandom seeds a stream may legitimately sample EOS as its first token)
+    pkg.serve.BatchingServer(T, max_len=9, temperature=0.9, top_k=50, base_seed=20240).serve(
         [f"{rid}\t{','.join(map(str, t))}\n" for rid, t in reqs.items()], out=out, err=io.StringIO())
     ans = [l.split("\t") for l in out.getvalue().splitlines()]
-    assert len(ans) == len(reqs) and all(a[0] == "OK" and 1 <= int(a[2]) <= 9 for a in ans)
+    assert len(ans) == len(reqs) and all(a[0] == "OK" and 0 <= int(a[2]) <= 9 for a in ans)
+    assert sum(int(a[2]) for a in ans) > 0
     T.unload_model()
