@@ -100,6 +100,7 @@ struct BEmit {
     float * part32 = nullptr;            // deferred split-K: second half's partial sums, laid out like the output
     bool defer = false;
     const float * pending_x = nullptr;   // output of a deferred-split projection whose partial has not been added yet
+    std::string bad;                     // first shape the kernel cannot run (checked by the caller: fail loudly, never fault)
 
     void gemm(const TiledW & T, int rows_act, int in_kind, const void * in, int in_row_stride, int in_tok_stride,
               const float * norm_w, const float * ssq_in, int n_parts_in, int epi, float * out32, __half * out16,
@@ -136,6 +137,18 @@ struct BEmit {
         const int m_total = (rows_act + 127) / 128;
         const int msplit = (msplit_on && in_kind == BIN_F16 && T.ksplit == 1 && m_total % 2 == 0 && 2 * T.n_tiles <= e->n_sms) ? 2 : 1;
         o.msplit = msplit; o.n_tiles = T.n_tiles * msplit;
+        if (in_kind == BIN_F16) {
+            // TMEM budget of bstage_gemm_tma: every issuer (one per activation buffer in use) keeps one accumulator of n_tile
+            // columns per M tile of a work item; 512 columns are allocated.  Same rule as the device code.
+            const int rg = (rows_act + 7) / 8, m_tiles = m_total / msplit;
+            const int a_bufs = B > 64 ? 4 : 2;
+            const bool four_full = rg > 8 && a_bufs == 4 && m_tiles <= 2 && 4 * m_tiles * T.n_tile <= 512;
+            const int nab = (rg <= 8 || four_full) ? 4 : 2;
+            if (nab * m_tiles * T.n_tile > 512 && bad.empty())
+                bad = "batched kernel: a projection with " + std::to_string(T.n_tile) + "-row weight tiles over " + std::to_string(m_tiles) +
+                      " M tiles (" + std::to_string(rows_act) + " activation rows) needs " + std::to_string(nab * m_tiles * T.n_tile) +
+                      " TMEM columns (512 available); use smaller tiles (QTTS_NTILE) or a group size whose two-token pass has an even number of M tiles";
+        }
         o.in_kind = in_kind; o.in = in; o.in_row_stride = in_row_stride; o.in_tok_stride = in_tok_stride;
         o.norm_w = norm_w; o.ssq_in = ssq_in; o.n_parts_in = n_parts_in; o.eps = e->cfg.rms_norm_eps;
         o.epi = epi; o.out32 = out32; o.out16 = out16; o.res = res; o.bias = bias;
@@ -351,6 +364,7 @@ bool batched_build_groups(Engine * e) {
         if (const char * v = getenv("QTTS_BROWS")) E.rows_signal = atoi(v) != 0;
         if (const char * v = getenv("QTTS_MSPLIT")) E.msplit_on = atoi(v) != 0;
         emit_bframe(e, G, E);
+        if (!E.bad.empty()) return e->fail(E.bad);
         G.n_ops = (int) E.P.size(); G.n_sched = (int) E.S.size();
         G.ops = e->dalloc<BOp>(E.P.size(), false);
         G.sched = e->dalloc<BSched>(E.S.size(), false);
@@ -367,6 +381,7 @@ bool batched_build_groups(Engine * e) {
         BEmit F{e, {}, {}, G.n, 0, G.part_ll, G.xn16};
         F.part32 = G.part32; F.defer = E.defer; F.norm_stage = E.norm_stage; F.rows_signal = E.rows_signal; F.msplit_on = E.msplit_on;
         emit_btalker(e, G, F, G.pf_x, G.pf_ssq_e, G.pf_logits, G.pf_hidden);
+        if (!F.bad.empty()) return e->fail(F.bad);
         G.pf_n_ops = (int) F.P.size(); G.pf_n_sched = (int) F.S.size();
         G.pf_ops = e->dalloc<BOp>(F.P.size(), false);
         G.pf_sched = e->dalloc<BSched>(F.S.size(), false);
